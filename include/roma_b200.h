@@ -1,0 +1,202 @@
+/*
+ * roma_b200 — C ABI of the B200-native (sm_100a) RoMa matching hot path.
+ *
+ * The reference (techshoww/RoMa) is pure Python/PyTorch and has NO FFI or operator
+ * registry: its "plugin API" is a set of Python call sites that all
+ * resolve to ATen library calls.  Each entry point below replaces one such group of
+ * call sites; the reference file:line it stands in for is cited on the declaration.
+ * `INTEGRATION.md` shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions (all entry points)
+ *  - plain pointers + sizes; device pointers unless stated; no torch types.
+ *  - the CALLER owns every buffer (outputs and workspaces); the library never
+ *    allocates or frees device memory and keeps no pointer across calls.
+ *  - asynchronous on `stream` (a cudaStream_t passed as void*); no hidden syncs.
+ *  - return 0 on success, a negative ROMA_ERR_* for bad arguments, a positive
+ *    cudaError_t for a failed launch.  `roma_last_error_string()` describes the
+ *    last failure on the calling thread.  Nothing throws across the ABI.
+ *  - there is NO CPU fallback and no non-sm_100 code path.
+ *  - feature maps are channels-last: element (b, y, x, c) lives at
+ *    ((b*h + y)*w + x)*C + c.  Flow / certainty / delta tensors carry explicit
+ *    element strides so NCHW tensors and permuted views are consumed in place.
+ */
+#ifndef ROMA_B200_H
+#define ROMA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ROMA_B200_ABI_VERSION 1
+
+/* feature / output element types */
+#define ROMA_F32  0
+#define ROMA_F16  1
+#define ROMA_BF16 2
+
+/* error codes (negative); positive return values are cudaError_t */
+#define ROMA_OK               0
+#define ROMA_ERR_BAD_ARG     -1   /* null pointer, non-positive size, unknown dtype   */
+#define ROMA_ERR_UNSUPPORTED -2   /* shape/layout the kernels do not implement       */
+#define ROMA_ERR_ALIGNMENT   -3   /* pointer or stride not aligned as documented     */
+#define ROMA_ERR_WORKSPACE   -4   /* workspace too small (see *_workspace_bytes)     */
+#define ROMA_ERR_ARCH        -5   /* device is not compute capability 10.x           */
+
+int         roma_abi_version(void);
+const char* roma_last_error_string(void);
+/* 0 if `device` is an sm_100-class GPU usable by this library, else ROMA_ERR_ARCH / cudaError_t */
+int         roma_check_device(int device);
+
+/* element strides of a (b, c, y, x)-indexed fp32 tensor */
+typedef struct roma_strides4 {
+    int64_t b, c, y, x;
+} roma_strides4;
+
+/* ---------------------------------------------------------------------------------------
+ * K2  refiner gather: bilinear warp of f1 + local correlation + displacement embedding,
+ *     written straight into the ConvRefiner input buffer `d`.
+ *
+ * Replaces (reference):
+ *   romatch/models/matcher.py:109        x_hat = F.grid_sample(y, flow^T, bilinear, align_corners=False)
+ *   romatch/models/matcher.py:111-120    in_displacement = flow - pixel_grid ; disp_emb(40/32*scale_factor*.)
+ *   romatch/utils/local_correlation.py:4-48   local_correlation(x, y, r, flow)
+ *   romatch/models/matcher.py:130,132    d = cat(x, x_hat, emb[, local_corr])
+ *
+ * f0 : (B, h, w, C) channels-last features of image A (query), dtype `dtype`
+ * f1 : (B, h1, w1, C) channels-last features of image B (support), dtype `dtype`
+ * flow : fp32, element (b, c, y, x) at flow[b*fs.b + c*fs.c + y*fs.y + x*fs.x]; c=0 is x, c=1 is y,
+ *        normalised to [-1, 1] with align_corners=False semantics.
+ * d  : (B, h, w, d_channels) channels-last, dtype `dtype`, dense.  Segments (channel offsets):
+ *        [off_x,    off_x+C)      copy of f0           (skipped when off_x    < 0)
+ *        [off_xhat, off_xhat+C)   warped f1            (skipped when off_xhat < 0)
+ *        [off_emb,  off_emb+E)    disp_w @ (disp_scale*(flow - grid)) + disp_b  (skipped when off_emb < 0 or E == 0)
+ *        [off_corr, off_corr+K)   local correlation, K=(2r+1)^2, k = ky*(2r+1)+kx   (skipped when r == 0 or off_corr < 0)
+ * disp_w : fp32 (E, 2) row-major, disp_b : fp32 (E)   (host-visible DEVICE pointers)
+ * Zero padding: taps outside f1 contribute 0 (grid_sample padding_mode="zeros").
+ * The correlation is sum_c f0[c] * f1_sampled[c] / sqrt(C).
+ */
+int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_strides4 flow_strides,
+                        const float* disp_w, const float* disp_b, float disp_scale,
+                        void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,
+                        int B, int C, int h, int w, int h1, int w1, int E, int r, int dtype,
+                        void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3a  flow / certainty update + bilinear resample to the next scale.
+ *
+ * Replaces (reference):
+ *   romatch/models/matcher.py:397-402   flow += ins*(dx/(4*W_full), dy/(4*H_full)); certainty += dcert
+ *   romatch/models/matcher.py:349-360, 407-417   F.interpolate(flow|certainty, size, bilinear, align_corners=False)
+ *
+ * flow_in (B,2,h,w), cert_in (B,1,h,w), delta (B,3,h,w: dx, dy, dcert) — fp32 with explicit strides.
+ *   cert_in may be NULL (treated as 0: first scale of the coarse pass, matcher.py:347).
+ *   delta may be NULL (pure resample, e.g. the 560^2 -> 108^2 entry of the upsample pass).
+ * ins = scale (16, 8, ...), den_x = 4*W_full, den_y = 4*H_full: flow += ins*(delta/den)  (matcher.py:397-398,
+ *   same operation order as the reference so the update is bit-identical)
+ * flow_out (B,h,w,2) interleaved fp32, cert_out (B,h,w) fp32: updated values at this scale (may be NULL).
+ * flow_next (B,h2,w2,2), cert_next (B,h2,w2): bilinear resample of the UPDATED values (may be NULL with h2=w2=0).
+ */
+int roma_flow_update_resample(const float* flow_in, roma_strides4 flow_strides,
+                              const float* cert_in, roma_strides4 cert_strides,
+                              const float* delta, roma_strides4 delta_strides,
+                              float ins, float den_x, float den_y,
+                              float* flow_out, float* cert_out,
+                              float* flow_next, float* cert_next,
+                              int B, int h, int w, int h2, int w2, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3a  match epilogue: certainty attenuation, sigmoid, out-of-range mask, clamp, grid concat
+ *      and the symmetric side-by-side layout, in one pass and without a host sync.
+ *
+ * Replaces (reference): romatch/models/matcher.py:656-662 and 684-730.
+ *
+ * flow (Bd,2,H,W), cert (Bd,1,H,W) fp32 strided: finest-scale decoder outputs.  Bd = 2*B when
+ *   `symmetric` (first B elements A->B, last B elements B->A, matcher.py:516-528) else B.
+ * cert16 (Bd,1,h16,w16) fp32 strided or NULL (attenuate_cert False).
+ * warp : fp32 (B, H, Wout, 4), Wout = 2*W when symmetric else W.
+ * certainty : fp32 (B, H, Wout)   probabilities after sigmoid and masking.
+ * logits_out : optional fp32 (B, H, Wout): cert - low (pre-sigmoid, pre-mask), for parity checks.
+ */
+int roma_match_epilogue(const float* flow, roma_strides4 flow_strides,
+                        const float* cert, roma_strides4 cert_strides,
+                        const float* cert16, roma_strides4 cert16_strides, int h16, int w16,
+                        float* warp, float* certainty, float* logits_out,
+                        int B, int H, int W, int symmetric, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K1  GP coarse matcher posterior mean.
+ *
+ * Replaces (reference):
+ *   romatch/models/matcher.py:154-163   CosKernel: K = exp((x.y^T/(|x||y|+eps) - 1)/T)
+ *   romatch/models/matcher.py:232-247,224   f = cos(8*pi*pos_conv(grid))
+ *   romatch/models/matcher.py:249-264   mu = K_xy (K_yy + sigma I)^-1 f, returned as (b, D, h1, w1)
+ *
+ * x : (B, Nx, C) token-major features of image A (channels-last feature map flattened), dtype `dtype`
+ * y : (B, Ny, C) same for image B; Ny = hy*wy
+ * pos_w : fp32 (D, 2), pos_b : fp32 (D)   (GP.pos_conv weight/bias)
+ * mu : fp32 (B, Nx, D) token-major == channels-last (B, D, h1, w1)
+ * workspace: roma_gp_workspace_bytes(B, Nx, Ny, C, D) bytes, 256-byte aligned.
+ */
+size_t roma_gp_workspace_bytes(int B, int Nx, int Ny, int C, int D);
+int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const float* pos_b,
+                      float* mu, int B, int Nx, int Ny, int C, int D, int hy, int wy,
+                      float T, float sigma_noise, float eps, int dtype,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3b  Gaussian kde over 4-D matches, streaming (no N x N temporary).
+ *
+ * Replaces (reference): romatch/utils/kde.py:4-12 (torch.cdist + exp + row-sum) and the
+ *   p computation of romatch/models/matcher.py:490-491.
+ *
+ * x : fp32 (N, 4) query points; refs are x[::down] (down >= 1).
+ * half != 0 reproduces the reference's fp16 rounding chain (kde.py:6-7), else fp32.
+ * density : fp32 (N)  (holds the fp16-rounded value when half != 0)
+ * p_out : optional fp32 (N): 1/(density+1), 1e-7 where density < 10   (matcher.py:490-491)
+ */
+int roma_kde(const float* x, int N, int down, float std, int half,
+             float* density, float* p_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3c  match_keypoints: warp keypoints of A into B, mutual nearest neighbours.
+ *
+ * Replaces (reference): romatch/models/matcher.py:576-591.
+ *
+ * x_A (Na,2), x_B (Nb,2) fp32 normalised coords; warp (H, Wp, 4) fp32; certainty (H, Wp) fp32.
+ * The last two warp channels are sampled bilinearly at x_A (zeros padding, align_corners=False).
+ * workspace: roma_match_keypoints_workspace_bytes(Na, Nb).
+ * inds_A, inds_B: int64 (capacity min(Na,Nb)) — mutual-NN pairs with cert > thresh, ordered by
+ *   (a, b) like torch.nonzero; *count (device int32) receives the number of pairs.
+ */
+size_t roma_match_keypoints_workspace_bytes(int Na, int Nb);
+int roma_match_keypoints(const float* x_A, int Na, const float* x_B, int Nb,
+                         const float* warp, const float* certainty, int H, int Wp,
+                         float thresh, int64_t* inds_A, int64_t* inds_B, int* count,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * (f-1) cls_to_flow_refine: softmax over res^2 bins, argmax, 5-tap weighted mean.
+ *
+ * Replaces (reference): romatch/utils/utils.py:301-323.
+ * cls : (B, C=res*res, H, W) logits, dtype `dtype`, explicit strides; flow_out: fp32 (B, H, W, 2).
+ */
+int roma_cls_to_flow_refine(const void* cls, roma_strides4 cls_strides, int dtype,
+                            float* flow_out, int B, int C, int H, int W, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * KT  Tiny-RoMa fused correlation volume + approximate soft-argmax position embedding.
+ *
+ * Replaces (reference): romatch/models/tiny.py:241-254 (corr_volume) and :178-199 (pos_embed,
+ *   inference branch) without materialising the (B, H1*W1, H0*W0) volume.
+ * feat0 (B, H0*W0, C), feat1 (B, H1*W1, C) fp32 token-major; out : fp32 (B, 2, H0, W0).
+ */
+int roma_tiny_corr_posembed(const float* feat0, const float* feat1, float* out,
+                            int B, int C, int H0, int W0, int H1, int W1, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ROMA_B200_H */

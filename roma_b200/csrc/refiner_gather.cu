@@ -1,0 +1,363 @@
+// K2: fused bilinear warp (grid_sample) + local correlation + displacement embedding, written
+// directly into the channels-last ConvRefiner input buffer.
+//
+// Reference behaviour being replaced:
+//   romatch/models/matcher.py:109-132 and romatch/utils/local_correlation.py:4-48.
+//
+// Algorithm (local correlation): the (2r+1)^2 window offsets are exact integer pixel steps
+// (local_correlation.py:30-39: linspace(-2r/h, 2r/h, 2r+1) has step 2/h == 1 px), so every window
+// tap shares the centre's bilinear fractional weights.  Per output pixel we therefore compute the
+// (2r+2)^2 integer-neighbour dot products D[j][i] = f0 . f1[y0+j-r, x0+i-r] once and blend
+//   corr[ky][kx] = wy0*(wx0*D[ky][kx] + wx1*D[ky][kx+1]) + wy1*(wx0*D[ky+1][kx] + wx1*D[ky+1][kx+1]).
+// x_hat is the same 4-tap blend of the four centre neighbours' channel vectors.  Out-of-image
+// neighbours contribute 0 (padding_mode="zeros").
+//
+// Data layout: features channels-last so one pixel's C-vector is a single contiguous burst; one
+// warp per output pixel, lanes over 16-byte channel vectors, fp32 accumulation, butterfly
+// transpose-reduction (1 shuffle per neighbour), results staged in shared memory per CTA tile and
+// written back as ONE contiguous, 16-byte-vectorised span (the rows of `d` are odd-sized, e.g.
+// 1377 channels, so per-row vector stores are impossible but the tile span is contiguous).
+#include "common.cuh"
+
+namespace roma {
+
+struct GatherParams {
+    const void* f0; const void* f1; const float* flow; roma_strides4 fs;
+    const float* disp_w; const float* disp_b; float disp_scale;
+    void* d; int dch; int off_x, off_xhat, off_emb, off_corr;
+    int B, C, h, w, h1, w1, E, r;
+    long long npix;
+    int tile_px;     // pixels per CTA tile (local-corr kernel)
+};
+
+__device__ __forceinline__ void pixel_coords(const GatherParams& p, long long pix, int& b, int& y, int& x,
+                                             float& gx, float& gy) {
+    const int hw = p.h * p.w;
+    b = (int)(pix / hw);
+    const int rem = (int)(pix - (long long)b * hw);
+    y = rem / p.w;
+    x = rem - y * p.w;
+    const float* f = p.flow + (long long)b * p.fs.b + (long long)y * p.fs.y + (long long)x * p.fs.x;
+    gx = __ldg(f);
+    gy = __ldg(f + p.fs.c);
+}
+
+__device__ __forceinline__ void sample_coords(float gx, float gy, int w1, int h1, int& x0, int& y0,
+                                              float& wx0, float& wx1, float& wy0, float& wy1) {
+    float ix = unnormalize(gx, w1), iy = unnormalize(gy, h1);
+    // keep floor() in int range; anything this far out is all-zero padding anyway
+    ix = fminf(fmaxf(ix, -1048576.f), 1048576.f);
+    iy = fminf(fmaxf(iy, -1048576.f), 1048576.f);
+    const float fx = floorf(ix), fy = floorf(iy);
+    x0 = (int)fx; y0 = (int)fy;
+    wx0 = (fx + 1.f) - ix; wx1 = ix - fx;
+    wy0 = (fy + 1.f) - iy; wy1 = iy - fy;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel A: r > 0.  One warp per pixel; CTA tile = tile_px consecutive (b,y,x)-flattened pixels.
+// ------------------------------------------------------------------------------------------------
+template <typename T, int VPL>
+__global__ void __launch_bounds__(256)
+local_corr_kernel(const GatherParams p) {
+    constexpr int kVec = Elem<T>::kVec;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nwarps = blockDim.x >> 5;
+    const int W2 = 2 * p.r + 2, NN = W2 * W2, K1 = 2 * p.r + 1, K = K1 * K1;
+    const int nvec = p.C / kVec;
+
+    const long long tile_start = (long long)blockIdx.x * p.tile_px;
+    int tile_n = p.tile_px;
+    if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
+
+    // staging laid out exactly like the global span, with the same 16-byte misalignment
+    T* gspan = reinterpret_cast<T*>(p.d) + tile_start * p.dch;
+    const unsigned mis = (unsigned)(reinterpret_cast<uintptr_t>(gspan) & 15u);
+    T* stage = reinterpret_cast<T*>(smem_raw + mis);
+    const size_t stage_bytes = ((size_t)p.tile_px * p.dch * sizeof(T) + 16 + 15) & ~(size_t)15;
+    float* Dsm = reinterpret_cast<float*>(smem_raw + stage_bytes) + warp * (NN + 1);
+
+    const float inv_sqrt_c = rsqrtf((float)p.C);
+    const T* f0 = reinterpret_cast<const T*>(p.f0);
+    const T* f1 = reinterpret_cast<const T*>(p.f1);
+
+    for (int lp = warp; lp < tile_n; lp += nwarps) {
+        const long long pix = tile_start + lp;
+        int b, y, x; float gx, gy;
+        pixel_coords(p, pix, b, y, x, gx, gy);
+        int x0, y0; float wx0, wx1, wy0, wy1;
+        sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+        T* row = stage + (size_t)lp * p.dch;
+
+        // f0 channel vectors of this pixel, kept in registers as fp32
+        float a[VPL][kVec];
+        const T* f0p = f0 + pix * p.C;
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+            const int v = lane + 32 * q;
+            if (v < nvec) {
+                const uint4 raw = ldg16(f0p + v * kVec);
+                unpack16<T>(raw, a[q]);
+                if (p.off_x >= 0) {
+                    const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+                    for (int t = 0; t < kVec; ++t) row[p.off_x + v * kVec + t] = e[t];
+                }
+            } else {
+#pragma unroll
+                for (int t = 0; t < kVec; ++t) a[q][t] = 0.f;
+            }
+        }
+        float xh[VPL][kVec];
+#pragma unroll
+        for (int q = 0; q < VPL; ++q)
+#pragma unroll
+            for (int t = 0; t < kVec; ++t) xh[q][t] = 0.f;
+
+        const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
+        int j = 0, i = 0;   // neighbour (row, col) in the (2r+2)^2 grid
+        for (int n0 = 0; n0 < NN; n0 += 32) {
+            float part[32];
+#pragma unroll
+            for (int t = 0; t < 32; ++t) {
+                float acc = 0.f;
+                if (n0 + t < NN) {
+                    const int yy = y0 + j - p.r, xx = x0 + i - p.r;
+                    if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
+                        const T* src = f1b + ((long long)yy * p.w1 + xx) * p.C;
+                        const bool cy = (j == p.r) | (j == p.r + 1), cx = (i == p.r) | (i == p.r + 1);
+                        const float wgt = (j == p.r ? wy0 : wy1) * (i == p.r ? wx0 : wx1);
+#pragma unroll
+                        for (int q = 0; q < VPL; ++q) {
+                            const int v = lane + 32 * q;
+                            if (v < nvec) {
+                                float u[kVec];
+                                unpack16<T>(ldg16(src + v * kVec), u);
+#pragma unroll
+                                for (int e = 0; e < kVec; ++e) acc = fmaf(a[q][e], u[e], acc);
+                                if (cy && cx) {
+#pragma unroll
+                                    for (int e = 0; e < kVec; ++e) xh[q][e] = fmaf(wgt, u[e], xh[q][e]);
+                                }
+                            }
+                        }
+                    }
+                    if (++i == W2) { i = 0; ++j; }
+                }
+                part[t] = acc;
+            }
+            // butterfly transpose-reduce: afterwards lane L holds the full sum of neighbour n0+L
+#pragma unroll
+            for (int s = 16; s >= 1; s >>= 1) {
+                const bool up = (lane & s) != 0;
+#pragma unroll
+                for (int t = 0; t < s; ++t) {
+                    const float send = up ? part[t] : part[t + s];
+                    const float keep = up ? part[t + s] : part[t];
+                    part[t] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+                }
+            }
+            if (n0 + lane < NN) Dsm[n0 + lane] = part[0];
+        }
+        __syncwarp();
+
+        if (p.off_xhat >= 0) {
+#pragma unroll
+            for (int q = 0; q < VPL; ++q) {
+                const int v = lane + 32 * q;
+                if (v < nvec) {
+#pragma unroll
+                    for (int t = 0; t < kVec; ++t) row[p.off_xhat + v * kVec + t] = Elem<T>::from_f(xh[q][t]);
+                }
+            }
+        }
+        if (p.off_corr >= 0) {
+            for (int k = lane; k < K; k += 32) {
+                const int ky = k / K1, kx = k - ky * K1;
+                const float* D0 = Dsm + ky * W2 + kx;
+                const float c = wy0 * (wx0 * D0[0] + wx1 * D0[1]) + wy1 * (wx0 * D0[W2] + wx1 * D0[W2 + 1]);
+                row[p.off_corr + k] = Elem<T>::from_f(c * inv_sqrt_c);
+            }
+        }
+        if (p.off_emb >= 0 && p.E > 0) {
+            const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+            const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+            for (int e = lane; e < p.E; e += 32)
+                row[p.off_emb + e] = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx,
+                                                          fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // contiguous span write-back: scalar head, 16-byte body, scalar tail
+    const size_t total = (size_t)tile_n * p.dch;          // elements
+    const size_t head = mis ? (16 - mis) / sizeof(T) : 0;  // elements until 16-byte alignment
+    const size_t head_n = head < total ? head : total;
+    for (size_t e = threadIdx.x; e < head_n; e += blockDim.x) gspan[e] = stage[e];
+    if (total > head_n) {
+        const size_t body_elems = ((total - head_n) / kVec) * kVec;
+        const uint4* s4 = reinterpret_cast<const uint4*>(stage + head_n);
+        uint4* g4 = reinterpret_cast<uint4*>(gspan + head_n);
+        const size_t nv = body_elems / kVec;
+        for (size_t v = threadIdx.x; v < nv; v += blockDim.x) g4[v] = s4[v];
+        for (size_t e = head_n + body_elems + threadIdx.x; e < total; e += blockDim.x) gspan[e] = stage[e];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel B: r == 0 (gather-only scales 2 and 1, Tiny-RoMa).  One thread per (pixel, VEC-channel chunk).
+// ------------------------------------------------------------------------------------------------
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256)
+gather_only_kernel(const GatherParams p, long long nthreads, int cpp) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nthreads) return;
+    const long long pix = idx / cpp;
+    const int ch = (int)(idx - pix * cpp) * VEC;
+    int b, y, x; float gx, gy;
+    pixel_coords(p, pix, b, y, x, gx, gy);
+    T* out = reinterpret_cast<T*>(p.d) + pix * p.dch + ch;
+    const T* f0 = reinterpret_cast<const T*>(p.f0);
+    const T* f1 = reinterpret_cast<const T*>(p.f1);
+
+    if (p.off_x >= 0 && ch >= p.off_x && ch < p.off_x + p.C) {
+        const T* src = f0 + pix * p.C + (ch - p.off_x);
+        if (VEC > 1) *reinterpret_cast<uint4*>(out) = ldg16(src);
+        else *out = *src;
+        return;
+    }
+    if (p.off_xhat >= 0 && ch >= p.off_xhat && ch < p.off_xhat + p.C) {
+        const int c = ch - p.off_xhat;
+        int x0, y0; float wx0, wx1, wy0, wy1;
+        sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+        float acc[VEC];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) acc[e] = 0.f;
+        const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C + c;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
+            if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
+                const float wgt = ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0);
+                const T* src = f1b + ((long long)yy * p.w1 + xx) * p.C;
+                if (VEC > 1) {
+                    float u[VEC > 1 ? VEC : 8];
+                    unpack16<T>(ldg16(src), u);
+#pragma unroll
+                    for (int e = 0; e < VEC; ++e) acc[e] = fmaf(wgt, u[e], acc[e]);
+                } else {
+                    acc[0] = fmaf(wgt, Elem<T>::to_f(*src), acc[0]);
+                }
+            }
+        }
+        if (VEC > 1) *reinterpret_cast<uint4*>(out) = pack16<T>(acc);
+        else *out = Elem<T>::from_f(acc[0]);
+        return;
+    }
+    if (p.off_emb >= 0 && ch >= p.off_emb && ch < p.off_emb + p.E) {
+        const int e0 = ch - p.off_emb;
+        const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+        const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+        float v[VEC];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e)
+            v[e] = fmaf(__ldg(p.disp_w + 2 * (e0 + e)), dx, fmaf(__ldg(p.disp_w + 2 * (e0 + e) + 1), dy, __ldg(p.disp_b + e0 + e)));
+        if (VEC > 1) *reinterpret_cast<uint4*>(out) = pack16<T>(v);
+        else *out = Elem<T>::from_f(v[0]);
+    }
+}
+
+template <typename T>
+static int launch_gather(GatherParams p, cudaStream_t st) {
+    constexpr int kVec = Elem<T>::kVec;
+    const bool ptr16 = ((reinterpret_cast<uintptr_t>(p.f0) | reinterpret_cast<uintptr_t>(p.f1)) & 15u) == 0;
+    if (p.r > 0) {
+        ROMA_REQUIRE(p.C % kVec == 0 && ptr16, ROMA_ERR_ALIGNMENT,
+                     "roma_refiner_gather: local correlation needs C*sizeof(T) %% 16 == 0 and 16-byte aligned features (C=%d)", p.C);
+        const int nvec = p.C / kVec;
+        ROMA_REQUIRE(nvec <= 128, ROMA_ERR_UNSUPPORTED, "roma_refiner_gather: C=%d too large for the local-correlation kernel", p.C);
+        ROMA_REQUIRE(p.r <= 15, ROMA_ERR_UNSUPPORTED, "roma_refiner_gather: radius %d > 15", p.r);
+        const int W2 = 2 * p.r + 2, NN = W2 * W2;
+        const int nwarps = 8;
+        // tile size: keep the staging buffer under ~40 KB so several CTAs fit per SM
+        int tile_px = (int)((40 * 1024) / ((size_t)p.dch * sizeof(T)));
+        tile_px = tile_px < nwarps ? nwarps : (tile_px > 32 ? 32 : tile_px);
+        p.tile_px = tile_px;
+        const size_t stage_bytes = ((size_t)tile_px * p.dch * sizeof(T) + 16 + 15) & ~(size_t)15;
+        const size_t smem = stage_bytes + (size_t)nwarps * (NN + 1) * sizeof(float);
+        const int grid = cdiv(p.npix, tile_px);
+        auto launch = [&](auto kern) -> int {
+            if (smem > 48 * 1024) {
+                cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return fail((int)e, "roma_refiner_gather: smem opt-in (%zu B): %s", smem, cudaGetErrorString(e));
+            }
+            kern<<<grid, nwarps * 32, smem, st>>>(p);
+            return check_launch("roma_refiner_gather(local_corr)");
+        };
+        if (nvec <= 32) return launch(local_corr_kernel<T, 1>);
+        if (nvec <= 64) return launch(local_corr_kernel<T, 2>);
+        return launch(local_corr_kernel<T, 4>);
+    }
+    // gather-only
+    const bool d16 = (reinterpret_cast<uintptr_t>(p.d) & 15u) == 0;
+    auto seg_ok = [&](int off, int len) { return off < 0 || (off % kVec == 0 && len % kVec == 0); };
+    const bool vec = ptr16 && d16 && p.C % kVec == 0 && p.dch % kVec == 0 &&
+                     seg_ok(p.off_x, p.C) && seg_ok(p.off_xhat, p.C) && seg_ok(p.off_emb, p.E);
+    if (vec) {
+        const int cpp = p.dch / kVec;
+        const long long n = p.npix * cpp;
+        gather_only_kernel<T, kVec><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);
+    } else {
+        const long long n = p.npix * p.dch;
+        gather_only_kernel<T, 1><<<cdiv(n, 256), 256, 0, st>>>(p, n, p.dch);
+    }
+    return check_launch("roma_refiner_gather(gather_only)");
+}
+
+}  // namespace roma
+
+extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_strides4 fs,
+                                   const float* disp_w, const float* disp_b, float disp_scale,
+                                   void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,
+                                   int B, int C, int h, int w, int h1, int w1, int E, int r, int dtype,
+                                   void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(f1 && flow && d, ROMA_ERR_BAD_ARG, "roma_refiner_gather: null pointer");
+    ROMA_REQUIRE(B > 0 && C > 0 && h > 0 && w > 0 && h1 > 0 && w1 > 0 && r >= 0 && E >= 0 && d_channels > 0,
+                 ROMA_ERR_BAD_ARG, "roma_refiner_gather: bad sizes B=%d C=%d h=%d w=%d h1=%d w1=%d E=%d r=%d", B, C, h, w, h1, w1, E, r);
+    if (E == 0) off_emb = -1;
+    if (r == 0) off_corr = -1;
+    ROMA_REQUIRE(!(off_emb >= 0) || (disp_w && disp_b), ROMA_ERR_BAD_ARG, "roma_refiner_gather: embedding requested without weights");
+    ROMA_REQUIRE(f0 || (off_x < 0 && off_corr < 0), ROMA_ERR_BAD_ARG, "roma_refiner_gather: f0 is required for the copy / correlation segments");
+    // the enabled segments must tile [0, d_channels) exactly (the tile span is written as a whole)
+    const int K = (2 * r + 1) * (2 * r + 1);
+    int offs[4] = {off_x, off_xhat, off_emb, off_corr};
+    int lens[4] = {C, C, E, K};
+    int covered = 0;
+    for (int guard = 0; guard < 5; ++guard) {
+        bool found = false;
+        for (int s = 0; s < 4; ++s)
+            if (offs[s] == covered) { covered += lens[s]; offs[s] = -2; found = true; break; }
+        if (!found) break;
+    }
+    bool leftover = false;
+    for (int s = 0; s < 4; ++s) leftover |= (offs[s] >= 0);
+    ROMA_REQUIRE(covered == d_channels && !leftover, ROMA_ERR_BAD_ARG,
+                 "roma_refiner_gather: enabled segments must tile [0,%d) exactly (covered %d)", d_channels, covered);
+
+    GatherParams p;
+    p.f0 = f0; p.f1 = f1; p.flow = flow; p.fs = fs;
+    p.disp_w = disp_w; p.disp_b = disp_b; p.disp_scale = disp_scale;
+    p.d = d; p.dch = d_channels; p.off_x = off_x; p.off_xhat = off_xhat; p.off_emb = off_emb; p.off_corr = off_corr;
+    p.B = B; p.C = C; p.h = h; p.w = w; p.h1 = h1; p.w1 = w1; p.E = E; p.r = r;
+    p.npix = (long long)B * h * w; p.tile_px = 0;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    switch (dtype) {
+        case ROMA_F32:  return launch_gather<float>(p, st);
+        case ROMA_F16:  return launch_gather<__half>(p, st);
+        case ROMA_BF16: return launch_gather<__nv_bfloat16>(p, st);
+        default: return fail(ROMA_ERR_BAD_ARG, "roma_refiner_gather: unknown dtype %d", dtype);
+    }
+}

@@ -1,0 +1,228 @@
+"""Tensor-level wrappers over the C ABI (include/roma_b200.h), with the reference's call signatures.
+
+PyTorch is plumbing here: it owns device memory and the stream; every computation below is one of the
+hand-written sm_100a kernels.  Nothing in this module falls back to ATen or the CPU — tensors that are
+not on a CUDA device raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import Strides4
+
+_DT = {torch.float32: _lib.ROMA_F32, torch.float16: _lib.ROMA_F16, torch.bfloat16: _lib.ROMA_BF16}
+
+
+def _cuda(*ts: Optional[torch.Tensor]) -> torch.device:
+    dev = None
+    for t in ts:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("roma_b200 kernels run on sm_100a only; got a tensor on "
+                               f"{t.device} (there is no CPU fallback)")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
+    return dev
+
+
+def _ptr(t: Optional[torch.Tensor]) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream(dev: torch.device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _s4(t: Optional[torch.Tensor]) -> Strides4:
+    """Element strides of a (b, c, y, x)-indexed tensor."""
+    if t is None:
+        return Strides4(0, 0, 0, 0)
+    assert t.dim() == 4
+    return Strides4(*t.stride())
+
+
+def _nhwc(t: torch.Tensor) -> torch.Tensor:
+    """(B,C,H,W) tensor -> same tensor laid out channels-last and dense (no copy if it already is)."""
+    if t.dim() != 4:
+        raise ValueError(f"expected a (B,C,H,W) tensor, got {tuple(t.shape)}")
+    return t.contiguous(memory_format=torch.channels_last)
+
+
+def _f32(t: torch.Tensor) -> torch.Tensor:
+    return t if t.dtype == torch.float32 else t.float()
+
+
+# --------------------------------------------------------------------------------------------------
+# K2
+# --------------------------------------------------------------------------------------------------
+def refiner_inputs(x: torch.Tensor, y: torch.Tensor, flow: torch.Tensor,
+                   disp_w: Optional[torch.Tensor] = None, disp_b: Optional[torch.Tensor] = None,
+                   disp_scale: float = 1.0, local_corr_radius: Optional[int] = None) -> torch.Tensor:
+    """ConvRefiner input d = cat(x, x_hat, disp_emb, local_corr) in ONE kernel (matcher.py:105-132).
+
+    x, y: (B,C,h,w) features of image A / B (any of fp32/fp16/bf16, same dtype); flow: (B,2,h,w) fp32 view.
+    Returns d as a (B, 2C+E+K, h, w) tensor in channels-last memory format, dtype of x.
+    """
+    dev = _cuda(x, y, flow, disp_w, disp_b)
+    if x.dtype != y.dtype or x.dtype not in _DT:
+        raise ValueError(f"unsupported feature dtypes {x.dtype}/{y.dtype}")
+    B, Cc, h, w = x.shape
+    _, _, h1, w1 = y.shape
+    x, y, flow = _nhwc(x), _nhwc(y), _f32(flow)
+    r = int(local_corr_radius or 0)
+    E = 0 if disp_w is None else disp_w.shape[0]
+    K = (2 * r + 1) ** 2 if r > 0 else 0
+    if E:
+        disp_w = disp_w.reshape(E, 2).float().contiguous()
+        disp_b = disp_b.reshape(E).float().contiguous()
+    dch = 2 * Cc + E + K
+    d = torch.empty((B, dch, h, w), device=dev, dtype=x.dtype, memory_format=torch.channels_last)
+    rc = _lib.load().roma_refiner_gather(
+        _ptr(x), _ptr(y), _ptr(flow), _s4(flow), _ptr(disp_w), _ptr(disp_b), float(disp_scale),
+        _ptr(d), dch, 0, Cc, (2 * Cc if E else -1), (2 * Cc + E if r > 0 else -1),
+        B, Cc, h, w, h1, w1, E, r, _DT[x.dtype], _stream(dev))
+    _lib.check(rc, "roma_refiner_gather")
+    return d
+
+
+def local_correlation(feature0: torch.Tensor, feature1: torch.Tensor, local_radius: int,
+                      padding_mode: str = "zeros", flow: Optional[torch.Tensor] = None,
+                      sample_mode: str = "bilinear") -> torch.Tensor:
+    """Drop-in for romatch.utils.local_correlation.local_correlation (local_correlation.py:4-48)."""
+    if padding_mode != "zeros" or sample_mode != "bilinear":
+        raise NotImplementedError("roma_b200.local_correlation implements padding_mode='zeros', sample_mode='bilinear'")
+    dev = _cuda(feature0, feature1, flow)
+    B, Cc, h, w = feature0.shape
+    r = int(local_radius)
+    if flow is None:   # aligned features: sample around the pixel's own centre (local_correlation.py:16-27)
+        ys = torch.linspace(-1 + 1 / h, 1 - 1 / h, h, device=dev)
+        xs = torch.linspace(-1 + 1 / w, 1 - 1 / w, w, device=dev)
+        flow = torch.stack((xs[None, :].expand(h, w), ys[:, None].expand(h, w)))[None].expand(B, 2, h, w)
+    f0, f1, flow = _nhwc(feature0), _nhwc(feature1), _f32(flow)
+    K = (2 * r + 1) ** 2
+    out = torch.empty((B, K, h, w), device=dev, dtype=feature0.dtype, memory_format=torch.channels_last)
+    rc = _lib.load().roma_refiner_gather(
+        _ptr(f0), _ptr(f1), _ptr(flow), _s4(flow), _ptr(None), _ptr(None), 0.0,
+        _ptr(out), K, -1, -1, -1, 0,
+        B, Cc, h, w, feature1.shape[2], feature1.shape[3], 0, r, _DT[feature0.dtype], _stream(dev))
+    _lib.check(rc, "roma_refiner_gather(local_correlation)")
+    return out
+
+
+def grid_sample(input: torch.Tensor, grid: torch.Tensor) -> torch.Tensor:
+    """F.grid_sample(input, grid, mode='bilinear', padding_mode='zeros', align_corners=False) (matcher.py:109)."""
+    dev = _cuda(input, grid)
+    B, Cc, h1, w1 = input.shape
+    _, h, w, two = grid.shape
+    assert two == 2
+    f1 = _nhwc(input)
+    flow = _f32(grid).permute(0, 3, 1, 2)   # view: (B,2,h,w) with arbitrary strides, consumed in place
+    out = torch.empty((B, Cc, h, w), device=dev, dtype=input.dtype, memory_format=torch.channels_last)
+    rc = _lib.load().roma_refiner_gather(
+        _ptr(None), _ptr(f1), _ptr(flow), _s4(flow), _ptr(None), _ptr(None), 0.0,
+        _ptr(out), Cc, -1, 0, -1, -1,
+        B, Cc, h, w, h1, w1, 0, 0, _DT[input.dtype], _stream(dev))
+    _lib.check(rc, "roma_refiner_gather(grid_sample)")
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# K3a
+# --------------------------------------------------------------------------------------------------
+def flow_update_resample(flow: torch.Tensor, certainty: Optional[torch.Tensor], delta: Optional[torch.Tensor],
+                         ins: int, full_hw: Tuple[int, int], next_hw: Optional[Tuple[int, int]],
+                         want_current: bool = True):
+    """flow += ins*(delta_xy/(4*W,4*H)); certainty += delta_c; then bilinear resample to next_hw.
+
+    matcher.py:397-402 and :349-360 / :407-417.  flow (B,2,h,w), certainty (B,1,h,w) or None, delta (B,3,h,w) or None.
+    Returns (flow_cur, cert_cur, flow_next, cert_next) as (B,2,·,·)/(B,1,·,·) views over interleaved storage;
+    entries not requested are None.
+    """
+    dev = _cuda(flow, certainty, delta)
+    B, _, h, w = flow.shape
+    flow = _f32(flow)
+    certainty = None if certainty is None else _f32(certainty)
+    delta = None if delta is None else _f32(delta)
+    H, W = full_hw
+    fo = co = fn = cn = None
+    if want_current:
+        fo = torch.empty((B, h, w, 2), device=dev, dtype=torch.float32)
+        co = torch.empty((B, h, w), device=dev, dtype=torch.float32)
+    h2 = w2 = 0
+    if next_hw is not None:
+        h2, w2 = int(next_hw[0]), int(next_hw[1])
+        fn = torch.empty((B, h2, w2, 2), device=dev, dtype=torch.float32)
+        cn = torch.empty((B, h2, w2), device=dev, dtype=torch.float32)
+    rc = _lib.load().roma_flow_update_resample(
+        _ptr(flow), _s4(flow), _ptr(certainty), _s4(certainty), _ptr(delta), _s4(delta),
+        float(ins), float(4 * W), float(4 * H),
+        _ptr(fo), _ptr(co), _ptr(fn), _ptr(cn), B, h, w, h2, w2, _stream(dev))
+    _lib.check(rc, "roma_flow_update_resample")
+    v = lambda f: None if f is None else f.permute(0, 3, 1, 2)
+    u = lambda c: None if c is None else c[:, None]
+    return v(fo), u(co), v(fn), u(cn)
+
+
+def match_epilogue(flow: torch.Tensor, certainty: torch.Tensor, cert16: Optional[torch.Tensor],
+                   symmetric: bool, return_logits: bool = False):
+    """matcher.py:656-662 + 684-718 in one pass.  Returns (warp (B,H,Wout,4), certainty (B,H,Wout)[, logits])."""
+    dev = _cuda(flow, certainty, cert16)
+    Bd, _, H, W = flow.shape
+    if symmetric and Bd % 2:
+        raise ValueError("symmetric epilogue needs an even decoder batch")
+    B = Bd // 2 if symmetric else Bd
+    Wout = 2 * W if symmetric else W
+    flow, certainty = _f32(flow), _f32(certainty)
+    cert16 = None if cert16 is None else _f32(cert16)
+    warp = torch.empty((B, H, Wout, 4), device=dev, dtype=torch.float32)
+    cert = torch.empty((B, H, Wout), device=dev, dtype=torch.float32)
+    logits = torch.empty((B, H, Wout), device=dev, dtype=torch.float32) if return_logits else None
+    h16, w16 = (cert16.shape[2], cert16.shape[3]) if cert16 is not None else (0, 0)
+    rc = _lib.load().roma_match_epilogue(
+        _ptr(flow), _s4(flow), _ptr(certainty), _s4(certainty), _ptr(cert16), _s4(cert16), h16, w16,
+        _ptr(warp), _ptr(cert), _ptr(logits), B, H, W, int(bool(symmetric)), _stream(dev))
+    _lib.check(rc, "roma_match_epilogue")
+    return (warp, cert, logits) if return_logits else (warp, cert)
+
+
+# --------------------------------------------------------------------------------------------------
+# K1
+# --------------------------------------------------------------------------------------------------
+_gp_ws = {}
+
+
+def gp_posterior(x: torch.Tensor, y: torch.Tensor, pos_w: torch.Tensor, pos_b: torch.Tensor,
+                 T: float = 0.2, sigma_noise: float = 0.1, eps: float = 1e-6) -> torch.Tensor:
+    """GP.forward with CosKernel, fourier basis, no_cov=True (matcher.py:249-273).
+
+    x (B,C,h1,w1), y (B,C,h2,w2) features (fp32/fp16/bf16); returns mu (B,D,h1,w1) fp32 (channels-last)."""
+    dev = _cuda(x, y, pos_w, pos_b)
+    if x.dtype != y.dtype or x.dtype not in _DT:
+        raise ValueError(f"unsupported feature dtypes {x.dtype}/{y.dtype}")
+    B, Cc, h1, w1 = x.shape
+    _, _, h2, w2 = y.shape
+    D = pos_w.shape[0]
+    x, y = _nhwc(x), _nhwc(y)
+    pos_w = pos_w.reshape(D, 2).float().contiguous()
+    pos_b = pos_b.reshape(D).float().contiguous()
+    lib = _lib.load()
+    need = lib.roma_gp_workspace_bytes(B, h1 * w1, h2 * w2, Cc, D)
+    key = (dev, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _gp_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need, device=dev, dtype=torch.uint8)
+        _gp_ws[key] = ws
+    mu = torch.empty((B, D, h1, w1), device=dev, dtype=torch.float32, memory_format=torch.channels_last)
+    rc = lib.roma_gp_posterior(_ptr(x), _ptr(y), _ptr(pos_w), _ptr(pos_b), _ptr(mu),
+                               B, h1 * w1, h2 * w2, Cc, D, h2, w2, float(T), float(sigma_noise), float(eps),
+                               _DT[x.dtype], _ptr(ws), ws.numel(), _stream(dev))
+    _lib.check(rc, "roma_gp_posterior")
+    return mu
