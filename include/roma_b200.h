@@ -156,9 +156,12 @@ int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const fl
  * half != 0 reproduces the reference's fp16 rounding chain (kde.py:6-7), else fp32.
  * density : fp32 (N)  (holds the fp16-rounded value when half != 0)
  * p_out : optional fp32 (N): 1/(density+1), 1e-7 where density < 10   (matcher.py:490-491)
+ * workspace: roma_kde_workspace_bytes(N) bytes (deterministic split-sum partials; a smaller buffer of at
+ *   least N floats is accepted and only reduces parallelism).
  */
-int roma_kde(const float* x, int N, int down, float std, int half,
-             float* density, float* p_out, void* stream);
+size_t roma_kde_workspace_bytes(int N);
+int roma_kde(const float* x, int N, int down, double std, int half,
+             float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * K3c  match_keypoints: warp keypoints of A into B, mutual nearest neighbours.
@@ -168,13 +171,14 @@ int roma_kde(const float* x, int N, int down, float std, int half,
  * x_A (Na,2), x_B (Nb,2) fp32 normalised coords; warp (H, Wp, 4) fp32; certainty (H, Wp) fp32.
  * The last two warp channels are sampled bilinearly at x_A (zeros padding, align_corners=False).
  * workspace: roma_match_keypoints_workspace_bytes(Na, Nb).
- * inds_A, inds_B: int64 (capacity min(Na,Nb)) — mutual-NN pairs with cert > thresh, ordered by
- *   (a, b) like torch.nonzero; *count (device int32) receives the number of pairs.
+ * inds_A, inds_B: int64 arrays of `capacity` entries — mutual-NN pairs with cert > thresh, ordered by
+ *   (a, b) like torch.nonzero; *count (device int32) receives the TOTAL number of pairs found (pairs
+ *   beyond `capacity` are counted but not stored; without exact distance ties there are <= min(Na,Nb)).
  */
 size_t roma_match_keypoints_workspace_bytes(int Na, int Nb);
 int roma_match_keypoints(const float* x_A, int Na, const float* x_B, int Nb,
                          const float* warp, const float* certainty, int H, int Wp,
-                         float thresh, int64_t* inds_A, int64_t* inds_B, int* count,
+                         float thresh, int64_t* inds_A, int64_t* inds_B, int capacity, int* count,
                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------

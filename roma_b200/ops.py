@@ -226,3 +226,112 @@ def gp_posterior(x: torch.Tensor, y: torch.Tensor, pos_w: torch.Tensor, pos_b: t
                                _DT[x.dtype], _ptr(ws), ws.numel(), _stream(dev))
     _lib.check(rc, "roma_gp_posterior")
     return mu
+
+
+# --------------------------------------------------------------------------------------------------
+# K3b: kde + sampling
+# --------------------------------------------------------------------------------------------------
+def kde(x: torch.Tensor, std: float = 0.1, half: bool = True, down: Optional[int] = None,
+        return_p: bool = False):
+    """Drop-in for romatch.utils.kde.kde (kde.py:4-12): streaming, no N x N temporary.
+
+    Returns the density as fp16 when `half` (like the reference) else fp32; with return_p also the sampling
+    weights p = 1/(density+1), p[density<10] = 1e-7 of matcher.py:490-491 in the same dtype."""
+    dev = _cuda(x)
+    if x.dim() != 2 or x.shape[1] != 4:
+        raise ValueError(f"kde expects (N,4) points, got {tuple(x.shape)}")
+    N = x.shape[0]
+    xf = x.float().contiguous()
+    lib = _lib.load()
+    dens = torch.empty(N, device=dev, dtype=torch.float32)
+    p = torch.empty(N, device=dev, dtype=torch.float32) if return_p else None
+    ws = torch.empty(lib.roma_kde_workspace_bytes(N), device=dev, dtype=torch.uint8)
+    rc = lib.roma_kde(_ptr(xf), N, int(down or 1), float(std), int(bool(half)), _ptr(dens), _ptr(p),
+                      _ptr(ws), ws.numel(), _stream(dev))
+    _lib.check(rc, "roma_kde")
+    if half:   # values are already fp16-representable: the cast is exact
+        dens = dens.half()
+        p = None if p is None else p.half()
+    return (dens, p) if return_p else dens
+
+
+def sample(matches: torch.Tensor, certainty: torch.Tensor, num: int = 10000, sample_thresh: float = 0.05,
+           sample_mode: str = "threshold_balanced", kde_half: bool = True, kde_down: Optional[int] = None,
+           generator: Optional[torch.Generator] = None, return_indices: bool = False):
+    """RegressionMatcher.sample (matcher.py:468-495) / TinyRoMa.sample (tiny.py:297-327).
+
+    The two draws stay on torch.multinomial so the device generator's Philox stream is consumed exactly as
+    in the reference (that is what makes the sampled indices reproducible against it); thresholding is a
+    torch elementwise op, the density and the weights p come from the kde kernel."""
+    _cuda(matches, certainty)
+    if "threshold" in sample_mode:
+        certainty = torch.where(certainty > sample_thresh, torch.ones_like(certainty), certainty)
+    matches, certainty = matches.reshape(-1, 4), certainty.reshape(-1)
+    expansion = 4 if "balanced" in sample_mode else 1
+    good = torch.multinomial(certainty, num_samples=min(expansion * num, len(certainty)), replacement=False,
+                             generator=generator)
+    good_matches, good_certainty = matches[good], certainty[good]
+    if "balanced" not in sample_mode:
+        return (good_matches, good_certainty, good) if return_indices else (good_matches, good_certainty)
+    _, p = kde(good_matches, std=0.1, half=kde_half, down=kde_down, return_p=True)
+    bal = torch.multinomial(p, num_samples=min(num, len(good_certainty)), replacement=False, generator=generator)
+    out = (good_matches[bal], good_certainty[bal])
+    return out + (good[bal],) if return_indices else out
+
+
+# --------------------------------------------------------------------------------------------------
+# K3c: match_keypoints
+# --------------------------------------------------------------------------------------------------
+def match_keypoints(x_A: torch.Tensor, x_B: torch.Tensor, warp: torch.Tensor, certainty: torch.Tensor,
+                    sample_thresh: float = 0.05):
+    """matcher.py:576-580: int64 (inds_A, inds_B) of mutual nearest neighbours with certainty > thresh."""
+    dev = _cuda(x_A, x_B, warp, certainty)
+    Na, Nb = x_A.shape[0], x_B.shape[0]
+    H, Wp, four = warp.shape
+    assert four == 4 and certainty.shape == (H, Wp)
+    xa, xb = x_A.float().contiguous(), x_B.float().contiguous()
+    warp, certainty = warp.float().contiguous(), certainty.float().contiguous()
+    lib = _lib.load()
+    cap = max(Na, Nb)
+    ia = torch.empty(cap, device=dev, dtype=torch.int64)
+    ib = torch.empty(cap, device=dev, dtype=torch.int64)
+    count = torch.zeros(1, device=dev, dtype=torch.int32)
+    ws = torch.empty(lib.roma_match_keypoints_workspace_bytes(Na, Nb), device=dev, dtype=torch.uint8)
+    rc = lib.roma_match_keypoints(_ptr(xa), Na, _ptr(xb), Nb, _ptr(warp), _ptr(certainty), H, Wp,
+                                  float(sample_thresh), _ptr(ia), _ptr(ib), cap, _ptr(count),
+                                  _ptr(ws), ws.numel(), _stream(dev))
+    _lib.check(rc, "roma_match_keypoints")
+    n = int(count.item())   # the reference's torch.nonzero has the same inherent sync (matcher.py:580)
+    if n > cap:
+        raise RuntimeError(f"match_keypoints: {n} tied pairs exceed capacity {cap}")
+    return ia[:n], ib[:n]
+
+
+# --------------------------------------------------------------------------------------------------
+# (f-1) cls_to_flow_refine, KT tiny
+# --------------------------------------------------------------------------------------------------
+def cls_to_flow_refine(cls: torch.Tensor) -> torch.Tensor:
+    """romatch/utils/utils.py:301-323: (B,C=res^2,H,W) logits -> (B,H,W,2) flow.  Strided input consumed in place."""
+    dev = _cuda(cls)
+    if cls.dtype not in _DT:
+        raise ValueError(f"unsupported dtype {cls.dtype}")
+    B, Cc, H, W = cls.shape
+    out = torch.empty((B, H, W, 2), device=dev, dtype=torch.float32)
+    rc = _lib.load().roma_cls_to_flow_refine(_ptr(cls), _s4(cls), _DT[cls.dtype], _ptr(out), B, Cc, H, W, _stream(dev))
+    _lib.check(rc, "roma_cls_to_flow_refine")
+    return out
+
+
+def tiny_corr_posembed(feat0: torch.Tensor, feat1: torch.Tensor) -> torch.Tensor:
+    """TinyRoMa.pos_embed(TinyRoMa.corr_volume(feat0, feat1)) (tiny.py:241-254 + 178-199), fused.
+
+    feat0 (B,C,H0,W0), feat1 (B,C,H1,W1) -> (B,2,H0,W0); the (B,H1,W1,H0,W0) volume is never formed."""
+    dev = _cuda(feat0, feat1)
+    B, Cc, H0, W0 = feat0.shape
+    _, _, H1, W1 = feat1.shape
+    f0 = _nhwc(feat0.float())
+    f1 = _nhwc(feat1.float())
+    out = torch.empty((B, 2, H0, W0), device=dev, dtype=torch.float32)
+    rc = _lib.load().roma_tiny_corr_posembed(_ptr(f0), _ptr(f1), _ptr(out), B, Cc, H0, W0, H1, W1, _stream(dev))
+    _lib.check(rc, "roma_tiny_corr_posembed")
+    return out

@@ -1,0 +1,253 @@
+"""Parity of every CUDA entry point (through the C ABI) against the CPU oracle and the reference goldens.
+
+Tolerances: north_star asks for warp <= 1e-3 and certainty logits <= 1e-2 end to end; per kernel we hold
+fp32 paths to ~1e-5..1e-4 (accumulation-order noise) and 16-bit feature paths to the rounding of their
+output dtype.  Integer outputs (indices) are compared exactly.
+"""
+import math
+
+import pytest
+import torch
+
+from oracle import roma_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops(cuda):
+    from roma_b200 import _lib, ops as _ops
+    lib = _lib.load()
+    assert lib.roma_check_device(0) == 0, lib.roma_last_error_string()
+    return _ops
+
+
+def err(a, b):
+    return (a.float().cpu() - b.float().cpu()).abs().max().item()
+
+
+def make_flow(g, B, h, w, mode):
+    grid = O.pixel_grid(B, h, w)
+    if mode == "coherent":
+        low = torch.randn(B, 2, max(h // 8, 2), max(w // 8, 2), generator=g) * 0.05
+        return (grid + O.bilinear_resize(low, (h, w))).contiguous()
+    return torch.rand(B, 2, h, w, generator=g) * 2.2 - 1.1      # incoherent, includes out-of-range taps
+
+
+# ---------------------------------------------------------------------------------------------- K2
+@pytest.mark.parametrize("tag", ["r2", "r3", "r7"])
+def test_local_corr_golden(ops, cuda, golden, tag):
+    """Kernel vs the REFERENCE's own outputs (tests/golden), fp32."""
+    g = golden(f"local_corr_{tag}")
+    # golden channel counts (16, 24, 8) are multiples of 4 -> vector path in fp32
+    corr = ops.local_correlation(g["f0"].to(cuda), g["f1"].to(cuda), g["r"], flow=g["flow"].to(cuda))
+    assert err(corr, g["corr"]) < 1e-4
+    xhat = ops.grid_sample(g["f1"].to(cuda), g["flow"].permute(0, 2, 3, 1).to(cuda))
+    assert err(xhat, g["xhat"]) < 1e-5
+
+
+def test_local_corr_aligned_golden(ops, cuda, golden):
+    g = golden("local_corr_noflow")
+    assert err(ops.local_correlation(g["f0"].to(cuda), g["f1"].to(cuda), g["r"]), g["corr"]) < 1e-4
+
+
+@pytest.mark.parametrize("tag", ["corr", "nocorr"])
+def test_refiner_inputs_golden(ops, cuda, golden, tag):
+    g = golden(f"refiner_inputs_{tag}")
+    d = ops.refiner_inputs(g["x"].to(cuda), g["y"].to(cuda), g["flow"].to(cuda), g["disp_w"].to(cuda), g["disp_b"].to(cuda),
+                           40 / 32 * g["scale_factor"], g["r"] or None)
+    assert d.shape == g["d"].shape
+    assert err(d, g["d"]) < 1e-4
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-4), (torch.float16, 6e-3), (torch.bfloat16, 4e-2)])
+@pytest.mark.parametrize("C,E,r,h,w", [(512, 128, 7, 20, 20), (512, 64, 3, 35, 33), (256, 32, 2, 40, 44),
+                                        (64, 16, 0, 48, 40), (9, 6, 0, 50, 46), (24, 0, 0, 30, 40)])
+@pytest.mark.parametrize("flow_mode", ["coherent", "incoherent"])
+def test_refiner_inputs_vs_oracle(ops, cuda, dtype, tol, C, E, r, h, w, flow_mode):
+    """The five roma_outdoor refiner configurations (channel counts of roma_models.py:40-114) + a Tiny gather,
+    at reduced spatial size, in the three feature dtypes, for coherent and incoherent flows."""
+    g = torch.Generator().manual_seed(7)
+    B = 2
+    x = torch.randn(B, C, h, w, generator=g).to(dtype)
+    y = torch.randn(B, C, h, w, generator=g).to(dtype)
+    flow = make_flow(g, B, h, w, flow_mode)
+    dw = torch.randn(E, 2, generator=g) if E else None
+    db = torch.randn(E, generator=g) if E else None
+    want = O.refiner_inputs(x.float(), y.float(), flow, dw, db, 1.9, r or None)      # oracle on the SAME rounded inputs
+    got = ops.refiner_inputs(x.to(cuda), y.to(cuda), flow.to(cuda), None if dw is None else dw.to(cuda),
+                             None if db is None else db.to(cuda), 1.9, r or None)
+    assert got.dtype == dtype and got.shape == want.shape
+    assert got.is_contiguous(memory_format=torch.channels_last)
+    scale = max(1.0, want.abs().max().item())
+    assert err(got, want) < tol * scale
+
+
+def test_refiner_inputs_strided_flow_and_nchw_features(ops, cuda):
+    """Permuted flow views and NCHW-contiguous features are accepted (SURVEY §8a 'strided inputs')."""
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(2, 64, 12, 10, generator=g); y = torch.randn(2, 64, 12, 10, generator=g)
+    flow_nhwc = make_flow(g, 2, 12, 10, "incoherent").permute(0, 2, 3, 1).contiguous()
+    flow = flow_nhwc.permute(0, 3, 1, 2)   # (B,2,h,w) view over interleaved storage
+    want = O.refiner_inputs(x, y, flow, None, None, 1.0, 2)
+    got = ops.refiner_inputs(x.to(cuda), y.to(cuda), flow_nhwc.to(cuda).permute(0, 3, 1, 2), None, None, 1.0, 2)
+    assert err(got, want) < 1e-4
+
+
+def test_refiner_gather_rejects_cpu_tensors(ops):
+    with pytest.raises(RuntimeError):
+        ops.refiner_inputs(torch.zeros(1, 8, 4, 4), torch.zeros(1, 8, 4, 4), torch.zeros(1, 2, 4, 4))
+
+
+# --------------------------------------------------------------------------------------------- K3a
+def test_update_resample_golden(ops, cuda, golden):
+    g = golden("update_resample")
+    for k in ("up", "odd", "down"):
+        size = tuple(int(v) for v in g[f"size_{k}"])
+        fo, co, fn, cn = ops.flow_update_resample(g["flow"].to(cuda), g["cert"].to(cuda), g["delta"].to(cuda),
+                                                  g["ins"], (g["Hf"], g["Wf"]), size)
+        assert torch.equal(fo.cpu(), g["flow_u"]) and torch.equal(co.cpu(), g["cert_u"])   # update is bit-exact
+        assert err(fn, g[f"flow_{k}"]) < 1e-5 and err(cn, g[f"cert_{k}"]) < 1e-5
+
+
+@pytest.mark.parametrize("h,w,h2,w2", [(40, 40, 70, 70), (70, 70, 140, 140), (560, 560, 108, 108), (36, 52, 63, 91)])
+def test_update_resample_vs_oracle(ops, cuda, h, w, h2, w2):
+    g = torch.Generator().manual_seed(11)
+    B = 2
+    flow = make_flow(g, B, h, w, "coherent"); cert = torch.randn(B, 1, h, w, generator=g) * 2
+    delta = (torch.randn(B, h, w, 3, generator=g) * 4).permute(0, 3, 1, 2)     # channels-last delta like out_conv gives
+    fu, cu = O.flow_update(flow, cert, delta, 8, 4 * h, 4 * w)
+    fo, co, fn, cn = ops.flow_update_resample(flow.to(cuda), cert.to(cuda), delta.to(cuda), 8, (4 * h, 4 * w), (h2, w2))
+    assert torch.equal(fo.cpu(), fu) and torch.equal(co.cpu(), cu)
+    assert err(fn, O.bilinear_resize(fu, (h2, w2))) < 1e-5
+    assert err(cn, O.bilinear_resize(cu, (h2, w2))) < 2e-5
+    # pure resample, no certainty (entry of the coarse pass / upsample pass)
+    _, _, fn2, cn2 = ops.flow_update_resample(flow.to(cuda), None, None, 8, (h, w), (h2, w2), want_current=False)
+    assert err(fn2, O.bilinear_resize(flow, (h2, w2))) < 1e-5 and cn2.abs().max().item() == 0
+
+
+@pytest.mark.parametrize("tag", ["sym", "asym"])
+def test_epilogue_golden(ops, cuda, golden, tag):
+    g = golden(f"epilogue_{tag}")
+    warp, cert = ops.match_epilogue(g["flow"].to(cuda), g["cert"].to(cuda),
+                                    g["cert16"].to(cuda) if g["attenuate"] else None, bool(g["symmetric"]))
+    assert err(warp[0], g["warp"]) < 1e-6 and err(cert[0], g["certainty"]) < 1e-6
+
+
+def test_epilogue_vs_oracle_batched(ops, cuda):
+    g = torch.Generator().manual_seed(5)
+    B, H, W = 3, 96, 80
+    flow = make_flow(g, 2 * B, H, W, "coherent") * 1.05        # some coordinates beyond +-1
+    cert = torch.randn(2 * B, 1, H, W, generator=g) * 3
+    c16 = torch.randn(2 * B, 1, 7, 5, generator=g) * 2
+    w0, c0, l0 = O.match_epilogue(flow, cert, c16, True)
+    w1, c1, l1 = ops.match_epilogue(flow.to(cuda), cert.to(cuda), c16.to(cuda), True, return_logits=True)
+    assert w1.shape == (B, H, 2 * W, 4)
+    assert err(w1, w0) < 1e-6 and err(c1, c0) < 1e-6 and err(l1, l0) < 1e-5
+    assert (c1 == 0).sum().item() == (c0 == 0).sum().item() > 0
+
+
+# ---------------------------------------------------------------------------------------------- K1
+@pytest.mark.parametrize("tag", ["sq", "rect"])
+def test_gp_golden(ops, cuda, golden, tag):
+    g = golden(f"gp_{tag}")
+    mu = ops.gp_posterior(g["x"].to(cuda), g["y"].to(cuda), g["pos_w"].to(cuda), g["pos_b"].to(cuda))
+    assert mu.shape == g["mu"].shape
+    assert err(mu, g["mu"]) < 1e-4
+
+
+@pytest.mark.parametrize("h1,w1,h2,w2,C,D", [(20, 20, 20, 20, 512, 512), (12, 17, 15, 11, 128, 96)])
+def test_gp_vs_oracle_fp64(ops, cuda, h1, w1, h2, w2, C, D):
+    """Error budget: |mu - mu_fp64| <= 1e-3 (GP error feeds the warp with gain ~0.55)."""
+    g = torch.Generator().manual_seed(21)
+    b = 2
+    base = O.bilinear_resize(torch.randn(b, C, 4, 4, generator=g), (h1, w1))
+    x = base + 0.3 * torch.randn(b, C, h1, w1, generator=g)
+    y = O.bilinear_resize(base, (h2, w2)) + 0.3 * torch.randn(b, C, h2, w2, generator=g)
+    pw = torch.randn(D, 2, generator=g) * 0.5; pb = torch.randn(D, generator=g) * 0.5
+    want = O.gp_posterior(x, y, pw, pb, dtype=torch.float64)
+    ref32 = O.gp_posterior(x, y, pw, pb)
+    got = ops.gp_posterior(x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda))
+    e_kernel, e_ref = err(got, want), err(ref32, want)
+    assert e_kernel < 1e-3, (e_kernel, e_ref)
+    assert e_kernel < max(10 * e_ref, 2e-4), (e_kernel, e_ref)      # as good as the reference's own fp32 path
+
+
+# --------------------------------------------------------------------------------------------- K3b
+def test_kde_golden_and_oracle(ops, cuda, golden):
+    g = golden("kde")
+    d32 = ops.kde(g["x"].to(cuda), half=False)
+    assert err(d32, g["dens_f32"]) < 2e-3 * g["dens_f32"].max().item()
+    assert err(ops.kde(g["x"].to(cuda), half=False, down=8), g["dens_down"]) < 1e-3 * g["dens_down"].max().item()
+    d16 = ops.kde(g["x"].to(cuda), half=True)
+    assert d16.dtype == torch.float16
+    rel = ((d16.float().cpu() - g["dens_half"]).abs() / g["dens_half"].clamp(min=1)).max().item()
+    assert rel < 4e-3          # within a few fp16 ulps of the reference's CPU fp16 chain
+
+
+def test_kde_weights(ops, cuda):
+    g = torch.Generator().manual_seed(2)
+    x = torch.cat((torch.rand(3000, 4, generator=g) * 2 - 1, torch.randn(1000, 4, generator=g) * 0.02)).to(cuda)
+    dens, p = ops.kde(x, half=False, return_p=True)
+    want = 1 / (dens + 1)
+    want[dens < 10] = 1e-7
+    assert torch.equal(p, want)
+
+
+def test_sample_matches_oracle_given_same_density(ops, cuda):
+    """With the kde swapped for the kernel inside the oracle's sample(), both consume the SAME CUDA generator
+    stream: the sampled flat indices must be bit-identical."""
+    g = torch.Generator().manual_seed(8)
+    H, W = 64, 96
+    warp = torch.rand(H, W, 4, generator=g).to(cuda) * 2 - 1
+    cert = (torch.rand(H, W, generator=g) * (torch.rand(H, W, generator=g) < 0.6)).to(cuda)
+    gen = torch.Generator(device=cuda)
+    gen.manual_seed(1234)
+    m1, c1, i1 = ops.sample(warp, cert, num=500, generator=gen, return_indices=True)
+    gen.manual_seed(1234)
+    m0, c0, i0 = O.sample(warp, cert, num=500, generator=gen, kde_fn=lambda x, std: ops.kde(x, std=std), return_indices=True)
+    assert i1.dtype == torch.int64 and torch.equal(i1, i0) and torch.equal(m1, m0) and torch.equal(c1, c0)
+
+
+# --------------------------------------------------------------------------------------------- K3c
+def test_match_keypoints_golden(ops, cuda, golden):
+    g = golden("match_keypoints")
+    ia, ib = ops.match_keypoints(g["xA"].to(cuda), g["xB"].to(cuda), g["warp"].to(cuda), g["cert"].to(cuda))
+    assert ia.dtype == torch.int64
+    assert torch.equal(ia.cpu(), g["inds_A"]) and torch.equal(ib.cpu(), g["inds_B"])
+
+
+def test_match_keypoints_vs_oracle_large(ops, cuda):
+    g = torch.Generator().manual_seed(13)
+    H, W = 60, 160
+    warp = torch.cat((O.pixel_grid(1, H, W), make_flow(g, 1, H, W, "coherent")), dim=1)[0].permute(1, 2, 0).contiguous()
+    cert = torch.rand(H, W, generator=g)
+    xA = torch.rand(1500, 2, generator=g) * 2 - 1
+    xB = torch.rand(1700, 2, generator=g) * 2 - 1
+    ia0, ib0 = O.match_keypoints(xA, xB, warp, cert)
+    ia1, ib1 = ops.match_keypoints(xA.to(cuda), xB.to(cuda), warp.to(cuda), cert.to(cuda))
+    assert torch.equal(ia1.cpu(), ia0) and torch.equal(ib1.cpu(), ib0)
+
+
+# ------------------------------------------------------------------------------------- f-1, Tiny
+def test_cls_to_flow_golden_and_strided(ops, cuda, golden):
+    g = golden("cls_to_flow")
+    assert err(ops.cls_to_flow_refine(g["cls"].to(cuda)), g["flow"]) < 1e-5
+    # token-major logits with a trailing certainty column, as TransformerDecoder produces them
+    gg = torch.Generator().manual_seed(4)
+    out = torch.randn(2, 6 * 7, 4097, generator=gg) * 2
+    cls = out.permute(0, 2, 1).reshape(2, 4097, 6, 7)[:, :-1]
+    want = O.cls_to_flow_refine(cls)
+    got = ops.cls_to_flow_refine(out.to(cuda).permute(0, 2, 1).reshape(2, 4097, 6, 7)[:, :-1])
+    assert err(got, want) < 1e-5
+    got16 = ops.cls_to_flow_refine(out.half().to(cuda).permute(0, 2, 1).reshape(2, 4097, 6, 7)[:, :-1])
+    assert err(got16, O.cls_to_flow_refine(out.half().float().permute(0, 2, 1).reshape(2, 4097, 6, 7)[:, :-1])) < 1e-5
+
+
+def test_tiny_golden_and_oracle(ops, cuda, golden):
+    g = golden("tiny")
+    assert err(ops.tiny_corr_posembed(g["feat0"].to(cuda), g["feat1"].to(cuda)), g["pos_embed"]) < 1e-5
+    gg = torch.Generator().manual_seed(6)
+    f0 = torch.randn(2, 64, 12, 16, generator=gg); f1 = torch.randn(2, 64, 12, 16, generator=gg)
+    want = torch.cat([O.tiny_pos_embed(O.tiny_corr_volume(f0[i:i + 1], f1[i:i + 1])) for i in range(2)])
+    assert err(ops.tiny_corr_posembed(f0.to(cuda), f1.to(cuda)), want) < 1e-5
