@@ -1,0 +1,183 @@
+"""Host-side mirror of the reference decoder (romatch/models/matcher.py:17-422) with the hot ops replaced by
+the sm_100a kernels in `roma_b200.ops`.  The conv / transformer bodies stay PyTorch (north_star); module and
+parameter names equal the reference's so `load_state_dict` takes the same checkpoints:
+
+  decoder.embedding_decoder.{blocks.N.*, to_out.*}     transformer/__init__.py:10-46
+  decoder.gps.16.pos_conv.*                            matcher.py:165-273
+  decoder.proj.{16,8,4,2,1}.{0,1}.*                    model_zoo/roma_models.py:131-142
+  decoder.conv_refiner.{s}.{block1,hidden_blocks.N,out_conv,disp_emb}.*   matcher.py:17-103
+
+Inference only: the training-mode keys of matcher.py:386-396 are not produced (`match` forces eval, :623).
+There is no CPU path: the kernels raise on non-CUDA tensors.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from .encoder import _autocast
+from .vit import Block
+
+
+class ConvRefiner(nn.Module):
+    """matcher.py:17-143.  forward(x, y, flow, scale_factor, logits) -> (delta_flow (B,2,h,w), delta_certainty (B,1,h,w))."""
+
+    def __init__(self, in_dim: int, hidden_dim: int, out_dim: int = 3, kernel_size: int = 5, hidden_blocks: int = 8,
+                 displacement_emb_dim: Optional[int] = None, local_corr_radius: Optional[int] = None,
+                 bn_momentum: float = 0.01, amp_dtype: torch.dtype = torch.float16):
+        super().__init__()
+        self.block1 = self._block(in_dim, hidden_dim, kernel_size, bn_momentum)
+        self.hidden_blocks = nn.Sequential(*[self._block(hidden_dim, hidden_dim, kernel_size, bn_momentum)
+                                             for _ in range(hidden_blocks)])
+        self.out_conv = nn.Conv2d(hidden_dim, out_dim, 1, 1, 0)
+        self.has_displacement_emb = bool(displacement_emb_dim)
+        if self.has_displacement_emb:
+            self.disp_emb = nn.Conv2d(2, displacement_emb_dim, 1, 1, 0)
+        self.local_corr_radius = local_corr_radius
+        self.amp_dtype = amp_dtype
+
+    @staticmethod
+    def _block(cin: int, cout: int, k: int, momentum: float) -> nn.Sequential:
+        assert cout % cin == 0, "depthwise block needs out_dim divisible by in_dim"
+        return nn.Sequential(nn.Conv2d(cin, cout, k, 1, k // 2, groups=cin), nn.BatchNorm2d(cout, momentum=momentum),
+                             nn.ReLU(inplace=True), nn.Conv2d(cout, cout, 1, 1, 0))
+
+    def forward(self, x, y, flow, scale_factor: float = 1, logits=None):
+        # K2: x_hat = grid_sample(y, flow), disp_emb(40/32*scale_factor*(flow-grid)), local_correlation and the
+        # concat of matcher.py:109-132 in one launch, written channels-last in the feature dtype.
+        dw = self.disp_emb.weight if self.has_displacement_emb else None
+        db = self.disp_emb.bias if self.has_displacement_emb else None
+        d = ops.refiner_inputs(x, y, flow, dw, db, 40 / 32 * scale_factor, self.local_corr_radius)
+        with _autocast(x.device, self.amp_dtype):
+            d = self.hidden_blocks(self.block1(d))
+        d = self.out_conv(d.float())
+        return d[:, :-1], d[:, -1:]
+
+    def delta(self, x, y, flow, scale_factor: float = 1) -> torch.Tensor:
+        """Same as forward but returns the undivided (B,3,h,w) out_conv tensor for the fused update kernel."""
+        dw = self.disp_emb.weight if self.has_displacement_emb else None
+        db = self.disp_emb.bias if self.has_displacement_emb else None
+        d = ops.refiner_inputs(x, y, flow, dw, db, 40 / 32 * scale_factor, self.local_corr_radius)
+        with _autocast(x.device, self.amp_dtype):
+            d = self.hidden_blocks(self.block1(d))
+        return self.out_conv(d.float())
+
+
+class CosKernel(nn.Module):
+    """Holder of the temperature (matcher.py:145-163); the kernel itself is fused into ops.gp_posterior."""
+
+    def __init__(self, T: float):
+        super().__init__()
+        self.T = T
+
+
+class GP(nn.Module):
+    """GP coarse matcher with CosKernel, fourier basis, no covariance output (matcher.py:165-273)."""
+
+    def __init__(self, T: float = 0.2, gp_dim: int = 512, sigma_noise: float = 0.1):
+        super().__init__()
+        self.K = CosKernel(T)
+        self.sigma_noise = sigma_noise
+        self.pos_conv = nn.Conv2d(2, gp_dim, 1, 1)
+        self.dim = gp_dim
+
+    def forward(self, x, y, **kwargs):
+        return ops.gp_posterior(x, y, self.pos_conv.weight, self.pos_conv.bias, T=self.K.T, sigma_noise=self.sigma_noise)
+
+
+class TransformerDecoder(nn.Module):
+    """transformer/__init__.py:10-46: tokens = cat(gp_posterior, features) -> blocks -> Linear -> (cls, certainty)."""
+
+    def __init__(self, blocks: nn.Sequential, hidden_dim: int, out_dim: int, amp_dtype: torch.dtype = torch.float16):
+        super().__init__()
+        self.blocks = blocks
+        self.to_out = nn.Linear(hidden_dim, out_dim)
+        self.hidden_dim, self.out_dim = hidden_dim, out_dim
+        self.is_classifier = True
+        self.amp_dtype = amp_dtype
+
+    def scales(self):
+        return [16]
+
+    def forward(self, gp_posterior, features, old_stuff=None, new_scale=None):
+        B, _, H, W = gp_posterior.shape
+        with _autocast(gp_posterior.device, self.amp_dtype):
+            # both inputs are channels-last, so (B,C,H,W)->(B,HW,C) is a view
+            tok = torch.cat((gp_posterior.permute(0, 2, 3, 1).reshape(B, H * W, -1),
+                             features.permute(0, 2, 3, 1).reshape(B, H * W, -1).to(gp_posterior.dtype)), dim=-1)
+            out = self.to_out(self.blocks(tok))                      # (B, HW, out_dim) token-major
+        out = out.view(B, H, W, self.out_dim).permute(0, 3, 1, 2)    # (B, out_dim, H, W) view, strides kept
+        return out[:, :-1], out[:, -1:], None
+
+
+class Decoder(nn.Module):
+    """Scale loop 16 -> 8 -> 4 -> 2 -> 1 (matcher.py:275-422)."""
+
+    def __init__(self, embedding_decoder: TransformerDecoder, gps: nn.ModuleDict, proj: nn.ModuleDict,
+                 conv_refiner: nn.ModuleDict, scales: Sequence[str] = ("16", "8", "4", "2", "1"),
+                 amp_dtype: torch.dtype = torch.float16):
+        super().__init__()
+        self.embedding_decoder = embedding_decoder
+        self.gps = gps
+        self.proj = proj
+        self.conv_refiner = conv_refiner
+        self.scales = list(scales)
+        self.refine_init = 4
+        self.amp_dtype = amp_dtype
+
+    def forward(self, f1: Dict[int, torch.Tensor], f2: Dict[int, torch.Tensor], gt_warp=None, gt_prob=None,
+                upsample: bool = False, flow: Optional[torch.Tensor] = None,
+                certainty: Optional[torch.Tensor] = None, scale_factor: float = 1):
+        coarse_scales = self.embedding_decoder.scales()
+        all_scales = self.scales if not upsample else ["8", "4", "2", "1"]
+        sizes = {s: f1[s].shape[-2:] for s in f1}
+        h, w = sizes[1]
+        corresps = {}
+        if upsample:
+            # matcher.py:349-360: previous pass' finest flow / certainty resampled to the coarsest size of this pass
+            _, _, flow, certainty = ops.flow_update_resample(flow, certainty, None, 1, (h, w),
+                                                             tuple(sizes[int(all_scales[0])]), want_current=False)
+        else:
+            flow, certainty = None, None
+        for new_scale in all_scales:
+            ins = int(new_scale)
+            f1_s, f2_s = f1[ins], f2[ins]
+            if new_scale in self.proj:
+                with _autocast(f1_s.device, self.amp_dtype):
+                    if self.amp_dtype == torch.float32:
+                        f1_s, f2_s = f1_s.float(), f2_s.float()
+                    f1_s, f2_s = self.proj[new_scale](f1_s), self.proj[new_scale](f2_s)
+            if ins in coarse_scales:
+                gp_posterior = self.gps[new_scale](f1_s, f2_s)                                  # K1
+                cls, certainty, _ = self.embedding_decoder(gp_posterior, f1_s, None, new_scale)
+                flow = ops.cls_to_flow_refine(cls).permute(0, 3, 1, 2)                          # (f-1)
+            if new_scale in self.conv_refiner:
+                delta = self.conv_refiner[new_scale].delta(f1_s, f2_s, flow, scale_factor=scale_factor)
+            else:
+                delta = None
+            nxt = tuple(sizes[ins // 2]) if new_scale != "1" else None
+            # K3a: flow += ins*(delta/(4w,4h)); certainty += dcert; bilinear resample to the next scale
+            flow_s, cert_s, flow, certainty = ops.flow_update_resample(flow, certainty, delta, ins, (h, w), nxt)
+            corresps[ins] = {"certainty": cert_s, "flow": flow_s}
+        return corresps
+
+
+def build_decoder(amp_dtype: torch.dtype = torch.float16) -> Decoder:
+    """Hyper-parameters of model_zoo/roma_models.py:23-152 (roma_outdoor / roma_indoor)."""
+    gp_dim = feat_dim = 512
+    dec_dim = gp_dim + feat_dim
+    emb = TransformerDecoder(nn.Sequential(*[Block(dec_dim, 8) for _ in range(5)]), dec_dim, 64 ** 2 + 1, amp_dtype)
+    spec = {   # scale: (feature C, disp emb dim, radius)
+        "16": (512, 128, 7), "8": (512, 64, 3), "4": (256, 32, 2), "2": (64, 16, None), "1": (9, 6, None)}
+    refiners = nn.ModuleDict()
+    for s, (c, e, r) in spec.items():
+        dim = 2 * c + e + ((2 * r + 1) ** 2 if r else 0)
+        refiners[s] = ConvRefiner(dim, dim, 3, 5, 8, e, r, 0.01, amp_dtype)
+    gps = nn.ModuleDict({"16": GP(0.2, gp_dim)})
+    proj = nn.ModuleDict({s: nn.Sequential(nn.Conv2d(ci, co, 1, 1), nn.BatchNorm2d(co))
+                          for s, (ci, co) in {"16": (1024, 512), "8": (512, 512), "4": (256, 256),
+                                              "2": (128, 64), "1": (64, 9)}.items()})
+    return Decoder(emb, gps, proj, refiners, amp_dtype=amp_dtype)

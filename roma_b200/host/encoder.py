@@ -1,0 +1,84 @@
+"""Feature pyramid encoder (stays PyTorch per north_star): VGG19-bn slices at strides 1/2/4/8 plus DINOv2
+ViT-L/14 patch tokens as the "scale 16" map (really stride 14).
+
+Mirrors romatch/models/encoders.py:61-121 (state_dict keys `cnn.layers.N.*`; the ViT is deliberately NOT a
+registered sub-module there — encoders.py:104 — so its weights travel separately as `dinov2_weights`).
+Differences that do not change results: the last max-pool of features[:40] (whose output the reference
+discards) is not executed, and feature maps are produced channels-last because the kernels consume NHWC.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+import torch.nn as nn
+import torchvision.models as tvm
+
+from .vit import DinoViT
+
+
+def _autocast(device: torch.device, dtype: torch.dtype):
+    """The reference forces autocast on for CUDA and off elsewhere (utils.py:640-654); fp32 means 'off'."""
+    on = device.type == "cuda" and dtype in (torch.float16, torch.bfloat16)
+    return torch.autocast(device.type if device.type == "cuda" else "cpu", enabled=on,
+                          dtype=dtype if on else torch.bfloat16)
+
+
+class VGG19(nn.Module):
+    def __init__(self, amp_dtype: torch.dtype = torch.float16):
+        super().__init__()
+        self.layers = nn.ModuleList(tvm.vgg19_bn(weights=None).features[:40])
+        self.amp_dtype = amp_dtype
+
+    def forward(self, x: torch.Tensor) -> Dict[int, torch.Tensor]:
+        feats, scale = {}, 1
+        last = len(self.layers) - 1
+        with _autocast(x.device, self.amp_dtype):
+            for i, layer in enumerate(self.layers):
+                if isinstance(layer, nn.MaxPool2d):
+                    feats[scale] = x
+                    scale *= 2
+                    if i == last:
+                        break
+                x = layer(x)
+        return feats
+
+
+class CNNandDinov2(nn.Module):
+    def __init__(self, dinov2_weights: Optional[dict] = None, amp_dtype: torch.dtype = torch.float16):
+        super().__init__()
+        if isinstance(dinov2_weights, DinoViT):
+            vit = dinov2_weights.eval()
+        else:
+            vit = DinoViT(init=dinov2_weights is None).eval()
+            if dinov2_weights is not None:
+                vit.load_state_dict(dinov2_weights)
+        self.cnn = VGG19(amp_dtype)
+        self.amp_dtype = amp_dtype
+        self.dinov2_vitl14 = [vit]          # hidden from state_dict / DDP like encoders.py:104
+
+    def train(self, mode: bool = True):
+        self.cnn.train(mode)
+        return self
+
+    def _vit(self, device) -> DinoViT:
+        vit = self.dinov2_vitl14[0]
+        want = self.amp_dtype if device.type == "cuda" else torch.float32
+        p = vit.cls_token
+        if p.device != device or p.dtype != want:
+            vit = vit.to(device=device, dtype=want)
+            self.dinov2_vitl14[0] = vit
+        return vit
+
+    def forward(self, x: torch.Tensor, upsample: bool = False) -> Dict[int, torch.Tensor]:
+        B, _, H, W = x.shape
+        if x.is_cuda:
+            x = x.contiguous(memory_format=torch.channels_last)
+        pyramid = self.cnn(x)
+        if not upsample:
+            with torch.no_grad():
+                vit = self._vit(x.device)
+                tok = vit.patch_tokens(x.to(vit.cls_token.dtype))          # (B, hw, 1024): already NHWC
+                hp, wp = H // 14, W // 14
+                pyramid[16] = tok.view(B, hp, wp, -1).permute(0, 3, 1, 2)  # (B,1024,hp,wp) channels-last view
+        return pyramid

@@ -1,0 +1,132 @@
+"""Plain-PyTorch ViT bodies that stay PyTorch (north_star): the DINOv2 ViT-L/14 feature encoder and the
+5-block "embedding decoder" transformer.
+
+Parameter names mirror the reference so the same checkpoints load unchanged:
+  DINOv2       romatch/models/transformer/dinov2.py:43-358 (cls_token, pos_embed, mask_token, patch_embed.proj,
+               blocks.N.{norm1, attn.qkv, attn.proj, ls1.gamma, norm2, mlp.fc1, mlp.fc2, ls2.gamma}, norm)
+  Block        romatch/models/transformer/layers/block.py:36-105, attention.py:29-81, mlp.py, layer_scale.py
+Attention runs through F.scaled_dot_product_attention (library flash kernel on the GPU).
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class SelfAttention(nn.Module):
+    def __init__(self, dim: int, num_heads: int, qkv_bias: bool, proj_bias: bool = True):
+        super().__init__()
+        self.num_heads = num_heads
+        self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
+        self.proj = nn.Linear(dim, dim, bias=proj_bias)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        B, N, C = x.shape
+        q, k, v = self.qkv(x).view(B, N, 3, self.num_heads, C // self.num_heads).permute(2, 0, 3, 1, 4)
+        o = F.scaled_dot_product_attention(q, k, v)          # softmax(q k^T / sqrt(d)) v
+        return self.proj(o.transpose(1, 2).reshape(B, N, C))
+
+
+class FeedForward(nn.Module):
+    def __init__(self, dim: int, hidden: int, bias: bool = True):
+        super().__init__()
+        self.fc1 = nn.Linear(dim, hidden, bias=bias)
+        self.fc2 = nn.Linear(hidden, dim, bias=bias)
+
+    def forward(self, x):
+        return self.fc2(F.gelu(self.fc1(x)))
+
+
+class ChannelScale(nn.Module):
+    def __init__(self, dim: int, init: float):
+        super().__init__()
+        self.gamma = nn.Parameter(init * torch.ones(dim))
+
+    def forward(self, x):
+        return x * self.gamma
+
+
+class Block(nn.Module):
+    """Pre-norm transformer block; `init_values` adds DINOv2's per-channel residual scale."""
+
+    def __init__(self, dim: int, num_heads: int, mlp_ratio: float = 4.0, qkv_bias: bool = False,
+                 init_values: Optional[float] = None, norm_eps: float = 1e-5):
+        super().__init__()
+        self.norm1 = nn.LayerNorm(dim, eps=norm_eps)
+        self.attn = SelfAttention(dim, num_heads, qkv_bias)
+        self.ls1 = ChannelScale(dim, init_values) if init_values else nn.Identity()
+        self.norm2 = nn.LayerNorm(dim, eps=norm_eps)
+        self.mlp = FeedForward(dim, int(dim * mlp_ratio))
+        self.ls2 = ChannelScale(dim, init_values) if init_values else nn.Identity()
+
+    def forward(self, x):
+        x = x + self.ls1(self.attn(self.norm1(x)))
+        return x + self.ls2(self.mlp(self.norm2(x)))
+
+
+class PatchEmbed(nn.Module):
+    def __init__(self, patch: int, in_chans: int, dim: int):
+        super().__init__()
+        self.proj = nn.Conv2d(in_chans, dim, kernel_size=patch, stride=patch)
+
+    def forward(self, x):
+        return self.proj(x).flatten(2).transpose(1, 2)
+
+
+class DinoViT(nn.Module):
+    """DINOv2 ViT (defaults = ViT-L/14 as built by encoders.py:86-95: img 518, patch 14, LayerScale 1.0, MLP FFN)."""
+
+    def __init__(self, img_size: int = 518, patch_size: int = 14, embed_dim: int = 1024, depth: int = 24,
+                 num_heads: int = 16, init_values: float = 1.0, init: bool = True):
+        super().__init__()
+        self.patch_size = patch_size
+        self.patch_embed = PatchEmbed(patch_size, 3, embed_dim)
+        n = (img_size // patch_size) ** 2
+        self.cls_token = nn.Parameter(torch.zeros(1, 1, embed_dim))
+        self.pos_embed = nn.Parameter(torch.zeros(1, n + 1, embed_dim))
+        self.blocks = nn.ModuleList(Block(embed_dim, num_heads, 4.0, qkv_bias=True, init_values=init_values,
+                                          norm_eps=1e-6) for _ in range(depth))
+        self.norm = nn.LayerNorm(embed_dim, eps=1e-6)
+        self.mask_token = nn.Parameter(torch.zeros(1, embed_dim))
+        if init:
+            nn.init.normal_(self.pos_embed, std=0.02)
+            nn.init.normal_(self.cls_token, std=1e-6)
+            for m in self.modules():
+                if isinstance(m, nn.Linear):
+                    nn.init.normal_(m.weight, std=0.02)
+                    if m.bias is not None:
+                        nn.init.zeros_(m.bias)
+        self.requires_grad_(False)
+        self._pos_cache = {}
+
+    def _pos(self, hp: int, wp: int, dtype) -> torch.Tensor:
+        """Position table resampled to an hp x wp patch grid (dinov2.py:166-191: bicubic, +0.1 scale nudge)."""
+        N = self.pos_embed.shape[1] - 1
+        side = int(math.sqrt(N))
+        if hp * wp == N and hp == wp:
+            return self.pos_embed.to(dtype)
+        key = (hp, wp, dtype, self.pos_embed.device, self.pos_embed._version)
+        hit = self._pos_cache.get(key)
+        if hit is not None:
+            return hit
+        pe = self.pos_embed.float()
+        grid = pe[:, 1:].reshape(1, side, side, -1).permute(0, 3, 1, 2)
+        grid = F.interpolate(grid, scale_factor=((hp + 0.1) / side, (wp + 0.1) / side), mode="bicubic")
+        assert grid.shape[-2:] == (hp, wp)
+        out = torch.cat((pe[:, :1], grid.permute(0, 2, 3, 1).reshape(1, hp * wp, -1)), dim=1).to(dtype)
+        self._pos_cache = {key: out}
+        return out
+
+    def patch_tokens(self, x: torch.Tensor) -> torch.Tensor:
+        """forward_features(x)['x_norm_patchtokens'] (dinov2.py:225-241): (B,3,H,W) -> (B, H/14*W/14, dim)."""
+        B, _, H, W = x.shape
+        t = self.patch_embed(x)
+        t = torch.cat((self.cls_token.expand(B, -1, -1).to(t.dtype), t), dim=1)
+        t = t + self._pos(H // self.patch_size, W // self.patch_size, t.dtype)
+        for blk in self.blocks:
+            t = blk(t)
+        return self.norm(t)[:, 1:]

@@ -1,0 +1,196 @@
+"""RegressionMatcher: the public matching API of the reference (romatch/models/matcher.py:425-766) on top of the
+sm_100a kernels.  Same method names, argument meaning, return shapes and mutable attributes
+(`w_resized, h_resized, upsample_res, upsample_preds, symmetric, attenuate_cert, sample_mode, sample_thresh`).
+
+Deliberate differences (all documented in DESIGN.md):
+  * tensor / batched inputs work (the reference raises on them) — uint8 or float (B,3,H,W);
+  * no torch.cuda.empty_cache() between passes (matcher.py:666), no second image decode (:670-672);
+  * the epilogue (:656-662, :684-730) is one kernel without the `.any()` host sync of :708;
+  * there is no CPU path: `device` must be a CUDA device.
+"""
+from __future__ import annotations
+
+import math
+import os
+from typing import Optional, Tuple, Union
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+from PIL import Image
+
+from . import ops
+
+_MEAN = (0.485, 0.456, 0.406)
+_STD = (0.229, 0.224, 0.225)
+
+
+def _load_rgb(im) -> Image.Image:
+    if isinstance(im, (str, os.PathLike)):
+        im = Image.open(im)
+        if im.mode == "I;16":                       # utils.py:656-658
+            raise NotImplementedError("Can't handle 16 bit images")
+        return im.convert("RGB")
+    if isinstance(im, Image.Image):
+        if im.mode != "RGB":                        # utils.py:660-662
+            raise NotImplementedError("Can't handle non-RGB images")
+        return im
+    raise TypeError(f"unsupported image input {type(im)}")
+
+
+def _pil_to_tensor(im: Image.Image, size_hw: Tuple[int, int]) -> torch.Tensor:
+    """PIL bicubic resize + /255 (utils.py:165-174, 234-239); normalisation happens on the device."""
+    im = im.resize((size_hw[1], size_hw[0]), resample=Image.BICUBIC)
+    return torch.from_numpy(np.asarray(im, dtype=np.float32).transpose(2, 0, 1) / 255.0)
+
+
+class RegressionMatcher(nn.Module):
+    def __init__(self, encoder: nn.Module, decoder: nn.Module, h: int = 448, w: int = 448,
+                 sample_mode: str = "threshold_balanced", upsample_preds: bool = False, symmetric: bool = False,
+                 name: Optional[str] = None, attenuate_cert: Optional[bool] = None):
+        super().__init__()
+        self.attenuate_cert = attenuate_cert
+        self.encoder = encoder
+        self.decoder = decoder
+        self.name = name
+        self.w_resized = w
+        self.h_resized = h
+        self.sample_mode = sample_mode
+        self.upsample_preds = upsample_preds
+        self.upsample_res = (14 * 16 * 6, 14 * 16 * 6)
+        self.symmetric = symmetric
+        self.sample_thresh = 0.05
+
+    # ------------------------------------------------------------------------------------------ helpers
+    def get_output_resolution(self):
+        return (self.h_resized, self.w_resized) if not self.upsample_preds else self.upsample_res
+
+    def _normalise(self, im: torch.Tensor) -> torch.Tensor:
+        if im.dtype == torch.uint8:
+            im = im.float() / 255.0
+        mean = torch.tensor(_MEAN, device=im.device, dtype=im.dtype).view(1, 3, 1, 1)
+        std = torch.tensor(_STD, device=im.device, dtype=im.dtype).view(1, 3, 1, 1)
+        return (im[:, :3] - mean) / std
+
+    def extract_backbone_features(self, batch, batched: bool = True, upsample: bool = False):
+        x = torch.cat((batch["im_A"], batch["im_B"]), dim=0)
+        return self.encoder(x, upsample=upsample)
+
+    def forward(self, batch, batched: bool = True, upsample: bool = False, scale_factor: float = 1):
+        pyr = self.extract_backbone_features(batch, upsample=upsample)
+        f_q = {s: f.chunk(2)[0] for s, f in pyr.items()}
+        f_s = {s: f.chunk(2)[1] for s, f in pyr.items()}
+        return self.decoder(f_q, f_s, upsample=upsample, **(batch.get("corresps") or {}), scale_factor=scale_factor)
+
+    def forward_symmetric(self, batch, batched: bool = True, upsample: bool = False, scale_factor: float = 1):
+        pyr = self.extract_backbone_features(batch, upsample=upsample)
+        f_s = {s: torch.cat((f.chunk(2)[1], f.chunk(2)[0]), dim=0) for s, f in pyr.items()}
+        return self.decoder(pyr, f_s, upsample=upsample, **(batch.get("corresps") or {}), scale_factor=scale_factor)
+
+    # ------------------------------------------------------------------------------------------ match
+    @torch.inference_mode()
+    def match(self, im_A_input, im_B_input, *args, batched: bool = False, device=None, return_logits: bool = False):
+        """matcher.py:593-730.  Paths / PIL images (one pair) or tensors (B,3,H,W) (uint8, or float in [0,1]
+        BEFORE ImageNet normalisation when `batched` tensors are float and `normalised=False`... see below).
+
+        Tensor inputs: uint8 RGB or float32 already ImageNet-normalised (what the reference's batched mode
+        expects, matcher.py:639-645), any resolution; they are resized on the device (bicubic, antialiased)
+        to the coarse and upsample resolutions when they differ."""
+        if device is None:
+            device = torch.device("cuda")
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("roma_b200 runs on sm_100a GPUs only; there is no CPU path (use the reference for CPU)")
+        self.train(False)
+        hs, ws = self.h_resized, self.w_resized
+        tensor_in = torch.is_tensor(im_A_input)
+        if tensor_in:
+            imA, imB = im_A_input.to(device, non_blocking=True), im_B_input.to(device, non_blocking=True)
+            if imA.dim() == 3:
+                imA, imB = imA[None], imB[None]
+            assert imA.shape == imB.shape, "For batched images we assume same size"
+            if imA.dtype == torch.uint8:
+                imA, imB = self._normalise(imA), self._normalise(imB)
+            full_A, full_B = imA, imB
+
+            def at(res, t):
+                return t if tuple(t.shape[-2:]) == tuple(res) else F.interpolate(t, size=tuple(res), mode="bicubic",
+                                                                                 antialias=True, align_corners=False)
+            coarse = {"im_A": at((hs, ws), full_A), "im_B": at((hs, ws), full_B)}
+        else:
+            pilA, pilB = _load_rgb(im_A_input), _load_rgb(im_B_input)
+            coarse = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
+                      "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
+        symmetric = self.symmetric
+        corresps = self.forward_symmetric(coarse) if symmetric else self.forward(coarse)
+        cert16 = corresps[16]["certainty"] if self.attenuate_cert else None
+        if self.upsample_preds:
+            hs, ws = self.upsample_res
+            if tensor_in:
+                fine = {"im_A": at((hs, ws), full_A), "im_B": at((hs, ws), full_B)}
+            else:
+                fine = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
+                        "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
+            scale_factor = math.sqrt(self.upsample_res[0] * self.upsample_res[1] / (self.w_resized * self.h_resized))
+            fine["corresps"] = corresps[1]
+            corresps = (self.forward_symmetric(fine, upsample=True, scale_factor=scale_factor) if symmetric
+                        else self.forward(fine, upsample=True, scale_factor=scale_factor))
+        out = ops.match_epilogue(corresps[1]["flow"], corresps[1]["certainty"], cert16, symmetric,
+                                 return_logits=return_logits)                                          # K3a
+        if batched or (tensor_in and im_A_input.dim() == 4):
+            return out
+        return tuple(o[0] for o in out)
+
+    # ------------------------------------------------------------------------------------------ sample
+    def sample(self, matches, certainty, num: int = 10000, generator: Optional[torch.Generator] = None):
+        """matcher.py:468-495: threshold -> multinomial(4*num) -> kde -> multinomial(num)."""
+        return ops.sample(matches, certainty, num=num, sample_thresh=self.sample_thresh,
+                          sample_mode=self.sample_mode, generator=generator)
+
+    # ------------------------------------------------------------------------------------------ keypoints
+    def match_keypoints(self, x_A, x_B, warp, certainty, return_tuple: bool = True, return_inds: bool = False):
+        """matcher.py:576-591."""
+        inds_A, inds_B = ops.match_keypoints(x_A, x_B, warp, certainty, self.sample_thresh)
+        if return_tuple:
+            return (inds_A, inds_B) if return_inds else (x_A[inds_A], x_B[inds_B])
+        return torch.cat((inds_A, inds_B), dim=-1) if return_inds else torch.cat((x_A[inds_A], x_B[inds_B]), dim=-1)
+
+    def conf_from_fb_consistency(self, flow_forward, flow_backward, th: float = 2):
+        """matcher.py:530-551: forward-backward consistency mask; flows are (..., H, W, 2)."""
+        has_batch = flow_forward.dim() == 4
+        if not has_batch:
+            flow_forward, flow_backward = flow_forward[None], flow_backward[None]
+        H, W = flow_forward.shape[-3:-1]
+        th_n = 2 * th / max(H, W)
+        dev = flow_forward.device
+        xs = torch.linspace(-1 + 1 / W, 1 - 1 / W, W, device=dev)
+        ys = torch.linspace(-1 + 1 / H, 1 - 1 / H, H, device=dev)
+        coords = torch.stack((xs[None, :].expand(H, W), ys[:, None].expand(H, W)), dim=-1)
+        fb = ops.grid_sample(flow_backward.permute(0, 3, 1, 2).float(), flow_forward.float()).permute(0, 2, 3, 1)
+        in_th = ((coords - fb).norm(dim=-1) < th_n).float()
+        return in_th if has_batch else in_th[0]
+
+    # ------------------------------------------------------------------------------------------ coordinates
+    def to_pixel_coordinates(self, coords, H_A, W_A, H_B=None, W_B=None):
+        if coords.shape[-1] == 2:
+            return self._to_pixel_coordinates(coords, H_A, W_A)
+        if isinstance(coords, (list, tuple)):
+            kA, kB = coords[0], coords[1]
+        else:
+            kA, kB = coords[..., :2], coords[..., 2:]
+        return self._to_pixel_coordinates(kA, H_A, W_A), self._to_pixel_coordinates(kB, H_B, W_B)
+
+    @staticmethod
+    def _to_pixel_coordinates(coords, H, W):
+        return torch.stack((W / 2 * (coords[..., 0] + 1), H / 2 * (coords[..., 1] + 1)), dim=-1)
+
+    @staticmethod
+    def to_normalized_coordinates(coords, H_A, W_A, H_B, W_B):
+        if isinstance(coords, (list, tuple)):
+            kA, kB = coords[0], coords[1]
+        else:
+            kA, kB = coords[..., :2], coords[..., 2:]
+        kA = torch.stack((2 / W_A * kA[..., 0] - 1, 2 / H_A * kA[..., 1] - 1), dim=-1)
+        kB = torch.stack((2 / W_B * kB[..., 0] - 1, 2 / H_B * kB[..., 1] - 1), dim=-1)
+        return kA, kB

