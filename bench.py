@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""Headline benchmark: image pairs / s of the RoMa matching hot path (roma_outdoor, 560 -> 864) on N B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+One "step" = one pass of the hot path over one batch of synthetic input: `model.match(im_A, im_B, batched=True)`
+on `--batch` (default 8) pairs per GPU (BASELINE.json configs[1]; configs[2] is the same per-GPU micro-batch on
+2/4/8 GPUs) followed by `model.sample(warp, certainty, num=10000)` for every pair — the call sequence of the
+reference's benchmarks.  Pairs are independent, so ranks shard them with no collective in the
+timed region ("weak" scaling: per-GPU work fixed); NCCL is used only for the barrier and the max-over-ranks time.
+
+  value  : pairs/s with the uint8 input images already resident in HBM.
+  e2e    : the same call with pinned HOST images — H2D copy in, D2H copy of the sampled matches out, per step.
+  roofline / kernels : per-kernel CUDA-event timings taken live inside the timed region (ops.KernelTimer).
+  cpu_baseline / --impl reference : the CPU oracle port of the same path (oracle/, fp32, all host threads)
+           on a bounded sample (1 pair per step) — there is no compiled reference to run (the reference is
+           Python and cannot travel to the GPU box).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+import torch
+import torch.nn.functional as F
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "image_pairs_per_s_roma_outdoor_560_864"
+UNIT = "pairs/s"
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "_source": "fallback"}
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        try:
+            p.update(json.loads(f.read_text()))
+            p["_source"] = "measured"
+        except Exception:
+            pass
+    return p
+
+
+def synthetic_pairs(batch: int, res, seed: int):
+    """uint8 RGB pairs at the upsample resolution (rand images, the coarse pass sees the same
+    content resized on the device)."""
+    g = torch.Generator().manual_seed(seed)
+    shape = (batch, 3, res[0], res[1])
+    low = torch.rand(batch, 3, res[0] // 16, res[1] // 16, generator=g)
+    base = F.interpolate(low, size=res, mode="bilinear", align_corners=False)
+    A = (0.7 * base + 0.3 * torch.rand(shape, generator=g))
+    B = (0.7 * base.roll(shifts=(res[0] // 20, res[1] // 30), dims=(2, 3)) + 0.3 * torch.rand(shape, generator=g))
+    to8 = lambda t: (t.clamp(0, 1) * 255).round().to(torch.uint8)
+    return to8(A), to8(B)
+
+
+# ------------------------------------------------------------------------------------------------------
+# algorithmic work per launch (restated in DESIGN.md)
+# ------------------------------------------------------------------------------------------------------
+def alg_work(name: str, d: dict):
+    """-> (bound, amount) with amount in bytes (hbm) or FLOPs (tensor) for ONE launch."""
+    if name == "roma_refiner_gather":
+        e, hw, K = d["esize"], d["B"] * d["h"] * d["w"], (2 * d["r"] + 1) ** 2 if d["r"] else 0
+        if d.get("only") == "corr":
+            return "hbm", hw * (2 * e * d["C"] + 8 + e * K)
+        if d.get("only") == "xhat":
+            return "hbm", hw * (2 * e * d["C"] + 8)
+        dch = 2 * d["C"] + d["E"] + K
+        return "hbm", hw * (e * d["C"] + e * d["C"] + 8 + e * dch)         # read f0, f1, flow; write d
+    if name == "roma_gp_posterior":
+        N, M, C, D = d["Nx"], d["Ny"], d["C"], d["D"]
+        return "tensor", d["B"] * (2.0 * M * M * C + 2.0 * N * M * C + M ** 3 / 3.0 + 2.0 * M * M * D + 2.0 * N * M * D)
+    if name == "roma_flow_update_resample":
+        src, dst = d["B"] * d["h"] * d["w"], d["B"] * d["h2"] * d["w2"]
+        return "hbm", 4 * (src * (3 + (3 if d["delta"] else 0) + (3 if d["cur"] else 0)) + dst * 3)
+    if name == "roma_match_epilogue":
+        n = d["B"] * d["H"] * d["Wout"]
+        return "hbm", 4 * n * (3 + 4 + 1 + (1 if d["logits"] else 0))
+    if name == "roma_cls_to_flow_refine":
+        return "hbm", d["B"] * d["H"] * d["W"] * (d["C"] * d["esize"] + 8)
+    if name == "roma_kde":
+        return "sfu", float(d["N"]) * (d["N"] // d["down"])
+    return "hbm", 0
+
+
+def summarise_kernels(summary: dict, steps: int, pk: dict):
+    rows = []
+    for name, recs in summary.items():
+        groups = {}
+        for dims, ms in recs:
+            key = json.dumps(dims, sort_keys=True)
+            groups.setdefault(key, []).append(ms)
+        for key, mss in groups.items():
+            dims = json.loads(key)
+            bound, amount = alg_work(name, dims)
+            avg = sum(mss) / len(mss)
+            row = {"kernel": name, "dims": dims, "launches_per_step": len(mss) / steps, "avg_ms": round(avg, 4),
+                   "ms_per_step": round(sum(mss) / steps, 4), "bound": bound}
+            if bound == "hbm" and amount:
+                row.update(achieved=round(amount / avg / 1e6, 1), unit="GB/s", peak=pk["hbm_gbs"],
+                           frac=round(amount / avg / 1e6 / pk["hbm_gbs"], 4), alg=amount)
+            elif bound == "tensor":
+                row.update(achieved=round(amount / avg / 1e9, 2), unit="TFLOP/s", peak=pk["bf16_tflops_sustained"],
+                           frac=round(amount / avg / 1e9 / pk["bf16_tflops_sustained"], 5), alg=amount)
+            elif bound == "sfu":
+                row.update(achieved=round(amount / avg / 1e6, 1), unit="Gpair/s", alg=amount)
+            rows.append(row)
+    rows.sort(key=lambda r: -r["ms_per_step"])
+    return rows
+
+
+# ------------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.proc = None
+        try:
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            ident = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", ident, f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            text, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            return out
+        sm, reasons, mx = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in text.strip().splitlines():
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU baseline (oracle port) — also the --impl reference arm
+# ------------------------------------------------------------------------------------------------------
+def cpu_pair_fn(coarse, upsample, weights, dinov2):
+    import roma_b200
+    from oracle import roma_model_oracle as MO
+    from oracle import roma_oracle as O
+    cpu = roma_b200.roma_outdoor("cpu", weights, dinov2, coarse_res=coarse, upsample_res=upsample, amp_dtype=torch.float32)
+
+    def run(A8: torch.Tensor, B8: torch.Tensor, seed: int = 0):
+        with torch.inference_mode():
+            fA, fB = cpu._normalise(A8), cpu._normalise(B8)
+            rs = lambda t: F.interpolate(t, size=tuple(coarse), mode="bicubic", antialias=True, align_corners=False)
+            warp, cert = MO.match_tensors(cpu, rs(fA), rs(fB), fA, fB)
+            g = torch.Generator().manual_seed(seed)
+            return O.sample(warp[0], cert[0], num=10000, generator=g)
+    return run
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    import roma_b200
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    weights, dinov2 = roma_b200.random_init_weights(seed=0)
+    run = cpu_pair_fn(args.coarse, args.upsample, weights, dinov2)
+    A8, B8 = synthetic_pairs(1, args.upsample, 1234)
+    budget_s = args.ref_budget
+    t_all = time.perf_counter()
+    warm = min(args.warmup, 1)
+    for _ in range(warm):
+        run(A8, B8)
+    times = []
+    for i in range(args.steps):
+        t0 = time.perf_counter()
+        run(A8, B8, seed=i)
+        times.append(time.perf_counter() - t0)
+        if time.perf_counter() - t_all + times[-1] > budget_s:
+            break
+    per = sum(times) / len(times)
+    val = 1.0 / per
+    sample = (f"1 pair per step (of the {args.batch}-pair batch) at {args.coarse[0]}->{args.upsample[0]}, match+sample(10000), "
+              f"fp32 oracle port on {cores} host threads; {warm} warm-up + {len(times)} timed steps "
+              f"(of {args.steps} requested, capped at {int(budget_s)} s)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(val, 5), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(times), "warmup": warm, "ms_per_step": round(per * 1e3, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(args, cpu=True),
+        "cpu_baseline": {"value": round(val, 5), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(val, 5), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def config_dict(args, cpu=False):
+    return {"workload": f"roma_outdoor random-init, {args.batch} synthetic pairs/GPU, coarse {args.coarse[0]}x{args.coarse[1]} -> "
+                        f"upsample {args.upsample[0]}x{args.upsample[1]}, symmetric, match + sample(10000) per pair",
+            "pairs_per_gpu_per_step": 1 if cpu else args.batch, "coarse_res": list(args.coarse), "upsample_res": list(args.upsample),
+            "amp_dtype": "float32" if cpu else args.dtype, "weights": "seeded random init (seed 0)",
+            "l2": "no explicit flush: each step streams > 10 GB of activations through a 126 MB L2",
+            "parallelism": f"pair-sharded x{args.gpus}, no collective in the timed region"}
+
+
+# ------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="roma_b200", choices=["roma_b200", "reference"])
+    ap.add_argument("--batch", type=int, default=8, help="pairs per GPU per step")
+    ap.add_argument("--coarse", type=int, nargs=2, default=[560, 560])
+    ap.add_argument("--upsample", type=int, nargs=2, default=[864, 864])
+    ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16", "float32"])
+    ap.add_argument("--num", type=int, default=10000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-budget", type=float, default=200.0, help="wall-clock cap (s) of the CPU reference arm")
+    args = ap.parse_args()
+    args.coarse, args.upsample = tuple(args.coarse), tuple(args.upsample)
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import roma_b200
+    from roma_b200 import _lib, ops
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    if lib.roma_check_device(local) != 0:
+        raise RuntimeError(lib.roma_last_error_string().decode())
+    amp = getattr(torch, args.dtype)
+    weights, dinov2 = roma_b200.random_init_weights(seed=0)
+    model = roma_b200.roma_outdoor(dev, weights, dinov2, coarse_res=args.coarse, upsample_res=args.upsample, amp_dtype=amp)
+
+    A8, B8 = synthetic_pairs(args.batch, args.upsample, 1234 + rank)
+    A_host, B_host = A8.pin_memory(), B8.pin_memory()
+    A_dev, B_dev = A8.to(dev), B8.to(dev)
+    out_host = torch.empty((args.batch, args.num, 5), dtype=torch.float32).pin_memory()
+    gens = [torch.Generator(device=dev) for _ in range(args.batch)]
+
+    def step(a, b, to_host: bool):
+        warp, cert = model.match(a, b, batched=True, device=dev)
+        for i in range(args.batch):
+            m, c = model.sample(warp[i], cert[i], num=args.num, generator=gens[i])
+            if to_host:
+                out_host[i, :, :4].copy_(m, non_blocking=True)
+                out_host[i, :, 4].copy_(c, non_blocking=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            fn()
+        e.record()
+        barrier()
+        ms = s.elapsed_time(e)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for i, g in enumerate(gens):
+        g.manual_seed(100 + i)
+    for _ in range(args.warmup):
+        step(A_dev, B_dev, False)
+    # ---- timed region 1: device-resident inputs (value) with live per-kernel events ----------------------
+    clocks = ClockSampler(local)
+    l0 = lib.roma_kernel_launches()
+    with ops.KernelTimer() as kt:
+        ms_dev = timed(lambda: step(A_dev, B_dev, False), args.steps)
+    launches = int(lib.roma_kernel_launches() - l0)
+    # ---- timed region 2: end to end from pinned host memory ----------------------------------------------
+    step(A_host, B_host, True)
+    ms_e2e = timed(lambda: step(A_host.to(dev, non_blocking=True), B_host.to(dev, non_blocking=True), True), args.steps)
+    clk = clocks.stop()
+
+    pairs = args.batch * world * args.steps
+    value = pairs / (ms_dev / 1e3)
+    e2e = pairs / (ms_e2e / 1e3)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    rows = summarise_kernels(kt.summary(), args.steps, pk)
+    own_ms = sum(r["ms_per_step"] for r in rows)
+    top = next((r for r in rows if r["bound"] in ("hbm", "tensor") and r.get("alg")), None)
+    roofline = None
+    if top:
+        roofline = {"kernel": top["kernel"], "dims": top["dims"], "bound": top["bound"], "achieved": top["achieved"],
+                    "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": None,
+                    "peak_source": pk["_source"] + (" sustained" if top["bound"] == "tensor" else ""),
+                    "avg_launch_ms": top["avg_ms"], "share_of_step": round(top["ms_per_step"] / (ms_dev / args.steps), 4)}
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms_dev / args.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": {"bfloat16": "bf16", "float16": "f16", "float32": "f32"}[args.dtype], "data": "synthetic",
+        "config": config_dict(args),
+        "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": int(A_host.numel() + B_host.numel()),
+                "d2h_bytes_per_step": int(out_host.numel() * 4), "ms_per_step": round(ms_e2e / args.steps, 3)},
+        "gpu_launches": launches, "clocks": clk, "roofline": roofline,
+        "own_kernels_ms_per_step": round(own_ms, 3), "kernels": rows[:12],
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        run = cpu_pair_fn(args.coarse, args.upsample, weights, dinov2)
+        t0 = time.perf_counter()
+        run(A8[:1], B8[:1])
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": round(1.0 / dt, 5), "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"1 pair (first of the batch) at {args.coarse[0]}->{args.upsample[0]}, match+sample(10000), "
+                                          f"fp32 oracle port, one cold run of {dt:.1f} s on {cores} host threads"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -49,6 +49,8 @@ int         roma_abi_version(void);
 const char* roma_last_error_string(void);
 /* 0 if `device` is an sm_100-class GPU usable by this library, else ROMA_ERR_ARCH / cudaError_t */
 int         roma_check_device(int device);
+/* number of kernels this library has launched in the calling process so far (monotonic; for bench accounting) */
+unsigned long long roma_kernel_launches(void);
 
 /* element strides of a (b, c, y, x)-indexed fp32 tensor */
 typedef struct roma_strides4 {

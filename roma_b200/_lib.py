@@ -30,6 +30,7 @@ SIGNATURES = {
     "roma_abi_version": (_i, []),
     "roma_last_error_string": (C.c_char_p, []),
     "roma_check_device": (_i, [_i]),
+    "roma_kernel_launches": (C.c_ulonglong, []),
     "roma_refiner_gather": (_i, [_vp, _vp, _vp, Strides4, _vp, _vp, _f,
                                  _vp, _i, _i, _i, _i, _i,
                                  _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),

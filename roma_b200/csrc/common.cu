@@ -1,5 +1,6 @@
 // Error reporting, device checks and ABI bookkeeping for libroma_b200.so.
 #include "common.cuh"
+#include <atomic>
 
 namespace roma {
 
@@ -20,12 +21,15 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 
-int check_launch(const char* what) {
+static std::atomic<unsigned long long> g_launches{0};
+
+int check_launch(const char* what, int launches) {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         set_error("%s: %s", what, cudaGetErrorString(e));
         return (int)e;
     }
+    g_launches.fetch_add((unsigned long long)launches, std::memory_order_relaxed);
     return 0;
 }
 
@@ -45,6 +49,8 @@ int sm_count() {
 }  // namespace roma
 
 extern "C" int roma_abi_version(void) { return ROMA_B200_ABI_VERSION; }
+
+extern "C" unsigned long long roma_kernel_launches(void) { return roma::g_launches.load(std::memory_order_relaxed); }
 
 extern "C" const char* roma_last_error_string(void) { return roma::g_err; }
 

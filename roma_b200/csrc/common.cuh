@@ -16,7 +16,7 @@ namespace roma {
 // ---- error reporting -------------------------------------------------------------------
 void set_error(const char* fmt, ...);
 int  fail(int code, const char* fmt, ...);
-int  check_launch(const char* what);   // cudaGetLastError -> positive code + message
+int  check_launch(const char* what, int launches = 1);   // cudaGetLastError -> positive code + message; counts launches
 
 #define ROMA_REQUIRE(cond, code, ...) \
     do { if (!(cond)) return ::roma::fail((code), __VA_ARGS__); } while (0)

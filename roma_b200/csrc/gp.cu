@@ -49,7 +49,7 @@ static int run(const T* x, const T* y, const float* pos_w, const float* pos_b, f
     // 1. norms
     norms_kernel<T><<<cdiv((long long)B * Nx * 32, 256), 256, 0, st>>>(x, w.xn, (long long)B * Nx, C);
     norms_kernel<T><<<cdiv((long long)B * Ny * 32, 256), 256, 0, st>>>(y, w.yn, (long long)B * Ny, C);
-    if ((rc = check_launch("gp norms"))) return rc;
+    if ((rc = check_launch("gp norms", 2))) return rc;
     // 2. Gram + cosine/exp epilogue
     {
         GemmShape s{Ny, Ny, C, C, C, Ny, (long long)Ny * C, (long long)Ny * C, (long long)Ny * Ny};
@@ -61,7 +61,7 @@ static int run(const T* x, const T* y, const float* pos_w, const float* pos_b, f
         EpiCosKernel e{w.xn, w.yn, Nx, Ny, eps, 1.f / Tk, 0.f};
         gemm64_kernel<T, T, true, EpiCosKernel><<<dim3(cdiv(Ny, 64), cdiv(Nx, 64), B), 256, 0, st>>>(x, y, w.Kxy, s, e);
     }
-    if ((rc = check_launch("gp gram"))) return rc;
+    if ((rc = check_launch("gp gram", 2))) return rc;
     // 3. RHS
     {
         const long long n = (long long)B * Ny * D;
@@ -78,11 +78,11 @@ static int run(const T* x, const T* y, const float* pos_w, const float* pos_b, f
         const int gx = rem > 0 ? cdiv(rem, 64) : 1;
         chol_panel_kernel<<<dim3(gx, B), 256, 0, st>>>(w.A, w.Ld, Ny, k, (long long)Ny * Ny, (long long)nb * kNB * kNB);
     }
-    if ((rc = check_launch("gp cholesky"))) return rc;
+    if ((rc = check_launch("gp cholesky", nb))) return rc;
     // 5. substitutions
     subst_kernel<false><<<dim3(cdiv(D, kNB), B), 256, 0, st>>>(w.A, w.Ld, w.Z, Ny, D, (long long)Ny * Ny, (long long)nb * kNB * kNB, (long long)Ny * D);
     subst_kernel<true><<<dim3(cdiv(D, kNB), B), 256, 0, st>>>(w.A, w.Ld, w.Z, Ny, D, (long long)Ny * Ny, (long long)nb * kNB * kNB, (long long)Ny * D);
-    if ((rc = check_launch("gp substitution"))) return rc;
+    if ((rc = check_launch("gp substitution", 2))) return rc;
     // 6. mu = K_xy alpha
     {
         GemmShape s{Nx, D, Ny, Ny, D, D, (long long)Nx * Ny, (long long)Ny * D, (long long)Nx * D};

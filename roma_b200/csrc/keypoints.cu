@@ -148,5 +148,5 @@ extern "C" int roma_match_keypoints(const float* x_A, int Na, const float* x_B, 
     kp::mutual_kernel<false><<<cdiv(Na, 256), 256, 0, st>>>(w.xab, w.certa, Na, x_B, Nb, w.rowmin, w.colmin, thresh, w.cnt, nullptr, nullptr, 0);
     kp::scan_kernel<<<1, 1024, 0, st>>>(w.cnt, Na, count);
     kp::mutual_kernel<true><<<cdiv(Na, 256), 256, 0, st>>>(w.xab, w.certa, Na, x_B, Nb, w.rowmin, w.colmin, thresh, w.cnt, inds_A, inds_B, capacity);
-    return check_launch("roma_match_keypoints");
+    return check_launch("roma_match_keypoints", 6);
 }

@@ -18,6 +18,45 @@ from ._lib import Strides4
 _DT = {torch.float32: _lib.ROMA_F32, torch.float16: _lib.ROMA_F16, torch.bfloat16: _lib.ROMA_BF16}
 
 
+class KernelTimer:
+    """Optional per-launch CUDA-event timing of the C-ABI calls (used by bench.py for the roofline block).
+
+    with KernelTimer() as t: ...   records (name, dims, start_event, end_event) for every kernel call made on the
+    current stream inside the block; t.summary() synchronises and returns {name: [(dims, ms), ...]}."""
+    active = None
+
+    def __init__(self):
+        self.records = []
+
+    def __enter__(self):
+        KernelTimer.active = self
+        return self
+
+    def __exit__(self, *exc):
+        KernelTimer.active = None
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, dims, s, e in self.records:
+            out.setdefault(name, []).append((dims, s.elapsed_time(e)))
+        return out
+
+
+def _run(name: str, dims: dict, call):
+    """Invoke one C-ABI entry point (optionally bracketed by events on the current stream) and check its code."""
+    t = KernelTimer.active
+    if t is None:
+        rc = call()
+    else:
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        rc = call()
+        e.record()
+        t.records.append((name, dims, s, e))
+    _lib.check(rc, name)
+
+
 def _cuda(*ts: Optional[torch.Tensor]) -> torch.device:
     dev = None
     for t in ts:
@@ -85,11 +124,12 @@ def refiner_inputs(x: torch.Tensor, y: torch.Tensor, flow: torch.Tensor,
         disp_b = disp_b.reshape(E).float().contiguous()
     dch = 2 * Cc + E + K
     d = torch.empty((B, dch, h, w), device=dev, dtype=x.dtype, memory_format=torch.channels_last)
-    rc = _lib.load().roma_refiner_gather(
-        _ptr(x), _ptr(y), _ptr(flow), _s4(flow), _ptr(disp_w), _ptr(disp_b), float(disp_scale),
-        _ptr(d), dch, 0, Cc, (2 * Cc if E else -1), (2 * Cc + E if r > 0 else -1),
-        B, Cc, h, w, h1, w1, E, r, _DT[x.dtype], _stream(dev))
-    _lib.check(rc, "roma_refiner_gather")
+    lib = _lib.load()
+    _run("roma_refiner_gather", dict(B=B, C=Cc, h=h, w=w, r=r, E=E, esize=x.element_size()),
+         lambda: lib.roma_refiner_gather(
+             _ptr(x), _ptr(y), _ptr(flow), _s4(flow), _ptr(disp_w), _ptr(disp_b), float(disp_scale),
+             _ptr(d), dch, 0, Cc, (2 * Cc if E else -1), (2 * Cc + E if r > 0 else -1),
+             B, Cc, h, w, h1, w1, E, r, _DT[x.dtype], _stream(dev)))
     return d
 
 
@@ -109,11 +149,12 @@ def local_correlation(feature0: torch.Tensor, feature1: torch.Tensor, local_radi
     f0, f1, flow = _nhwc(feature0), _nhwc(feature1), _f32(flow)
     K = (2 * r + 1) ** 2
     out = torch.empty((B, K, h, w), device=dev, dtype=feature0.dtype, memory_format=torch.channels_last)
-    rc = _lib.load().roma_refiner_gather(
-        _ptr(f0), _ptr(f1), _ptr(flow), _s4(flow), _ptr(None), _ptr(None), 0.0,
-        _ptr(out), K, -1, -1, -1, 0,
-        B, Cc, h, w, feature1.shape[2], feature1.shape[3], 0, r, _DT[feature0.dtype], _stream(dev))
-    _lib.check(rc, "roma_refiner_gather(local_correlation)")
+    lib = _lib.load()
+    _run("roma_refiner_gather", dict(B=B, C=Cc, h=h, w=w, r=r, E=0, esize=f0.element_size(), only="corr"),
+         lambda: lib.roma_refiner_gather(
+             _ptr(f0), _ptr(f1), _ptr(flow), _s4(flow), _ptr(None), _ptr(None), 0.0,
+             _ptr(out), K, -1, -1, -1, 0,
+             B, Cc, h, w, feature1.shape[2], feature1.shape[3], 0, r, _DT[feature0.dtype], _stream(dev)))
     return out
 
 
@@ -126,11 +167,12 @@ def grid_sample(input: torch.Tensor, grid: torch.Tensor) -> torch.Tensor:
     f1 = _nhwc(input)
     flow = _f32(grid).permute(0, 3, 1, 2)   # view: (B,2,h,w) with arbitrary strides, consumed in place
     out = torch.empty((B, Cc, h, w), device=dev, dtype=input.dtype, memory_format=torch.channels_last)
-    rc = _lib.load().roma_refiner_gather(
-        _ptr(None), _ptr(f1), _ptr(flow), _s4(flow), _ptr(None), _ptr(None), 0.0,
-        _ptr(out), Cc, -1, 0, -1, -1,
-        B, Cc, h, w, h1, w1, 0, 0, _DT[input.dtype], _stream(dev))
-    _lib.check(rc, "roma_refiner_gather(grid_sample)")
+    lib = _lib.load()
+    _run("roma_refiner_gather", dict(B=B, C=Cc, h=h, w=w, r=0, E=0, esize=f1.element_size(), only="xhat"),
+         lambda: lib.roma_refiner_gather(
+             _ptr(None), _ptr(f1), _ptr(flow), _s4(flow), _ptr(None), _ptr(None), 0.0,
+             _ptr(out), Cc, -1, 0, -1, -1,
+             B, Cc, h, w, h1, w1, 0, 0, _DT[input.dtype], _stream(dev)))
     return out
 
 
@@ -161,11 +203,12 @@ def flow_update_resample(flow: torch.Tensor, certainty: Optional[torch.Tensor], 
         h2, w2 = int(next_hw[0]), int(next_hw[1])
         fn = torch.empty((B, h2, w2, 2), device=dev, dtype=torch.float32)
         cn = torch.empty((B, h2, w2), device=dev, dtype=torch.float32)
-    rc = _lib.load().roma_flow_update_resample(
-        _ptr(flow), _s4(flow), _ptr(certainty), _s4(certainty), _ptr(delta), _s4(delta),
-        float(ins), float(4 * W), float(4 * H),
-        _ptr(fo), _ptr(co), _ptr(fn), _ptr(cn), B, h, w, h2, w2, _stream(dev))
-    _lib.check(rc, "roma_flow_update_resample")
+    lib = _lib.load()
+    _run("roma_flow_update_resample", dict(B=B, h=h, w=w, h2=h2, w2=w2, cur=bool(want_current), delta=delta is not None),
+         lambda: lib.roma_flow_update_resample(
+             _ptr(flow), _s4(flow), _ptr(certainty), _s4(certainty), _ptr(delta), _s4(delta),
+             float(ins), float(4 * W), float(4 * H),
+             _ptr(fo), _ptr(co), _ptr(fn), _ptr(cn), B, h, w, h2, w2, _stream(dev)))
     v = lambda f: None if f is None else f.permute(0, 3, 1, 2)
     u = lambda c: None if c is None else c[:, None]
     return v(fo), u(co), v(fn), u(cn)
@@ -186,10 +229,11 @@ def match_epilogue(flow: torch.Tensor, certainty: torch.Tensor, cert16: Optional
     cert = torch.empty((B, H, Wout), device=dev, dtype=torch.float32)
     logits = torch.empty((B, H, Wout), device=dev, dtype=torch.float32) if return_logits else None
     h16, w16 = (cert16.shape[2], cert16.shape[3]) if cert16 is not None else (0, 0)
-    rc = _lib.load().roma_match_epilogue(
-        _ptr(flow), _s4(flow), _ptr(certainty), _s4(certainty), _ptr(cert16), _s4(cert16), h16, w16,
-        _ptr(warp), _ptr(cert), _ptr(logits), B, H, W, int(bool(symmetric)), _stream(dev))
-    _lib.check(rc, "roma_match_epilogue")
+    lib = _lib.load()
+    _run("roma_match_epilogue", dict(B=B, H=H, W=W, Wout=Wout, logits=bool(return_logits)),
+         lambda: lib.roma_match_epilogue(
+             _ptr(flow), _s4(flow), _ptr(certainty), _s4(certainty), _ptr(cert16), _s4(cert16), h16, w16,
+             _ptr(warp), _ptr(cert), _ptr(logits), B, H, W, int(bool(symmetric)), _stream(dev)))
     return (warp, cert, logits) if return_logits else (warp, cert)
 
 
@@ -221,10 +265,10 @@ def gp_posterior(x: torch.Tensor, y: torch.Tensor, pos_w: torch.Tensor, pos_b: t
         ws = torch.empty(need, device=dev, dtype=torch.uint8)
         _gp_ws[key] = ws
     mu = torch.empty((B, D, h1, w1), device=dev, dtype=torch.float32, memory_format=torch.channels_last)
-    rc = lib.roma_gp_posterior(_ptr(x), _ptr(y), _ptr(pos_w), _ptr(pos_b), _ptr(mu),
-                               B, h1 * w1, h2 * w2, Cc, D, h2, w2, float(T), float(sigma_noise), float(eps),
-                               _DT[x.dtype], _ptr(ws), ws.numel(), _stream(dev))
-    _lib.check(rc, "roma_gp_posterior")
+    _run("roma_gp_posterior", dict(B=B, Nx=h1 * w1, Ny=h2 * w2, C=Cc, D=D),
+         lambda: lib.roma_gp_posterior(_ptr(x), _ptr(y), _ptr(pos_w), _ptr(pos_b), _ptr(mu),
+                                       B, h1 * w1, h2 * w2, Cc, D, h2, w2, float(T), float(sigma_noise), float(eps),
+                                       _DT[x.dtype], _ptr(ws), ws.numel(), _stream(dev)))
     return mu
 
 
@@ -246,9 +290,9 @@ def kde(x: torch.Tensor, std: float = 0.1, half: bool = True, down: Optional[int
     dens = torch.empty(N, device=dev, dtype=torch.float32)
     p = torch.empty(N, device=dev, dtype=torch.float32) if return_p else None
     ws = torch.empty(lib.roma_kde_workspace_bytes(N), device=dev, dtype=torch.uint8)
-    rc = lib.roma_kde(_ptr(xf), N, int(down or 1), float(std), int(bool(half)), _ptr(dens), _ptr(p),
-                      _ptr(ws), ws.numel(), _stream(dev))
-    _lib.check(rc, "roma_kde")
+    _run("roma_kde", dict(N=N, down=int(down or 1), half=bool(half)),
+         lambda: lib.roma_kde(_ptr(xf), N, int(down or 1), float(std), int(bool(half)), _ptr(dens), _ptr(p),
+                              _ptr(ws), ws.numel(), _stream(dev)))
     if half:   # values are already fp16-representable: the cast is exact
         dens = dens.half()
         p = None if p is None else p.half()
@@ -297,10 +341,10 @@ def match_keypoints(x_A: torch.Tensor, x_B: torch.Tensor, warp: torch.Tensor, ce
     ib = torch.empty(cap, device=dev, dtype=torch.int64)
     count = torch.zeros(1, device=dev, dtype=torch.int32)
     ws = torch.empty(lib.roma_match_keypoints_workspace_bytes(Na, Nb), device=dev, dtype=torch.uint8)
-    rc = lib.roma_match_keypoints(_ptr(xa), Na, _ptr(xb), Nb, _ptr(warp), _ptr(certainty), H, Wp,
-                                  float(sample_thresh), _ptr(ia), _ptr(ib), cap, _ptr(count),
-                                  _ptr(ws), ws.numel(), _stream(dev))
-    _lib.check(rc, "roma_match_keypoints")
+    _run("roma_match_keypoints", dict(Na=Na, Nb=Nb),
+         lambda: lib.roma_match_keypoints(_ptr(xa), Na, _ptr(xb), Nb, _ptr(warp), _ptr(certainty), H, Wp,
+                                          float(sample_thresh), _ptr(ia), _ptr(ib), cap, _ptr(count),
+                                          _ptr(ws), ws.numel(), _stream(dev)))
     n = int(count.item())   # the reference's torch.nonzero has the same inherent sync (matcher.py:580)
     if n > cap:
         raise RuntimeError(f"match_keypoints: {n} tied pairs exceed capacity {cap}")
@@ -317,8 +361,9 @@ def cls_to_flow_refine(cls: torch.Tensor) -> torch.Tensor:
         raise ValueError(f"unsupported dtype {cls.dtype}")
     B, Cc, H, W = cls.shape
     out = torch.empty((B, H, W, 2), device=dev, dtype=torch.float32)
-    rc = _lib.load().roma_cls_to_flow_refine(_ptr(cls), _s4(cls), _DT[cls.dtype], _ptr(out), B, Cc, H, W, _stream(dev))
-    _lib.check(rc, "roma_cls_to_flow_refine")
+    lib = _lib.load()
+    _run("roma_cls_to_flow_refine", dict(B=B, C=Cc, H=H, W=W, esize=cls.element_size()),
+         lambda: lib.roma_cls_to_flow_refine(_ptr(cls), _s4(cls), _DT[cls.dtype], _ptr(out), B, Cc, H, W, _stream(dev)))
     return out
 
 
@@ -332,6 +377,7 @@ def tiny_corr_posembed(feat0: torch.Tensor, feat1: torch.Tensor) -> torch.Tensor
     f0 = _nhwc(feat0.float())
     f1 = _nhwc(feat1.float())
     out = torch.empty((B, 2, H0, W0), device=dev, dtype=torch.float32)
-    rc = _lib.load().roma_tiny_corr_posembed(_ptr(f0), _ptr(f1), _ptr(out), B, Cc, H0, W0, H1, W1, _stream(dev))
-    _lib.check(rc, "roma_tiny_corr_posembed")
+    lib = _lib.load()
+    _run("roma_tiny_corr_posembed", dict(B=B, C=Cc, n0=H0 * W0, n1=H1 * W1),
+         lambda: lib.roma_tiny_corr_posembed(_ptr(f0), _ptr(f1), _ptr(out), B, Cc, H0, W0, H1, W1, _stream(dev)))
     return out
