@@ -143,6 +143,9 @@ int roma_match_epilogue(const float* flow, roma_strides4 flow_strides,
  * workspace: roma_gp_workspace_bytes(B, Nx, Ny, C, D) bytes, 256-byte aligned.
  */
 size_t roma_gp_workspace_bytes(int B, int Nx, int Ny, int C, int D);
+/* Testing / profiling aid: 0 = auto (tcgen05 tensor-core path when the shapes allow, default), 1 = force the fp32
+ * SIMT path, 2 = require the tcgen05 path (ROMA_ERR_UNSUPPORTED from roma_gp_posterior when it cannot be used). */
+int roma_gp_set_path(int path);
 int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const float* pos_b,
                       float* mu, int B, int Nx, int Ny, int C, int D, int hy, int wy,
                       float T, float sigma_noise, float eps, int dtype,

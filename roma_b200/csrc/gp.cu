@@ -10,6 +10,8 @@
 //   5. alpha = L^-T L^-1 f  by two one-launch block substitutions (RHS columns are independent)
 //   6. mu = K_xy alpha, written token-major == channels-last (the rearrange of matcher.py:264 is free)
 #include "gp_simt.cuh"
+#include "gp_tc.cuh"
+#include <atomic>
 
 namespace roma {
 namespace gp {
@@ -95,9 +97,19 @@ static int run(const T* x, const T* y, const float* pos_w, const float* pos_b, f
 }  // namespace gp
 }  // namespace roma
 
+namespace roma { namespace gp { static std::atomic<int> g_path{0}; } }   // 0 auto, 1 SIMT fp32, 2 tcgen05
+
+extern "C" int roma_gp_set_path(int path) {
+    if (path < 0 || path > 2) return roma::fail(ROMA_ERR_BAD_ARG, "roma_gp_set_path: path must be 0 (auto), 1 (simt) or 2 (tcgen05)");
+    roma::gp::g_path.store(path);
+    return ROMA_OK;
+}
+
 extern "C" size_t roma_gp_workspace_bytes(int B, int Nx, int Ny, int C, int D) {
     if (B <= 0 || Nx <= 0 || Ny <= 0 || C <= 0 || D <= 0) return 0;
-    return roma::gp::carve(nullptr, B, Nx, Ny, C, D).bytes;
+    const size_t a = roma::gp::carve(nullptr, B, Nx, Ny, C, D).bytes;
+    const size_t b = roma::gp::carve_tc(nullptr, B, Nx, Ny, D).bytes;
+    return a > b ? a : b;
 }
 
 extern "C" int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const float* pos_b,
@@ -110,9 +122,24 @@ extern "C" int roma_gp_posterior(const void* x, const void* y, const float* pos_
     ROMA_REQUIRE(hy * wy == Ny, ROMA_ERR_BAD_ARG, "roma_gp_posterior: hy*wy (%d) != Ny (%d)", hy * wy, Ny);
     ROMA_REQUIRE(T > 0.f, ROMA_ERR_BAD_ARG, "roma_gp_posterior: temperature must be positive");
     ROMA_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, ROMA_ERR_ALIGNMENT, "roma_gp_posterior: workspace must be 256-byte aligned");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // tcgen05 path: 16-byte aligned rows for the operand staging (16-bit: C % 8, fp32: C % 4)
+    const int esz = dtype == ROMA_F32 ? 4 : 2;
+    const bool tc_ok = (C * esz) % 16 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15u) == 0 && D % 4 == 0;
+    const int path = gp::g_path.load();
+    ROMA_REQUIRE(path != 2 || tc_ok, ROMA_ERR_UNSUPPORTED, "roma_gp_posterior: tcgen05 path needs 16-byte aligned token rows (C=%d) and D %% 4 == 0", C);
+    if (tc_ok && path != 1) {
+        gp::WorkspaceTC w = gp::carve_tc(workspace, B, Nx, Ny, D);
+        ROMA_REQUIRE(workspace_bytes >= w.bytes, ROMA_ERR_WORKSPACE, "roma_gp_posterior: workspace %zu < required %zu", workspace_bytes, w.bytes);
+        switch (dtype) {
+            case ROMA_F32:  return gp::run_tc<float>((const float*)x, (const float*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
+            case ROMA_F16:  return gp::run_tc<__half>((const __half*)x, (const __half*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
+            case ROMA_BF16: return gp::run_tc<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
+            default: return fail(ROMA_ERR_BAD_ARG, "roma_gp_posterior: unknown dtype %d", dtype);
+        }
+    }
     gp::Workspace w = gp::carve(workspace, B, Nx, Ny, C, D);
     ROMA_REQUIRE(workspace_bytes >= w.bytes, ROMA_ERR_WORKSPACE, "roma_gp_posterior: workspace %zu < required %zu", workspace_bytes, w.bytes);
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (dtype) {
         case ROMA_F32:  return gp::run<float>((const float*)x, (const float*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
         case ROMA_F16:  return gp::run<__half>((const __half*)x, (const __half*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);

@@ -173,6 +173,33 @@ def test_gp_vs_oracle_fp64(ops, cuda, h1, w1, h2, w2, C, D):
     assert e_kernel < max(10 * e_ref, 2e-4), (e_kernel, e_ref)      # as good as the reference's own fp32 path
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("h1,w1,h2,w2", [(16, 16, 16, 16), (13, 21, 19, 15), (40, 40, 40, 40)])
+def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2):
+    """The tcgen05/TMEM pipeline (forced) vs the fp64 oracle and vs the fp32 SIMT path, on the SAME (already
+    rounded) features: 16-bit inputs are exact in the tensor-core Gram, fp32 inputs go through split-bf16."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(33)
+    b, C, D = 2, 512, 512
+    base = O.bilinear_resize(torch.randn(b, C, 5, 5, generator=g), (h1, w1))
+    x = (base + 0.4 * torch.randn(b, C, h1, w1, generator=g)).to(dtype)
+    y = (O.bilinear_resize(base, (h2, w2)) + 0.4 * torch.randn(b, C, h2, w2, generator=g)).to(dtype)
+    pw = torch.randn(D, 2, generator=g) * 0.5; pb = torch.randn(D, generator=g) * 0.5
+    want = O.gp_posterior(x.float(), y.float(), pw, pb, dtype=torch.float64)
+    ref32 = O.gp_posterior(x.float(), y.float(), pw, pb)
+    try:
+        assert lib.roma_gp_set_path(2) == 0
+        got_tc = ops.gp_posterior(x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda))
+        assert lib.roma_gp_set_path(1) == 0
+        got_simt = ops.gp_posterior(x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda))
+    finally:
+        lib.roma_gp_set_path(0)
+    e_tc, e_simt, e_ref = err(got_tc, want), err(got_simt, want), err(ref32, want)
+    assert e_tc < max(10 * e_ref, 2e-4), (e_tc, e_simt, e_ref)
+    assert err(got_tc, got_simt) < 5e-4
+
+
 # --------------------------------------------------------------------------------------------- K3b
 def test_kde_golden_and_oracle(ops, cuda, golden):
     g = golden("kde")
