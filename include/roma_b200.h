@@ -146,6 +146,12 @@ size_t roma_gp_workspace_bytes(int B, int Nx, int Ny, int C, int D);
 /* Testing / profiling aid: 0 = auto (tcgen05 tensor-core path when the shapes allow, default), 1 = force the fp32
  * SIMT path, 2 = require the tcgen05 path (ROMA_ERR_UNSUPPORTED from roma_gp_posterior when it cannot be used). */
 int roma_gp_set_path(int path);
+/* The tensor-core building block of K1, exposed for unit tests and timing: batched C = A * B^T with
+ * A (batch, M, K), B (batch, N, K) row-major in `dtype`, C (batch, M, N) fp32.  fp32 operands are split on the
+ * fly into `split` (2 or 3) bf16 planes (3 / 6 tcgen05.mma per k-step, fp32 TMEM accumulate); bf16 / fp16
+ * operands need split = 1 and are exact.  Rows must be 16-byte aligned. */
+int roma_tc_gemm_nt(const void* A, const void* B, float* C, int batch, int M, int N, int K,
+                    int dtype, int split, void* stream);
 int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const float* pos_b,
                       float* mu, int B, int Nx, int Ny, int C, int D, int hy, int wy,
                       float T, float sigma_noise, float eps, int dtype,

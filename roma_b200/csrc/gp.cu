@@ -97,10 +97,10 @@ static int run(const T* x, const T* y, const float* pos_w, const float* pos_b, f
 }  // namespace gp
 }  // namespace roma
 
-namespace roma { namespace gp { static std::atomic<int> g_path{0}; } }   // 0 auto, 1 SIMT fp32, 2 tcgen05
+namespace roma { namespace gp { static std::atomic<int> g_path{0}; } }   // 0 auto, 1 SIMT fp32, 2 tcgen05 (3-plane solve), 3 tcgen05 (2-plane solve)
 
 extern "C" int roma_gp_set_path(int path) {
-    if (path < 0 || path > 2) return roma::fail(ROMA_ERR_BAD_ARG, "roma_gp_set_path: path must be 0 (auto), 1 (simt) or 2 (tcgen05)");
+    if (path < 0 || path > 3) return roma::fail(ROMA_ERR_BAD_ARG, "roma_gp_set_path: path must be 0 (auto), 1 (simt) or 2 (tcgen05)");
     roma::gp::g_path.store(path);
     return ROMA_OK;
 }
@@ -127,16 +127,19 @@ extern "C" int roma_gp_posterior(const void* x, const void* y, const float* pos_
     const int esz = dtype == ROMA_F32 ? 4 : 2;
     const bool tc_ok = (C * esz) % 16 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15u) == 0 && D % 4 == 0;
     const int path = gp::g_path.load();
-    ROMA_REQUIRE(path != 2 || tc_ok, ROMA_ERR_UNSUPPORTED, "roma_gp_posterior: tcgen05 path needs 16-byte aligned token rows (C=%d) and D %% 4 == 0", C);
+    ROMA_REQUIRE(path < 2 || tc_ok, ROMA_ERR_UNSUPPORTED, "roma_gp_posterior: tcgen05 path needs 16-byte aligned token rows (C=%d) and D %% 4 == 0", C);
     if (tc_ok && path != 1) {
         gp::WorkspaceTC w = gp::carve_tc(workspace, B, Nx, Ny, D);
         ROMA_REQUIRE(workspace_bytes >= w.bytes, ROMA_ERR_WORKSPACE, "roma_gp_posterior: workspace %zu < required %zu", workspace_bytes, w.bytes);
+#define ROMA_GP_TC(TT, SP) gp::run_tc<TT, SP>((const TT*)x, (const TT*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st)
+        const bool two = (path != 2);      // auto: 2-plane solve (3 MMAs per k-step); path 2 keeps 3 planes
         switch (dtype) {
-            case ROMA_F32:  return gp::run_tc<float>((const float*)x, (const float*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
-            case ROMA_F16:  return gp::run_tc<__half>((const __half*)x, (const __half*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
-            case ROMA_BF16: return gp::run_tc<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
+            case ROMA_F32:  return two ? ROMA_GP_TC(float, 2) : ROMA_GP_TC(float, 3);
+            case ROMA_F16:  return two ? ROMA_GP_TC(__half, 2) : ROMA_GP_TC(__half, 3);
+            case ROMA_BF16: return two ? ROMA_GP_TC(__nv_bfloat16, 2) : ROMA_GP_TC(__nv_bfloat16, 3);
             default: return fail(ROMA_ERR_BAD_ARG, "roma_gp_posterior: unknown dtype %d", dtype);
         }
+#undef ROMA_GP_TC
     }
     gp::Workspace w = gp::carve(workspace, B, Nx, Ny, C, D);
     ROMA_REQUIRE(workspace_bytes >= w.bytes, ROMA_ERR_WORKSPACE, "roma_gp_posterior: workspace %zu < required %zu", workspace_bytes, w.bytes);
@@ -146,4 +149,29 @@ extern "C" int roma_gp_posterior(const void* x, const void* y, const float* pos_
         case ROMA_BF16: return gp::run<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st);
         default: return fail(ROMA_ERR_BAD_ARG, "roma_gp_posterior: unknown dtype %d", dtype);
     }
+}
+
+
+// Batched C = A * B^T on the tcgen05 path (tc_gemm.cuh), exposed so the tensor-core building block of K1 can be
+// unit-tested and timed on its own.  A: batch x M x K, B: batch x N x K (row-major), C: batch x M x N fp32.
+extern "C" int roma_tc_gemm_nt(const void* A, const void* Bm, float* Cm, int batch, int M, int N, int K,
+                               int dtype, int split, void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(A && Bm && Cm && batch > 0 && M > 0 && N > 0 && K > 0, ROMA_ERR_BAD_ARG, "roma_tc_gemm_nt: bad arguments");
+    const int esz = dtype == ROMA_F32 ? 4 : 2;
+    ROMA_REQUIRE((K * esz) % 16 == 0 && ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(Bm)) & 15u) == 0,
+                 ROMA_ERR_ALIGNMENT, "roma_tc_gemm_nt: rows must be 16-byte aligned (K=%d)", K);
+    tc::Launch L{};
+    L.p[0] = tc::make_problem(A, Bm, Cm, M, N, K, K, K, N, (long long)M * K, (long long)N * K, (long long)M * N, tc::EPI_STORE);
+    L.nprob = 1; L.tiles0 = L.p[0].tiles_m * L.p[0].tiles_n;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (dtype == ROMA_F32) {
+        if (split == 2) return tc::launch_gemm_nt<float, 2>(L, batch, st, "roma_tc_gemm_nt");
+        if (split == 3) return tc::launch_gemm_nt<float, 3>(L, batch, st, "roma_tc_gemm_nt");
+        return fail(ROMA_ERR_BAD_ARG, "roma_tc_gemm_nt: fp32 operands need split 2 or 3");
+    }
+    ROMA_REQUIRE(split == 1, ROMA_ERR_BAD_ARG, "roma_tc_gemm_nt: 16-bit operands are exact with split 1");
+    if (dtype == ROMA_F16) return tc::launch_gemm_nt<__half, 1>(L, batch, st, "roma_tc_gemm_nt");
+    if (dtype == ROMA_BF16) return tc::launch_gemm_nt<__nv_bfloat16, 1>(L, batch, st, "roma_tc_gemm_nt");
+    return fail(ROMA_ERR_BAD_ARG, "roma_tc_gemm_nt: unknown dtype %d", dtype);
 }

@@ -22,32 +22,37 @@ namespace roma {
 namespace gp {
 
 constexpr int kDB = 128;                 // diagonal block = UMMA tile
-constexpr int kSolveSplit = 3;           // bf16 planes per fp32 operand in the solve GEMMs
 
-// f^T = cos(8*pi*(W g + bias))^T : (B, D, Mp), zero for m >= M   (matcher.py:232-247, :224)
+// R[0:D] = f^T = cos(8*pi*(W g + bias))^T : (D x Mp) per batch element (row stride Mp, batch stride sR), zero
+// for m >= M.  f does not depend on the batch element: each thread evaluates 4 consecutive m once and stores
+// them to every batch element (matcher.py:232-247, :224).
 __global__ void __launch_bounds__(256)
-posenc_t_kernel(float* __restrict__ Ft, const float* __restrict__ pw, const float* __restrict__ pb,
-                int B, int hy, int wy, int D, int Mp) {
-    const long long n = (long long)B * D * Mp;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    const int M = hy * wy;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
-        const int m = (int)(idx % Mp);
-        const int d = (int)((idx / Mp) % D);
-        float v = 0.f;
+posenc_t_kernel(float* __restrict__ R, const float* __restrict__ pw, const float* __restrict__ pb,
+                int B, int hy, int wy, int D, int Mp, long long sR) {
+    const int M = hy * wy, q = Mp >> 2;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= D * q) return;
+    const int d = idx / q, m4 = (idx - d * q) * 4;
+    const float wx = pw[2 * d], wyy = pw[2 * d + 1], bias = pb[d];
+    float v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        const int m = m4 + e;
+        v[e] = 0.f;
         if (m < M) {
             const int y = m / wy, x = m - y * wy;
-            const float gx = pixel_center(x, wy), gy = pixel_center(y, hy);
-            const float lin = fmaf(pw[2 * d + 1], gy, pw[2 * d] * gx) + pb[d];
-            v = cosf(25.132741228718345f * lin);
+            const float lin = fmaf(wyy, pixel_center(y, hy), wx * pixel_center(x, wy)) + bias;
+            v[e] = cosf(25.132741228718345f * lin);
         }
-        Ft[idx] = v;
     }
+    const float4 o = make_float4(v[0], v[1], v[2], v[3]);
+    float* dst = R + (long long)d * Mp + m4;
+    for (int b = 0; b < B; ++b) *reinterpret_cast<float4*>(dst + (long long)b * sR) = o;
 }
 
 // ---- Cholesky + inverse of one 128x128 diagonal block, one CTA per batch element -------------------
-// S (lower) <- chol(A_kk); V <- S^-1 (lower).  Writes L_kk back into A (lower part of the block, upper
-// zeroed is NOT needed: nothing reads the diagonal block of L again) and V, V^T into Ld.
+// S (lower) <- chol(A_kk); V <- S^-1 (lower).  L_kk is written back into A (lower part of the block; nothing
+// reads it again, it is kept for inspection) and V into Ld.
 constexpr int kDiagLd = kDB + 1;
 constexpr size_t kDiagSmem = (size_t)2 * kDB * kDiagLd * sizeof(float) + 32 * 33 * sizeof(float);
 
@@ -59,78 +64,104 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
     float (*Tm)[33] = reinterpret_cast<float (*)[33]>(dsm + 2 * kDB * kDiagLd);
     const int b = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     float* Ab = A + (long long)b * sA + (long long)k0 * ld + k0;
-    float* Lo = Ld + (long long)b * sLd + (long long)kblk * 2 * kDB * kDB;
+    float* Lo = Ld + (long long)b * sLd + (long long)kblk * kDB * kDB;
 
-    for (int e = tid; e < kDB * kDB; e += 256) {
-        const int r = e >> 7, c = e & 127;
-        S[r][c] = (c <= r) ? Ab[(long long)r * ld + c] : 0.f;
-        V[r][c] = 0.f;
+    for (int e = tid; e < kDB * (kDB / 4); e += 256) {
+        const int r = e >> 5, c = (e & 31) * 4;
+        const float4 v = *reinterpret_cast<const float4*>(Ab + (long long)r * ld + c);
+        S[r][c] = (c <= r) ? v.x : 0.f; S[r][c + 1] = (c + 1 <= r) ? v.y : 0.f;
+        S[r][c + 2] = (c + 2 <= r) ? v.z : 0.f; S[r][c + 3] = (c + 3 <= r) ? v.w : 0.f;
+        V[r][c] = 0.f; V[r][c + 1] = 0.f; V[r][c + 2] = 0.f; V[r][c + 3] = 0.f;
     }
     __syncthreads();
 
     for (int jb = 0; jb < 4; ++jb) {
         const int j0 = jb * 32;
         if (warp == 0) {
-            // potrf of the 32x32 block (left-looking inside the block), lane = row
-            const int r = j0 + lane;
+            // potrf of the 32x32 block in registers: lane = row, a[c] = S[j0+lane][j0+c]; the column of L needed
+            // by the rank-1 update comes from the owning lanes by shuffle (no shared-memory round trips)
+            float a[32];
+#pragma unroll
+            for (int c = 0; c < 32; ++c) a[c] = S[j0 + lane][j0 + c];
+#pragma unroll
             for (int j = 0; j < 32; ++j) {
-                float s = S[r][j0 + j];
-                for (int t = 0; t < j; ++t) s = fmaf(-S[r][j0 + t], S[j0 + j][j0 + t], s);
-                const float d = sqrtf(__shfl_sync(0xffffffffu, s, j));
-                __syncwarp();
-                if (lane == j) S[r][j0 + j] = d;
-                else if (lane > j) S[r][j0 + j] = s / d;
-                __syncwarp();
-            }
-            // inverse of the 32x32 lower-triangular block: lane = column c of the inverse
-            float x[32];
+                const float d = sqrtf(__shfl_sync(0xffffffffu, a[j], j));
+                a[j] = (lane == j) ? d : a[j] / d;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                float s = (i == lane) ? 1.f : 0.f;
-#pragma unroll
-                for (int t = 0; t < 32; ++t)
-                    if (t < i) s = fmaf(-S[j0 + i][j0 + t], x[t], s);        // x[t] == 0 for t < lane
-                x[i] = (i >= lane) ? s / S[j0 + i][j0 + i] : 0.f;
+                for (int k = j + 1; k < 32; ++k) {
+                    const float lk = __shfl_sync(0xffffffffu, a[j], k);
+                    a[k] = fmaf(-a[j], lk, a[k]);               // meaningful for lane >= k
+                }
             }
 #pragma unroll
-            for (int i = 0; i < 32; ++i) V[j0 + i][j0 + lane] = x[i];
+            for (int c = 0; c < 32; ++c)
+                if (c <= lane) S[j0 + lane][j0 + c] = a[c];
         }
         __syncthreads();
-        // panel below: X = S_panel * Vjj^T, one thread per row (row cached in registers; in-place)
+        // panel below: X * Ljj^T = S_panel by forward substitution, one thread per row (row in registers)
         {
             const int r = j0 + 32 + tid;
             if (r < kDB) {
-                float row[32], out[32];
-#pragma unroll
-                for (int t = 0; t < 32; ++t) row[t] = S[r][j0 + t];
+                float x[32];
 #pragma unroll
                 for (int c = 0; c < 32; ++c) {
-                    float s = 0.f;
+                    float s = S[r][j0 + c];
 #pragma unroll
                     for (int t = 0; t < 32; ++t)
-                        if (t <= c) s = fmaf(row[t], V[j0 + c][j0 + t], s);
-                    out[c] = s;
+                        if (t < c) s = fmaf(-x[t], S[j0 + c][j0 + t], s);
+                    x[c] = s / S[j0 + c][j0 + c];
                 }
 #pragma unroll
-                for (int c = 0; c < 32; ++c) S[r][j0 + c] = out[c];
+                for (int c = 0; c < 32; ++c) S[r][j0 + c] = x[c];
             }
         }
         __syncthreads();
-        // trailing update of the block: S[r][c] -= sum_t S[r][j0+t] * S[c][j0+t], r >= c >= j0+32
+        // trailing update inside the block: S[r][c] -= sum_t S[r][j0+t] * S[c][j0+t], r >= c >= j0+32 (4x4 per thread)
         {
-            const int n = kDB - (j0 + 32);
-            for (int e = tid; e < n * n; e += 256) {
-                const int rr = e / n, cc = e - rr * n;
+            const int n4 = (kDB - (j0 + 32)) >> 2;
+            for (int e = tid; e < n4 * n4; e += 256) {
+                const int rr = e / n4, cc = e - rr * n4;
                 if (cc > rr) continue;
-                const int r = j0 + 32 + rr, c = j0 + 32 + cc;
-                float s = S[r][c];
+                const int r = j0 + 32 + rr * 4, c = j0 + 32 + cc * 4;
+                float acc[4][4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 #pragma unroll 8
-                for (int t = 0; t < 32; ++t) s = fmaf(-S[r][j0 + t], S[c][j0 + t], s);
-                S[r][c] = s;
+                for (int t = 0; t < 32; ++t) {
+                    float ar[4], ac[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { ar[i] = S[r + i][j0 + t]; ac[i] = S[c + i][j0 + t]; }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(ar[i], ac[j], acc[i][j]);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) S[r + i][c + j] -= acc[i][j];
             }
         }
         __syncthreads();
     }
+    // inverses of the four 32x32 diagonal blocks, one warp each: lane = column c of the inverse
+    if (warp < 4) {
+        const int j0 = warp * 32;
+        float x[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            float s = (i == lane) ? 1.f : 0.f;
+#pragma unroll
+            for (int t = 0; t < 32; ++t)
+                if (t < i) s = fmaf(-S[j0 + i][j0 + t], x[t], s);            // x[t] == 0 for t < lane
+            x[i] = (i >= lane) ? s / S[j0 + i][j0 + i] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) V[j0 + i][j0 + lane] = x[i];
+    }
+    __syncthreads();
     // off-diagonal blocks of the inverse: V_ij = -V_ii * sum_{t=j}^{i-1} S_it V_tj   (i > j)
     for (int j = 0; j < 3; ++j) {
         for (int i = j + 1; i < 4; ++i) {
@@ -154,7 +185,6 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
 #pragma unroll
                 for (int e = 0; e < 4; ++e) o[e] = fmaf(a, Tm[kk][c4 + e], o[e]);
             }
-            __syncthreads();
 #pragma unroll
             for (int e = 0; e < 4; ++e) V[i * 32 + r][j * 32 + c4 + e] = -o[e];
             __syncthreads();
@@ -165,14 +195,10 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
         if (c <= r) Ab[(long long)r * ld + c] = S[r][c];
         Lo[e] = V[r][c];                                  // L_kk^-1
     }
-    for (int e = tid; e < kDB * kDB; e += 256) {
-        const int r = e >> 7, c = e & 127;
-        Lo[kDB * kDB + e] = V[c][r];                      // (L_kk^-1)^T
-    }
 }
 
 struct WorkspaceTC {
-    float *xn, *yn, *A, *Kxy, *Ft, *Ld;
+    float *xn, *yn, *A, *R, *Ld;
     int Mp, nb;
     size_t bytes;
 };
@@ -190,32 +216,34 @@ static inline WorkspaceTC carve_tc(void* base, int B, int Nx, int Ny, int D) {
     w.xn = take((size_t)B * Nx);
     w.yn = take((size_t)B * Ny);
     w.A = take((size_t)B * w.Mp * w.Mp);
-    w.Kxy = take((size_t)B * Nx * w.Mp);
-    w.Ft = take((size_t)B * D * w.Mp);
-    w.Ld = take((size_t)B * w.nb * 2 * kDB * kDB);
+    w.R = take((size_t)B * (D + Nx) * w.Mp);
+    w.Ld = take((size_t)B * w.nb * kDB * kDB);
     w.bytes = off;
     return w;
 }
 
-template <typename T>
+// The solve, all as "X * Y^T with both operands K-major" tcgen05 GEMMs.  R = [f^T ; K_xy] ((D + Nx) x Mp) is the
+// TRANSPOSED right-hand side block: forward substitution turns it into [Z^T ; W^T] = [f^T ; K_xy] L^-T, and
+//   mu = K_xy (L L^T)^-1 f = (K_xy L^-T)(L^-1 f) = W^T Z,
+// so no backward sweep is needed.  Left-looking blocked Cholesky, per 128-column block k:
+//   update   T_ik = A_ik - sum_{j<k} L_ij L_kj^T (i >= k)      R_k -= R_{0:k} L_{k,0:k}^T        (K = 128 k)
+//   diag     L_kk = chol(T_kk), L_kk^-1                                           (fp32 SIMT, one CTA per element)
+//   panel    L_ik = T_ik L_kk^-T (i > k)                        R_k  = R_k L_kk^-T               (K = 128)
+template <typename T, int SOLVE_SPLIT>
 static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b, float* mu,
                   int B, int Nx, int Ny, int C, int D, int hy, int wy, float Tk, float sigma, float eps,
                   const WorkspaceTC& w, cudaStream_t st) {
     using namespace tc;
     int rc;
-    const int Mp = w.Mp, nb = w.nb;
-    const long long sA = (long long)Mp * Mp, sK = (long long)Nx * Mp, sF = (long long)D * Mp, sLd = (long long)nb * 2 * kDB * kDB;
+    const int Mp = w.Mp, nb = w.nb, RR = D + Nx;
+    const long long sA = (long long)Mp * Mp, sR = (long long)RR * Mp, sLd = (long long)nb * kDB * kDB;
     constexpr int kGramSplit = std::is_same<T, float>::value ? 3 : 1;
+    float* Kxy = w.R + (long long)D * Mp;
 
     // 1. norms, RHS
     norms_kernel<T><<<cdiv((long long)B * Nx * 32, 256), 256, 0, st>>>(x, w.xn, (long long)B * Nx, C);
     norms_kernel<T><<<cdiv((long long)B * Ny * 32, 256), 256, 0, st>>>(y, w.yn, (long long)B * Ny, C);
-    {
-        const long long n = (long long)B * D * Mp;
-        long long blocks = (n + 255) / 256;
-        const long long cap = (long long)sm_count() * 8;
-        posenc_t_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, st>>>(w.Ft, pos_w, pos_b, B, hy, wy, D, Mp);
-    }
+    posenc_t_kernel<<<cdiv((long long)D * (Mp / 4), 256), 256, 0, st>>>(w.R, pos_w, pos_b, B, hy, wy, D, Mp, sR);
     if ((rc = check_launch("gp prologue", 3))) return rc;
 
     // 2. Gram tiles with the cosine/exp epilogue: K_yy + sigma I (lower, identity padded) and K_xy, one launch
@@ -226,10 +254,9 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
         p0.tiles_m = p0.tiles_n = nb; p0.lower_only = 1; p0.store_m = p0.store_n = Mp;
         p0.rn = w.yn; p0.cn = w.yn; p0.srn = p0.scn = Ny; p0.eps = eps; p0.inv_T = 1.f / Tk; p0.diag_add = sigma;
         Problem& p1 = L.p[1];
-        p1 = make_problem(x, y, w.Kxy, Nx, Ny, C, C, C, Mp, (long long)Nx * C, (long long)Ny * C, sK, EPI_COS);
+        p1 = make_problem(x, y, Kxy, Nx, Ny, C, C, C, Mp, (long long)Nx * C, (long long)Ny * C, sR, EPI_COS);
         p1.rn = w.xn; p1.cn = w.yn; p1.srn = Nx; p1.scn = Ny; p1.eps = eps; p1.inv_T = 1.f / Tk; p1.diag_add = 0.f;
-        // the cos epilogue adds diag_add on m == n and writes identity on padding: K_xy has neither
-        p1.store_m = Nx; p1.store_n = Ny;
+        p1.no_diag = 1; p1.tiles_n = nb; p1.store_n = Mp;          // zero-fill the padded columns of K_xy
         L.nprob = 2; L.tiles0 = p0.tiles_m * p0.tiles_n;
         if ((rc = launch_gemm_nt<T, kGramSplit>(L, B, st, "gp gram"))) return rc;
     }
@@ -241,57 +268,38 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
         diag_cfg = true;
     }
 
-    // 3. forward: blocked right-looking Cholesky with the forward substitution riding along
+    // 3. left-looking blocked Cholesky with the transposed right-hand sides riding along
     for (int k = 0; k < nb; ++k) {
-        const int k0 = k * kDB, rem = Mp - k0 - kDB;            // rows below the block
+        const int k0 = k * kDB, rows = Mp - k0, rem = rows - kDB;
+        if (k > 0) {
+            const float* Lk = w.A + (long long)k0 * Mp;                 // L_{k,0:k}: 128 rows x k0
+            Launch L{};
+            L.p[0] = make_problem(Lk, Lk, w.A + (long long)k0 * Mp + k0, rows, kDB, k0, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
+            L.p[1] = make_problem(w.R, Lk, w.R + k0, RR, kDB, k0, Mp, Mp, Mp, sR, sA, sR, EPI_SUB);
+            L.nprob = 2; L.tiles0 = L.p[0].tiles_m;
+            if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update"))) return rc;
+        }
         diag_block_kernel<<<B, 256, kDiagSmem, st>>>(w.A, w.Ld, Mp, k0, sA, sLd, k);
         if ((rc = check_launch("gp diag"))) return rc;
-        const float* Linv = w.Ld + (long long)k * 2 * kDB * kDB;
-        {   // panel: Z^T_k = F^T_k Linv^T  [and L_ik = A_ik Linv^T with its transposed mirror]
+        {
+            const float* Linv = w.Ld + (long long)k * kDB * kDB;
             Launch L{};
-            L.p[0] = make_problem(w.Ft + k0, Linv, w.Ft + k0, D, kDB, kDB, Mp, kDB, Mp, sF, sLd, sF, EPI_STORE);
+            L.p[0] = make_problem(w.R + k0, Linv, w.R + k0, RR, kDB, kDB, Mp, kDB, Mp, sR, sLd, sR, EPI_STORE);
             L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
             if (rem > 0) {
                 float* Ap = w.A + (long long)(k0 + kDB) * Mp + k0;
                 L.p[1] = make_problem(Ap, Linv, Ap, rem, kDB, kDB, Mp, kDB, Mp, sA, sLd, sA, EPI_STORE);
-                L.p[1].Ct = w.A + (long long)k0 * Mp + (k0 + kDB); L.p[1].ldct = Mp; L.p[1].sCt = sA;
                 L.nprob = 2;
             }
-            if ((rc = launch_gemm_nt<float, kSolveSplit>(L, B, st, "gp panel"))) return rc;
-        }
-        if (rem > 0) {   // trailing update
-            const float* Lp = w.A + (long long)(k0 + kDB) * Mp + k0;
-            Launch L{};
-            L.p[0] = make_problem(Lp, Lp, w.A + (long long)(k0 + kDB) * Mp + (k0 + kDB), rem, rem, kDB, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
-            L.p[0].lower_only = 1;
-            L.p[1] = make_problem(w.Ft + k0, Lp, w.Ft + k0 + kDB, D, rem, kDB, Mp, Mp, Mp, sF, sA, sF, EPI_SUB);
-            L.nprob = 2; L.tiles0 = L.p[0].tiles_m * L.p[0].tiles_n;
-            if ((rc = launch_gemm_nt<float, kSolveSplit>(L, B, st, "gp update"))) return rc;
+            if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp panel"))) return rc;
         }
     }
-    // 4. backward substitution on the transposed RHS
-    for (int k = nb - 1; k >= 0; --k) {
-        const int k0 = k * kDB;
-        const float* LinvT = w.Ld + (long long)k * 2 * kDB * kDB + kDB * kDB;
-        {
-            Launch L{};
-            L.p[0] = make_problem(w.Ft + k0, LinvT, w.Ft + k0, D, kDB, kDB, Mp, kDB, Mp, sF, sLd, sF, EPI_STORE);
-            L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
-            if ((rc = launch_gemm_nt<float, kSolveSplit>(L, B, st, "gp back diag"))) return rc;
-        }
-        if (k > 0) {   // Z^T_j -= a^T_k * L_kj for all j < k, using the L^T mirror rows [0, k0) x cols [k0, k0+128)
-            Launch L{};
-            L.p[0] = make_problem(w.Ft + k0, w.A + k0, w.Ft, D, k0, kDB, Mp, Mp, Mp, sF, sA, sF, EPI_SUB);
-            L.nprob = 1; L.tiles0 = L.p[0].tiles_m * L.p[0].tiles_n;
-            if ((rc = launch_gemm_nt<float, kSolveSplit>(L, B, st, "gp back update"))) return rc;
-        }
-    }
-    // 5. mu = K_xy alpha  (token-major == channels-last)
+    // 4. mu = W^T Z  (token-major == channels-last)
     {
         Launch L{};
-        L.p[0] = make_problem(w.Kxy, w.Ft, mu, Nx, D, Ny, Mp, Mp, D, sK, sF, (long long)Nx * D, EPI_STORE);
+        L.p[0] = make_problem(Kxy, w.R, mu, Nx, D, Ny, Mp, Mp, D, sR, sR, (long long)Nx * D, EPI_STORE);
         L.nprob = 1; L.tiles0 = L.p[0].tiles_m * L.p[0].tiles_n;
-        if ((rc = launch_gemm_nt<float, kSolveSplit>(L, B, st, "gp posterior"))) return rc;
+        if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp posterior"))) return rc;
     }
     return ROMA_OK;
 }

@@ -25,7 +25,7 @@ namespace tc {
 constexpr int BM = 128, BN = 128, BK = 64;
 constexpr int kThreads = 256;
 constexpr int kPlaneBytes = BM * BK * 2;          // 16 KB: one bf16 plane of one operand k-block
-constexpr int kTmemCols = 128;
+template <int SPLIT> constexpr int tmem_cols() { return SPLIT == 1 ? 128 : 256; }
 
 enum Epi : int { EPI_STORE = 0, EPI_SUB = 1, EPI_COS = 2 };
 
@@ -37,6 +37,7 @@ struct Problem {
     int lda, ldb, ldc, ldct;
     int tiles_m, tiles_n;
     int lower_only;                      // skip tiles strictly above the diagonal (tn > tm)
+    int no_diag;                         // EPI_COS: no diag_add / identity padding (rectangular cross kernel)
     int epi;
     int store_m, store_n;                // store bounds (>= M, N when padded rows/cols must be written)
     // EPI_COS: K = exp((acc / (rn[m]*cn[n] + eps) - 1) * inv_T) (+ diag_add on m == n); padding -> identity
@@ -108,74 +109,92 @@ __host__ __device__ constexpr uint32_t instr_desc(uint32_t fmt) {
 }
 
 // ---------------------------------------------------------------------------------------------- operand staging
-// fp32 source: split into SPLIT bf16 planes.  Tile = 128 rows x 64 k; thread handles 8 float4.
-template <int SPLIT>
-__device__ __forceinline__ void stage_f32(const float* src, long long ld, int rows_valid, int k0, int K,
-                                          unsigned char* planes, int tid) {
-#pragma unroll
-    for (int it = 0; it < 8; ++it) {
-        const int idx = it * kThreads + tid;
-        const int row = idx >> 4, c4 = idx & 15;
-        const int k = k0 + c4 * 4;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row < rows_valid && k < K) {
-            const float* p = src + (long long)row * ld + k;
-            if (k + 4 <= K) v = *reinterpret_cast<const float4*>(p);   // plain load: panels are updated in place
-            else { v.x = p[0]; if (k + 1 < K) v.y = p[1]; if (k + 2 < K) v.z = p[2]; }
-        }
-        const uint32_t off = row * 128 + ((((c4 >> 1) ^ (row & 7)) << 4) | ((c4 & 1) << 3));
-        float r[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int s = 0; s < SPLIT; ++s) {
-            __nv_bfloat16 h[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { h[e] = __float2bfloat16_rn(r[e]); r[e] -= __bfloat162float(h[e]); }
-            uint2 pk;
-            pk.x = (uint32_t)__bfloat16_as_ushort(h[0]) | ((uint32_t)__bfloat16_as_ushort(h[1]) << 16);
-            pk.y = (uint32_t)__bfloat16_as_ushort(h[2]) | ((uint32_t)__bfloat16_as_ushort(h[3]) << 16);
-            *reinterpret_cast<uint2*>(planes + s * kPlaneBytes + off) = pk;
-        }
-    }
-}
-// 16-bit source (bf16 / fp16): straight 16-byte copies into the swizzled plane.  Needs ld % 8 == 0, K % 8 == 0.
-__device__ __forceinline__ void stage_b16(const uint16_t* __restrict__ src, long long ld, int rows_valid, int k0, int K,
-                                          unsigned char* plane, int tid) {
-#pragma unroll
-    for (int it = 0; it < 4; ++it) {
-        const int idx = it * kThreads + tid;
-        const int row = idx >> 3, j = idx & 7;
-        const int k = k0 + j * 8;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (row < rows_valid && k < K) v = __ldg(reinterpret_cast<const uint4*>(src + (long long)row * ld + k));
-        *reinterpret_cast<uint4*>(plane + row * 128 + ((j ^ (row & 7)) << 4)) = v;
-    }
-}
-
+// A k-block of one operand (128 rows x 64 k) travels global -> registers -> shared; the two halves are split
+// so the loads of k-block i+1 are in flight while k-block i is converted, stored and multiplied.
 template <typename T, int SPLIT> struct Stager;
-template <int SPLIT> struct Stager<float, SPLIT> {
-    static __device__ __forceinline__ void run(const void* src, long long ld, int rows, int k0, int K, unsigned char* planes, int tid) {
-        stage_f32<SPLIT>(reinterpret_cast<const float*>(src), ld, rows, k0, K, planes, tid);
-    }
-};
-template <> struct Stager<__nv_bfloat16, 1> {
-    static __device__ __forceinline__ void run(const void* src, long long ld, int rows, int k0, int K, unsigned char* planes, int tid) {
-        stage_b16(reinterpret_cast<const uint16_t*>(src), ld, rows, k0, K, planes, tid);
-    }
-};
-template <> struct Stager<__half, 1> {
-    static __device__ __forceinline__ void run(const void* src, long long ld, int rows, int k0, int K, unsigned char* planes, int tid) {
-        stage_b16(reinterpret_cast<const uint16_t*>(src), ld, rows, k0, K, planes, tid);
-    }
-};
 
-template <int SPLIT> constexpr size_t smem_bytes() { return (size_t)2 * 2 * SPLIT * kPlaneBytes + 1024; }
+// fp32 source: split into SPLIT bf16 planes.  Thread handles 8 float4 (row = idx/16, 4 consecutive k).
+template <int SPLIT> struct Stager<float, SPLIT> {
+    struct Regs { float4 v[8]; };
+    static __device__ __forceinline__ void load(Regs& r, const void* srcv, long long ld, int rows_valid, int k0, int K, int tid) {
+        const float* src = reinterpret_cast<const float*>(srcv);
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int idx = it * kThreads + tid;
+            const int row = idx >> 4, c4 = idx & 15;
+            const int k = k0 + c4 * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row < rows_valid && k < K) {
+                const float* p = src + (long long)row * ld + k;
+                if (k + 4 <= K) v = *reinterpret_cast<const float4*>(p);   // plain load: panels are updated in place
+                else { v.x = p[0]; if (k + 1 < K) v.y = p[1]; if (k + 2 < K) v.z = p[2]; }
+            }
+            r.v[it] = v;
+        }
+    }
+    static __device__ __forceinline__ void store(const Regs& rg, unsigned char* planes, int tid) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int idx = it * kThreads + tid;
+            const int row = idx >> 4, c4 = idx & 15;
+            const uint32_t off = row * 128 + ((((c4 >> 1) ^ (row & 7)) << 4) | ((c4 & 1) << 3));
+            float r[4] = {rg.v[it].x, rg.v[it].y, rg.v[it].z, rg.v[it].w};
+#pragma unroll
+            for (int s = 0; s < SPLIT; ++s) {
+                __nv_bfloat16 h[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { h[e] = __float2bfloat16_rn(r[e]); r[e] -= __bfloat162float(h[e]); }
+                uint2 pk;
+                pk.x = (uint32_t)__bfloat16_as_ushort(h[0]) | ((uint32_t)__bfloat16_as_ushort(h[1]) << 16);
+                pk.y = (uint32_t)__bfloat16_as_ushort(h[2]) | ((uint32_t)__bfloat16_as_ushort(h[3]) << 16);
+                *reinterpret_cast<uint2*>(planes + s * kPlaneBytes + off) = pk;
+            }
+        }
+    }
+};
+// 16-bit source (bf16 / fp16): straight 16-byte copies into the swizzled plane.  Needs ld % 8 == 0.
+struct StagerB16 {
+    struct Regs { uint4 v[4]; };
+    static __device__ __forceinline__ void load(Regs& r, const void* srcv, long long ld, int rows_valid, int k0, int K, int tid) {
+        const uint16_t* src = reinterpret_cast<const uint16_t*>(srcv);
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int idx = it * kThreads + tid;
+            const int row = idx >> 3, j = idx & 7;
+            const int k = k0 + j * 8;
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (row < rows_valid && k + 8 <= K) v = __ldg(reinterpret_cast<const uint4*>(src + (long long)row * ld + k));
+            else if (row < rows_valid && k < K) {
+                uint16_t* e = reinterpret_cast<uint16_t*>(&v);
+                for (int t = 0; t < 8 && k + t < K; ++t) e[t] = src[(long long)row * ld + k + t];
+            }
+            r.v[it] = v;
+        }
+    }
+    static __device__ __forceinline__ void store(const Regs& r, unsigned char* plane, int tid) {
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int idx = it * kThreads + tid;
+            const int row = idx >> 3, j = idx & 7;
+            *reinterpret_cast<uint4*>(plane + row * 128 + ((j ^ (row & 7)) << 4)) = r.v[it];
+        }
+    }
+};
+template <> struct Stager<__nv_bfloat16, 1> : StagerB16 {};
+template <> struct Stager<__half, 1> : StagerB16 {};
+
+// 16-bit operands: 2 stages x 32 KB (3 CTAs/SM); split fp32 operands: 1 stage of 64 / 96 KB (3 / 2 CTAs/SM) —
+// co-resident CTAs overlap one tile's epilogue and operand staging with another tile's MMAs.
+template <int SPLIT> constexpr int num_stages() { return SPLIT == 1 ? 2 : 1; }
+template <int SPLIT> constexpr size_t smem_bytes() { return (size_t)num_stages<SPLIT>() * 2 * SPLIT * kPlaneBytes + 1024; }
 
 // ---------------------------------------------------------------------------------------------- kernel
 template <typename T, int SPLIT>
-__global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
+__global__ void __launch_bounds__(kThreads, 2) gemm_nt_kernel(const Launch L) {
     extern __shared__ unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t mma_bar[2];
     __shared__ uint32_t tmem_slot;
+    constexpr int STAGES = num_stages<SPLIT>();
 
     // ---- tile decode ----
     int t = blockIdx.x;
@@ -192,13 +211,6 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
     auto stageA = [&](int s) { return smem + (size_t)s * (2 * SPLIT * kPlaneBytes); };
     auto stageB = [&](int s) { return smem + (size_t)s * (2 * SPLIT * kPlaneBytes) + SPLIT * kPlaneBytes; };
 
-    if (warp == 0) tmem_alloc(&tmem_slot, kTmemCols);
-    if (tid == 0) { mbar_init(&mma_bar[0], 1); mbar_init(&mma_bar[1], 1); fence_barrier_init(); }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = tmem_slot;
-
     const char* Ab = reinterpret_cast<const char*>(P.A) + ((long long)b * P.sA + (long long)m0 * P.lda) * (long long)sizeof(T);
     const char* Bb = reinterpret_cast<const char*>(P.B) + ((long long)b * P.sB + (long long)n0 * P.ldb) * (long long)sizeof(T);
     const int rowsA = P.M - m0 < BM ? P.M - m0 : BM;
@@ -207,11 +219,27 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
     constexpr uint32_t kFmt = std::is_same<T, __half>::value ? 0u : 1u;
     constexpr uint32_t idesc = instr_desc(kFmt);
 
+    using St = Stager<T, SPLIT>;
+    typename St::Regs ra, rb;
+    St::load(ra, Ab, P.lda, rowsA, 0, P.K, tid);           // first k-block in flight during the TMEM / barrier setup
+    St::load(rb, Bb, P.ldb, rowsB, 0, P.K, tid);
+
+    if (warp == 0) tmem_alloc(&tmem_slot, tmem_cols<SPLIT>());
+    if (tid == 0) { mbar_init(&mma_bar[0], 1); mbar_init(&mma_bar[1], 1); fence_barrier_init(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
     for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb & 1;
-        if (kb >= 2) mbar_wait(&mma_bar[s], (uint32_t)(((kb >> 1) - 1) & 1));     // MMAs that read this stage are done
-        Stager<T, SPLIT>::run(Ab, P.lda, rowsA, kb * BK, P.K, stageA(s), tid);
-        Stager<T, SPLIT>::run(Bb, P.ldb, rowsB, kb * BK, P.K, stageB(s), tid);
+        const int s = kb % STAGES;
+        if (kb >= STAGES) mbar_wait(&mma_bar[s], (uint32_t)((kb / STAGES - 1) & 1));    // MMAs that read this stage are done
+        St::store(ra, stageA(s), tid);
+        St::store(rb, stageB(s), tid);
+        if (kb + 1 < nkb) {
+            St::load(ra, Ab, P.lda, rowsA, (kb + 1) * BK, P.K, tid);
+            St::load(rb, Bb, P.ldb, rowsB, (kb + 1) * BK, P.K, tid);
+        }
         fence_proxy_async();
         __syncthreads();
         if (tid == 0) {
@@ -226,7 +254,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
                         if (i + j >= SPLIT) continue;
                         const uint64_t ad = smem_desc_sw128(a0 + i * kPlaneBytes + kk * 32);
                         const uint64_t bd = smem_desc_sw128(b0 + j * kPlaneBytes + kk * 32);
-                        umma_f16(tmem_base, ad, bd, idesc, (kb | kk | i | j) ? 1u : 0u);
+                        // The tensor core's fp32 accumulate truncates, so every extra MMA into the same tile costs
+                        // ~2^-24 of the ACCUMULATOR's magnitude.  The small cross terms (i + j > 0) therefore get
+                        // their own TMEM tile (columns 128..255): their rounding is relative to a 2^-8 smaller sum,
+                        // and the leading a0*b0 tile sees exactly the K/16 accumulations of a plain bf16 GEMM.
+                        if (i + j == 0) umma_f16(tmem_base, ad, bd, idesc, (kb | kk) ? 1u : 0u);
+                        else umma_f16(tmem_base + 128u, ad, bd, idesc, (kb | kk | (i + j - 1) | i) ? 1u : 0u);
                     }
                 }
             }
@@ -235,7 +268,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
     }
     {   // all MMAs complete when the last commit fires
         const int last = nkb - 1;
-        mbar_wait(&mma_bar[last & 1], (uint32_t)((last >> 1) & 1));
+        mbar_wait(&mma_bar[last % STAGES], (uint32_t)((last / STAGES) & 1));
         tc_fence_after();
     }
 
@@ -251,6 +284,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
         const int c0 = hf * 64 + cc * 32;
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+        if (SPLIT > 1) {
+            float lo[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 128u + (uint32_t)c0, lo);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] += lo[i];
+        }
         const int nb0 = n0 + c0;
         if (P.epi == EPI_COS) {
 #pragma unroll
@@ -260,9 +299,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
                 if (m < P.M && n < P.N) {
                     const float c = v[i] / (rn * __ldg(P.cn + (long long)b * P.scn + n) + P.eps);
                     k = expf((c - 1.f) * P.inv_T);
-                    if (m == n) k += P.diag_add;
+                    if (m == n && !P.no_diag) k += P.diag_add;
                 } else {
-                    k = (m == n) ? 1.f : 0.f;            // padding: identity block keeps the factorisation trivial there
+                    k = (m == n && !P.no_diag) ? 1.f : 0.f;     // padding: identity block keeps the factorisation trivial there
                 }
                 v[i] = k;
             }
@@ -298,7 +337,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_kernel(const Launch L) {
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem_base, kTmemCols);
+    if (warp == 0) tmem_dealloc(tmem_base, tmem_cols<SPLIT>());
 }
 
 template <typename T, int SPLIT>
@@ -323,7 +362,7 @@ static inline Problem make_problem(const void* A, const void* B, float* C, int M
     p.sA = sA; p.sB = sB; p.sC = sC; p.sCt = 0;
     p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.ldct = 0;
     p.tiles_m = (M + BM - 1) / BM; p.tiles_n = (N + BN - 1) / BN;
-    p.lower_only = 0; p.epi = epi; p.store_m = M; p.store_n = N;
+    p.lower_only = 0; p.no_diag = 0; p.epi = epi; p.store_m = M; p.store_n = N;
     p.rn = p.cn = nullptr; p.srn = p.scn = 0; p.eps = 0.f; p.inv_T = 0.f; p.diag_add = 0.f;
     return p;
 }

@@ -272,6 +272,22 @@ def gp_posterior(x: torch.Tensor, y: torch.Tensor, pos_w: torch.Tensor, pos_b: t
     return mu
 
 
+def tc_gemm_nt(a: torch.Tensor, b: torch.Tensor, split: Optional[int] = None) -> torch.Tensor:
+    """Batched a @ b^T on the tcgen05 path of K1: a (batch,M,K), b (batch,N,K) -> (batch,M,N) fp32."""
+    dev = _cuda(a, b)
+    if a.dtype != b.dtype or a.dtype not in _DT:
+        raise ValueError(f"unsupported dtypes {a.dtype}/{b.dtype}")
+    a, b = a.contiguous(), b.contiguous()
+    batch, M, K = a.shape
+    N = b.shape[1]
+    split = split or (3 if a.dtype == torch.float32 else 1)
+    out = torch.empty((batch, M, N), device=dev, dtype=torch.float32)
+    lib = _lib.load()
+    _run("roma_tc_gemm_nt", dict(batch=batch, M=M, N=N, K=K, split=split),
+         lambda: lib.roma_tc_gemm_nt(_ptr(a), _ptr(b), _ptr(out), batch, M, N, K, _DT[a.dtype], split, _stream(dev)))
+    return out
+
+
 # --------------------------------------------------------------------------------------------------
 # K3b: kde + sampling
 # --------------------------------------------------------------------------------------------------

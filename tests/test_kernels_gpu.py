@@ -173,9 +173,10 @@ def test_gp_vs_oracle_fp64(ops, cuda, h1, w1, h2, w2, C, D):
     assert e_kernel < max(10 * e_ref, 2e-4), (e_kernel, e_ref)      # as good as the reference's own fp32 path
 
 
+@pytest.mark.parametrize("path", [2, 3])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("h1,w1,h2,w2", [(16, 16, 16, 16), (13, 21, 19, 15), (40, 40, 40, 40)])
-def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2):
+def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2, path):
     """The tcgen05/TMEM pipeline (forced) vs the fp64 oracle and vs the fp32 SIMT path, on the SAME (already
     rounded) features: 16-bit inputs are exact in the tensor-core Gram, fp32 inputs go through split-bf16."""
     from roma_b200 import _lib
@@ -189,7 +190,7 @@ def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2):
     want = O.gp_posterior(x.float(), y.float(), pw, pb, dtype=torch.float64)
     ref32 = O.gp_posterior(x.float(), y.float(), pw, pb)
     try:
-        assert lib.roma_gp_set_path(2) == 0
+        assert lib.roma_gp_set_path(path) == 0        # 2: 3-plane solve GEMMs, 3: 2-plane (the default)
         got_tc = ops.gp_posterior(x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda))
         assert lib.roma_gp_set_path(1) == 0
         got_simt = ops.gp_posterior(x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda))
@@ -198,6 +199,17 @@ def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2):
     e_tc, e_simt, e_ref = err(got_tc, want), err(got_simt, want), err(ref32, want)
     assert e_tc < max(10 * e_ref, 2e-4), (e_tc, e_simt, e_ref)
     assert err(got_tc, got_simt) < 5e-4
+
+
+@pytest.mark.parametrize("dtype,split,tol", [(torch.float32, 3, 2e-6), (torch.float32, 2, 2e-5), (torch.bfloat16, 1, 2e-6), (torch.float16, 1, 2e-6)])
+@pytest.mark.parametrize("batch,M,N,K", [(2, 300, 200, 136), (1, 128, 128, 64), (3, 129, 257, 520)])
+def test_tc_gemm_nt(ops, cuda, dtype, split, tol, batch, M, N, K):
+    """The tcgen05 building block on ragged shapes (row/column/K tails) against fp64."""
+    g = torch.Generator().manual_seed(5)
+    a = torch.randn(batch, M, K, generator=g).to(dtype); b = torch.randn(batch, N, K, generator=g).to(dtype)
+    want = a.double() @ b.double().mT
+    got = ops.tc_gemm_nt(a.to(cuda), b.to(cuda), split)
+    assert (got.double().cpu() - want).abs().max().item() < tol * want.abs().max().item()
 
 
 # --------------------------------------------------------------------------------------------- K3b
