@@ -167,10 +167,13 @@ int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const fl
  * half != 0 reproduces the reference's fp16 rounding chain (kde.py:6-7), else fp32.
  * density : fp32 (N)  (holds the fp16-rounded value when half != 0)
  * p_out : optional fp32 (N): 1/(density+1), 1e-7 where density < 10   (matcher.py:490-491)
- * workspace: roma_kde_workspace_bytes(N) bytes (deterministic split-sum partials; a smaller buffer of at
- *   least N floats is accepted and only reduces parallelism).
+ * workspace: roma_kde_workspace_bytes(N) bytes (deterministic split-sum partials + the 128 KB table of the half
+ *   path; a smaller buffer of at least N floats is accepted and only reduces parallelism / disables the table).
  */
 size_t roma_kde_workspace_bytes(int N);
+/* Testing aid: 1 = evaluate the half-precision op chain directly per pair instead of through the (bit-identical)
+ * lookup table of the chain's single half-valued argument; 0 = auto (default). */
+int roma_kde_set_direct(int direct);
 int roma_kde(const float* x, int N, int down, double std, int half,
              float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream);
 
@@ -200,6 +203,18 @@ int roma_match_keypoints(const float* x_A, int Na, const float* x_B, int Nb,
  */
 int roma_cls_to_flow_refine(const void* cls, roma_strides4 cls_strides, int dtype,
                             float* flow_out, int B, int C, int H, int W, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * (f-2) ConvRefiner body: depthwise 5x5 convolution (padding 2, stride 1) + bias + optional ReLU, channels-last.
+ *
+ * Replaces (reference): the conv1 -> BatchNorm2d -> ReLU triple of every ConvRefiner block as it runs at
+ *   inference, romatch/models/matcher.py:77-103 (create_block) / :139-140; the eval-mode BatchNorm is an affine
+ *   map that the caller folds into `weight` and `bias`.
+ * x, out : (B, h, w, C) channels-last, dtype `dtype`, C even, out != x.
+ * weight : fp32 (25, C), tap-major (tap = ky*5 + kx, cross-correlation like conv2d); bias : fp32 (C).
+ */
+int roma_dwconv5x5_bias_act(const void* x, const float* weight, const float* bias, void* out,
+                            int B, int h, int w, int C, int relu, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * KT  Tiny-RoMa fused correlation volume + approximate soft-argmax position embedding.

@@ -81,12 +81,93 @@ kde_partial_kernel(const float* __restrict__ x, int N, int M, int down, float in
     if (i < N) partial[(long long)split * N + i] = acc;
 }
 
+// ---- half mode, table-driven -----------------------------------------------------------------------
+// After d2 = half(|a|^2 + |b|^2 - 2ab) the rest of the reference chain (clamp_min(0), sqrt, **2, neg, /(2 std^2),
+// exp, each rounded to half) is a pure function of ONE non-negative half value, i.e. of at most 31745 bit
+// patterns, and it is exactly 0 beyond a cutoff (exp underflows in half).  kde_lut_kernel tabulates it with the
+// very same op sequence as kde_partial_kernel<true>; the streaming kernel then needs 4 FMA + 2 FADD + one
+// F2F + one shared-memory lookup per pair instead of two MUFU and ten conversions.  Results are bit-identical
+// to the direct chain (tests/test_kernels_gpu.py::test_kde_lut_equals_direct).
+constexpr int kLutMax = 14336;          // table entries that fit next to the reference tile (56 KB)
+constexpr int kQPT = 4;                 // queries per thread
+
+__global__ void kde_lut_kernel(float* __restrict__ lut, int* __restrict__ poison, float inv_two_var, int bound) {
+    const int bits = blockIdx.x * blockDim.x + threadIdx.x;         // 0 .. 0x7C00 (= +inf)
+    if (bits > 0x7C00) return;
+    const float d2 = __half2float(__ushort_as_half((unsigned short)bits));
+    const float d = rh(sqrtf(fmaxf(d2, 0.f)));
+    const float s = rh(d * d);
+    const float a = rh(-s * inv_two_var);
+    const float e = rh(expf(a));
+    lut[bits] = e;
+    if (e != 0.f && bits >= bound) atomicExch(poison, 1);          // host-side cutoff estimate violated: fail loudly (NaN)
+}
+
+__global__ void __launch_bounds__(kKdeThreads)
+kde_partial_lut_kernel(const float* __restrict__ x, int N, int M, int down, const float* __restrict__ lut_g,
+                       int cutoff, float* __restrict__ partial, int nsplit) {
+    extern __shared__ float ksm[];
+    float* lut = ksm;                                               // [cutoff + 1]; every entry >= cutoff is 0
+    float4* ref = reinterpret_cast<float4*>(ksm + ((cutoff + 1 + 3) & ~3));
+    float* refn = reinterpret_cast<float*>(ref + kKdeTile);
+    for (int t = threadIdx.x; t <= cutoff; t += kKdeThreads) lut[t] = (t < cutoff) ? lut_g[t] : 0.f;
+
+    const int split = blockIdx.y;
+    const int per = (M + nsplit - 1) / nsplit;
+    const int j_begin = split * per, j_end = min(M, j_begin + per);
+    const int i0 = (blockIdx.x * kKdeThreads + threadIdx.x) * kQPT;
+
+    float4 q[kQPT]; float qn[kQPT], acc[kQPT];
+#pragma unroll
+    for (int u = 0; u < kQPT; ++u) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i0 + u < N) v = reinterpret_cast<const float4*>(x)[i0 + u];
+        v = make_float4(rh(v.x), rh(v.y), rh(v.z), rh(v.w));
+        qn[u] = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
+        q[u] = make_float4(-2.f * v.x, -2.f * v.y, -2.f * v.z, -2.f * v.w);       // exact
+        acc[u] = 0.f;
+    }
+    for (int j0 = j_begin; j0 < j_end; j0 += kKdeTile) {
+        const int n = min(kKdeTile, j_end - j0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < n; t += kKdeThreads) {
+            float4 r = reinterpret_cast<const float4*>(x)[(long long)(j0 + t) * down];
+            r = make_float4(rh(r.x), rh(r.y), rh(r.z), rh(r.w));
+            refn[t] = rh(rh(r.x * r.x) + rh(r.y * r.y) + rh(r.z * r.z) + rh(r.w * r.w));
+            ref[t] = r;
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int t = 0; t < n; ++t) {
+            const float4 r = ref[t];
+            const float rn = refn[t];
+#pragma unroll
+            for (int u = 0; u < kQPT; ++u) {
+                float d2 = q[u].x * r.x;
+                d2 = fmaf(q[u].y, r.y, d2);
+                d2 = fmaf(q[u].z, r.z, d2);
+                d2 = fmaf(q[u].w, r.w, d2);
+                d2 = d2 + qn[u];
+                d2 = d2 + rn;
+                // half(d2) as an index: negatives (sign bit set -> huge unsigned... clamp_min(0) -> entry 0) and NaN never occur
+                const unsigned short hb = __half_as_ushort(__float2half_rn(fmaxf(d2, 0.f)));
+                const int idx = min((int)hb, cutoff);
+                acc[u] += lut[idx];
+            }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < kQPT; ++u)
+        if (i0 + u < N) partial[(long long)split * N + i0 + u] = acc[u];
+}
+
 __global__ void kde_finalize_kernel(const float* __restrict__ partial, int N, int nsplit, int half,
-                                    float* __restrict__ density, float* __restrict__ p_out) {
+                                    float* __restrict__ density, float* __restrict__ p_out, const int* __restrict__ poison) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     float s = 0.f;
     for (int k = 0; k < nsplit; ++k) s += partial[(long long)k * N + i];
+    if (poison && *poison) s = __int_as_float(0x7fc00000);
     if (half) s = rh(s);
     density[i] = s;
     if (p_out) {
@@ -111,10 +192,18 @@ static int kde_nsplit(int N) {
 }
 }  // namespace roma
 
+namespace roma {
+constexpr size_t kKdeLutBytes = 32768 * sizeof(float) + 256;      // table + cutoff word, at the END of the workspace
+}
+
 extern "C" size_t roma_kde_workspace_bytes(int N) {
     if (N <= 0) return 0;
-    return (size_t)64 * (size_t)N * sizeof(float);
+    return (size_t)64 * (size_t)N * sizeof(float) + roma::kKdeLutBytes;
 }
+
+// 0 = auto (table-driven half path when its table fits), 1 = always the direct op chain (testing aid)
+namespace roma { static int g_kde_direct = 0; }
+extern "C" int roma_kde_set_direct(int direct) { roma::g_kde_direct = direct ? 1 : 0; return ROMA_OK; }
 
 extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
                            float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream) {
@@ -134,10 +223,44 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     float* partial = reinterpret_cast<float*>(workspace);
     dim3 grid((N + kKdeThreads - 1) / kKdeThreads, nsplit);
-    if (half) kde_partial_kernel<true><<<grid, kKdeThreads, 0, st>>>(x, N, M, down, inv_two_var, partial, nsplit);
-    else      kde_partial_kernel<false><<<grid, kKdeThreads, 0, st>>>(x, N, M, down, inv_two_var, partial, nsplit);
-    int rc = check_launch("roma_kde(partial)");
-    if (rc) return rc;
-    kde_finalize_kernel<<<(N + 255) / 256, 256, 0, st>>>(partial, N, nsplit, half, density, p_out);
+    int rc;
+    int* poison = nullptr;
+    // table-driven half path: the cutoff is a property of std alone; evaluate it on the host with the same
+    // half arithmetic (exp(-s/(2 std^2)) < 2^-25 rounds to 0) so no device round trip is needed to size smem.
+    bool use_lut = half && !g_kde_direct && workspace_bytes >= (size_t)N * sizeof(float) + kKdeLutBytes;
+    int cutoff_bound = 0;
+    if (use_lut) {
+        // s beyond which exp underflows to 0 in half: exp(-s*inv) < 2^-25  <=>  s > 25 ln2 / inv ; +12.5% margin
+        const float s_max = 1.125f * 17.33f / inv_two_var;
+        __half hs = __float2half_rn(s_max);
+        cutoff_bound = (int)__half_as_ushort(hs) + 2;
+        use_lut = s_max < 60000.f && cutoff_bound <= kLutMax;
+    }
+    if (use_lut) {
+        float* lut = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + workspace_bytes - kKdeLutBytes);
+        poison = reinterpret_cast<int*>(lut + 32768);
+        if (nsplit > (int)((workspace_bytes - kKdeLutBytes) / ((size_t)N * sizeof(float)))) nsplit = (int)((workspace_bytes - kKdeLutBytes) / ((size_t)N * sizeof(float)));
+        cudaMemsetAsync(poison, 0, sizeof(int), st);
+        kde_lut_kernel<<<(0x7C00 + 256) / 256, 256, 0, st>>>(lut, poison, inv_two_var, cutoff_bound);
+        const size_t smem = ((size_t)(cutoff_bound + 1 + 3) & ~(size_t)3) * sizeof(float) + kKdeTile * (sizeof(float4) + sizeof(float));
+        static bool cfg = false;
+        if (!cfg) {
+            cudaError_t e = cudaFuncSetAttribute(kde_partial_lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((kLutMax + 4) * sizeof(float)) + kKdeTile * 20));
+            if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
+            cfg = true;
+        }
+        const int qblocks = (N + kKdeThreads * kQPT - 1) / (kKdeThreads * kQPT);
+        int ns = (2 * 3 * sm_count() + qblocks - 1) / qblocks;
+        ns = ns < 1 ? 1 : (ns > nsplit ? nsplit : ns);
+        if (ns > (M + 255) / 256) ns = (M + 255) / 256;
+        nsplit = ns;
+        kde_partial_lut_kernel<<<dim3(qblocks, nsplit), kKdeThreads, smem, st>>>(x, N, M, down, lut, cutoff_bound, partial, nsplit);
+        if ((rc = check_launch("roma_kde(lut)", 2))) return rc;
+    } else {
+        if (half) kde_partial_kernel<true><<<grid, kKdeThreads, 0, st>>>(x, N, M, down, inv_two_var, partial, nsplit);
+        else      kde_partial_kernel<false><<<grid, kKdeThreads, 0, st>>>(x, N, M, down, inv_two_var, partial, nsplit);
+        if ((rc = check_launch("roma_kde(partial)"))) return rc;
+    }
+    kde_finalize_kernel<<<(N + 255) / 256, 256, 0, st>>>(partial, N, nsplit, half, density, p_out, poison);
     return check_launch("roma_kde(finalize)");
 }

@@ -28,6 +28,7 @@ struct GatherParams {
     int B, C, h, w, h1, w1, E, r;
     long long npix;
     int tile_px;     // pixels per CTA tile (local-corr kernel)
+    int covered;     // channels written by the enabled segments; [covered, dch) is zero-filled pitch padding
 };
 
 __device__ __forceinline__ void pixel_coords(const GatherParams& p, long long pix, int& b, int& y, int& x,
@@ -187,6 +188,7 @@ local_corr_kernel(const GatherParams p) {
                 row[p.off_emb + e] = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx,
                                                           fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
         }
+        if (lane < p.dch - p.covered) row[p.covered + lane] = Elem<T>::from_f(0.f);
         __syncwarp();
     }
     __syncthreads();
@@ -194,6 +196,194 @@ local_corr_kernel(const GatherParams p) {
     // contiguous span write-back: scalar head, 16-byte body, scalar tail
     const size_t total = (size_t)tile_n * p.dch;          // elements
     const size_t head = mis ? (16 - mis) / sizeof(T) : 0;  // elements until 16-byte alignment
+    const size_t head_n = head < total ? head : total;
+    for (size_t e = threadIdx.x; e < head_n; e += blockDim.x) gspan[e] = stage[e];
+    if (total > head_n) {
+        const size_t body_elems = ((total - head_n) / kVec) * kVec;
+        const uint4* s4 = reinterpret_cast<const uint4*>(stage + head_n);
+        uint4* g4 = reinterpret_cast<uint4*>(gspan + head_n);
+        const size_t nv = body_elems / kVec;
+        for (size_t v = threadIdx.x; v < nv; v += blockDim.x) g4[v] = s4[v];
+        for (size_t e = head_n + body_elems + threadIdx.x; e < total; e += blockDim.x) gspan[e] = stage[e];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel A2: r > 0, 16-byte aligned rows (C = 64*VPL channels, every segment offset and the row pitch a multiple
+// of 8 elements — what ops.refiner_inputs produces with its padded pitch).  No output staging: all segments are
+// stored straight from registers with 16-byte (features) / 2-byte coalesced (corr, emb) stores, which frees the
+// shared memory and the registers the staged version spent on the transpose-reduction.
+//
+// One warp per pixel, four neighbour rows in flight per warp: lane = (group g = lane/8, gl = lane%8); group g
+// takes neighbour n0+g, its 8 lanes cover the row as VPL interleaved 16-byte vectors (8 lanes x 16 B = one
+// 128-byte line per load instruction), i.e. VPL independent 16-byte loads per lane per step, then a 3-step
+// shuffle reduction inside the group.  f0 stays in registers as fp32.
+// ------------------------------------------------------------------------------------------------
+template <typename T, int VPL>
+__global__ void __launch_bounds__(256, 2)
+local_corr_v2_kernel(const GatherParams p) {
+    constexpr int kVec = Elem<T>::kVec;          // 8 (16-bit types only)
+    static_assert(kVec == 8, "local_corr_v2 is for 16-bit feature types");
+    constexpr int kMaxNN = 256;                  // (2r+2)^2 for r <= 7
+    __shared__ float Dall[8][kMaxNN + 4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int grp = lane >> 3, gl = lane & 7;
+    const int W2 = 2 * p.r + 2, NN = W2 * W2, K1 = 2 * p.r + 1, K = K1 * K1;
+    float* Dsm = Dall[warp];
+    const float inv_sqrt_c = rsqrtf((float)p.C);
+    const T* f0 = reinterpret_cast<const T*>(p.f0);
+    const T* f1 = reinterpret_cast<const T*>(p.f1);
+    T* dout = reinterpret_cast<T*>(p.d);
+    const int covered = p.covered;
+
+    const long long tile_start = (long long)blockIdx.x * p.tile_px;
+    int tile_n = p.tile_px;
+    if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
+
+    for (int lp = warp; lp < tile_n; lp += 8) {
+        const long long pix = tile_start + lp;
+        int b, y, x; float gx, gy;
+        pixel_coords(p, pix, b, y, x, gx, gy);
+        int x0, y0; float wx0, wx1, wy0, wy1;
+        sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+        T* row = dout + pix * p.dch;
+
+        // f0 slice of this lane: vectors gl + 8*q
+        float a[VPL][8];
+        const T* f0p = f0 + pix * p.C;
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+            const uint4 raw = ldg16(f0p + (gl + 8 * q) * 8);
+            unpack16<T>(raw, a[q]);
+            if (p.off_x >= 0 && (q & 3) == grp) *reinterpret_cast<uint4*>(row + p.off_x + (gl + 8 * q) * 8) = raw;
+        }
+        const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
+        for (int n0 = 0; n0 < NN; n0 += 4) {
+            const int n = n0 + grp;
+            const int j = n / W2, i = n - j * W2;
+            const int yy = y0 + j - p.r, xx = x0 + i - p.r;
+            float acc = 0.f;
+            if (n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
+                const T* src = f1b + ((long long)yy * p.w1 + xx) * p.C + gl * 8;
+                uint4 u[VPL];
+#pragma unroll
+                for (int q = 0; q < VPL; ++q) u[q] = ldg16(src + 64 * q);
+#pragma unroll
+                for (int q = 0; q < VPL; ++q) {
+                    float f[8];
+                    unpack16<T>(u[q], f);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) acc = fmaf(a[q][e], f[e], acc);
+                }
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            if (gl == 0 && n < NN) Dsm[n] = acc;
+        }
+        __syncwarp();
+        // x_hat: 4-tap blend of the centre neighbours, lanes over the row's 16-byte vectors (lines just loaded: L1 hits)
+        if (p.off_xhat >= 0) {
+#pragma unroll
+            for (int q = 0; q < (VPL + 3) / 4; ++q) {
+                const int v = lane + 32 * q;
+                if (v < 8 * VPL) {
+                    float xh[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) xh[e] = 0.f;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
+                        if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
+                            const float wgt = ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0);
+                            float f[8];
+                            unpack16<T>(ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C + v * 8), f);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) xh[e] = fmaf(wgt, f[e], xh[e]);
+                        }
+                    }
+                    *reinterpret_cast<uint4*>(row + p.off_xhat + v * 8) = pack16<T>(xh);
+                }
+            }
+        }
+        if (p.off_corr >= 0) {
+            for (int k = lane; k < K; k += 32) {
+                const int ky = k / K1, kx = k - ky * K1;
+                const float* D0 = Dsm + ky * W2 + kx;
+                const float c = wy0 * (wx0 * D0[0] + wx1 * D0[1]) + wy1 * (wx0 * D0[W2] + wx1 * D0[W2 + 1]);
+                row[p.off_corr + k] = Elem<T>::from_f(c * inv_sqrt_c);
+            }
+        }
+        if (p.off_emb >= 0 && p.E > 0) {
+            const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+            const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+            for (int e = lane; e < p.E; e += 32)
+                row[p.off_emb + e] = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx,
+                                                          fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
+        }
+        if (lane < p.dch - covered) row[covered + lane] = Elem<T>::from_f(0.f);      // zero the pitch padding (< 8 channels)
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel C: r == 0 with rows that cannot be vectorised (C*sizeof(T) not a multiple of 16, e.g. the 9-channel
+// finest scale).  One thread per pixel computes its whole output row (x copy, x_hat, emb) into a shared-memory
+// stage; the CTA then writes the contiguous span of its 256 rows with 16-byte stores.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_rowstage_kernel(const GatherParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int kVec = Elem<T>::kVec;
+    const long long tile_start = (long long)blockIdx.x * 256;
+    int tile_n = 256;
+    if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
+    T* gspan = reinterpret_cast<T*>(p.d) + tile_start * p.dch;
+    const unsigned mis = (unsigned)(reinterpret_cast<uintptr_t>(gspan) & 15u);
+    T* stage = reinterpret_cast<T*>(smem_raw + mis);
+    const T* f0 = reinterpret_cast<const T*>(p.f0);
+    const T* f1 = reinterpret_cast<const T*>(p.f1);
+    const int lp = threadIdx.x;
+    if (lp < tile_n) {
+        const long long pix = tile_start + lp;
+        int b, y, x; float gx, gy;
+        pixel_coords(p, pix, b, y, x, gx, gy);
+        T* row = stage + (size_t)lp * p.dch;
+        if (p.off_x >= 0) {
+            const T* src = f0 + pix * p.C;
+            for (int c = 0; c < p.C; ++c) row[p.off_x + c] = src[c];
+        }
+        if (p.off_xhat >= 0) {
+            int x0, y0; float wx0, wx1, wy0, wy1;
+            sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+            const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
+            const T* tap[4]; float wgt[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
+                const bool ok = yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+                tap[t] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C : f1b;
+                wgt[t] = ok ? ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0) : 0.f;
+            }
+            for (int c = 0; c < p.C; ++c) {
+                float acc = 0.f;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) acc = fmaf(wgt[t], Elem<T>::to_f(tap[t][c]), acc);
+                row[p.off_xhat + c] = Elem<T>::from_f(acc);
+            }
+        }
+        if (p.off_emb >= 0 && p.E > 0) {
+            const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+            const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+            for (int e = 0; e < p.E; ++e)
+                row[p.off_emb + e] = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx, fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
+        }
+        for (int c = p.covered; c < p.dch; ++c) row[c] = Elem<T>::from_f(0.f);
+    }
+    __syncthreads();
+    const size_t total = (size_t)tile_n * p.dch;
+    const size_t head = mis ? (16 - mis) / sizeof(T) : 0;
     const size_t head_n = head < total ? head : total;
     for (size_t e = threadIdx.x; e < head_n; e += blockDim.x) gspan[e] = stage[e];
     if (total > head_n) {
@@ -266,6 +456,11 @@ gather_only_kernel(const GatherParams p, long long nthreads, int cpp) {
             v[e] = fmaf(__ldg(p.disp_w + 2 * (e0 + e)), dx, fmaf(__ldg(p.disp_w + 2 * (e0 + e) + 1), dy, __ldg(p.disp_b + e0 + e)));
         if (VEC > 1) *reinterpret_cast<uint4*>(out) = pack16<T>(v);
         else *out = Elem<T>::from_f(v[0]);
+        return;
+    }
+    if (ch >= p.covered) {      // pitch padding
+        if (VEC > 1) *reinterpret_cast<uint4*>(out) = make_uint4(0u, 0u, 0u, 0u);
+        else *out = Elem<T>::from_f(0.f);
     }
 }
 
@@ -279,6 +474,23 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
         const int nvec = p.C / kVec;
         ROMA_REQUIRE(nvec <= 128, ROMA_ERR_UNSUPPORTED, "roma_refiner_gather: C=%d too large for the local-correlation kernel", p.C);
         ROMA_REQUIRE(p.r <= 15, ROMA_ERR_UNSUPPORTED, "roma_refiner_gather: radius %d > 15", p.r);
+        // aligned fast path: 16-bit features, C = 64*VPL, every segment and the pitch 16-byte aligned
+        auto al8 = [](int off) { return off < 0 || (off & 7) == 0; };
+        const bool d16 = (reinterpret_cast<uintptr_t>(p.d) & 15u) == 0;
+        if (sizeof(T) == 2 && d16 && (p.dch & 7) == 0 && al8(p.off_x) && al8(p.off_xhat) && p.r <= 7 &&
+            (p.C == 512 || p.C == 256 || p.C == 128 || p.C == 64)) {
+            p.tile_px = 32;
+            const int grid = cdiv(p.npix, p.tile_px);
+            if constexpr (sizeof(T) == 2) {
+                switch (p.C) {
+                    case 512: local_corr_v2_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
+                    case 256: local_corr_v2_kernel<T, 4><<<grid, 256, 0, st>>>(p); break;
+                    case 128: local_corr_v2_kernel<T, 2><<<grid, 256, 0, st>>>(p); break;
+                    default:  local_corr_v2_kernel<T, 1><<<grid, 256, 0, st>>>(p); break;
+                }
+            }
+            return check_launch("roma_refiner_gather(local_corr_v2)");
+        }
         const int W2 = 2 * p.r + 2, NN = W2 * W2;
         const int nwarps = 8;
         // tile size: keep the staging buffer under ~40 KB so several CTAs fit per SM
@@ -305,10 +517,19 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
     auto seg_ok = [&](int off, int len) { return off < 0 || (off % kVec == 0 && len % kVec == 0); };
     const bool vec = ptr16 && d16 && p.C % kVec == 0 && p.dch % kVec == 0 &&
                      seg_ok(p.off_x, p.C) && seg_ok(p.off_xhat, p.C) && seg_ok(p.off_emb, p.E);
-    if (vec) {
+    auto seg_pad_ok = p.covered % kVec == 0;
+    if (vec && seg_pad_ok) {
         const int cpp = p.dch / kVec;
         const long long n = p.npix * cpp;
         gather_only_kernel<T, kVec><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);
+    } else if ((size_t)256 * p.dch * sizeof(T) + 32 <= 96 * 1024 && p.C <= 64) {
+        // small, unalignable rows (the 9-channel finest scale): one thread per pixel + staged span write
+        const size_t smem = (size_t)256 * p.dch * sizeof(T) + 32;
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(gather_rowstage_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return fail((int)e, "roma_refiner_gather: smem opt-in (%zu B): %s", smem, cudaGetErrorString(e));
+        }
+        gather_rowstage_kernel<T><<<cdiv(p.npix, 256), 256, smem, st>>>(p);
     } else {
         const long long n = p.npix * p.dch;
         gather_only_kernel<T, 1><<<cdiv(n, 256), 256, 0, st>>>(p, n, p.dch);
@@ -344,15 +565,15 @@ extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* 
     }
     bool leftover = false;
     for (int s = 0; s < 4; ++s) leftover |= (offs[s] >= 0);
-    ROMA_REQUIRE(covered == d_channels && !leftover, ROMA_ERR_BAD_ARG,
-                 "roma_refiner_gather: enabled segments must tile [0,%d) exactly (covered %d)", d_channels, covered);
+    ROMA_REQUIRE(covered <= d_channels && d_channels - covered < 32 && !leftover, ROMA_ERR_BAD_ARG,
+                 "roma_refiner_gather: enabled segments must be contiguous from 0 and fill [0,%d) up to < 32 padding channels (covered %d)", d_channels, covered);
 
     GatherParams p;
     p.f0 = f0; p.f1 = f1; p.flow = flow; p.fs = fs;
     p.disp_w = disp_w; p.disp_b = disp_b; p.disp_scale = disp_scale;
     p.d = d; p.dch = d_channels; p.off_x = off_x; p.off_xhat = off_xhat; p.off_emb = off_emb; p.off_corr = off_corr;
     p.B = B; p.C = C; p.h = h; p.w = w; p.h1 = h1; p.w1 = w1; p.E = E; p.r = r;
-    p.npix = (long long)B * h * w; p.tile_px = 0;
+    p.npix = (long long)B * h * w; p.tile_px = 0; p.covered = covered;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (dtype) {
         case ROMA_F32:  return launch_gather<float>(p, st);

@@ -16,6 +16,7 @@ from typing import Dict, Optional, Sequence
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from .. import ops
 from .encoder import _autocast
@@ -23,7 +24,13 @@ from .vit import Block
 
 
 class ConvRefiner(nn.Module):
-    """matcher.py:17-143.  forward(x, y, flow, scale_factor, logits) -> (delta_flow (B,2,h,w), delta_certainty (B,1,h,w))."""
+    """matcher.py:17-143.  forward(x, y, flow, scale_factor, logits) -> (delta_flow (B,2,h,w), delta_certainty (B,1,h,w)).
+
+    Parameters / buffers are the reference's (block1, hidden_blocks.N, out_conv, disp_emb).  At inference the conv
+    stack runs from a *prepared* copy of them: eval-mode BatchNorm folded into the depthwise conv, channels padded
+    to a multiple of 8 with zeros (rows of the channels-last activations become 16-byte aligned, so the gather
+    kernel vectorises and the 1x1 convs hit aligned tensor-core GEMMs), depthwise conv + bias + ReLU as one launch
+    of the (f-2) kernel and each 1x1 conv as one library GEMM with the bias in its epilogue."""
 
     def __init__(self, in_dim: int, hidden_dim: int, out_dim: int = 3, kernel_size: int = 5, hidden_blocks: int = 8,
                  displacement_emb_dim: Optional[int] = None, local_corr_radius: Optional[int] = None,
@@ -38,6 +45,9 @@ class ConvRefiner(nn.Module):
             self.disp_emb = nn.Conv2d(2, displacement_emb_dim, 1, 1, 0)
         self.local_corr_radius = local_corr_radius
         self.amp_dtype = amp_dtype
+        self.in_dim, self.hidden_dim, self.kernel_size = in_dim, hidden_dim, kernel_size
+        self._prep = None
+        self._prep_key = None
 
     @staticmethod
     def _block(cin: int, cout: int, k: int, momentum: float) -> nn.Sequential:
@@ -45,25 +55,59 @@ class ConvRefiner(nn.Module):
         return nn.Sequential(nn.Conv2d(cin, cout, k, 1, k // 2, groups=cin), nn.BatchNorm2d(cout, momentum=momentum),
                              nn.ReLU(inplace=True), nn.Conv2d(cout, cout, 1, 1, 0))
 
-    def forward(self, x, y, flow, scale_factor: float = 1, logits=None):
+    # ---- prepared (folded / padded) weights -------------------------------------------------------------------
+    def _prepare(self, device, dtype):
+        key = (device, dtype, tuple(t._version for t in self.state_dict(keep_vars=True).values()),
+               tuple(t.data_ptr() for t in self.parameters()))
+        if self._prep_key == key:
+            return self._prep
+        assert self.in_dim == self.hidden_dim and self.kernel_size == 5, "prepared path: depthwise multiplier 1, 5x5"
+        C = self.hidden_dim
+        Cp = (C + 7) // 8 * 8
+        blocks = []
+        with torch.no_grad():
+            for blk in [self.block1, *self.hidden_blocks]:
+                conv1, bn, _, conv2 = blk
+                scale = bn.weight.float() / torch.sqrt(bn.running_var.float() + bn.eps)
+                shift = bn.bias.float() - bn.running_mean.float() * scale
+                k2 = self.kernel_size ** 2
+                w_dw = torch.zeros(k2, Cp, device=device)                       # tap-major fp32 for the dwconv kernel
+                b_dw = torch.zeros(Cp, device=device)
+                w_dw[:, :C] = (conv1.weight.float() * scale.view(-1, 1, 1, 1)).view(C, k2).t()
+                b_dw[:C] = (conv1.bias.float() if conv1.bias is not None else 0) * scale + shift
+                w_pw = torch.zeros(Cp, Cp, device=device)
+                b_pw = torch.zeros(Cp, device=device)
+                w_pw[:C, :C] = conv2.weight.float().view(C, C)
+                b_pw[:C] = conv2.bias.float()
+                blocks.append((w_dw.contiguous(), b_dw, w_pw.to(dtype).contiguous(), b_pw.to(dtype)))
+            w_out = torch.zeros(self.out_conv.out_channels, Cp, 1, 1, device=device)
+            w_out[:, :C] = self.out_conv.weight.float()
+            b_out = self.out_conv.bias.float().clone()
+        self._prep = (Cp, blocks, w_out, b_out)
+        self._prep_key = key
+        return self._prep
+
+    def _body(self, d: torch.Tensor) -> torch.Tensor:
+        """d (B, Cp, h, w) channels-last -> (B, 3, h, w) fp32 out_conv output."""
+        Cp, blocks, w_out, b_out = self._prepare(d.device, d.dtype)
+        B, _, h, w = d.shape
+        for w_dw, b_dw, w_pw, b_pw in blocks:
+            d = ops.dwconv5x5_bias_act(d, w_dw, b_dw, relu=True)                      # (f-2): dw conv + folded BN + ReLU
+            d = F.linear(d.permute(0, 2, 3, 1), w_pw, b_pw).permute(0, 3, 1, 2)       # NHWC GEMM, bias in the epilogue
+        return F.conv2d(d.float(), w_out, b_out)                                      # matcher.py:141 (fp32)
+
+    def delta(self, x, y, flow, scale_factor: float = 1) -> torch.Tensor:
+        """The (B,3,h,w) out_conv tensor (dx, dy, dcertainty) consumed by the fused update kernel."""
         # K2: x_hat = grid_sample(y, flow), disp_emb(40/32*scale_factor*(flow-grid)), local_correlation and the
         # concat of matcher.py:109-132 in one launch, written channels-last in the feature dtype.
         dw = self.disp_emb.weight if self.has_displacement_emb else None
         db = self.disp_emb.bias if self.has_displacement_emb else None
-        d = ops.refiner_inputs(x, y, flow, dw, db, 40 / 32 * scale_factor, self.local_corr_radius)
-        with _autocast(x.device, self.amp_dtype):
-            d = self.hidden_blocks(self.block1(d))
-        d = self.out_conv(d.float())
-        return d[:, :-1], d[:, -1:]
+        d = ops.refiner_inputs(x, y, flow, dw, db, 40 / 32 * scale_factor, self.local_corr_radius, pad_to=8)
+        return self._body(d)
 
-    def delta(self, x, y, flow, scale_factor: float = 1) -> torch.Tensor:
-        """Same as forward but returns the undivided (B,3,h,w) out_conv tensor for the fused update kernel."""
-        dw = self.disp_emb.weight if self.has_displacement_emb else None
-        db = self.disp_emb.bias if self.has_displacement_emb else None
-        d = ops.refiner_inputs(x, y, flow, dw, db, 40 / 32 * scale_factor, self.local_corr_radius)
-        with _autocast(x.device, self.amp_dtype):
-            d = self.hidden_blocks(self.block1(d))
-        return self.out_conv(d.float())
+    def forward(self, x, y, flow, scale_factor: float = 1, logits=None):
+        d = self.delta(x, y, flow, scale_factor)
+        return d[:, :-1], d[:, -1:]
 
 
 class CosKernel(nn.Module):

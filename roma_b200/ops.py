@@ -104,11 +104,14 @@ def _f32(t: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------------------------------
 def refiner_inputs(x: torch.Tensor, y: torch.Tensor, flow: torch.Tensor,
                    disp_w: Optional[torch.Tensor] = None, disp_b: Optional[torch.Tensor] = None,
-                   disp_scale: float = 1.0, local_corr_radius: Optional[int] = None) -> torch.Tensor:
+                   disp_scale: float = 1.0, local_corr_radius: Optional[int] = None, pad_to: int = 1) -> torch.Tensor:
     """ConvRefiner input d = cat(x, x_hat, disp_emb, local_corr) in ONE kernel (matcher.py:105-132).
 
     x, y: (B,C,h,w) features of image A / B (any of fp32/fp16/bf16, same dtype); flow: (B,2,h,w) fp32 view.
-    Returns d as a (B, 2C+E+K, h, w) tensor in channels-last memory format, dtype of x.
+    Returns d as a (B, 2C+E+K, h, w) tensor in channels-last memory format, dtype of x.  With pad_to > 1 the
+    channel count is rounded up to a multiple of pad_to and the extra channels are zero: rows become 16-byte
+    aligned (pad_to=8 for 16-bit features), which is what the vectorised kernel path and the tensor-core GEMMs of
+    the refiner body want; the caller pads its weights accordingly.
     """
     dev = _cuda(x, y, flow, disp_w, disp_b)
     if x.dtype != y.dtype or x.dtype not in _DT:
@@ -123,6 +126,8 @@ def refiner_inputs(x: torch.Tensor, y: torch.Tensor, flow: torch.Tensor,
         disp_w = disp_w.reshape(E, 2).float().contiguous()
         disp_b = disp_b.reshape(E).float().contiguous()
     dch = 2 * Cc + E + K
+    if pad_to > 1:
+        dch = (dch + pad_to - 1) // pad_to * pad_to
     d = torch.empty((B, dch, h, w), device=dev, dtype=x.dtype, memory_format=torch.channels_last)
     lib = _lib.load()
     _run("roma_refiner_gather", dict(B=B, C=Cc, h=h, w=w, r=r, E=E, esize=x.element_size()),
@@ -365,6 +370,25 @@ def match_keypoints(x_A: torch.Tensor, x_B: torch.Tensor, warp: torch.Tensor, ce
     if n > cap:
         raise RuntimeError(f"match_keypoints: {n} tied pairs exceed capacity {cap}")
     return ia[:n], ib[:n]
+
+
+# --------------------------------------------------------------------------------------------------
+# (f-2) refiner body: depthwise 5x5 + folded BN + ReLU
+# --------------------------------------------------------------------------------------------------
+def dwconv5x5_bias_act(x: torch.Tensor, weight_taps: torch.Tensor, bias: torch.Tensor, relu: bool = True) -> torch.Tensor:
+    """Depthwise 5x5 conv (pad 2) + bias (+ ReLU) on a channels-last (B,C,h,w) tensor (matcher.py:77-103 at inference,
+    BatchNorm folded by the caller).  weight_taps: fp32 (25, C) tap-major; bias: fp32 (C).  C must be even."""
+    dev = _cuda(x, weight_taps, bias)
+    if x.dtype not in _DT:
+        raise ValueError(f"unsupported dtype {x.dtype}")
+    B, Cc, h, w = x.shape
+    x = _nhwc(x)
+    out = torch.empty_like(x, memory_format=torch.channels_last)
+    lib = _lib.load()
+    _run("roma_dwconv5x5_bias_act", dict(B=B, C=Cc, h=h, w=w, esize=x.element_size()),
+         lambda: lib.roma_dwconv5x5_bias_act(_ptr(x), _ptr(weight_taps), _ptr(bias), _ptr(out), B, h, w, Cc, int(bool(relu)),
+                                             _DT[x.dtype], _stream(dev)))
+    return out
 
 
 # --------------------------------------------------------------------------------------------------

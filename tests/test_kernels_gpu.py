@@ -213,6 +213,29 @@ def test_tc_gemm_nt(ops, cuda, dtype, split, tol, batch, M, N, K):
 
 
 # --------------------------------------------------------------------------------------------- K3b
+@pytest.mark.parametrize("N,down", [(5000, 1), (40000, 1), (24001, 8)])
+def test_kde_lut_equals_direct(ops, cuda, N, down):
+    """The table-driven half path is bit-identical to evaluating the reference's half op chain per pair."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(9)
+    centres = torch.rand(12, 4, generator=g) * 1.6 - 0.8
+    x = (centres[torch.randint(0, 12, (N,), generator=g)] + 0.08 * torch.randn(N, 4, generator=g)).clamp(-1, 1).to(cuda)
+    try:
+        lib.roma_kde_set_direct(1)
+        d_direct, p_direct = ops.kde(x, half=True, down=down, return_p=True)
+        lib.roma_kde_set_direct(0)
+        d_lut, p_lut = ops.kde(x, half=True, down=down, return_p=True)
+    finally:
+        lib.roma_kde_set_direct(0)
+    assert d_direct.float().max().item() > 50          # a non-trivial density field
+    # every pair contributes the identical half value; only the fp32 grouping of the row sum differs between the
+    # two launch shapes, which can move the final half rounding of a few rows by one ulp
+    diff = (d_direct.float() - d_lut.float()).abs()
+    ulp = d_direct.float().abs().clamp(min=1.0) * 2.0 ** -10
+    assert (diff <= ulp).all() and (diff > 0).float().mean().item() < 2e-3
+
+
 def test_kde_golden_and_oracle(ops, cuda, golden):
     g = golden("kde")
     d32 = ops.kde(g["x"].to(cuda), half=False)
@@ -290,3 +313,21 @@ def test_tiny_golden_and_oracle(ops, cuda, golden):
     f0 = torch.randn(2, 64, 12, 16, generator=gg); f1 = torch.randn(2, 64, 12, 16, generator=gg)
     want = torch.cat([O.tiny_pos_embed(O.tiny_corr_volume(f0[i:i + 1], f1[i:i + 1])) for i in range(2)])
     assert err(ops.tiny_corr_posembed(f0.to(cuda), f1.to(cuda)), want) < 1e-5
+
+
+# --------------------------------------------------------------------------------------------- (f-2)
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2), (torch.float16, 3e-3)])
+@pytest.mark.parametrize("B,C,h,w", [(2, 24, 17, 23), (1, 144, 9, 8), (2, 576, 5, 13), (1, 2, 40, 3)])
+def test_dwconv5x5_bias_relu(ops, cuda, dtype, tol, B, C, h, w):
+    """Depthwise 5x5 + bias + ReLU vs F.conv2d(groups=C) + relu in fp32 on the same (rounded) inputs."""
+    g = torch.Generator().manual_seed(17)
+    x = torch.randn(B, C, h, w, generator=g).to(dtype)
+    wt = torch.randn(C, 1, 5, 5, generator=g) * 0.2
+    bias = torch.randn(C, generator=g)
+    want = torch.relu(torch.nn.functional.conv2d(x.float(), wt, bias, padding=2, groups=C))
+    taps = wt.view(C, 25).t().contiguous()
+    got = ops.dwconv5x5_bias_act(x.to(cuda), taps.to(cuda), bias.to(cuda), relu=True)
+    assert got.dtype == dtype and got.shape == want.shape
+    assert err(got, want) < tol * max(1.0, want.abs().max().item())
+    lin = ops.dwconv5x5_bias_act(x.to(cuda), taps.to(cuda), bias.to(cuda), relu=False)
+    assert err(lin, torch.nn.functional.conv2d(x.float(), wt, bias, padding=2, groups=C)) < tol * max(1.0, want.abs().max().item())

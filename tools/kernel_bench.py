@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--only", default="")
+    ap.add_argument("--scales", default="", help="comma list of refiner visits for --only gather (s16,s8,...,s1u)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     dt = DT[args.dtype]
@@ -78,7 +79,10 @@ def main():
         shapes = [("s16", 512, 128, 7, 40, 40), ("s8", 512, 64, 3, 70, 70), ("s4", 256, 32, 2, 140, 140),
                   ("s2", 64, 16, 0, 280, 280), ("s1", 9, 6, 0, 560, 560), ("s8u", 512, 64, 3, 108, 108),
                   ("s4u", 256, 32, 2, 216, 216), ("s2u", 64, 16, 0, 432, 432), ("s1u", 9, 6, 0, 864, 864)]
+        keep = set(filter(None, args.scales.split(",")))
         for name, C, E, r, h, w in shapes:
+            if keep and name not in keep:
+                continue
             x = torch.randn(B, C, h, w, device=dev, dtype=dt).contiguous(memory_format=torch.channels_last)
             y = torch.randn(B, C, h, w, device=dev, dtype=dt).contiguous(memory_format=torch.channels_last)
             dw, db = torch.randn(E, 2, device=dev), torch.randn(E, device=dev)
