@@ -173,6 +173,7 @@ def cpu_pair_fn(coarse, upsample, weights, dinov2):
     from oracle import roma_model_oracle as MO
     from oracle import roma_oracle as O
     cpu = roma_b200.roma_outdoor("cpu", weights, dinov2, coarse_res=coarse, upsample_res=upsample, amp_dtype=torch.float32)
+    O.set_aten(True)      # issue the reference's own ATen calls (F.grid_sample, torch.cdist) at its call sites: faithful CPU speed
 
     def run(A8: torch.Tensor, B8: torch.Tensor, seed: int = 0):
         with torch.inference_mode():
@@ -255,6 +256,7 @@ def main():
 
     import roma_b200
     from roma_b200 import _lib, ops
+    from roma_b200.sharding import aggregate
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local)
@@ -298,11 +300,7 @@ def main():
             fn()
         e.record()
         barrier()
-        ms = s.elapsed_time(e)
-        if world > 1:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
+        _, ms = aggregate(0, s.elapsed_time(e), dev)         # max over ranks (NCCL all-reduce of one scalar)
         return ms
 
     for i, g in enumerate(gens):

@@ -19,6 +19,19 @@ import math
 from typing import Optional, Tuple
 
 import torch
+import torch.nn.functional as F
+
+# The explicit-index restatements below are what parity tests compare against.  For the TIMED CPU baseline
+# (bench.py cpu_baseline / --impl reference) the same functions can instead issue the ATen library calls the
+# reference itself issues at those call sites (F.grid_sample, torch.cdist), so that the baseline has the
+# reference's CPU performance characteristics rather than those of a gather-by-index_select restatement.
+# tests/test_oracle_golden.py checks that both modes agree.
+USE_ATEN = False
+
+
+def set_aten(flag: bool) -> None:
+    global USE_ATEN
+    USE_ATEN = bool(flag)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -45,6 +58,8 @@ def grid_sample_zeros(inp: torch.Tensor, grid: torch.Tensor) -> torch.Tensor:
     inp (B,C,H,W), grid (B,h,w,2) normalised (x, y).  ATen semantics: x = ((g+1)*W - 1)/2, four integer
     neighbours, each weighted by the opposite-corner area, neighbours outside the image contribute 0.
     """
+    if USE_ATEN:
+        return F.grid_sample(inp.float(), grid.float(), mode="bilinear", padding_mode="zeros", align_corners=False)
     B, C, H, W = inp.shape
     _, h, w, _ = grid.shape
     src = inp.permute(0, 2, 3, 1).reshape(B * H * W, C).float()
@@ -88,6 +103,16 @@ def local_correlation(feature0: torch.Tensor, feature1: torch.Tensor, local_radi
     ox = torch.linspace(-2 * r / w, 2 * r / w, K1, device=feature0.device)
     f0 = feature0.float() / (C ** 0.5)
     f1 = feature1.float()
+    if USE_ATEN:
+        # the reference's formulation (local_correlation.py:30-47): per batch element ONE grid_sample over all
+        # (2r+1)^2 shifted copies of the coordinate field, then a channel reduction against f0
+        off = torch.stack(torch.meshgrid(oy, ox, indexing="ij")[::-1], dim=-1).reshape(1, 1, K1 * K1, 2)    # (x, y)
+        out = []
+        for b in range(B):
+            g = (coords[b][:, :, None, :] + off).reshape(1, h, w * K1 * K1, 2)
+            win = F.grid_sample(f1[b:b + 1], g, mode="bilinear", padding_mode="zeros", align_corners=False)
+            out.append((f0[b, :, :, :, None] * win.reshape(C, h, w, K1 * K1)).sum(dim=0).permute(2, 0, 1))
+        return torch.stack(out)
     corr = torch.empty(B, K1 * K1, h, w, dtype=torch.float32, device=feature0.device)
     for ky in range(K1):
         for kx in range(K1):
@@ -212,7 +237,10 @@ def gp_posterior(x: torch.Tensor, y: torch.Tensor, pos_w: torch.Tensor, pos_b: t
     f = gp_pos_basis(b, h2, w2, pos_w.to(dtype), pos_b.to(dtype))
     K_yy = cos_kernel(yf, yf, T, eps)
     K_xy = cos_kernel(xf, yf, T, eps)
-    K_yy_inv = torch.linalg.inv(K_yy + sigma_noise * torch.eye(h2 * w2, dtype=dtype, device=x.device)[None])
+    A = K_yy + sigma_noise * torch.eye(h2 * w2, dtype=dtype, device=x.device)[None]
+    # one LAPACK getrf/getri per element: the same arithmetic as the reference's batched torch.linalg.inv
+    # (matcher.py:261), which dead-locks inside oneMKL (SLASWP) on this torch CPU build for batch > 1 and n >~ 100
+    K_yy_inv = torch.stack([torch.linalg.inv(a) for a in A])
     mu = K_xy.matmul(K_yy_inv.matmul(f))
     return mu.transpose(1, 2).reshape(b, -1, h1, w1).float()
 
@@ -239,6 +267,8 @@ def kde(x: torch.Tensor, std: float = 0.1, half: bool = True, down: Optional[int
     if half:
         x = x.half()
     ref = x if down is None else x[::down]
+    if USE_ATEN:
+        return (-torch.cdist(x, ref) ** 2 / (2 * std ** 2)).exp().sum(dim=-1)          # kde.py:9-12 verbatim op chain
     out = torch.empty(x.shape[0], dtype=x.dtype, device=x.device)
     for s in range(0, x.shape[0], chunk):
         d = _euclid_dist(x[s:s + chunk], ref)

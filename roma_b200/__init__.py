@@ -10,5 +10,6 @@ rebinds the hot ops of an already-built reference `romatch` model to the kernels
 """
 from .factory import roma_model, roma_outdoor, roma_indoor, random_init_weights, state_digest, weight_urls  # noqa: F401
 from .matcher import RegressionMatcher  # noqa: F401
+from .patch import patch  # noqa: F401
 
 __version__ = "0.1.0"

@@ -25,12 +25,58 @@ def _autocast(device: torch.device, dtype: torch.dtype):
 
 
 class VGG19(nn.Module):
+    """VGG19-bn trunk (encoders.py:61-78).  On CUDA at inference the conv -> BatchNorm(eval) -> ReLU triples run from
+    a prepared copy of the weights: BatchNorm folded into the conv, bias + ReLU fused into cuDNN's conv epilogue
+    (one library launch per layer instead of four).  Same function; the parameters stay the reference's."""
+
     def __init__(self, amp_dtype: torch.dtype = torch.float16):
         super().__init__()
         self.layers = nn.ModuleList(tvm.vgg19_bn(weights=None).features[:40])
         self.amp_dtype = amp_dtype
+        self._prep, self._prep_key = None, None
+
+    def _prepare(self, device, dtype):
+        key = (device, dtype, tuple(t._version for t in self.state_dict(keep_vars=True).values()),
+               tuple(t.data_ptr() for t in self.parameters()))
+        if self._prep_key == key:
+            return self._prep
+        plan, i = [], 0
+        with torch.no_grad():
+            while i < len(self.layers):
+                layer = self.layers[i]
+                if isinstance(layer, nn.MaxPool2d):
+                    plan.append(("pool", layer))
+                    i += 1
+                    continue
+                conv, bn = layer, self.layers[i + 1]
+                assert isinstance(conv, nn.Conv2d) and isinstance(bn, nn.BatchNorm2d) and isinstance(self.layers[i + 2], nn.ReLU)
+                scale = bn.weight.float() / torch.sqrt(bn.running_var.float() + bn.eps)
+                w = (conv.weight.float() * scale.view(-1, 1, 1, 1)).to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last)
+                b = ((conv.bias.float() if conv.bias is not None else 0) * scale + bn.bias.float() - bn.running_mean.float() * scale)
+                plan.append(("conv", w, b.to(device=device, dtype=dtype), conv.padding))
+                i += 3
+        self._prep, self._prep_key = plan, key
+        return plan
+
+    def _forward_prepared(self, x: torch.Tensor) -> Dict[int, torch.Tensor]:
+        dtype = self.amp_dtype if self.amp_dtype in (torch.float16, torch.bfloat16) else torch.float32
+        plan = self._prepare(x.device, dtype)
+        x = x.to(dtype).contiguous(memory_format=torch.channels_last)
+        feats, scale = {}, 1
+        for n, step in enumerate(plan):
+            if step[0] == "pool":
+                feats[scale] = x
+                scale *= 2
+                if n == len(plan) - 1:
+                    break
+                x = step[1](x)
+            else:
+                x = torch.cudnn_convolution_relu(x, step[1], step[2], (1, 1), step[3], (1, 1), 1)
+        return feats
 
     def forward(self, x: torch.Tensor) -> Dict[int, torch.Tensor]:
+        if x.is_cuda and not self.training:
+            return self._forward_prepared(x)
         feats, scale = {}, 1
         last = len(self.layers) - 1
         with _autocast(x.device, self.amp_dtype):

@@ -89,3 +89,21 @@ def test_tiny(golden):
     cv = O.tiny_corr_volume(g["feat0"], g["feat1"])
     close(cv, g["corr_volume"], 1e-5)
     close(O.tiny_pos_embed(g["corr_volume"]), g["pos_embed"], 1e-5)
+
+
+def test_aten_mode_equals_explicit_restatement():
+    """The ATen-call mode used for the timed CPU baseline computes the same thing as the explicit restatements."""
+    import torch
+    from oracle import roma_oracle as O
+    g = torch.Generator().manual_seed(3)
+    f0, f1 = torch.randn(2, 16, 9, 11, generator=g), torch.randn(2, 16, 9, 11, generator=g)
+    flow = torch.rand(2, 2, 9, 11, generator=g) * 2.4 - 1.2
+    pts = torch.rand(700, 4, generator=g) * 2 - 1
+    a = (O.local_correlation(f0, f1, 2, flow), O.grid_sample_zeros(f1, flow.permute(0, 2, 3, 1)), O.kde(pts, half=False))
+    O.set_aten(True)
+    try:
+        b = (O.local_correlation(f0, f1, 2, flow), O.grid_sample_zeros(f1, flow.permute(0, 2, 3, 1)), O.kde(pts, half=False))
+    finally:
+        O.set_aten(False)
+    for u, v in zip(a, b):
+        assert (u - v).abs().max().item() < 1e-4 * max(1.0, u.abs().max().item())
