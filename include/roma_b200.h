@@ -215,6 +215,9 @@ int roma_cls_to_flow_refine(const void* cls, roma_strides4 cls_strides, int dtyp
  */
 int roma_dwconv5x5_bias_act(const void* x, const float* weight, const float* bias, void* out,
                             int B, int h, int w, int C, int relu, int dtype, void* stream);
+/* Testing aid: 0 = automatic (TMA-tiled input when C * sizeof(dtype) is a multiple of 16 and x is 16-byte
+ * aligned, per-thread cp.async staging otherwise), 1 = always the cp.async variant.  Results are identical. */
+int roma_dwconv_set_path(int path);
 
 /* ---------------------------------------------------------------------------------------
  * KT  Tiny-RoMa fused correlation volume + approximate soft-argmax position embedding.

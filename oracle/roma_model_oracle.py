@@ -112,3 +112,39 @@ def match_tensors(model, coarse_A, coarse_B, fine_A: Optional[torch.Tensor] = No
         corresps = fwd(model, fine_A.float(), fine_B.float(), upsample=True, scale_factor=sf, corresps=corresps[1])
     warp, cert, logits = O.match_epilogue(corresps[1]["flow"], corresps[1]["certainty"], cert16, model.symmetric)
     return (warp, cert, logits) if return_logits else (warp, cert)
+
+
+# ----------------------------------------------------------------------------------------------
+# Tiny-RoMa (BASELINE config 5)
+# ----------------------------------------------------------------------------------------------
+def tiny_forward(model, im0: torch.Tensor, im1: torch.Tensor):
+    """TinyRoMa.forward — romatch/models/tiny.py:330-369 (inference branch of pos_embed, :186-197).
+    `model` is a roma_b200.host.tiny.TinyRoMa on the CPU; only its torch modules are used."""
+    import torch.nn.functional as F
+    im0, _, _ = model.preprocess_tensor(im0)
+    im1, _, _ = model.preprocess_tensor(im1)
+    H1, W1 = im1.shape[-2:]
+    to_normalized = torch.tensor((2 / W1, 2 / H1, 1.0))[None, :, None, None]
+    f0, c0 = model.forward_single(im0)
+    f1, c1 = model.forward_single(im1)
+    warp = O.tiny_pos_embed(O.tiny_corr_volume(c0, c1))
+    coarse = torch.cat((warp, torch.zeros_like(warp[:, -1:])), dim=1)
+    c1w = O.grid_sample_zeros(c1, coarse.permute(0, 2, 3, 1)[..., :2])
+    coarse = coarse + model.coarse_matcher(torch.cat((c0, c1w, warp), dim=1)) * to_normalized
+    out = {8: {"flow": coarse[:, :2], "certainty": coarse[:, 2:]}}
+    up = F.interpolate(coarse, size=f0.shape[-2:], mode="bilinear", align_corners=False)
+    f1w = O.grid_sample_zeros(f1, up.permute(0, 2, 3, 1)[..., :2])
+    fine = up + model.fine_matcher(torch.cat((f0, f1w, up[:, :2]), dim=1)) * to_normalized
+    out[4] = {"flow": fine[:, :2], "certainty": fine[:, 2:]}
+    return out
+
+
+def tiny_match(model, im0: torch.Tensor, im1: torch.Tensor):
+    """TinyRoMa.match — tiny.py:262-295 -> (warp (B,H0,W0,4), certainty (B,H0,W0))."""
+    B, _, H0, W0 = im0.shape
+    c = tiny_forward(model, im0, im1)[8]
+    flow = O.bilinear_resize(c["flow"], (H0, W0)).permute(0, 2, 3, 1)
+    cert = O.bilinear_resize(c["certainty"], (H0, W0))[:, 0].sigmoid()
+    xs, ys = O.pixel_centers(W0, flow.device), O.pixel_centers(H0, flow.device)
+    grid = torch.stack((xs[None, :].expand(H0, W0), ys[:, None].expand(H0, W0)), dim=-1)[None].expand(B, H0, W0, 2)
+    return torch.cat((grid, flow), dim=-1), cert

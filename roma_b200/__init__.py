@@ -8,7 +8,8 @@
 `roma_b200.ops` holds the tensor-level wrappers over the C ABI (include/roma_b200.h); `roma_b200.patch(model)`
 rebinds the hot ops of an already-built reference `romatch` model to the kernels.
 """
-from .factory import roma_model, roma_outdoor, roma_indoor, random_init_weights, state_digest, weight_urls  # noqa: F401
+from .factory import (roma_model, roma_outdoor, roma_indoor, tiny_roma_v1_model, tiny_roma_v1_outdoor,  # noqa: F401
+                      random_init_weights, state_digest, weight_urls)
 from .matcher import RegressionMatcher  # noqa: F401
 from .patch import patch  # noqa: F401
 

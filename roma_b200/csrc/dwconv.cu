@@ -8,12 +8,22 @@
 //
 // Layout: x, out (B, h, w, Cp) channels-last, Cp even; weights fp32 (25, Cp) tap-major so that one tap of
 // consecutive channels is contiguous; bias fp32 (Cp).  fp32 accumulation.
-// Mapping: a thread owns one channel PAIR (one 32-bit load for 16-bit types), a run of 4 output columns and a
-// strip of RY output rows.  It keeps the 5 x 8 input window (packed) in registers and slides it down the strip:
-// per output row it loads 8 new values and does 4 x 25 x 2 FMAs — the kernel is FP32-FMA bound (25 MACs per
-// output element, ~0.44 TMAC per 8-pair step), not HBM bound; lanes run over channel pairs, so a warp reads
-// 128 contiguous bytes per tap.
+// Mapping: a thread owns one channel PAIR (one 32-bit word for 16-bit types), a run of 4 output columns and a
+// strip of RY output rows.  It walks the RY+4 input rows of the strip once: each row (8 pixels, unpacked once)
+// is scattered into the accumulators of the five output rows it touches (ring of 5 x 4 float2 accumulators,
+// static slots, nothing is shifted).  The two channels of the pair ride one packed fma.rn.f32x2 (FFMA2): scalar
+// 3-register FFMA issues at half rate on sm_100, so FFMA2 is what reaches the FP32 pipe's peak.  The kernel sits
+// where the FP32 floor (25 MAC per output element) and the HBM floor (one read + one write of the activation)
+// meet; lanes run over channel pairs, so a warp touches 128 contiguous bytes per pixel.
+//
+// Two input paths:
+//   * TMA (default when the pixel stride is a multiple of 16 bytes — every padded refiner width): the block's
+//     whole input tile is fetched by cp.async.bulk.tensor boxes, borders and channel tail zero-filled by the copy
+//     engine;
+//   * per-thread cp.async staging (any even channel count).
+#include <atomic>
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace roma {
 
@@ -40,82 +50,304 @@ template <> struct Pair<__nv_bfloat16> {
     __device__ static __forceinline__ void store(__nv_bfloat16* p, float a, float b) { *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b); }
 };
 
-constexpr int kDwRY = 8;      // output rows per thread strip
+constexpr int kDwRY = 16;     // output rows per thread strip; kDwRY + 4 input rows = a whole number of 5-row chunks
 constexpr int kDwTW = 4;      // output columns per thread
+constexpr int kDwNV = kDwTW + 4;   // input columns per thread and row
+constexpr int kDwThreads = 128;
+constexpr int kDwAhead = 4;   // input rows in flight per thread (cp.async groups)
+constexpr int kDwChunks = (kDwRY + 4) / 5;
+static_assert((kDwRY + 4) % 5 == 0 && kDwChunks >= 2, "strip height + halo must be a multiple of the accumulator ring");
 
-template <typename T>
-__global__ void __launch_bounds__(128, 4)
-dwconv5_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const float* __restrict__ bias, T* __restrict__ out,
-               int B, int h, int w, int Cp, int relu, long long nthreads) {
+// One input row (8 unpacked pixels of the thread's channel pair) scattered into the output rows it feeds.
+// Input row r = r0 + I feeds the five output rows r-2..r+2 (tap row dy = r - o + 2); the accumulators of those
+// rows live in a ring of 5 whose slot indices are compile-time constants inside a 5-row chunk.  FIRST / LAST
+// prune the contributions to rows outside the strip.  Afterwards output row r - 2 is complete and is stored.
+template <typename T, bool FIRST, bool LAST, int I>
+__device__ __forceinline__ void dw_row(const float2 (&v)[kDwNV], T* __restrict__ ob, int r, int x0, unsigned storemask, int h, int w,
+                                       int Cp, int relu, const float2 (&wv)[25], float2 bv, float2 (&acc)[5][kDwTW]) {
     using P = Pair<T>;
-    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= nthreads) return;
-    const int npairs = Cp >> 1, runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRY - 1) / kDwRY;
-    const int pair = (int)(gid % npairs);
-    long long t = gid / npairs;
-    const int run = (int)(t % runs); t /= runs;
-    const int strip = (int)(t % strips);
-    const int b = (int)(t / strips);
-    const int c = pair * 2, x0 = run * kDwTW, y0 = strip * kDwRY;
+#pragma unroll
+    for (int d = 4; d >= 0; --d) {
+        if (FIRST && d < 4 - I) continue;              // output row above the strip
+        if (LAST && d > 4 - I) continue;               // output row below the strip
+        const int slot = (I + 1 + d) % 5, dy = 4 - d;
+        if (d == 4) {
+#pragma unroll
+            for (int ox = 0; ox < kDwTW; ++ox) acc[slot][ox] = bv;
+        }
+#pragma unroll
+        for (int dx = 0; dx < 5; ++dx)
+#pragma unroll
+            for (int ox = 0; ox < kDwTW; ++ox) acc[slot][ox] = __ffma2_rn(v[ox + dx], wv[dy * 5 + dx], acc[slot][ox]);
+    }
+    if (!(FIRST && I < 4)) {
+        const int o = r - 2, slot = (I + 1) % 5;
+        if (o < h) {
+            T* op = ob + ((long long)o * w + x0) * Cp;
+#pragma unroll
+            for (int ox = 0; ox < kDwTW; ++ox) {
+                if ((storemask >> ox) & 1u) {
+                    float a = acc[slot][ox].x, b = acc[slot][ox].y;
+                    if (relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+                    P::store(op + ox * Cp, a, b);
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- TMA-tiled variant
+// The block's whole input tile — (kDwRY + 4) rows x (4 * rpb + 4) columns x 2 * ppb channels — is fetched by
+// cp.async.bulk.tensor in 5-row boxes (one mbarrier per box, matching the 5-row compute chunks), so the image
+// border, the channel tail and every address computation of the input side are done by the copy engine; the
+// compute threads only issue LDS, FFMA2 and the output stores.  4 blocks per SM keep three tiles in flight
+// while one computes.
+struct DwTmaParams {
+    int h, w, Cp, relu;
+    int ppb, rpb, pair_groups;
+    int row_bytes, pix_bytes;        // of the shared tile
+    int chunk_stride, chunk_bytes;   // 5-row box: distance between boxes in shared memory (128-aligned), bytes transferred
+};
+
+template <typename T, bool FIRST, bool LAST>
+__device__ __forceinline__ void dw_chunk_smem(const unsigned char* __restrict__ rows, int row_bytes, int pix_bytes, T* __restrict__ ob,
+                                              int r0, int x0, unsigned storemask, int h, int w, int Cp, int relu,
+                                              const float2 (&wv)[25], float2 bv, float2 (&acc)[5][kDwTW]) {
+    using P = Pair<T>;
+    using Raw = typename P::Raw;
+    auto step = [&](auto Ic) {
+        constexpr int I = decltype(Ic)::value;
+        const unsigned char* rp = rows + I * row_bytes;
+        float2 v[kDwNV];
+#pragma unroll
+        for (int j = 0; j < kDwNV; ++j) v[j] = P::unpack(*reinterpret_cast<const Raw*>(rp + j * pix_bytes));
+        dw_row<T, FIRST, LAST, I>(v, ob, r0 + I, x0, storemask, h, w, Cp, relu, wv, bv, acc);
+    };
+    step(std::integral_constant<int, 0>{}); step(std::integral_constant<int, 1>{}); step(std::integral_constant<int, 2>{});
+    step(std::integral_constant<int, 3>{}); step(std::integral_constant<int, 4>{});
+}
+
+// PPB > 0 fixes the pairs per block at compile time (tile strides become immediates); PPB == 0 reads them from pr.
+template <typename T, int PPB>
+__global__ void __launch_bounds__(kDwThreads, 4)
+dwconv5_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restrict__ wgt, const float* __restrict__ bias,
+                   T* __restrict__ out, const DwTmaParams pr) {
+    struct Geo {
+        int ppb, rpb, pix_bytes, row_bytes, chunk_bytes, chunk_stride;
+    };
+    Geo p;
+    if (PPB > 0) {
+        p.ppb = PPB; p.rpb = kDwThreads / (PPB > 0 ? PPB : 1); p.pix_bytes = 2 * PPB * (int)sizeof(T);
+        p.row_bytes = (p.rpb * kDwTW + 4) * p.pix_bytes; p.chunk_bytes = 5 * p.row_bytes;
+        p.chunk_stride = (p.chunk_bytes + 127) / 128 * 128;
+    } else {
+        p.ppb = pr.ppb; p.rpb = pr.rpb; p.pix_bytes = pr.pix_bytes; p.row_bytes = pr.row_bytes;
+        p.chunk_bytes = pr.chunk_bytes; p.chunk_stride = pr.chunk_stride;
+    }
+    extern __shared__ unsigned char dw_smem_raw[];
+    unsigned char* tile = dw_smem_raw + ((128u - (tma::saddr(dw_smem_raw) & 127u)) & 127u);   // 128-byte aligned box destinations
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tile + kDwChunks * p.chunk_stride);
+
+    const int tid = threadIdx.x;
+    const int pg = blockIdx.x % pr.pair_groups, rg = blockIdx.x / pr.pair_groups;
+    const int b = blockIdx.z, y0 = blockIdx.y * kDwRY;
+    const int h = pr.h, w = pr.w, Cp = pr.Cp;
+    // chunk ch completes output rows y0 + 5 ch - 4 ...: it is needed only if the first of them is inside the image
+    int nch = kDwChunks;
+    while (nch > 1 && y0 + 5 * (nch - 1) - 4 >= h) --nch;
+
+    if (tid == 0) {
+        tma::prefetch_map(&map);
+        for (int k = 0; k < nch; ++k) tma::mbar_init(&bars[k], 1);
+        tma::fence_barrier_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        for (int k = 0; k < nch; ++k) {
+            tma::mbar_expect_tx(&bars[k], (uint32_t)p.chunk_bytes);
+            tma::load_4d(tile + k * p.chunk_stride, &map, &bars[k], pg * p.ppb * 2, rg * p.rpb * kDwTW - 2, y0 - 2 + 5 * k, b);
+        }
+    }
+
+    const int npairs = Cp >> 1, runs = (w + kDwTW - 1) / kDwTW;
+    const int pair_l = tid % p.ppb, run_l = tid / p.ppb;
+    const int pair = pg * p.ppb + pair_l, run = rg * p.rpb + run_l;
+    const bool active = run_l < p.rpb && pair < npairs && run < runs;   // thread 0 (the issuer) is always active
+    if (!active) return;
+    const int c = pair * 2, x0 = run * kDwTW;
+    T* ob = out + (long long)b * h * w * Cp + c;
+    unsigned storemask = 0;
+#pragma unroll
+    for (int ox = 0; ox < kDwTW; ++ox) storemask |= (x0 + ox < w) ? (1u << ox) : 0u;
 
     float2 wv[25];
 #pragma unroll
     for (int k = 0; k < 25; ++k) wv[k] = __ldg(reinterpret_cast<const float2*>(wgt + (long long)k * Cp + c));
     const float2 bv = __ldg(reinterpret_cast<const float2*>(bias + c));
 
-    const T* xb = x + (long long)b * h * w * Cp + c;
-    T* ob = out + (long long)b * h * w * Cp + c;
-    auto load_row = [&](int y, typename P::Raw* dst) {
-        const bool yok = y >= 0 && y < h;
-#pragma unroll
-        for (int j = 0; j < kDwTW + 4; ++j) {
-            const int xx = x0 - 2 + j;
-            dst[j] = (yok && xx >= 0 && xx < w) ? P::load(xb + ((long long)y * w + xx) * Cp) : P::zero();
-        }
-    };
-    typename P::Raw win[5][kDwTW + 4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) load_row(y0 - 2 + i, win[i]);
-
+    const unsigned char* tb = tile + run_l * kDwTW * p.pix_bytes + pair_l * (int)sizeof(typename Pair<T>::Raw);
+    float2 acc[5][kDwTW];
+    tma::mbar_wait(&bars[0], 0);
+    dw_chunk_smem<T, true, false>(tb, p.row_bytes, p.pix_bytes, ob, y0 - 2, x0, storemask, h, w, Cp, pr.relu, wv, bv, acc);
 #pragma unroll 1
-    for (int yy = 0; yy < kDwRY; ++yy) {
-        const int y = y0 + yy;
-        if (y >= h) break;
-        load_row(y + 2, win[4]);
-        float2 acc[kDwTW];
+    for (int ch = 1; ch < kDwChunks - 1; ++ch) {
+        if (ch >= nch) return;
+        tma::mbar_wait(&bars[ch], 0);
+        dw_chunk_smem<T, false, false>(tb + ch * p.chunk_stride, p.row_bytes, p.pix_bytes, ob, y0 - 2 + 5 * ch, x0, storemask,
+                                       h, w, Cp, pr.relu, wv, bv, acc);
+    }
+    if (nch < kDwChunks) return;
+    tma::mbar_wait(&bars[kDwChunks - 1], 0);
+    dw_chunk_smem<T, false, true>(tb + (kDwChunks - 1) * p.chunk_stride, p.row_bytes, p.pix_bytes, ob, y0 - 2 + 5 * (kDwChunks - 1),
+                                  x0, storemask, h, w, Cp, pr.relu, wv, bv, acc);
+}
+
+template <typename T>
+static int launch_dw_tma(const void* x, const float* weight, const float* bias, void* out, int B, int h, int w, int C, int relu,
+                         int dtype, cudaStream_t st) {
+    const int esz = (int)sizeof(T);
+    const int npairs = C / 2, runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRY - 1) / kDwRY;
+    const int pair_groups = cdiv(npairs, 32);
+    const int gran = 16 / (2 * esz);                               // pairs per 16 bytes
+    int ppb = cdiv(cdiv(npairs, pair_groups), gran) * gran;        // <= 32; box rows are whole 16-byte units
+    if (ppb > 32) ppb = 32;
+    const int rpb = kDwThreads / ppb;
+    const int tcols = rpb * kDwTW + 4;
+    DwTmaParams p;
+    p.h = h; p.w = w; p.Cp = C; p.relu = relu; p.ppb = ppb; p.rpb = rpb; p.pair_groups = pair_groups;
+    p.pix_bytes = 2 * ppb * esz;
+    p.row_bytes = tcols * p.pix_bytes;
+    p.chunk_bytes = 5 * p.row_bytes;
+    p.chunk_stride = (p.chunk_bytes + 127) / 128 * 128;
+    const size_t smem = (size_t)kDwChunks * p.chunk_stride + kDwChunks * sizeof(uint64_t) + 128;
+
+    CUtensorMap map;
+    const uint64_t dims[4] = {(uint64_t)C, (uint64_t)w, (uint64_t)h, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)C * esz, (uint64_t)w * C * esz, (uint64_t)h * w * C * esz};
+    const uint32_t box[4] = {(uint32_t)(2 * ppb), (uint32_t)tcols, 5u, 1u};
+    if (int rc = tma::encode_tiled(&map, dtype, 4, x, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+
+    const dim3 grid((unsigned)(pair_groups * cdiv(runs, rpb)), (unsigned)strips, (unsigned)B);
+    using Kernel = void (*)(const CUtensorMap, const float*, const float*, T*, const DwTmaParams);
+    Kernel kernel = ppb == 32 ? dwconv5_tma_kernel<T, 32> : ppb == 24 ? dwconv5_tma_kernel<T, 24>
+                  : ppb == 12 ? dwconv5_tma_kernel<T, 12> : dwconv5_tma_kernel<T, 0>;
+    // opt in to > 48 KB of dynamic shared memory (idempotent, cheap; done per call to stay per-instantiation correct)
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+    if (e != cudaSuccess) return fail((int)e, "roma_dwconv5x5_bias_act: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    kernel<<<grid, kDwThreads, smem, st>>>(map, weight, bias, (T*)out, p);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- cp.async variant
+// Asynchronous global -> shared copy of one channel pair; src_bytes = 0 zero-fills (image border).
+template <int BYTES>
+__device__ __forceinline__ void cp_async_pair(void* smem_dst, const void* gsrc, bool valid) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    const int n = valid ? BYTES : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;" ::"r"(d), "l"(gsrc), "n"(BYTES), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Per-thread private staging ring in shared memory: stage s, column j of thread t lives at [s][j][t]
+// (consecutive threads -> consecutive banks).  Nothing is shared between threads, so no block barrier is needed:
+// a thread only waits for its own copy groups.
+template <typename T>
+struct DwStage {
+    typename Pair<T>::Raw v[5][kDwNV][kDwThreads];
+};
+
+template <typename T>
+__device__ __forceinline__ void dw_issue_row(DwStage<T>& st, int stage, const T* __restrict__ xb, int r, int x0, unsigned colmask,
+                                             int h, int w, int Cp) {
+    using Raw = typename Pair<T>::Raw;
+    const bool yok = r >= 0 && r < h;
+    const T* rp = xb + ((long long)(yok ? r : 0) * w + (x0 - 2)) * Cp;
 #pragma unroll
-        for (int ox = 0; ox < kDwTW; ++ox) acc[ox] = bv;
-#pragma unroll
-        for (int i = 0; i < 5; ++i) {
-#pragma unroll
-            for (int j = 0; j < kDwTW + 4; ++j) {
-                const float2 v = P::unpack(win[i][j]);
-#pragma unroll
-                for (int ox = 0; ox < kDwTW; ++ox) {
-                    const int dx = j - ox;
-                    if (dx >= 0 && dx < 5) {
-                        acc[ox].x = fmaf(v.x, wv[i * 5 + dx].x, acc[ox].x);
-                        acc[ox].y = fmaf(v.y, wv[i * 5 + dx].y, acc[ox].y);
-                    }
-                }
-            }
-        }
-#pragma unroll
-        for (int ox = 0; ox < kDwTW; ++ox) {
-            if (x0 + ox < w) {
-                float a = acc[ox].x, bb = acc[ox].y;
-                if (relu) { a = fmaxf(a, 0.f); bb = fmaxf(bb, 0.f); }
-                P::store(ob + ((long long)y * w + x0 + ox) * Cp, a, bb);
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-            for (int j = 0; j < kDwTW + 4; ++j) win[i][j] = win[i + 1][j];
+    for (int j = 0; j < kDwNV; ++j) {
+        const bool ok = yok && ((colmask >> j) & 1u);
+        cp_async_pair<sizeof(Raw)>(&st.v[stage][j][threadIdx.x], ok ? (const void*)(rp + j * Cp) : (const void*)xb, ok);
     }
 }
 
+// Row r0 + I is read from staging slot I (it was requested kDwAhead steps earlier); row r0 + I + kDwAhead is
+// requested into slot (I + kDwAhead) % 5, whose previous content (row r0 + I - 1) has already been consumed.
+template <typename T, bool FIRST, bool LAST>
+__device__ __forceinline__ void dw_chunk(DwStage<T>& st, const T* __restrict__ xb, T* __restrict__ ob, int r0, int r_end, int x0,
+                                         unsigned colmask, int h, int w, int Cp, int relu, const float2 (&wv)[25], float2 bv,
+                                         float2 (&acc)[5][kDwTW]) {
+    using P = Pair<T>;
+    auto step = [&](auto Ic) {
+        constexpr int I = decltype(Ic)::value;
+        const int r = r0 + I;
+        if (r + kDwAhead < r_end) dw_issue_row<T>(st, (I + kDwAhead) % 5, xb, r + kDwAhead, x0, colmask, h, w, Cp);
+        cp_async_commit();                             // one group per step, empty or not: keeps the count uniform
+        cp_async_wait<kDwAhead>();                     // row r has landed
+        float2 v[kDwNV];
+#pragma unroll
+        for (int j = 0; j < kDwNV; ++j) v[j] = P::unpack(st.v[I][j][threadIdx.x]);
+        dw_row<T, FIRST, LAST, I>(v, ob, r, x0, colmask >> 2, h, w, Cp, relu, wv, bv, acc);
+    };
+    step(std::integral_constant<int, 0>{}); step(std::integral_constant<int, 1>{}); step(std::integral_constant<int, 2>{});
+    step(std::integral_constant<int, 3>{}); step(std::integral_constant<int, 4>{});
+}
+
+// Grid: x = pair groups * run groups, y = strips, z = batch.  Inside a block, threads run over ppb channel pairs
+// (fastest: a warp reads contiguous bytes of one pixel) and rpb = 128 / ppb adjacent 4-column runs, so that the
+// 4-column halo two neighbouring runs share is requested from the same SM's L1.
+template <typename T>
+__global__ void __launch_bounds__(kDwThreads, 4)
+dwconv5_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const float* __restrict__ bias, T* __restrict__ out,
+               int h, int w, int Cp, int relu, int ppb, int rpb, int pair_groups) {
+    __shared__ DwStage<T> st;
+    const int npairs = Cp >> 1, runs = (w + kDwTW - 1) / kDwTW;
+    const int pg = blockIdx.x % pair_groups, rg = blockIdx.x / pair_groups;
+    const int pair = pg * ppb + (int)threadIdx.x % ppb;
+    const int run = rg * rpb + (int)threadIdx.x / ppb;
+    if ((int)threadIdx.x >= ppb * rpb || pair >= npairs || run >= runs) return;
+    const int b = blockIdx.z;
+    const int c = pair * 2, x0 = run * kDwTW, y0 = blockIdx.y * kDwRY;
+
+    const T* xb = x + (long long)b * h * w * Cp + c;
+    T* ob = out + (long long)b * h * w * Cp + c;
+    unsigned colmask = 0;                              // bit j: column x0 - 2 + j lies inside the image
+#pragma unroll
+    for (int j = 0; j < kDwNV; ++j) colmask |= (x0 - 2 + j >= 0 && x0 - 2 + j < w) ? (1u << j) : 0u;
+
+    // rows past the image contribute nothing and no output row >= h exists: stop after input row h + 1
+    const int r_begin = y0 - 2;
+    const int r_end = min(y0 + kDwRY + 2, h + 2);
+#pragma unroll
+    for (int i = 0; i < kDwAhead; ++i) {
+        if (r_begin + i < r_end) dw_issue_row<T>(st, i, xb, r_begin + i, x0, colmask, h, w, Cp);
+        cp_async_commit();
+    }
+
+    float2 wv[25];
+#pragma unroll
+    for (int k = 0; k < 25; ++k) wv[k] = __ldg(reinterpret_cast<const float2*>(wgt + (long long)k * Cp + c));
+    const float2 bv = __ldg(reinterpret_cast<const float2*>(bias + c));
+
+    float2 acc[5][kDwTW];
+    dw_chunk<T, true, false>(st, xb, ob, r_begin, r_end, x0, colmask, h, w, Cp, relu, wv, bv, acc);
+#pragma unroll 1
+    for (int ch = 1; ch < kDwChunks - 1; ++ch) {
+        if (r_begin + 5 * ch - 2 >= h) break;          // every remaining output row is below the image
+        dw_chunk<T, false, false>(st, xb, ob, r_begin + 5 * ch, r_end, x0, colmask, h, w, Cp, relu, wv, bv, acc);
+    }
+    if (r_begin + 5 * (kDwChunks - 1) - 2 < h)
+        dw_chunk<T, false, true>(st, xb, ob, r_begin + 5 * (kDwChunks - 1), r_end, x0, colmask, h, w, Cp, relu, wv, bv, acc);
+    cp_async_wait<0>();
+}
+
 }  // namespace roma
+
+static std::atomic<int> g_dw_path{0};
+extern "C" int roma_dwconv_set_path(int path) {
+    if (path < 0 || path > 1) return roma::fail(ROMA_ERR_BAD_ARG, "roma_dwconv_set_path: path %d (0 auto, 1 per-thread cp.async)", path);
+    g_dw_path.store(path);
+    return 0;
+}
 
 extern "C" int roma_dwconv5x5_bias_act(const void* x, const float* weight, const float* bias, void* out,
                                        int B, int h, int w, int C, int relu, int dtype, void* stream) {
@@ -128,13 +360,32 @@ extern "C" int roma_dwconv5x5_bias_act(const void* x, const float* weight, const
     ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & al) == 0 &&
                  ((reinterpret_cast<uintptr_t>(weight) | reinterpret_cast<uintptr_t>(bias)) & 7u) == 0,
                  ROMA_ERR_ALIGNMENT, "roma_dwconv5x5_bias_act: misaligned pointer");
-    const long long n = (long long)B * ((h + kDwRY - 1) / kDwRY) * ((w + kDwTW - 1) / kDwTW) * (C / 2);
-    const int grid = cdiv(n, 128);
+    const int npairs = C / 2, runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRY - 1) / kDwRY;
+    ROMA_REQUIRE(B <= 65535 && strips <= 65535, ROMA_ERR_UNSUPPORTED, "roma_dwconv5x5_bias_act: batch / height too large");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int esz = dtype == ROMA_F32 ? 4 : 2;
+    // TMA path: 16-byte aligned base and pixel stride (every padded refiner width); otherwise per-thread cp.async
+    const bool tma_ok = g_dw_path.load() != 1 && ((long long)C * esz) % 16 == 0 && (reinterpret_cast<uintptr_t>(x) & 15u) == 0 &&
+                        tma::encode_fn() != nullptr;
+    if (tma_ok) {
+        int rc;
+        switch (dtype) {
+            case ROMA_F32:  rc = launch_dw_tma<float>(x, weight, bias, out, B, h, w, C, relu, dtype, st); break;
+            case ROMA_F16:  rc = launch_dw_tma<__half>(x, weight, bias, out, B, h, w, C, relu, dtype, st); break;
+            case ROMA_BF16: rc = launch_dw_tma<__nv_bfloat16>(x, weight, bias, out, B, h, w, C, relu, dtype, st); break;
+            default: return fail(ROMA_ERR_BAD_ARG, "roma_dwconv5x5_bias_act: unknown dtype %d", dtype);
+        }
+        if (rc) return rc;
+        return check_launch("roma_dwconv5x5_bias_act");
+    }
+    const int pair_groups = cdiv(npairs, 32);
+    const int ppb = cdiv(npairs, pair_groups);                  // <= 32 pairs per block, evenly split
+    const int rpb = kDwThreads / ppb;
+    const dim3 grid((unsigned)(pair_groups * cdiv(runs, rpb)), (unsigned)strips, (unsigned)B);
     switch (dtype) {
-        case ROMA_F32:  dwconv5_kernel<float><<<grid, 128, 0, st>>>((const float*)x, weight, bias, (float*)out, B, h, w, C, relu, n); break;
-        case ROMA_F16:  dwconv5_kernel<__half><<<grid, 128, 0, st>>>((const __half*)x, weight, bias, (__half*)out, B, h, w, C, relu, n); break;
-        case ROMA_BF16: dwconv5_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const __nv_bfloat16*)x, weight, bias, (__nv_bfloat16*)out, B, h, w, C, relu, n); break;
+        case ROMA_F32:  dwconv5_kernel<float><<<grid, kDwThreads, 0, st>>>((const float*)x, weight, bias, (float*)out, h, w, C, relu, ppb, rpb, pair_groups); break;
+        case ROMA_F16:  dwconv5_kernel<__half><<<grid, kDwThreads, 0, st>>>((const __half*)x, weight, bias, (__half*)out, h, w, C, relu, ppb, rpb, pair_groups); break;
+        case ROMA_BF16: dwconv5_kernel<__nv_bfloat16><<<grid, kDwThreads, 0, st>>>((const __nv_bfloat16*)x, weight, bias, (__nv_bfloat16*)out, h, w, C, relu, ppb, rpb, pair_groups); break;
         default: return fail(ROMA_ERR_BAD_ARG, "roma_dwconv5x5_bias_act: unknown dtype %d", dtype);
     }
     return check_launch("roma_dwconv5x5_bias_act");

@@ -15,6 +15,7 @@ import torch.nn as nn
 from .host.decoder import build_decoder
 from .host.encoder import CNNandDinov2
 from .host.vit import DinoViT
+from .host.tiny import TinyRoMa, XFeatBackbone
 from .matcher import RegressionMatcher
 
 weight_urls = {
@@ -113,3 +114,26 @@ def state_digest(sd: Dict[str, torch.Tensor]) -> str:
         h.update(k.encode())
         h.update(sd[k].detach().cpu().contiguous().numpy().tobytes())
     return h.hexdigest()[:16]
+
+
+def tiny_roma_v1_model(weights=None, freeze_xfeat=False, exact_softmax=False, xfeat=None):
+    """roma_models.py:9-16."""
+    model = TinyRoMa(xfeat=xfeat, freeze_xfeat=freeze_xfeat, exact_softmax=exact_softmax)
+    if weights is not None:
+        model.load_state_dict(weights)
+    return model
+
+
+def tiny_roma_v1_outdoor(device, weights=None, xfeat=None):
+    """model_zoo/__init__.py:16-28.  Offline: `weights` is the reference's `tiny_roma_v1_outdoor.pth` state_dict
+    and `xfeat` an XFeat `.net` (or an `XFeatBackbone` with XFeat's weights loaded); with neither, a seeded
+    random init of the same architecture (`roma_b200.host.tiny.random_init_tiny`) is used."""
+    if weights is None and xfeat is None:
+        from .host.tiny import random_init_tiny
+        weights, trunk_sd = random_init_tiny(seed=0)
+        xfeat = XFeatBackbone()
+        weights = {**weights, **{"xfeat.0." + k: v for k, v in trunk_sd.items()}}   # trunk is trainable here (:9)
+    elif xfeat is None:
+        raise ValueError("tiny_roma_v1_outdoor: pass the XFeat trunk (xfeat=...) together with trained weights; "
+                         "torch.hub is not reachable from this build")
+    return tiny_roma_v1_model(weights=weights, xfeat=xfeat).to(device)

@@ -317,9 +317,21 @@ def test_tiny_golden_and_oracle(ops, cuda, golden):
 
 # --------------------------------------------------------------------------------------------- (f-2)
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2), (torch.float16, 3e-3)])
-@pytest.mark.parametrize("B,C,h,w", [(2, 24, 17, 23), (1, 144, 9, 8), (2, 576, 5, 13), (1, 2, 40, 3)])
-def test_dwconv5x5_bias_relu(ops, cuda, dtype, tol, B, C, h, w):
-    """Depthwise 5x5 + bias + ReLU vs F.conv2d(groups=C) + relu in fp32 on the same (rounded) inputs."""
+@pytest.mark.parametrize("B,C,h,w", [(2, 24, 17, 23), (1, 144, 9, 8), (2, 576, 5, 13), (1, 2, 40, 3), (1, 1144, 33, 21),
+                                     (1, 40, 16, 64), (3, 72, 31, 4), (1, 10, 37, 41)])
+@pytest.mark.parametrize("path", [0, 1])
+def test_dwconv5x5_bias_relu(ops, cuda, dtype, tol, B, C, h, w, path):
+    """Depthwise 5x5 + bias + ReLU vs F.conv2d(groups=C) + relu in fp32 on the same (rounded) inputs; path 0 takes
+    the TMA-tiled kernel where the channel stride allows it, path 1 forces the cp.async kernel."""
+    from roma_b200 import _lib
+    assert _lib.load().roma_dwconv_set_path(path) == 0
+    try:
+        _dwconv_case(ops, cuda, dtype, tol, B, C, h, w)
+    finally:
+        _lib.load().roma_dwconv_set_path(0)
+
+
+def _dwconv_case(ops, cuda, dtype, tol, B, C, h, w):
     g = torch.Generator().manual_seed(17)
     x = torch.randn(B, C, h, w, generator=g).to(dtype)
     wt = torch.randn(C, 1, 5, 5, generator=g) * 0.2

@@ -148,6 +148,20 @@ def main():
         ms = timeit(lambda: ops.tiny_corr_posembed(f0, f1), max(3, args.iters // 4), flush)
         emit(kernel="tiny_corr_posembed", batch=Bt, ms=round(ms, 3), alg_GF=round(flops / 1e9, 2), TFLOPs=round(flops / ms / 1e9, 2))
 
+    if want("dwconv"):
+        # ConvRefiner bodies at the 560 -> 864 config: (padded channels, side) of every refiner visit
+        for name, Cp, side in (("s16", 1144, 40), ("s8", 1144, 70), ("s4", 576, 140), ("s2", 144, 280), ("s1", 24, 560),
+                               ("s8u", 1144, 108), ("s4u", 576, 216), ("s2u", 144, 432), ("s1u", 24, 864)):
+            x = torch.randn(B, side, side, Cp, device=dev, dtype=dt).permute(0, 3, 1, 2)
+            wt = torch.randn(25, Cp, device=dev) * 0.2
+            bs = torch.randn(Cp, device=dev)
+            alg = 2 * x.numel() * x.element_size()
+            macs = 25 * x.numel()
+            ms = timeit(lambda: ops.dwconv5x5_bias_act(x, wt, bs, True), args.iters, flush)
+            emit(kernel="dwconv5x5", visit=name, C=Cp, side=side, batch=B, dtype=args.dtype, ms=round(ms, 4),
+                 alg_MB=round(alg / 1e6, 1), GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4),
+                 fp32_TFLOPs=round(2 * macs / ms / 1e9, 2))
+
 
 if __name__ == "__main__":
     main()
