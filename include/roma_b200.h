@@ -215,6 +215,18 @@ int roma_cls_to_flow_refine(const void* cls, roma_strides4 cls_strides, int dtyp
  */
 int roma_dwconv5x5_bias_act(const void* x, const float* weight, const float* bias, void* out,
                             int B, int h, int w, int C, int relu, int dtype, void* stream);
+/* (f-2) ConvRefiner head: out[p, o] = bias[o] + sum_c weight[o, c] * x[p, c], o < OUT <= 3, fp32 accumulation.
+ *
+ * Replaces (reference): romatch/models/matcher.py:141 `self.out_conv(d.float())` (fp32 copy of the activation +
+ *   1x1 cudnn convolution + bias add); the activation is read once in its storage dtype.
+ * x      : (npix, C) channels-last activation (npix = B*h*w), dtype `dtype`, C a multiple of 8 (4 for fp32),
+ *          16-byte aligned.
+ * weight : fp32 (OUT, C); bias: fp32 (OUT).
+ * out    : fp32 (npix, 4): (dx, dy, dcertainty, 0) per pixel (components >= OUT are 0), 16-byte aligned; pass it
+ *          to roma_flow_update_resample as `delta` with strides (b: h*w*4, c: 1, y: w*4, x: 4).
+ */
+int roma_refiner_out_conv(const void* x, const float* weight, const float* bias, float* out,
+                          long long npix, int C, int OUT, int dtype, void* stream);
 /* Testing aid: 0 = automatic (TMA-tiled input when C * sizeof(dtype) is a multiple of 16 and x is 16-byte
  * aligned, per-thread cp.async staging otherwise), 1 = always the cp.async variant.  Results are identical. */
 int roma_dwconv_set_path(int path);

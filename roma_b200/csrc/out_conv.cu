@@ -1,0 +1,159 @@
+// (f-2) ConvRefiner head: out_conv (1x1 convolution, hidden_dim -> 3) evaluated in fp32 straight from the
+// channels-last activation in its storage dtype.
+//
+// Replaces (reference): romatch/models/matcher.py:141 `d = self.out_conv(d.float())` — an fp32 copy of the whole
+// activation (a full extra write + read) followed by a cudnn 1x1 convolution and its bias add.  Here the
+// activation is read exactly once (16-byte vectors), up-converted in registers (exact), and reduced with fp32
+// FMAs: HBM-bound, algorithmic bytes = B*h*w*(C*sizeof(T) + 16).
+//
+// Mapping: a group of G lanes (G = 1..32, power of two) owns one pixel at a time; lane l of the group holds the
+// weights of channel vectors l, l + G, ... (NV per lane) in registers for the whole kernel and walks pixels in a
+// grid-stride loop, two pixels in flight.  Partial sums are combined with xor-shuffles inside the group.
+// Output: fp32 (npix, 4) interleaved (dx, dy, dcert, 0) so that every pixel is one 16-byte store; the consumer
+// (`roma_flow_update_resample`) takes explicit strides.
+#include "common.cuh"
+
+namespace roma {
+
+constexpr int kOutMax = 3;
+
+template <typename T, int NV>
+__global__ void __launch_bounds__(256)
+out_conv_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const float* __restrict__ bias, float4* __restrict__ out,
+                long long npix, int C, int OUT, int G, int gshift) {
+    constexpr int kVec = Elem<T>::kVec;
+    const int lane = threadIdx.x & 31;
+    const int gl = lane & (G - 1);                       // lane inside the group
+    const int nvec = C / kVec;
+    float wv[NV][kOutMax][kVec];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int v = gl + i * G;
+#pragma unroll
+        for (int o = 0; o < kOutMax; ++o)
+#pragma unroll
+            for (int k = 0; k < kVec; ++k) wv[i][o][k] = (v < nvec && o < OUT) ? __ldg(wgt + (long long)o * C + v * kVec + k) : 0.f;
+    }
+    const float b0 = OUT > 0 ? __ldg(bias + 0) : 0.f, b1 = OUT > 1 ? __ldg(bias + 1) : 0.f, b2 = OUT > 2 ? __ldg(bias + 2) : 0.f;
+
+    const long long groups_total = ((long long)gridDim.x * blockDim.x) >> gshift;
+    // the trip count is uniform per warp (the shuffles below need all 32 lanes): a group past the end idles
+    const long long warp_first = (((long long)blockIdx.x * blockDim.x + threadIdx.x) & ~31LL) >> gshift;
+    for (long long base = warp_first; base < npix; base += 2 * groups_total) {
+        const long long p = base + (lane >> gshift), p1 = p + groups_total;
+        const bool has0 = p < npix, has1 = p1 < npix;    // uniform inside the group
+        uint4 ra[NV], rb[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int v = gl + i * G;
+            ra[i] = (v < nvec && has0) ? ldg16(x + p * C + v * kVec) : make_uint4(0, 0, 0, 0);
+            rb[i] = (v < nvec && has1) ? ldg16(x + p1 * C + v * kVec) : make_uint4(0, 0, 0, 0);
+        }
+        float sa[kOutMax] = {0.f, 0.f, 0.f}, sb[kOutMax] = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            float fa[kVec], fb[kVec];
+            unpack16<T>(ra[i], fa);
+            unpack16<T>(rb[i], fb);
+#pragma unroll
+            for (int o = 0; o < kOutMax; ++o)
+#pragma unroll
+                for (int k = 0; k < kVec; ++k) {
+                    sa[o] = fmaf(fa[k], wv[i][o][k], sa[o]);
+                    sb[o] = fmaf(fb[k], wv[i][o][k], sb[o]);
+                }
+        }
+        for (int off = G >> 1; off > 0; off >>= 1) {
+#pragma unroll
+            for (int o = 0; o < kOutMax; ++o) {
+                sa[o] += __shfl_xor_sync(0xffffffffu, sa[o], off);
+                sb[o] += __shfl_xor_sync(0xffffffffu, sb[o], off);
+            }
+        }
+        if (gl == 0 && has0) {
+            out[p] = make_float4(sa[0] + b0, sa[1] + b1, sa[2] + b2, 0.f);
+            if (has1) out[p1] = make_float4(sb[0] + b0, sb[1] + b1, sb[2] + b2, 0.f);
+        }
+    }
+}
+
+// Any width: one warp per pixel, weights re-read through L1 (used only when the register-resident variant does
+// not fit, i.e. C > 9 * 32 vectors: fp32 activations wider than 1152 channels).
+template <typename T>
+__global__ void __launch_bounds__(256)
+out_conv_wide_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const float* __restrict__ bias, float4* __restrict__ out,
+                     long long npix, int C, int OUT) {
+    constexpr int kVec = Elem<T>::kVec;
+    const int lane = threadIdx.x & 31;
+    const int nvec = C / kVec;
+    const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; p < npix; p += warps_total) {
+        float s[kOutMax] = {0.f, 0.f, 0.f};
+        for (int v = lane; v < nvec; v += 32) {
+            float f[kVec];
+            unpack16<T>(ldg16(x + p * C + v * kVec), f);
+#pragma unroll
+            for (int o = 0; o < kOutMax; ++o) {
+                if (o < OUT) {
+#pragma unroll
+                    for (int k = 0; k < kVec; ++k) s[o] = fmaf(f[k], __ldg(wgt + (long long)o * C + v * kVec + k), s[o]);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < kOutMax; ++o) s[o] = warp_sum(s[o]);
+        if (lane == 0)
+            out[p] = make_float4(s[0] + __ldg(bias), OUT > 1 ? s[1] + __ldg(bias + 1) : 0.f, OUT > 2 ? s[2] + __ldg(bias + 2) : 0.f, 0.f);
+    }
+}
+
+template <typename T>
+static int launch_out_conv(const void* x, const float* w, const float* b, float* out, long long npix, int C, int OUT, cudaStream_t st) {
+    constexpr int kVec = Elem<T>::kVec;
+    const int nvec = C / kVec;
+    int G = 1, gshift = 0;
+    while (G < 32 && G < nvec) { G <<= 1; ++gshift; }
+    const int nv = cdiv(nvec, G);
+    const long long groups_wanted = (npix + 1) / 2;
+    const int groups_per_block = 256 / G;
+    long long blocks = (groups_wanted + groups_per_block - 1) / groups_per_block;
+    const long long cap = (long long)sm_count() * 8;                   // grid-stride beyond 8 resident blocks per SM
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+#define ROMA_OUT_CONV(NVC) out_conv_kernel<T, NVC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, w, b, (float4*)out, npix, C, OUT, G, gshift)
+    if (nv <= 1) ROMA_OUT_CONV(1);
+    else if (nv <= 2) ROMA_OUT_CONV(2);
+    else if (nv <= 3) ROMA_OUT_CONV(3);
+    else if (nv <= 5) ROMA_OUT_CONV(5);
+    else if (nv <= 9) ROMA_OUT_CONV(9);
+    else {
+        long long wb = (npix + 7) / 8;
+        if (wb > cap) wb = cap;
+        out_conv_wide_kernel<T><<<(unsigned)wb, 256, 0, st>>>((const T*)x, w, b, (float4*)out, npix, C, OUT);
+    }
+#undef ROMA_OUT_CONV
+    return 0;
+}
+
+}  // namespace roma
+
+extern "C" int roma_refiner_out_conv(const void* x, const float* weight, const float* bias, float* out,
+                                     long long npix, int C, int OUT, int dtype, void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(x && weight && bias && out, ROMA_ERR_BAD_ARG, "roma_refiner_out_conv: null pointer");
+    ROMA_REQUIRE(npix > 0 && C > 0 && OUT >= 1 && OUT <= kOutMax, ROMA_ERR_BAD_ARG, "roma_refiner_out_conv: bad sizes (OUT must be 1..3)");
+    const int kvec = dtype == ROMA_F32 ? 4 : 8;
+    ROMA_REQUIRE(C % kvec == 0, ROMA_ERR_UNSUPPORTED, "roma_refiner_out_conv: C = %d must be a multiple of %d (pad it)", C, kvec);
+    ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0, ROMA_ERR_ALIGNMENT,
+                 "roma_refiner_out_conv: x and out must be 16-byte aligned");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    int rc;
+    switch (dtype) {
+        case ROMA_F32:  rc = launch_out_conv<float>(x, weight, bias, out, npix, C, OUT, st); break;
+        case ROMA_F16:  rc = launch_out_conv<__half>(x, weight, bias, out, npix, C, OUT, st); break;
+        case ROMA_BF16: rc = launch_out_conv<__nv_bfloat16>(x, weight, bias, out, npix, C, OUT, st); break;
+        default: return fail(ROMA_ERR_BAD_ARG, "roma_refiner_out_conv: unknown dtype %d", dtype);
+    }
+    if (rc) return rc;
+    return check_launch("roma_refiner_out_conv");
+}

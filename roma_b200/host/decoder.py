@@ -80,8 +80,8 @@ class ConvRefiner(nn.Module):
                 w_pw[:C, :C] = conv2.weight.float().view(C, C)
                 b_pw[:C] = conv2.bias.float()
                 blocks.append((w_dw.contiguous(), b_dw, w_pw.to(dtype).contiguous(), b_pw.to(dtype)))
-            w_out = torch.zeros(self.out_conv.out_channels, Cp, 1, 1, device=device)
-            w_out[:, :C] = self.out_conv.weight.float()
+            w_out = torch.zeros(self.out_conv.out_channels, Cp, device=device)
+            w_out[:, :C] = self.out_conv.weight.float().view(-1, C)
             b_out = self.out_conv.bias.float().clone()
         self._prep = (Cp, blocks, w_out, b_out)
         self._prep_key = key
@@ -94,7 +94,7 @@ class ConvRefiner(nn.Module):
         for w_dw, b_dw, w_pw, b_pw in blocks:
             d = ops.dwconv5x5_bias_act(d, w_dw, b_dw, relu=True)                      # (f-2): dw conv + folded BN + ReLU
             d = F.linear(d.permute(0, 2, 3, 1), w_pw, b_pw).permute(0, 3, 1, 2)       # NHWC GEMM, bias in the epilogue
-        return F.conv2d(d.float(), w_out, b_out)                                      # matcher.py:141 (fp32)
+        return ops.refiner_out_conv(d, w_out, b_out)                                  # matcher.py:141 (fp32 math)
 
     def delta(self, x, y, flow, scale_factor: float = 1) -> torch.Tensor:
         """The (B,3,h,w) out_conv tensor (dx, dy, dcertainty) consumed by the fused update kernel."""
@@ -171,10 +171,35 @@ class Decoder(nn.Module):
         self.scales = list(scales)
         self.refine_init = 4
         self.amp_dtype = amp_dtype
+        self._proj_prep = {}
 
-    def forward(self, f1: Dict[int, torch.Tensor], f2: Dict[int, torch.Tensor], gt_warp=None, gt_prob=None,
+    def _project(self, scale: str, f: torch.Tensor) -> torch.Tensor:
+        """proj[scale] = Conv2d(1x1) + BatchNorm2d (roma_models.py:131-142).  At inference the BatchNorm is an affine
+        map: it is folded into the convolution once and the result runs as ONE channels-last GEMM with the bias in
+        its epilogue (instead of cudnn conv + bias add + batch_norm)."""
+        conv, bn = self.proj[scale]
+        if self.training:
+            return self.proj[scale](f)
+        dtype = self.amp_dtype if f.is_cuda else torch.float32
+        key = (f.device, dtype, conv.weight._version, bn.weight._version, bn.running_mean._version, bn.running_var._version,
+               conv.weight.data_ptr())
+        prep = self._proj_prep.get(scale)
+        if prep is None or prep[0] != key:
+            with torch.no_grad():
+                g = bn.weight.float() / torch.sqrt(bn.running_var.float() + bn.eps)
+                wgt = (conv.weight.float().view(conv.out_channels, conv.in_channels) * g[:, None]).to(dtype).contiguous()
+                b0 = conv.bias.float() if conv.bias is not None else 0.0
+                bias = ((b0 - bn.running_mean.float()) * g + bn.bias.float()).to(dtype).contiguous()
+            prep = (key, wgt, bias)
+            self._proj_prep[scale] = prep
+        _, wgt, bias = prep
+        return F.linear(f.permute(0, 2, 3, 1).to(dtype), wgt, bias).permute(0, 3, 1, 2)
+
+    def forward(self, f1: Dict[int, torch.Tensor], f2: Optional[Dict[int, torch.Tensor]], gt_warp=None, gt_prob=None,
                 upsample: bool = False, flow: Optional[torch.Tensor] = None,
-                certainty: Optional[torch.Tensor] = None, scale_factor: float = 1):
+                certainty: Optional[torch.Tensor] = None, scale_factor: float = 1, swapped: bool = False):
+        """`swapped=True` (symmetric matching, matcher.py:455-466): the support pyramid is f1 with the two halves of
+        the batch exchanged; f2 may then be None and every projection is evaluated once instead of twice."""
         coarse_scales = self.embedding_decoder.scales()
         all_scales = self.scales if not upsample else ["8", "4", "2", "1"]
         sizes = {s: f1[s].shape[-2:] for s in f1}
@@ -188,12 +213,16 @@ class Decoder(nn.Module):
             flow, certainty = None, None
         for new_scale in all_scales:
             ins = int(new_scale)
-            f1_s, f2_s = f1[ins], f2[ins]
+            f1_s = f1[ins]
+            f2_s = None if swapped else f2[ins]
             if new_scale in self.proj:
-                with _autocast(f1_s.device, self.amp_dtype):
-                    if self.amp_dtype == torch.float32:
-                        f1_s, f2_s = f1_s.float(), f2_s.float()
-                    f1_s, f2_s = self.proj[new_scale](f1_s), self.proj[new_scale](f2_s)
+                f1_s = self._project(new_scale, f1_s)
+                f2_s = None if swapped else self._project(new_scale, f2_s)
+            if swapped:
+                a, b = f1_s.chunk(2)
+                f2_s = torch.cat((b, a), dim=0)
+                if f1_s.dim() == 4 and f1_s.is_contiguous(memory_format=torch.channels_last):
+                    f2_s = f2_s.contiguous(memory_format=torch.channels_last)
             if ins in coarse_scales:
                 gp_posterior = self.gps[new_scale](f1_s, f2_s)                                  # K1
                 cls, certainty, _ = self.embedding_decoder(gp_posterior, f1_s, None, new_scale)

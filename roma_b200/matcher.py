@@ -85,8 +85,10 @@ class RegressionMatcher(nn.Module):
 
     def forward_symmetric(self, batch, batched: bool = True, upsample: bool = False, scale_factor: float = 1):
         pyr = self.extract_backbone_features(batch, upsample=upsample)
-        f_s = {s: torch.cat((f.chunk(2)[1], f.chunk(2)[0]), dim=0) for s, f in pyr.items()}
-        return self.decoder(pyr, f_s, upsample=upsample, **(batch.get("corresps") or {}), scale_factor=scale_factor)
+        # support pyramid = query pyramid with the batch halves exchanged (matcher.py:459-463): the decoder swaps
+        # after its projections instead of being handed a second, copied pyramid
+        return self.decoder(pyr, None, upsample=upsample, **(batch.get("corresps") or {}), scale_factor=scale_factor,
+                            swapped=True)
 
     # ------------------------------------------------------------------------------------------ match
     @torch.inference_mode()

@@ -391,6 +391,27 @@ def dwconv5x5_bias_act(x: torch.Tensor, weight_taps: torch.Tensor, bias: torch.T
     return out
 
 
+def refiner_out_conv(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    """ConvRefiner.out_conv in fp32 from the channels-last activation (matcher.py:141), no fp32 copy of x.
+
+    x (B,C,h,w) channels-last, any of fp32/fp16/bf16; weight fp32 (OUT<=3, C); bias fp32 (OUT).
+    Returns a (B,OUT,h,w) fp32 view over (B,h,w,4) interleaved storage."""
+    dev = _cuda(x, weight, bias)
+    if x.dtype not in _DT:
+        raise ValueError(f"unsupported dtype {x.dtype}")
+    B, Cc, h, w = x.shape
+    OUT = weight.shape[0]
+    x = _nhwc(x)
+    weight = weight.reshape(OUT, Cc).float().contiguous()
+    bias = bias.float().contiguous()
+    out = torch.empty((B, h, w, 4), device=dev, dtype=torch.float32)
+    lib = _lib.load()
+    _run("roma_refiner_out_conv", dict(B=B, C=Cc, h=h, w=w, esize=x.element_size()),
+         lambda: lib.roma_refiner_out_conv(_ptr(x), _ptr(weight), _ptr(bias), _ptr(out), B * h * w, Cc, OUT,
+                                           _DT[x.dtype], _stream(dev)))
+    return out.permute(0, 3, 1, 2)[:, :OUT]
+
+
 # --------------------------------------------------------------------------------------------------
 # (f-1) cls_to_flow_refine, KT tiny
 # --------------------------------------------------------------------------------------------------

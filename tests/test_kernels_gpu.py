@@ -343,3 +343,20 @@ def _dwconv_case(ops, cuda, dtype, tol, B, C, h, w):
     assert err(got, want) < tol * max(1.0, want.abs().max().item())
     lin = ops.dwconv5x5_bias_act(x.to(cuda), taps.to(cuda), bias.to(cuda), relu=False)
     assert err(lin, torch.nn.functional.conv2d(x.float(), wt, bias, padding=2, groups=C)) < tol * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 2e-5), (torch.float16, 2e-5)])
+@pytest.mark.parametrize("B,C,h,w", [(2, 24, 17, 23), (1, 144, 9, 8), (2, 576, 5, 13), (1, 1144, 11, 7), (1, 8, 3, 5), (1, 64, 1, 1), (1, 1384, 6, 5),
+                                     (1, 2560, 3, 3)])
+def test_refiner_out_conv(ops, cuda, dtype, tol, B, C, h, w):
+    """out_conv (C -> 3) in fp32 from the stored activation vs F.conv2d on the up-converted tensor (matcher.py:141)."""
+    g = torch.Generator().manual_seed(23)
+    x = torch.randn(B, C, h, w, generator=g).to(dtype)
+    wt = torch.randn(3, C, generator=g) / C ** 0.5
+    bias = torch.randn(3, generator=g)
+    want = torch.nn.functional.conv2d(x.double(), wt.double().view(3, C, 1, 1), bias.double()).float()
+    got = ops.refiner_out_conv(x.to(cuda).contiguous(memory_format=torch.channels_last), wt.to(cuda), bias.to(cuda))
+    assert got.shape == want.shape and got.dtype == torch.float32
+    assert err(got, want) < tol * max(1.0, want.abs().max().item())
+    one = ops.refiner_out_conv(x.to(cuda), wt[:1].to(cuda), bias[:1].to(cuda))
+    assert err(one, want[:, :1]) < tol * max(1.0, want.abs().max().item())
