@@ -89,6 +89,10 @@ def alg_work(name: str, d: dict):
         return "hbm", 4 * n * (3 + 4 + 1 + (1 if d["logits"] else 0))
     if name == "roma_cls_to_flow_refine":
         return "hbm", d["B"] * d["H"] * d["W"] * (d["C"] * d["esize"] + 8)
+    if name == "roma_dwconv5x5_bias_act":                                   # one read + one write of the activation
+        return "hbm", 2 * d["B"] * d["h"] * d["w"] * d["C"] * d["esize"]
+    if name == "roma_refiner_out_conv":
+        return "hbm", d["B"] * d["h"] * d["w"] * (d["C"] * d["esize"] + 16)
     if name == "roma_kde":
         return "sfu", float(d["N"]) * (d["N"] // d["down"])
     return "hbm", 0
@@ -331,8 +335,15 @@ def main():
     top = next((r for r in rows if r["bound"] in ("hbm", "tensor") and r.get("alg")), None)
     roofline = None
     if top:
+        # DRAM bytes per launch of the same kernel and shape from the committed `ncu --set full` capture
+        traffic = None
+        try:
+            tj = json.loads((ROOT / "profiles" / "traffic.json").read_text())
+            traffic = tj.get(top["kernel"] + " " + json.dumps(top["dims"], sort_keys=True))
+        except Exception:
+            traffic = None
         roofline = {"kernel": top["kernel"], "dims": top["dims"], "bound": top["bound"], "achieved": top["achieved"],
-                    "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": None,
+                    "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": traffic,
                     "peak_source": pk["_source"] + (" sustained" if top["bound"] == "tensor" else ""),
                     "avg_launch_ms": top["avg_ms"], "share_of_step": round(top["ms_per_step"] / (ms_dev / args.steps), 4)}
     line = {

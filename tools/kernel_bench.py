@@ -91,7 +91,7 @@ def main():
             alg = B * h * w * (es * C + es * C + 8 + es * (2 * C + E + K))
             for mode in ("coherent", "incoherent"):
                 fl = flows(B, h, w, dev, mode, g)
-                ms = timeit(lambda: ops.refiner_inputs(x, y, fl, dw, db, 1.9, r or None), args.iters, flush)
+                ms = timeit(lambda: ops.refiner_inputs(x, y, fl, dw, db, 1.9, r or None, pad_to=8), args.iters, flush)
                 gbs = alg / ms / 1e6
                 emit(kernel="refiner_gather", scale=name, C=C, r=r, hw=[h, w], batch=B, dtype=args.dtype, flow=mode,
                      ms=round(ms, 4), alg_MB=round(alg / 1e6, 2), GBps=round(gbs, 1), frac_hbm=round(gbs / PEAKS["hbm_gbs"], 4))
