@@ -232,6 +232,15 @@ int roma_refiner_out_conv(const void* x, const float* weight, const float* bias,
 int roma_dwconv_set_path(int path);
 
 /* ---------------------------------------------------------------------------------------
+ * Encoder: 2x2 / stride-2 max pooling, channels-last (floor semantics: odd trailing row / column dropped).
+ *
+ * Replaces (reference): the nn.MaxPool2d(2, 2) layers of vgg19_bn.features walked by
+ *   romatch/models/encoders.py:57-66 (VGG19.forward).
+ * x : (B, h, w, C), out : (B, h/2, w/2, C), dtype `dtype`, C a multiple of 8 (4 for fp32), 16-byte aligned.
+ */
+int roma_maxpool2x2_nhwc(const void* x, void* out, int B, int h, int w, int C, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------
  * KT  Tiny-RoMa fused correlation volume + approximate soft-argmax position embedding.
  *
  * Replaces (reference): romatch/models/tiny.py:241-254 (corr_volume) and :178-199 (pos_embed,

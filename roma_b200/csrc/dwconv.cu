@@ -34,6 +34,7 @@ template <> struct Pair<float> {
     __device__ static __forceinline__ Raw load(const float* p) { return *reinterpret_cast<const float2*>(p); }
     __device__ static __forceinline__ float2 unpack(Raw r) { return r; }
     __device__ static __forceinline__ void store(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+    __device__ static __forceinline__ void store_relu(float* p, float a, float b) { store(p, fmaxf(a, 0.f), fmaxf(b, 0.f)); }
 };
 template <> struct Pair<__half> {
     using Raw = uint32_t;
@@ -41,6 +42,11 @@ template <> struct Pair<__half> {
     __device__ static __forceinline__ Raw load(const __half* p) { return *reinterpret_cast<const uint32_t*>(p); }
     __device__ static __forceinline__ float2 unpack(Raw r) { return __half22float2(*reinterpret_cast<const __half2*>(&r)); }
     __device__ static __forceinline__ void store(__half* p, float a, float b) { *reinterpret_cast<__half2*>(p) = __floats2half2_rn(a, b); }
+    __device__ static __forceinline__ void store_relu(__half* p, float a, float b) {        // ReLU rides the conversion
+        uint32_t r;
+        asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+        *reinterpret_cast<uint32_t*>(p) = r;
+    }
 };
 template <> struct Pair<__nv_bfloat16> {
     using Raw = uint32_t;
@@ -48,6 +54,11 @@ template <> struct Pair<__nv_bfloat16> {
     __device__ static __forceinline__ Raw load(const __nv_bfloat16* p) { return *reinterpret_cast<const uint32_t*>(p); }
     __device__ static __forceinline__ float2 unpack(Raw r) { return make_float2(__uint_as_float(r << 16), __uint_as_float(r & 0xffff0000u)); }
     __device__ static __forceinline__ void store(__nv_bfloat16* p, float a, float b) { *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b); }
+    __device__ static __forceinline__ void store_relu(__nv_bfloat16* p, float a, float b) {
+        uint32_t r;
+        asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+        *reinterpret_cast<uint32_t*>(p) = r;
+    }
 };
 
 constexpr int kDwRY = 16;     // output rows per thread strip; kDwRY + 4 input rows = a whole number of 5-row chunks
@@ -62,9 +73,20 @@ static_assert((kDwRY + 4) % 5 == 0 && kDwChunks >= 2, "strip height + halo must 
 // Input row r = r0 + I feeds the five output rows r-2..r+2 (tap row dy = r - o + 2); the accumulators of those
 // rows live in a ring of 5 whose slot indices are compile-time constants inside a 5-row chunk.  FIRST / LAST
 // prune the contributions to rows outside the strip.  Afterwards output row r - 2 is complete and is stored.
+// Output addressing: `orow` points at (row o, column x0) of the thread's channel pair and advances by one image
+// row after every completed row; `full` (all four columns inside the image) removes the per-column predicates.
+template <typename T>
+struct DwOut {
+    T* orow;
+    long long row_stride;      // elements between image rows: w * Cp
+    int col_stride;            // elements between columns: Cp
+    unsigned storemask;
+    bool full, relu;
+};
+
 template <typename T, bool FIRST, bool LAST, int I>
-__device__ __forceinline__ void dw_row(const float2 (&v)[kDwNV], T* __restrict__ ob, int r, int x0, unsigned storemask, int h, int w,
-                                       int Cp, int relu, const float2 (&wv)[25], float2 bv, float2 (&acc)[5][kDwTW]) {
+__device__ __forceinline__ void dw_row(const float2 (&v)[kDwNV], DwOut<T>& out, int r, int h, const float2 (&wv)[25], float2 bv,
+                                       float2 (&acc)[5][kDwTW]) {
     using P = Pair<T>;
 #pragma unroll
     for (int d = 4; d >= 0; --d) {
@@ -81,18 +103,24 @@ __device__ __forceinline__ void dw_row(const float2 (&v)[kDwNV], T* __restrict__
             for (int ox = 0; ox < kDwTW; ++ox) acc[slot][ox] = __ffma2_rn(v[ox + dx], wv[dy * 5 + dx], acc[slot][ox]);
     }
     if (!(FIRST && I < 4)) {
-        const int o = r - 2, slot = (I + 1) % 5;
-        if (o < h) {
-            T* op = ob + ((long long)o * w + x0) * Cp;
+        const int slot = (I + 1) % 5;
+        if (r - 2 < h) {
+            T* op = out.orow;
+            if (out.full && out.relu) {
 #pragma unroll
-            for (int ox = 0; ox < kDwTW; ++ox) {
-                if ((storemask >> ox) & 1u) {
-                    float a = acc[slot][ox].x, b = acc[slot][ox].y;
-                    if (relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
-                    P::store(op + ox * Cp, a, b);
+                for (int ox = 0; ox < kDwTW; ++ox) P::store_relu(op + ox * out.col_stride, acc[slot][ox].x, acc[slot][ox].y);
+            } else {
+#pragma unroll
+                for (int ox = 0; ox < kDwTW; ++ox) {
+                    if ((out.storemask >> ox) & 1u) {
+                        float a = acc[slot][ox].x, b = acc[slot][ox].y;
+                        if (out.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+                        P::store(op + ox * out.col_stride, a, b);
+                    }
                 }
             }
         }
+        out.orow += out.row_stride;
     }
 }
 
@@ -110,9 +138,8 @@ struct DwTmaParams {
 };
 
 template <typename T, bool FIRST, bool LAST>
-__device__ __forceinline__ void dw_chunk_smem(const unsigned char* __restrict__ rows, int row_bytes, int pix_bytes, T* __restrict__ ob,
-                                              int r0, int x0, unsigned storemask, int h, int w, int Cp, int relu,
-                                              const float2 (&wv)[25], float2 bv, float2 (&acc)[5][kDwTW]) {
+__device__ __forceinline__ void dw_chunk_smem(const unsigned char* __restrict__ rows, int row_bytes, int pix_bytes, DwOut<T>& out,
+                                              int r0, int h, const float2 (&wv)[25], float2 bv, float2 (&acc)[5][kDwTW]) {
     using P = Pair<T>;
     using Raw = typename P::Raw;
     auto step = [&](auto Ic) {
@@ -121,7 +148,7 @@ __device__ __forceinline__ void dw_chunk_smem(const unsigned char* __restrict__ 
         float2 v[kDwNV];
 #pragma unroll
         for (int j = 0; j < kDwNV; ++j) v[j] = P::unpack(*reinterpret_cast<const Raw*>(rp + j * pix_bytes));
-        dw_row<T, FIRST, LAST, I>(v, ob, r0 + I, x0, storemask, h, w, Cp, relu, wv, bv, acc);
+        dw_row<T, FIRST, LAST, I>(v, out, r0 + I, h, wv, bv, acc);
     };
     step(std::integral_constant<int, 0>{}); step(std::integral_constant<int, 1>{}); step(std::integral_constant<int, 2>{});
     step(std::integral_constant<int, 3>{}); step(std::integral_constant<int, 4>{});
@@ -175,10 +202,15 @@ dwconv5_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restr
     const bool active = run_l < p.rpb && pair < npairs && run < runs;   // thread 0 (the issuer) is always active
     if (!active) return;
     const int c = pair * 2, x0 = run * kDwTW;
-    T* ob = out + (long long)b * h * w * Cp + c;
-    unsigned storemask = 0;
+    DwOut<T> o;
+    o.row_stride = (long long)w * Cp;
+    o.col_stride = Cp;
+    o.orow = out + (long long)b * h * o.row_stride + ((long long)y0 * w + x0) * Cp + c;
+    o.storemask = 0;
 #pragma unroll
-    for (int ox = 0; ox < kDwTW; ++ox) storemask |= (x0 + ox < w) ? (1u << ox) : 0u;
+    for (int ox = 0; ox < kDwTW; ++ox) o.storemask |= (x0 + ox < w) ? (1u << ox) : 0u;
+    o.full = o.storemask == (1u << kDwTW) - 1u;
+    o.relu = pr.relu != 0;
 
     float2 wv[25];
 #pragma unroll
@@ -188,18 +220,17 @@ dwconv5_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restr
     const unsigned char* tb = tile + run_l * kDwTW * p.pix_bytes + pair_l * (int)sizeof(typename Pair<T>::Raw);
     float2 acc[5][kDwTW];
     tma::mbar_wait(&bars[0], 0);
-    dw_chunk_smem<T, true, false>(tb, p.row_bytes, p.pix_bytes, ob, y0 - 2, x0, storemask, h, w, Cp, pr.relu, wv, bv, acc);
+    dw_chunk_smem<T, true, false>(tb, p.row_bytes, p.pix_bytes, o, y0 - 2, h, wv, bv, acc);
 #pragma unroll 1
     for (int ch = 1; ch < kDwChunks - 1; ++ch) {
         if (ch >= nch) return;
         tma::mbar_wait(&bars[ch], 0);
-        dw_chunk_smem<T, false, false>(tb + ch * p.chunk_stride, p.row_bytes, p.pix_bytes, ob, y0 - 2 + 5 * ch, x0, storemask,
-                                       h, w, Cp, pr.relu, wv, bv, acc);
+        dw_chunk_smem<T, false, false>(tb + ch * p.chunk_stride, p.row_bytes, p.pix_bytes, o, y0 - 2 + 5 * ch, h, wv, bv, acc);
     }
     if (nch < kDwChunks) return;
     tma::mbar_wait(&bars[kDwChunks - 1], 0);
-    dw_chunk_smem<T, false, true>(tb + (kDwChunks - 1) * p.chunk_stride, p.row_bytes, p.pix_bytes, ob, y0 - 2 + 5 * (kDwChunks - 1),
-                                  x0, storemask, h, w, Cp, pr.relu, wv, bv, acc);
+    dw_chunk_smem<T, false, true>(tb + (kDwChunks - 1) * p.chunk_stride, p.row_bytes, p.pix_bytes, o, y0 - 2 + 5 * (kDwChunks - 1), h,
+                                  wv, bv, acc);
 }
 
 template <typename T>
@@ -273,8 +304,8 @@ __device__ __forceinline__ void dw_issue_row(DwStage<T>& st, int stage, const T*
 // Row r0 + I is read from staging slot I (it was requested kDwAhead steps earlier); row r0 + I + kDwAhead is
 // requested into slot (I + kDwAhead) % 5, whose previous content (row r0 + I - 1) has already been consumed.
 template <typename T, bool FIRST, bool LAST>
-__device__ __forceinline__ void dw_chunk(DwStage<T>& st, const T* __restrict__ xb, T* __restrict__ ob, int r0, int r_end, int x0,
-                                         unsigned colmask, int h, int w, int Cp, int relu, const float2 (&wv)[25], float2 bv,
+__device__ __forceinline__ void dw_chunk(DwStage<T>& st, const T* __restrict__ xb, DwOut<T>& out, int r0, int r_end, int x0,
+                                         unsigned colmask, int h, int w, int Cp, const float2 (&wv)[25], float2 bv,
                                          float2 (&acc)[5][kDwTW]) {
     using P = Pair<T>;
     auto step = [&](auto Ic) {
@@ -286,7 +317,7 @@ __device__ __forceinline__ void dw_chunk(DwStage<T>& st, const T* __restrict__ x
         float2 v[kDwNV];
 #pragma unroll
         for (int j = 0; j < kDwNV; ++j) v[j] = P::unpack(st.v[I][j][threadIdx.x]);
-        dw_row<T, FIRST, LAST, I>(v, ob, r, x0, colmask >> 2, h, w, Cp, relu, wv, bv, acc);
+        dw_row<T, FIRST, LAST, I>(v, out, r, h, wv, bv, acc);
     };
     step(std::integral_constant<int, 0>{}); step(std::integral_constant<int, 1>{}); step(std::integral_constant<int, 2>{});
     step(std::integral_constant<int, 3>{}); step(std::integral_constant<int, 4>{});
@@ -309,10 +340,16 @@ dwconv5_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const flo
     const int c = pair * 2, x0 = run * kDwTW, y0 = blockIdx.y * kDwRY;
 
     const T* xb = x + (long long)b * h * w * Cp + c;
-    T* ob = out + (long long)b * h * w * Cp + c;
     unsigned colmask = 0;                              // bit j: column x0 - 2 + j lies inside the image
 #pragma unroll
     for (int j = 0; j < kDwNV; ++j) colmask |= (x0 - 2 + j >= 0 && x0 - 2 + j < w) ? (1u << j) : 0u;
+    DwOut<T> o;
+    o.row_stride = (long long)w * Cp;
+    o.col_stride = Cp;
+    o.orow = out + (long long)b * h * o.row_stride + ((long long)y0 * w + x0) * Cp + c;
+    o.storemask = (colmask >> 2) & ((1u << kDwTW) - 1u);
+    o.full = o.storemask == (1u << kDwTW) - 1u;
+    o.relu = relu != 0;
 
     // rows past the image contribute nothing and no output row >= h exists: stop after input row h + 1
     const int r_begin = y0 - 2;
@@ -329,14 +366,14 @@ dwconv5_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const flo
     const float2 bv = __ldg(reinterpret_cast<const float2*>(bias + c));
 
     float2 acc[5][kDwTW];
-    dw_chunk<T, true, false>(st, xb, ob, r_begin, r_end, x0, colmask, h, w, Cp, relu, wv, bv, acc);
+    dw_chunk<T, true, false>(st, xb, o, r_begin, r_end, x0, colmask, h, w, Cp, wv, bv, acc);
 #pragma unroll 1
     for (int ch = 1; ch < kDwChunks - 1; ++ch) {
         if (r_begin + 5 * ch - 2 >= h) break;          // every remaining output row is below the image
-        dw_chunk<T, false, false>(st, xb, ob, r_begin + 5 * ch, r_end, x0, colmask, h, w, Cp, relu, wv, bv, acc);
+        dw_chunk<T, false, false>(st, xb, o, r_begin + 5 * ch, r_end, x0, colmask, h, w, Cp, wv, bv, acc);
     }
     if (r_begin + 5 * (kDwChunks - 1) - 2 < h)
-        dw_chunk<T, false, true>(st, xb, ob, r_begin + 5 * (kDwChunks - 1), r_end, x0, colmask, h, w, Cp, relu, wv, bv, acc);
+        dw_chunk<T, false, true>(st, xb, o, r_begin + 5 * (kDwChunks - 1), r_end, x0, colmask, h, w, Cp, wv, bv, acc);
     cp_async_wait<0>();
 }
 

@@ -3,17 +3,26 @@
 //
 //   mu = K_xy (K_yy + sigma I)^-1 f                                  (matcher.py:249-264)
 //
-// Workspace layout per batch element (Mp = M rounded up to 128, all fp32, K-major for the UMMA operands):
-//   A   (Mp x Mp)   lower triangle: K_yy + sigma I -> L (in place);  upper triangle: L^T mirror
-//   Kxy (Nx x Mp)   cross kernel
-//   Ft  (D  x Mp)   RHS TRANSPOSED: f^T -> Z^T = (L^-1 f)^T -> alpha^T = (L^-T L^-1 f)^T
-//   Ld  (nb x 2 x 128 x 128)   per diagonal block: L_kk^-1 and its transpose
-// Keeping the RHS transposed makes every product of the solve an "A * B^T with both operands K-major" GEMM:
-//   panel      L_ik   = A_ik  * (L_kk^-1)^T          Z^T_k  = F^T_k * (L_kk^-1)^T
-//   update     A_ij  -= L_ik  * L_jk^T  (i>=j>k)     F^T_j -= Z^T_k * L_jk^T  (j>k)
-//   backward   a^T_k  = Z^T_k * ((L_kk^-1)^T)^T      Z^T_j -= a^T_k * (L^T mirror rows j)^T  (j<k)
-//   posterior  mu     = Kxy   * (a^T)^T
-// Padding rows/cols (M..Mp) of A are the identity, of Ft zero, so they factor trivially and contribute 0.
+// With K_yy + sigma I = L L^T:   mu = K_xy L^-T L^-1 f = W^T Z,   W = L^-1 K_xy^T,   Z = L^-1 f
+// so ONE forward substitution applied to the stacked right-hand side [f | K_xy^T] is enough: no backward sweep,
+// no explicit inverse of K_yy.
+//
+// Workspace per batch element (Mp = Ny rounded up to 128; fp32, every matrix K-major for the UMMA operands):
+//   A  (Mp x Mp)        K_yy + sigma I (lower triangle, identity on the padding) -> L in place, block column
+//                        by block column
+//   R  ((D + Nx) x Mp)  the right-hand sides TRANSPOSED and stacked: rows 0..D-1 = f^T, rows D.. = K_xy;
+//                        overwritten by Z^T and W^T
+//   Ld (nb x 128 x 128) L_kk^-1 of every diagonal block
+//   xn, yn              inverse row norms of x and y (CosKernel)
+// Keeping the right-hand sides transposed makes every product an "A * B^T, both operands K-major" GEMM, which is
+// the only shape `tc::gemm_nt_kernel` implements.  Left-looking blocked Cholesky, block k of nb = Mp / 128:
+//   update  (k > 0)  A[k:, k]  -= L[k:, 0:k] * L[k, 0:k]^T        R[:, k] -= R[:, 0:k] * L[k, 0:k]^T     (one launch)
+//   diag             L_kk = chol(A_kk),  Ld_k = L_kk^-1            (fp32 SIMT, one CTA per batch element)
+//   panel            R[:, k] = R[:, k] * Ld_k^T                    L[k+1:, k] = A[k+1:, k] * Ld_k^T       (one launch)
+//   posterior        mu = R[D:, :] * R[0:D, :]^T = W^T Z           (Nx x D, token-major = channels-last)
+// Launches per call: 2 norms + 1 basis + 1 Gram (K_yy and K_xy as two problems of one launch) + nb diag +
+// (2 nb - 1) update/panel + 1 posterior; the Gram runs on bf16/fp16 operands as stored, the solve on split-bf16
+// planes of the fp32 workspace with the cross terms in a second TMEM accumulator (tc_gemm.cuh).
 #pragma once
 #include "tc_gemm.cuh"
 #include "gp_simt.cuh"

@@ -12,6 +12,8 @@ from typing import Dict, Optional
 
 import torch
 import torch.nn as nn
+
+from .. import ops
 import torchvision.models as tvm
 
 from .vit import DinoViT
@@ -69,7 +71,7 @@ class VGG19(nn.Module):
                 scale *= 2
                 if n == len(plan) - 1:
                     break
-                x = step[1](x)
+                x = ops.maxpool2x2(x) if x.shape[1] % 8 == 0 else step[1](x)
             else:
                 x = torch.cudnn_convolution_relu(x, step[1], step[2], (1, 1), step[3], (1, 1), 1)
         return feats

@@ -93,12 +93,15 @@ class RegressionMatcher(nn.Module):
     # ------------------------------------------------------------------------------------------ match
     @torch.inference_mode()
     def match(self, im_A_input, im_B_input, *args, batched: bool = False, device=None, return_logits: bool = False):
-        """matcher.py:593-730.  Paths / PIL images (one pair) or tensors (B,3,H,W) (uint8, or float in [0,1]
-        BEFORE ImageNet normalisation when `batched` tensors are float and `normalised=False`... see below).
+        """Dense warp and certainty for an image pair or a batch of pairs (matcher.py:593-730).
 
-        Tensor inputs: uint8 RGB or float32 already ImageNet-normalised (what the reference's batched mode
-        expects, matcher.py:639-645), any resolution; they are resized on the device (bicubic, antialiased)
-        to the coarse and upsample resolutions when they differ."""
+        Inputs: two paths, two PIL images (one pair), or two tensors (B,3,H,W) / (3,H,W).  Tensors are either
+        uint8 RGB, or float already ImageNet-normalised (what the reference's batched mode expects,
+        matcher.py:639-645); any resolution — they are resized on the device (bicubic, antialiased) to the coarse
+        and upsample resolutions where they differ.
+
+        Returns (warp, certainty): (H, 2W, 4) and (H, 2W) for one pair, with a leading batch dimension when
+        `batched=True`; W doubles only for symmetric models.  `return_logits=True` appends the certainty logits."""
         if device is None:
             device = torch.device("cuda")
         device = torch.device(device)

@@ -391,6 +391,20 @@ def dwconv5x5_bias_act(x: torch.Tensor, weight_taps: torch.Tensor, bias: torch.T
     return out
 
 
+def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
+    """nn.MaxPool2d(2, 2) on a channels-last (B,C,h,w) tensor (encoders.py:57-66); returns channels-last."""
+    dev = _cuda(x)
+    if x.dtype not in _DT:
+        raise ValueError(f"unsupported dtype {x.dtype}")
+    B, Cc, h, w = x.shape
+    x = _nhwc(x)
+    out = torch.empty((B, Cc, h // 2, w // 2), device=dev, dtype=x.dtype, memory_format=torch.channels_last)
+    lib = _lib.load()
+    _run("roma_maxpool2x2_nhwc", dict(B=B, C=Cc, h=h, w=w, esize=x.element_size()),
+         lambda: lib.roma_maxpool2x2_nhwc(_ptr(x), _ptr(out), B, h, w, Cc, _DT[x.dtype], _stream(dev)))
+    return out
+
+
 def refiner_out_conv(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
     """ConvRefiner.out_conv in fp32 from the channels-last activation (matcher.py:141), no fp32 copy of x.
 

@@ -360,3 +360,14 @@ def test_refiner_out_conv(ops, cuda, dtype, tol, B, C, h, w):
     assert err(got, want) < tol * max(1.0, want.abs().max().item())
     one = ops.refiner_out_conv(x.to(cuda), wt[:1].to(cuda), bias[:1].to(cuda))
     assert err(one, want[:, :1]) < tol * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("B,C,h,w", [(2, 64, 18, 22), (1, 128, 7, 9), (3, 8, 2, 2), (1, 512, 5, 4)])
+def test_maxpool2x2_bit_exact(ops, cuda, dtype, B, C, h, w):
+    """VGG19 stage pooling (encoders.py:57-66): bit-identical to F.max_pool2d(2, 2), odd row / column dropped."""
+    x = torch.randn(B, C, h, w, generator=torch.Generator().manual_seed(5)).to(dtype)
+    want = torch.nn.functional.max_pool2d(x.float(), 2, 2).to(dtype)
+    got = ops.maxpool2x2(x.to(cuda).contiguous(memory_format=torch.channels_last))
+    assert got.shape == want.shape and got.dtype == dtype
+    assert torch.equal(got.cpu(), want)

@@ -24,3 +24,20 @@ with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_sh
         m.sample(warp[i], cert[i])
     torch.cuda.synchronize()
 print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=90))
+
+if len(sys.argv) > 3 and sys.argv[3] == "shapes":
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof2:
+        warp, cert = m.match(A, Bm, batched=True, device=dev)
+        for i in range(B):
+            m.sample(warp[i], cert[i])
+        torch.cuda.synchronize()
+    rows = [e for e in prof2.key_averages(group_by_input_shape=True)
+            if e.key in ("aten::copy_", "aten::cat", "aten::add_", "aten::mul", "aten::add", "aten::sub", "aten::div", "aten::clone",
+                         "aten::contiguous", "aten::_to_copy", "aten::max_pool2d_with_indices", "aten::upsample_bicubic2d",
+                         "aten::_upsample_bicubic2d_aa", "aten::index", "aten::where", "aten::sigmoid", "aten::topk", "aten::sort",
+                         "aten::cumsum", "aten::exponential_", "aten::log", "aten::native_layer_norm", "aten::gelu", "aten::addmm",
+                         "aten::mm", "aten::bmm", "aten::cudnn_convolution", "aten::cudnn_convolution_relu")]
+    rows.sort(key=lambda e: -e.self_device_time_total)
+    print("\n== by input shape (self CUDA us, calls, shapes) ==")
+    for e in rows[:60]:
+        print(f"{e.key:34s} {e.self_device_time_total:10.0f} {e.count:4d} {str(e.input_shapes)[:150]}")
