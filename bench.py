@@ -91,6 +91,10 @@ def alg_work(name: str, d: dict):
         return "hbm", d["B"] * d["H"] * d["W"] * (d["C"] * d["esize"] + 8)
     if name == "roma_dwconv5x5_bias_act":                                   # one read + one write of the activation
         return "hbm", 2 * d["B"] * d["h"] * d["w"] * d["C"] * d["esize"]
+    if name == "roma_layernorm":
+        return "hbm", 2 * d["rows"] * d["D"] * d["esize"]
+    if name == "roma_pointwise_narrow":
+        return "hbm", d["B"] * d["h"] * d["w"] * (d["C"] + d["OUT"]) * d["esize"]
     if name == "roma_maxpool2x2_nhwc":
         return "hbm", d["B"] * d["h"] * d["w"] * d["C"] * d["esize"] * 5 // 4
     if name == "roma_refiner_out_conv":

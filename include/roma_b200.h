@@ -227,9 +227,31 @@ int roma_dwconv5x5_bias_act(const void* x, const float* weight, const float* bia
  */
 int roma_refiner_out_conv(const void* x, const float* weight, const float* bias, float* out,
                           long long npix, int C, int OUT, int dtype, void* stream);
+/* Narrow 1x1 convolution, OUT <= 16, output in the storage dtype: out[p, o] = bias[o] + sum_c weight[o, c] * x[p, c].
+ *
+ * Replaces (reference): the finest-scale feature projection proj["1"] = Conv2d(64, 9, 1) + BatchNorm2d,
+ *   romatch/models/model_zoo/roma_models.py:131-142 as applied at matcher.py:372-375 (eval-mode BatchNorm folded
+ *   into weight / bias by the caller).
+ * x : (npix, C) channels-last, dtype `dtype`, C a multiple of 8 (4 for fp32), 16-byte aligned;
+ * weight : fp32 (OUT, C); bias : fp32 (OUT); out : (npix, OUT) packed, dtype `dtype`.  fp32 accumulation.
+ */
+int roma_pointwise_narrow(const void* x, const float* weight, const float* bias, void* out,
+                          long long npix, int C, int OUT, int dtype, void* stream);
 /* Testing aid: 0 = automatic (TMA-tiled input when C * sizeof(dtype) is a multiple of 16 and x is 16-byte
  * aligned, per-thread cp.async staging otherwise), 1 = always the cp.async variant.  Results are identical. */
 int roma_dwconv_set_path(int path);
+
+/* ---------------------------------------------------------------------------------------
+ * Encoder: LayerNorm over the last dimension, out = (x - mean) / sqrt(var + eps) * gamma + beta (biased variance,
+ * fp32 statistics), one read and one write of the token matrix.
+ *
+ * Replaces (reference): nn.LayerNorm in romatch/models/transformer/layers/block.py:88-101 (norm1, norm2 of every
+ *   DINOv2 / embedding-decoder block) and dinov2.py:236 (final norm).
+ * x, out : (rows, D); gamma, beta : (D); all dtype `dtype`, D a multiple of 8 (4 for fp32) and <= 2048 (1024 for
+ * fp32), 16-byte aligned.  out may alias x.
+ */
+int roma_layernorm(const void* x, const void* gamma, const void* beta, void* out,
+                   long long rows, int D, float eps, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Encoder: 2x2 / stride-2 max pooling, channels-last (floor semantics: odd trailing row / column dropped).

@@ -17,6 +17,18 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 
+class RowNorm(nn.LayerNorm):
+    """nn.LayerNorm (same parameters / state_dict keys) that runs `roma_layernorm` on CUDA at inference."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        D = self.normalized_shape[0]
+        if (x.is_cuda and not self.training and x.dtype in (torch.float16, torch.bfloat16, torch.float32)
+                and D % 8 == 0 and D <= (1024 if x.dtype == torch.float32 else 2048)):
+            from .. import ops
+            return ops.layer_norm(x, self.weight, self.bias, self.eps)
+        return super().forward(x)
+
+
 class SelfAttention(nn.Module):
     def __init__(self, dim: int, num_heads: int, qkv_bias: bool, proj_bias: bool = True):
         super().__init__()
@@ -24,11 +36,15 @@ class SelfAttention(nn.Module):
         self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
         self.proj = nn.Linear(dim, dim, bias=proj_bias)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def attend(self, x: torch.Tensor) -> torch.Tensor:
+        """Attention output BEFORE the output projection, (B, N, C)."""
         B, N, C = x.shape
         q, k, v = self.qkv(x).view(B, N, 3, self.num_heads, C // self.num_heads).permute(2, 0, 3, 1, 4)
         o = F.scaled_dot_product_attention(q, k, v)          # softmax(q k^T / sqrt(d)) v
-        return self.proj(o.transpose(1, 2).reshape(B, N, C))
+        return o.transpose(1, 2).reshape(B, N, C)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.proj(self.attend(x))
 
 
 class FeedForward(nn.Module):
@@ -56,14 +72,33 @@ class Block(nn.Module):
     def __init__(self, dim: int, num_heads: int, mlp_ratio: float = 4.0, qkv_bias: bool = False,
                  init_values: Optional[float] = None, norm_eps: float = 1e-5):
         super().__init__()
-        self.norm1 = nn.LayerNorm(dim, eps=norm_eps)
+        self.norm1 = RowNorm(dim, eps=norm_eps)
         self.attn = SelfAttention(dim, num_heads, qkv_bias)
         self.ls1 = ChannelScale(dim, init_values) if init_values else nn.Identity()
-        self.norm2 = nn.LayerNorm(dim, eps=norm_eps)
+        self.norm2 = RowNorm(dim, eps=norm_eps)
         self.mlp = FeedForward(dim, int(dim * mlp_ratio))
         self.ls2 = ChannelScale(dim, init_values) if init_values else nn.Identity()
+        self._fold_key, self._fold = None, None
+
+    def _folded(self):
+        """LayerScale folded into the linear layer it follows (gamma * (W o + b) = (gamma W) o + gamma b): at
+        inference this removes two full-tensor multiplies per block.  Cached per parameter version."""
+        ps = (self.attn.proj.weight, self.attn.proj.bias, self.ls1.gamma, self.mlp.fc2.weight, self.mlp.fc2.bias, self.ls2.gamma)
+        key = tuple((p.data_ptr(), p._version, p.dtype) for p in ps)
+        if self._fold_key != key:
+            with torch.no_grad():
+                dt = ps[0].dtype
+                g1, g2 = self.ls1.gamma.float(), self.ls2.gamma.float()
+                self._fold = ((ps[0].float() * g1[:, None]).to(dt), (ps[1].float() * g1).to(dt),
+                              (ps[3].float() * g2[:, None]).to(dt), (ps[4].float() * g2).to(dt))
+            self._fold_key = key
+        return self._fold
 
     def forward(self, x):
+        if not self.training and x.is_cuda and isinstance(self.ls1, ChannelScale) and self.attn.proj.bias is not None:
+            w1, b1, w2, b2 = self._folded()
+            x = x + F.linear(self.attn.attend(self.norm1(x)), w1, b1)
+            return x + F.linear(F.gelu(self.mlp.fc1(self.norm2(x))), w2, b2)
         x = x + self.ls1(self.attn(self.norm1(x)))
         return x + self.ls2(self.mlp(self.norm2(x)))
 
@@ -90,7 +125,7 @@ class DinoViT(nn.Module):
         self.pos_embed = nn.Parameter(torch.zeros(1, n + 1, embed_dim))
         self.blocks = nn.ModuleList(Block(embed_dim, num_heads, 4.0, qkv_bias=True, init_values=init_values,
                                           norm_eps=1e-6) for _ in range(depth))
-        self.norm = nn.LayerNorm(embed_dim, eps=1e-6)
+        self.norm = RowNorm(embed_dim, eps=1e-6)
         self.mask_token = nn.Parameter(torch.zeros(1, embed_dim))
         if init:
             nn.init.normal_(self.pos_embed, std=0.02)

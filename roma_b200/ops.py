@@ -391,6 +391,41 @@ def dwconv5x5_bias_act(x: torch.Tensor, weight_taps: torch.Tensor, bias: torch.T
     return out
 
 
+def pointwise_narrow(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    """1x1 convolution to OUT <= 16 channels in the dtype of x (roma_models.py:131-142, proj["1"] with its BatchNorm
+    folded).  x (B,C,h,w) channels-last; weight fp32 (OUT,C); bias fp32 (OUT) -> (B,OUT,h,w) channels-last."""
+    dev = _cuda(x, weight, bias)
+    if x.dtype not in _DT:
+        raise ValueError(f"unsupported dtype {x.dtype}")
+    B, Cc, h, w = x.shape
+    OUT = weight.shape[0]
+    x = _nhwc(x)
+    weight = weight.reshape(OUT, Cc).float().contiguous()
+    bias = bias.float().contiguous()
+    out = torch.empty((B, h, w, OUT), device=dev, dtype=x.dtype)
+    lib = _lib.load()
+    _run("roma_pointwise_narrow", dict(B=B, C=Cc, OUT=OUT, h=h, w=w, esize=x.element_size()),
+         lambda: lib.roma_pointwise_narrow(_ptr(x), _ptr(weight), _ptr(bias), _ptr(out), B * h * w, Cc, OUT,
+                                           _DT[x.dtype], _stream(dev)))
+    return out.permute(0, 3, 1, 2)
+
+
+def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float) -> torch.Tensor:
+    """F.layer_norm(x, (D,), weight, bias, eps) over the last dimension (block.py:88-101, dinov2.py:236)."""
+    dev = _cuda(x, weight, bias)
+    if x.dtype not in _DT:
+        raise ValueError(f"unsupported dtype {x.dtype}")
+    D = x.shape[-1]
+    x = x.contiguous()
+    weight, bias = weight.to(x.dtype).contiguous(), bias.to(x.dtype).contiguous()
+    out = torch.empty_like(x)
+    rows = x.numel() // D
+    lib = _lib.load()
+    _run("roma_layernorm", dict(rows=rows, D=D, esize=x.element_size()),
+         lambda: lib.roma_layernorm(_ptr(x), _ptr(weight), _ptr(bias), _ptr(out), rows, D, float(eps), _DT[x.dtype], _stream(dev)))
+    return out
+
+
 def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
     """nn.MaxPool2d(2, 2) on a channels-last (B,C,h,w) tensor (encoders.py:57-66); returns channels-last."""
     dev = _cuda(x)

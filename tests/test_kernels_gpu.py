@@ -371,3 +371,34 @@ def test_maxpool2x2_bit_exact(ops, cuda, dtype, B, C, h, w):
     got = ops.maxpool2x2(x.to(cuda).contiguous(memory_format=torch.channels_last))
     assert got.shape == want.shape and got.dtype == dtype
     assert torch.equal(got.cpu(), want)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1e-2), (torch.float16, 2e-3)])
+@pytest.mark.parametrize("B,C,OUT,h,w", [(2, 64, 9, 17, 23), (1, 8, 1, 3, 5), (1, 128, 16, 4, 4), (3, 64, 9, 1, 1)])
+def test_pointwise_narrow(ops, cuda, dtype, tol, B, C, OUT, h, w):
+    """proj["1"] (Conv 64 -> 9 + folded BN) as a streaming kernel vs F.conv2d in fp64 on the stored inputs."""
+    g = torch.Generator().manual_seed(29)
+    x = torch.randn(B, C, h, w, generator=g).to(dtype)
+    wt = torch.randn(OUT, C, generator=g) / C ** 0.5
+    bias = torch.randn(OUT, generator=g)
+    want = torch.nn.functional.conv2d(x.double(), wt.double().view(OUT, C, 1, 1), bias.double()).float()
+    got = ops.pointwise_narrow(x.to(cuda).contiguous(memory_format=torch.channels_last), wt.to(cuda), bias.to(cuda))
+    assert got.shape == want.shape and got.dtype == dtype
+    assert err(got, want) < tol * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-6), (torch.bfloat16, 8e-3), (torch.float16, 1e-3)])
+@pytest.mark.parametrize("shape", [(3, 17, 1024), (5, 64), (2, 7, 384), (1, 2048), (4, 8)])
+def test_layer_norm(ops, cuda, dtype, tol, shape):
+    """LayerNorm vs F.layer_norm evaluated in fp64 on the stored inputs (block.py:88-101)."""
+    g = torch.Generator().manual_seed(31)
+    x = (torch.randn(*shape, generator=g) * 3 + 0.5).to(dtype)
+    D = shape[-1]
+    wt = (1 + 0.1 * torch.randn(D, generator=g)).to(dtype)
+    bias = (0.1 * torch.randn(D, generator=g)).to(dtype)
+    if dtype == torch.float32 and D > 1024:
+        pytest.skip("fp32 rows are limited to 1024 channels")
+    want = torch.nn.functional.layer_norm(x.double(), (D,), wt.double(), bias.double(), 1e-6).float()
+    got = ops.layer_norm(x.to(cuda), wt.to(cuda), bias.to(cuda), 1e-6)
+    assert got.shape == x.shape and got.dtype == dtype
+    assert err(got, want) < tol * max(1.0, want.abs().max().item())
