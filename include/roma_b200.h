@@ -227,12 +227,13 @@ int roma_dwconv5x5_bias_act(const void* x, const float* weight, const float* bia
  */
 int roma_refiner_out_conv(const void* x, const float* weight, const float* bias, float* out,
                           long long npix, int C, int OUT, int dtype, void* stream);
-/* Narrow 1x1 convolution, OUT <= 16, output in the storage dtype: out[p, o] = bias[o] + sum_c weight[o, c] * x[p, c].
+/* Narrow 1x1 convolution, OUT <= 32, output in the storage dtype: out[p, o] = bias[o] + sum_c weight[o, c] * x[p, c].
  *
  * Replaces (reference): the finest-scale feature projection proj["1"] = Conv2d(64, 9, 1) + BatchNorm2d,
  *   romatch/models/model_zoo/roma_models.py:131-142 as applied at matcher.py:372-375 (eval-mode BatchNorm folded
- *   into weight / bias by the caller).
- * x : (npix, C) channels-last, dtype `dtype`, C a multiple of 8 (4 for fp32), 16-byte aligned;
+ *   into weight / bias by the caller); the 24 -> 24 pointwise convolutions (conv2 of matcher.py:77-103) of the finest
+ *   ConvRefiner, where a GEMM with N = K = 24 leaves cuBLAS at a third of HBM speed.
+ * x : (npix, C) channels-last, dtype `dtype`, C a multiple of 8 (4 for fp32), x and out 16-byte aligned;
  * weight : fp32 (OUT, C); bias : fp32 (OUT); out : (npix, OUT) packed, dtype `dtype`.  fp32 accumulation.
  */
 int roma_pointwise_narrow(const void* x, const float* weight, const float* bias, void* out,

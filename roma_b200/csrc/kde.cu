@@ -103,56 +103,72 @@ __global__ void kde_lut_kernel(float* __restrict__ lut, int* __restrict__ poison
     if (e != 0.f && bits >= bound) atomicExch(poison, 1);          // host-side cutoff estimate violated: fail loudly (NaN)
 }
 
+// Packed arithmetic: queries are processed two at a time, their coordinates side by side in 64-bit register
+// pairs, so the distance chain (1 mul, 3 fma, 2 add — the order of kde_partial_kernel<true>, hence the same bits)
+// is 6 FMUL2/FFMA2/FADD2 for two pairs; the two half indices come out of one F2FP pack, are clamped at 0 / cutoff
+// with one 16-bit SIMD max and min each, and address the table twice.  Reference points sit in shared memory
+// already duplicated (x,x,y,y | z,z,w,w | n,n) so that a broadcast LDS.128 yields the packed operand.
 __global__ void __launch_bounds__(kKdeThreads)
 kde_partial_lut_kernel(const float* __restrict__ x, int N, int M, int down, const float* __restrict__ lut_g,
                        int cutoff, float* __restrict__ partial, int nsplit) {
     extern __shared__ float ksm[];
     float* lut = ksm;                                               // [cutoff + 1]; every entry >= cutoff is 0
-    float4* ref = reinterpret_cast<float4*>(ksm + ((cutoff + 1 + 3) & ~3));
-    float* refn = reinterpret_cast<float*>(ref + kKdeTile);
+    float4* ref = reinterpret_cast<float4*>(ksm + ((cutoff + 1 + 3) & ~3));    // [tile][2]: (x,x,y,y), (z,z,w,w)
+    float2* refn = reinterpret_cast<float2*>(ref + 2 * kKdeTile);              // [tile]: (n,n)
     for (int t = threadIdx.x; t <= cutoff; t += kKdeThreads) lut[t] = (t < cutoff) ? lut_g[t] : 0.f;
 
     const int split = blockIdx.y;
     const int per = (M + nsplit - 1) / nsplit;
     const int j_begin = split * per, j_end = min(M, j_begin + per);
     const int i0 = (blockIdx.x * kKdeThreads + threadIdx.x) * kQPT;
+    constexpr int kPairs = kQPT / 2;
 
-    float4 q[kQPT]; float qn[kQPT], acc[kQPT];
+    float2 qx[kPairs], qy[kPairs], qz[kPairs], qw[kPairs], qn[kPairs];
+    float acc[kQPT];
 #pragma unroll
     for (int u = 0; u < kQPT; ++u) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (i0 + u < N) v = reinterpret_cast<const float4*>(x)[i0 + u];
         v = make_float4(rh(v.x), rh(v.y), rh(v.z), rh(v.w));
-        qn[u] = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
-        q[u] = make_float4(-2.f * v.x, -2.f * v.y, -2.f * v.z, -2.f * v.w);       // exact
+        const float n = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
+        if (u & 1) { qx[u / 2].y = -2.f * v.x; qy[u / 2].y = -2.f * v.y; qz[u / 2].y = -2.f * v.z; qw[u / 2].y = -2.f * v.w; qn[u / 2].y = n; }
+        else       { qx[u / 2].x = -2.f * v.x; qy[u / 2].x = -2.f * v.y; qz[u / 2].x = -2.f * v.z; qw[u / 2].x = -2.f * v.w; qn[u / 2].x = n; }
         acc[u] = 0.f;
     }
+    const unsigned cut2 = (unsigned)cutoff | ((unsigned)cutoff << 16);
     for (int j0 = j_begin; j0 < j_end; j0 += kKdeTile) {
         const int n = min(kKdeTile, j_end - j0);
         __syncthreads();
         for (int t = threadIdx.x; t < n; t += kKdeThreads) {
             float4 r = reinterpret_cast<const float4*>(x)[(long long)(j0 + t) * down];
             r = make_float4(rh(r.x), rh(r.y), rh(r.z), rh(r.w));
-            refn[t] = rh(rh(r.x * r.x) + rh(r.y * r.y) + rh(r.z * r.z) + rh(r.w * r.w));
-            ref[t] = r;
+            const float rn = rh(rh(r.x * r.x) + rh(r.y * r.y) + rh(r.z * r.z) + rh(r.w * r.w));
+            ref[2 * t] = make_float4(r.x, r.x, r.y, r.y);
+            ref[2 * t + 1] = make_float4(r.z, r.z, r.w, r.w);
+            refn[t] = make_float2(rn, rn);
         }
         __syncthreads();
 #pragma unroll 2
         for (int t = 0; t < n; ++t) {
-            const float4 r = ref[t];
-            const float rn = refn[t];
+            const float4 rxy = ref[2 * t], rzw = ref[2 * t + 1];
+            const float2 rn = refn[t];
+            const float2 rx = make_float2(rxy.x, rxy.y), ry = make_float2(rxy.z, rxy.w);
+            const float2 rz = make_float2(rzw.x, rzw.y), rw = make_float2(rzw.z, rzw.w);
 #pragma unroll
-            for (int u = 0; u < kQPT; ++u) {
-                float d2 = q[u].x * r.x;
-                d2 = fmaf(q[u].y, r.y, d2);
-                d2 = fmaf(q[u].z, r.z, d2);
-                d2 = fmaf(q[u].w, r.w, d2);
-                d2 = d2 + qn[u];
-                d2 = d2 + rn;
-                // half(d2) as an index: negatives (sign bit set -> huge unsigned... clamp_min(0) -> entry 0) and NaN never occur
-                const unsigned short hb = __half_as_ushort(__float2half_rn(fmaxf(d2, 0.f)));
-                const int idx = min((int)hb, cutoff);
-                acc[u] += lut[idx];
+            for (int pr = 0; pr < kPairs; ++pr) {
+                float2 d2 = __fmul2_rn(qx[pr], rx);
+                d2 = __ffma2_rn(qy[pr], ry, d2);
+                d2 = __ffma2_rn(qz[pr], rz, d2);
+                d2 = __ffma2_rn(qw[pr], rw, d2);
+                d2 = __fadd2_rn(d2, qn[pr]);
+                d2 = __fadd2_rn(d2, rn);
+                // two half bit patterns; negative (sign bit -> negative int16) clamps to entry 0 = clamp_min(0), large
+                // values and +inf clamp to `cutoff` whose entry is 0; NaN never occurs
+                const __half2 h2 = __floats2half2_rn(d2.x, d2.y);
+                unsigned hb = *reinterpret_cast<const unsigned*>(&h2);
+                hb = __vminu2(__vmaxs2(hb, 0u), cut2);
+                acc[2 * pr] += lut[hb & 0xffffu];
+                acc[2 * pr + 1] += lut[hb >> 16];
             }
         }
     }
@@ -242,10 +258,10 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
         if (nsplit > (int)((workspace_bytes - kKdeLutBytes) / ((size_t)N * sizeof(float)))) nsplit = (int)((workspace_bytes - kKdeLutBytes) / ((size_t)N * sizeof(float)));
         cudaMemsetAsync(poison, 0, sizeof(int), st);
         kde_lut_kernel<<<(0x7C00 + 256) / 256, 256, 0, st>>>(lut, poison, inv_two_var, cutoff_bound);
-        const size_t smem = ((size_t)(cutoff_bound + 1 + 3) & ~(size_t)3) * sizeof(float) + kKdeTile * (sizeof(float4) + sizeof(float));
+        const size_t smem = ((size_t)(cutoff_bound + 1 + 3) & ~(size_t)3) * sizeof(float) + kKdeTile * (2 * sizeof(float4) + sizeof(float2));
         static bool cfg = false;
         if (!cfg) {
-            cudaError_t e = cudaFuncSetAttribute(kde_partial_lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((kLutMax + 4) * sizeof(float)) + kKdeTile * 20));
+            cudaError_t e = cudaFuncSetAttribute(kde_partial_lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((kLutMax + 4) * sizeof(float)) + kKdeTile * 40));
             if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
             cfg = true;
         }

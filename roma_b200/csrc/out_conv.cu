@@ -159,23 +159,24 @@ extern "C" int roma_refiner_out_conv(const void* x, const float* weight, const f
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Narrow 1x1 convolution: out[p, o] = bias[o] + sum_c weight[o, c] * x[p, c] for OUT <= 16, output in the
+// Narrow 1x1 convolution: out[p, o] = bias[o] + sum_c weight[o, c] * x[p, c] for OUT <= 32, output in the
 // storage dtype, packed (npix, OUT).
 //
 // Replaces (reference): the finest-scale feature projection `proj["1"]` = Conv2d(64, 9, 1x1) + BatchNorm2d
 //   (romatch/models/model_zoo/roma_models.py:131-142; the eval-mode BatchNorm is folded into weight / bias by the
-//   caller).  cuBLAS runs this N = 9 GEMM at ~13 % of HBM speed; here one thread owns two pixels, streams their
+//   caller), and the 24 -> 24 pointwise convolutions of the finest ConvRefiner (matcher.py:77-103, conv2).  cuBLAS runs this N = 9 GEMM at ~13 % of HBM speed; here one thread owns two pixels, streams their
 //   channels as 16-byte vectors and keeps the OUT accumulators in registers, the weights (C x OUTP fp32) are
 //   broadcast from shared memory.  HBM-bound: algorithmic bytes = npix * (C + OUT) * sizeof(T).
 namespace roma {
 
-constexpr int kNarrowMaxOut = 16;
+constexpr int kNarrowMaxOut = 32;
 
 template <typename T, int OUTP>
 __global__ void __launch_bounds__(128)
 pointwise_narrow_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const float* __restrict__ bias, T* __restrict__ out,
                         long long npix, int C, int OUT) {
     constexpr int kVec = Elem<T>::kVec;
+    constexpr int NP = OUTP / 2;                       // output channel pairs: one FFMA2 each
     extern __shared__ float wsm[];                     // [C][OUTP], zero padded
     for (int i = threadIdx.x; i < C * OUTP; i += blockDim.x) {
         const int c = i / OUTP, o = i - c * OUTP;
@@ -187,9 +188,10 @@ pointwise_narrow_kernel(const T* __restrict__ x, const float* __restrict__ wgt, 
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < half; t += stride) {
         const long long p0 = t, p1 = t + half;
         const bool has1 = p1 < npix;
-        float a0[OUTP], a1[OUTP];
+        float2 a0[NP], a1[NP];
 #pragma unroll
-        for (int o = 0; o < OUTP; ++o) a0[o] = a1[o] = o < OUT ? __ldg(bias + o) : 0.f;
+        for (int o = 0; o < NP; ++o)
+            a0[o] = a1[o] = make_float2(2 * o < OUT ? __ldg(bias + 2 * o) : 0.f, 2 * o + 1 < OUT ? __ldg(bias + 2 * o + 1) : 0.f);
         const T* x0 = x + p0 * C;
         const T* x1 = x + (has1 ? p1 : p0) * C;
         for (int v = 0; v < C / kVec; ++v) {
@@ -199,23 +201,39 @@ pointwise_narrow_kernel(const T* __restrict__ x, const float* __restrict__ wgt, 
 #pragma unroll
             for (int k = 0; k < kVec; ++k) {
                 const float4* wr = reinterpret_cast<const float4*>(wsm + (v * kVec + k) * OUTP);
+                const float2 d0 = make_float2(f0[k], f0[k]), d1 = make_float2(f1[k], f1[k]);
 #pragma unroll
                 for (int q = 0; q < OUTP / 4; ++q) {
                     const float4 w4 = wr[q];
-                    a0[4 * q + 0] = fmaf(f0[k], w4.x, a0[4 * q + 0]); a1[4 * q + 0] = fmaf(f1[k], w4.x, a1[4 * q + 0]);
-                    a0[4 * q + 1] = fmaf(f0[k], w4.y, a0[4 * q + 1]); a1[4 * q + 1] = fmaf(f1[k], w4.y, a1[4 * q + 1]);
-                    a0[4 * q + 2] = fmaf(f0[k], w4.z, a0[4 * q + 2]); a1[4 * q + 2] = fmaf(f1[k], w4.z, a1[4 * q + 2]);
-                    a0[4 * q + 3] = fmaf(f0[k], w4.w, a0[4 * q + 3]); a1[4 * q + 3] = fmaf(f1[k], w4.w, a1[4 * q + 3]);
+                    const float2 wa = make_float2(w4.x, w4.y), wb = make_float2(w4.z, w4.w);
+                    a0[2 * q] = __ffma2_rn(d0, wa, a0[2 * q]);         a1[2 * q] = __ffma2_rn(d1, wa, a1[2 * q]);
+                    a0[2 * q + 1] = __ffma2_rn(d0, wb, a0[2 * q + 1]); a1[2 * q + 1] = __ffma2_rn(d1, wb, a1[2 * q + 1]);
                 }
             }
         }
         T* o0 = out + p0 * OUT;
         T* o1 = out + p1 * OUT;
+        if (OUT % kVec == 0 && OUTP % kVec == 0) {     // rows are whole 16-byte vectors (out is 16-byte aligned: checked on the host)
 #pragma unroll
-        for (int o = 0; o < OUTP; ++o) {
-            if (o < OUT) {
-                o0[o] = Elem<T>::from_f(a0[o]);
-                if (has1) o1[o] = Elem<T>::from_f(a1[o]);
+            for (int q = 0; q < OUTP / kVec; ++q) {
+                if (q * kVec < OUT) {
+                    float r0[kVec], r1[kVec];
+#pragma unroll
+                    for (int k = 0; k < kVec / 2; ++k) {
+                        r0[2 * k] = a0[q * kVec / 2 + k].x; r0[2 * k + 1] = a0[q * kVec / 2 + k].y;
+                        r1[2 * k] = a1[q * kVec / 2 + k].x; r1[2 * k + 1] = a1[q * kVec / 2 + k].y;
+                    }
+                    *reinterpret_cast<uint4*>(o0 + q * kVec) = pack16<T>(r0);
+                    if (has1) *reinterpret_cast<uint4*>(o1 + q * kVec) = pack16<T>(r1);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int o = 0; o < OUTP; ++o) {
+                if (o < OUT) {
+                    o0[o] = Elem<T>::from_f((o & 1) ? a0[o / 2].y : a0[o / 2].x);
+                    if (has1) o1[o] = Elem<T>::from_f((o & 1) ? a1[o / 2].y : a1[o / 2].x);
+                }
             }
         }
     }
@@ -223,7 +241,9 @@ pointwise_narrow_kernel(const T* __restrict__ x, const float* __restrict__ wgt, 
 
 template <typename T>
 static int launch_narrow(const void* x, const float* w, const float* b, void* out, long long npix, int C, int OUT, cudaStream_t st) {
-    const int outp = (OUT + 3) / 4 * 4;
+    int outp = (OUT + 3) / 4 * 4;
+    if (outp == 20) outp = 24;
+    if (outp == 28) outp = 32;
     const size_t smem = (size_t)C * outp * sizeof(float);
     ROMA_REQUIRE(smem <= 48 * 1024, ROMA_ERR_UNSUPPORTED, "roma_pointwise_narrow: C * OUT too large (%d x %d)", C, OUT);
     long long blocks = ((npix + 1) / 2 + 127) / 128;
@@ -234,7 +254,9 @@ static int launch_narrow(const void* x, const float* w, const float* b, void* ou
         case 4:  pointwise_narrow_kernel<T, 4><<<(unsigned)blocks, 128, smem, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
         case 8:  pointwise_narrow_kernel<T, 8><<<(unsigned)blocks, 128, smem, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
         case 12: pointwise_narrow_kernel<T, 12><<<(unsigned)blocks, 128, smem, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
-        default: pointwise_narrow_kernel<T, 16><<<(unsigned)blocks, 128, smem, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
+        case 16: pointwise_narrow_kernel<T, 16><<<(unsigned)blocks, 128, smem, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
+        case 24: pointwise_narrow_kernel<T, 24><<<(unsigned)blocks, 128, smem, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
+        default: pointwise_narrow_kernel<T, 32><<<(unsigned)blocks, 128, smem, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
     }
     return 0;
 }
@@ -245,10 +267,11 @@ extern "C" int roma_pointwise_narrow(const void* x, const float* weight, const f
                                      long long npix, int C, int OUT, int dtype, void* stream) {
     using namespace roma;
     ROMA_REQUIRE(x && weight && bias && out, ROMA_ERR_BAD_ARG, "roma_pointwise_narrow: null pointer");
-    ROMA_REQUIRE(npix > 0 && C > 0 && OUT >= 1 && OUT <= kNarrowMaxOut, ROMA_ERR_BAD_ARG, "roma_pointwise_narrow: bad sizes (OUT must be 1..16)");
+    ROMA_REQUIRE(npix > 0 && C > 0 && OUT >= 1 && OUT <= kNarrowMaxOut, ROMA_ERR_BAD_ARG, "roma_pointwise_narrow: bad sizes (OUT must be 1..32)");
     const int kvec = dtype == ROMA_F32 ? 4 : 8;
     ROMA_REQUIRE(C % kvec == 0, ROMA_ERR_UNSUPPORTED, "roma_pointwise_narrow: C = %d must be a multiple of %d", C, kvec);
-    ROMA_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15u) == 0, ROMA_ERR_ALIGNMENT, "roma_pointwise_narrow: x must be 16-byte aligned");
+    ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0, ROMA_ERR_ALIGNMENT,
+                 "roma_pointwise_narrow: x and out must be 16-byte aligned");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     int rc;
     switch (dtype) {

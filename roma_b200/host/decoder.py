@@ -65,7 +65,7 @@ class ConvRefiner(nn.Module):
         C = self.hidden_dim
         Cp = (C + 7) // 8 * 8
         blocks = []
-        with torch.no_grad():
+        with torch.inference_mode(False), torch.no_grad():   # cached tensors must be normal (not inference) tensors
             for blk in [self.block1, *self.hidden_blocks]:
                 conv1, bn, _, conv2 = blk
                 scale = bn.weight.float() / torch.sqrt(bn.running_var.float() + bn.eps)
@@ -79,7 +79,10 @@ class ConvRefiner(nn.Module):
                 b_pw = torch.zeros(Cp, device=device)
                 w_pw[:C, :C] = conv2.weight.float().view(C, C)
                 b_pw[:C] = conv2.bias.float()
-                blocks.append((w_dw.contiguous(), b_dw, w_pw.to(dtype).contiguous(), b_pw.to(dtype)))
+                if Cp <= 32:      # N = K = 24: streaming kernel with fp32 weights instead of a cuBLAS GEMM
+                    blocks.append((w_dw.contiguous(), b_dw, w_pw.contiguous(), b_pw))
+                else:
+                    blocks.append((w_dw.contiguous(), b_dw, w_pw.to(dtype).contiguous(), b_pw.to(dtype)))
             w_out = torch.zeros(self.out_conv.out_channels, Cp, device=device)
             w_out[:, :C] = self.out_conv.weight.float().view(-1, C)
             b_out = self.out_conv.bias.float().clone()
@@ -93,7 +96,10 @@ class ConvRefiner(nn.Module):
         B, _, h, w = d.shape
         for w_dw, b_dw, w_pw, b_pw in blocks:
             d = ops.dwconv5x5_bias_act(d, w_dw, b_dw, relu=True)                      # (f-2): dw conv + folded BN + ReLU
-            d = F.linear(d.permute(0, 2, 3, 1), w_pw, b_pw).permute(0, 3, 1, 2)       # NHWC GEMM, bias in the epilogue
+            if Cp <= 32:
+                d = ops.pointwise_narrow(d, w_pw, b_pw)                               # conv2, N = K = 24
+            else:
+                d = F.linear(d.permute(0, 2, 3, 1), w_pw, b_pw).permute(0, 3, 1, 2)   # NHWC GEMM, bias in the epilogue
         return ops.refiner_out_conv(d, w_out, b_out)                                  # matcher.py:141 (fp32 math)
 
     def delta(self, x, y, flow, scale_factor: float = 1) -> torch.Tensor:
@@ -142,6 +148,7 @@ class TransformerDecoder(nn.Module):
         self.hidden_dim, self.out_dim = hidden_dim, out_dim
         self.is_classifier = True
         self.amp_dtype = amp_dtype
+        self._pad_key, self._pad = None, None
 
     def scales(self):
         return [16]
@@ -152,9 +159,29 @@ class TransformerDecoder(nn.Module):
             # both inputs are channels-last, so (B,C,H,W)->(B,HW,C) is a view
             tok = torch.cat((gp_posterior.permute(0, 2, 3, 1).reshape(B, H * W, -1),
                              features.permute(0, 2, 3, 1).reshape(B, H * W, -1).to(gp_posterior.dtype)), dim=-1)
-            out = self.to_out(self.blocks(tok))                      # (B, HW, out_dim) token-major
-        out = out.view(B, H, W, self.out_dim).permute(0, 3, 1, 2)    # (B, out_dim, H, W) view, strides kept
+            hid = self.blocks(tok)
+            if hid.is_cuda and not self.training and self.out_dim % 8:
+                # out_dim = 64^2 + 1 = 4097 is odd: cuBLAS falls back to an unaligned legacy kernel (~10x slower).
+                # Pad the output features to a multiple of 8 once; the extra columns are sliced off as a view.
+                wgt, bias, npad = self._padded_to_out(hid.dtype)
+                out = F.linear(hid, wgt, bias)
+            else:
+                out, npad = self.to_out(hid), self.out_dim
+        out = out.view(B, H, W, npad).permute(0, 3, 1, 2)[:, :self.out_dim]   # (B, out_dim, H, W) view, strides kept
         return out[:, :-1], out[:, -1:], None
+
+    def _padded_to_out(self, dtype):
+        w, b = self.to_out.weight, self.to_out.bias
+        key = (w.data_ptr(), w._version, b._version, dtype)
+        if self._pad_key != key:
+            npad = (self.out_dim + 7) // 8 * 8
+            with torch.inference_mode(False), torch.no_grad():   # cached tensors must be normal (not inference) tensors
+                wp = torch.zeros(npad, w.shape[1], device=w.device, dtype=dtype)
+                bp = torch.zeros(npad, device=w.device, dtype=dtype)
+                wp[:self.out_dim] = w.to(dtype)
+                bp[:self.out_dim] = b.to(dtype)
+            self._pad, self._pad_key = (wp, bp, npad), key
+        return self._pad
 
 
 class Decoder(nn.Module):
@@ -185,7 +212,7 @@ class Decoder(nn.Module):
                conv.weight.data_ptr())
         prep = self._proj_prep.get(scale)
         if prep is None or prep[0] != key:
-            with torch.no_grad():
+            with torch.inference_mode(False), torch.no_grad():   # cached tensors must be normal (not inference) tensors
                 g = bn.weight.float() / torch.sqrt(bn.running_var.float() + bn.eps)
                 w32 = (conv.weight.float().view(conv.out_channels, conv.in_channels) * g[:, None]).contiguous()
                 b0 = conv.bias.float() if conv.bias is not None else 0.0

@@ -12,6 +12,7 @@ from typing import Dict, Optional
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from .. import ops
 import torchvision.models as tvm
@@ -43,7 +44,7 @@ class VGG19(nn.Module):
         if self._prep_key == key:
             return self._prep
         plan, i = [], 0
-        with torch.no_grad():
+        with torch.inference_mode(False), torch.no_grad():   # cached tensors must be normal (not inference) tensors
             while i < len(self.layers):
                 layer = self.layers[i]
                 if isinstance(layer, nn.MaxPool2d):
@@ -53,7 +54,12 @@ class VGG19(nn.Module):
                 conv, bn = layer, self.layers[i + 1]
                 assert isinstance(conv, nn.Conv2d) and isinstance(bn, nn.BatchNorm2d) and isinstance(self.layers[i + 2], nn.ReLU)
                 scale = bn.weight.float() / torch.sqrt(bn.running_var.float() + bn.eps)
-                w = (conv.weight.float() * scale.view(-1, 1, 1, 1)).to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last)
+                w = conv.weight.float() * scale.view(-1, 1, 1, 1)
+                if w.shape[1] % 8 and dtype != torch.float32:
+                    # RGB stem: 3 input channels keep cuDNN on a legacy (sm80) kernel; zero-padding the input
+                    # channels to 8 puts it on the tensor-core implicit GEMM.  The input is padded to match below.
+                    w = F.pad(w, (0, 0, 0, 0, 0, 8 - w.shape[1] % 8))
+                w = w.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last)
                 b = ((conv.bias.float() if conv.bias is not None else 0) * scale + bn.bias.float() - bn.running_mean.float() * scale)
                 plan.append(("conv", w, b.to(device=device, dtype=dtype), conv.padding))
                 i += 3
@@ -73,6 +79,8 @@ class VGG19(nn.Module):
                     break
                 x = ops.maxpool2x2(x) if x.shape[1] % 8 == 0 else step[1](x)
             else:
+                if step[1].shape[1] != x.shape[1]:
+                    x = F.pad(x, (0, 0, 0, 0, 0, step[1].shape[1] - x.shape[1])).contiguous(memory_format=torch.channels_last)
                 x = torch.cudnn_convolution_relu(x, step[1], step[2], (1, 1), step[3], (1, 1), 1)
         return feats
 

@@ -86,7 +86,7 @@ class Block(nn.Module):
         ps = (self.attn.proj.weight, self.attn.proj.bias, self.ls1.gamma, self.mlp.fc2.weight, self.mlp.fc2.bias, self.ls2.gamma)
         key = tuple((p.data_ptr(), p._version, p.dtype) for p in ps)
         if self._fold_key != key:
-            with torch.no_grad():
+            with torch.inference_mode(False), torch.no_grad():   # cached tensors must be normal (not inference) tensors
                 dt = ps[0].dtype
                 g1, g2 = self.ls1.gamma.float(), self.ls2.gamma.float()
                 self._fold = ((ps[0].float() * g1[:, None]).to(dt), (ps[1].float() * g1).to(dt),

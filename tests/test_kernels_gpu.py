@@ -374,7 +374,8 @@ def test_maxpool2x2_bit_exact(ops, cuda, dtype, B, C, h, w):
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1e-2), (torch.float16, 2e-3)])
-@pytest.mark.parametrize("B,C,OUT,h,w", [(2, 64, 9, 17, 23), (1, 8, 1, 3, 5), (1, 128, 16, 4, 4), (3, 64, 9, 1, 1)])
+@pytest.mark.parametrize("B,C,OUT,h,w", [(2, 64, 9, 17, 23), (1, 8, 1, 3, 5), (1, 128, 16, 4, 4), (3, 64, 9, 1, 1),
+                                         (2, 24, 24, 9, 11), (1, 32, 32, 5, 5), (1, 16, 20, 3, 3)])
 def test_pointwise_narrow(ops, cuda, dtype, tol, B, C, OUT, h, w):
     """proj["1"] (Conv 64 -> 9 + folded BN) as a streaming kernel vs F.conv2d in fp64 on the stored inputs."""
     g = torch.Generator().manual_seed(29)
