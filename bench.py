@@ -357,8 +357,8 @@ def main():
         "ms_per_step": round(ms_dev / args.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": {"bfloat16": "bf16", "float16": "f16", "float32": "f32"}[args.dtype], "data": "synthetic",
         "config": config_dict(args),
-        "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": int(A_host.numel() + B_host.numel()),
-                "d2h_bytes_per_step": int(out_host.numel() * 4), "ms_per_step": round(ms_e2e / args.steps, 3)},
+        "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": int(A_host.numel() + B_host.numel()) * world,
+                "d2h_bytes_per_step": int(out_host.numel() * 4) * world, "ms_per_step": round(ms_e2e / args.steps, 3)},
         "gpu_launches": launches, "clocks": clk, "roofline": roofline,
         "own_kernels_ms_per_step": round(own_ms, 3), "kernels": rows[:12],
     }
