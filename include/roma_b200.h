@@ -152,6 +152,10 @@ int roma_gp_set_path(int path);
  * operands need split = 1 and are exact.  Rows must be 16-byte aligned. */
 int roma_tc_gemm_nt(const void* A, const void* B, float* C, int batch, int M, int N, int K,
                     int dtype, int split, void* stream);
+/* Testing aid: 1 (default) = 16-bit operands of the tcgen05 GEMMs (the GP Gram matrices, roma_tc_gemm_nt with
+ * fp16 / bf16) are fed by TMA (cp.async.bulk.tensor, warp-specialised producer / MMA issuer); 0 = the
+ * register-staged main loop.  Results are identical. */
+int roma_tc_set_tma(int on);
 int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const float* pos_b,
                       float* mu, int B, int Nx, int Ny, int C, int D, int hy, int wy,
                       float T, float sigma_noise, float eps, int dtype,

@@ -97,6 +97,11 @@ static int run(const T* x, const T* y, const float* pos_w, const float* pos_b, f
 }  // namespace gp
 }  // namespace roma
 
+namespace roma { namespace tc { std::atomic<int> g_tc_tma{1}; } }
+extern "C" int roma_tc_set_tma(int on) {
+    roma::tc::g_tc_tma.store(on ? 1 : 0);
+    return 0;
+}
 namespace roma { namespace gp { static std::atomic<int> g_path{0}; } }   // 0 auto, 1 SIMT fp32, 2 tcgen05 (3-plane solve), 3 tcgen05 (2-plane solve)
 
 extern "C" int roma_gp_set_path(int path) {
@@ -171,7 +176,7 @@ extern "C" int roma_tc_gemm_nt(const void* A, const void* Bm, float* Cm, int bat
         return fail(ROMA_ERR_BAD_ARG, "roma_tc_gemm_nt: fp32 operands need split 2 or 3");
     }
     ROMA_REQUIRE(split == 1, ROMA_ERR_BAD_ARG, "roma_tc_gemm_nt: 16-bit operands are exact with split 1");
-    if (dtype == ROMA_F16) return tc::launch_gemm_nt<__half, 1>(L, batch, st, "roma_tc_gemm_nt");
-    if (dtype == ROMA_BF16) return tc::launch_gemm_nt<__nv_bfloat16, 1>(L, batch, st, "roma_tc_gemm_nt");
+    if (dtype == ROMA_F16) return tc::launch_gemm_nt_16<__half>(L, batch, st, "roma_tc_gemm_nt", dtype);
+    if (dtype == ROMA_BF16) return tc::launch_gemm_nt_16<__nv_bfloat16>(L, batch, st, "roma_tc_gemm_nt", dtype);
     return fail(ROMA_ERR_BAD_ARG, "roma_tc_gemm_nt: unknown dtype %d", dtype);
 }

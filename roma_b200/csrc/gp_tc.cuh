@@ -267,7 +267,11 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
         p1.rn = w.xn; p1.cn = w.yn; p1.srn = Nx; p1.scn = Ny; p1.eps = eps; p1.inv_T = 1.f / Tk; p1.diag_add = 0.f;
         p1.no_diag = 1; p1.tiles_n = nb; p1.store_n = Mp;          // zero-fill the padded columns of K_xy
         L.nprob = 2; L.tiles0 = p0.tiles_m * p0.tiles_n;
-        if ((rc = launch_gemm_nt<T, kGramSplit>(L, B, st, "gp gram"))) return rc;
+        if constexpr (sizeof(T) == 2) {
+            if ((rc = launch_gemm_nt_16<T>(L, B, st, "gp gram", std::is_same<T, __half>::value ? ROMA_F16 : ROMA_BF16))) return rc;
+        } else {
+            if ((rc = launch_gemm_nt<T, kGramSplit>(L, B, st, "gp gram"))) return rc;
+        }
     }
 
     static bool diag_cfg = false;

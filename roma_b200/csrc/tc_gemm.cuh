@@ -16,8 +16,10 @@
 // all accumulated in the same fp32 TMEM tile.  This is what lets the reference's true-fp32 GP (TF32 off,
 // matcher.py:254-263) run on bf16 tensor cores without the 0.047 error of a plain bf16 Gram.
 #pragma once
+#include <atomic>
 #include <type_traits>
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace roma {
 namespace tc {
@@ -188,6 +190,75 @@ template <> struct Stager<__half, 1> : StagerB16 {};
 template <int SPLIT> constexpr int num_stages() { return SPLIT == 1 ? 2 : 1; }
 template <int SPLIT> constexpr size_t smem_bytes() { return (size_t)num_stages<SPLIT>() * 2 * SPLIT * kPlaneBytes + 1024; }
 
+// ---------------------------------------------------------------------------------------------- epilogue
+// Warp w drains lanes 32*(w&3).., columns 64*(w>>2).. of the 128 x 128 accumulator tile and applies the fused
+// epilogue (store / subtract-from-C / cosine kernel).  Shared by the register-staged and the TMA-fed main loops.
+template <int SPLIT>
+__device__ __forceinline__ void tile_epilogue(const Problem& P, int b, int m0, int n0, uint32_t tmem_base, int warp, int lane) {
+    const int q = warp & 3, hf = warp >> 2;
+    const int m = m0 + q * 32 + lane;
+    float* Cb = P.C ? P.C + (long long)b * P.sC : nullptr;
+    float* Ctb = P.Ct ? P.Ct + (long long)b * P.sCt : nullptr;
+    float rn = 0.f;
+    if (P.epi == EPI_COS && m < P.M) rn = P.rn[(long long)b * P.srn + m];
+#pragma unroll 1
+    for (int cc = 0; cc < 2; ++cc) {
+        const int c0 = hf * 64 + cc * 32;
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+        if (SPLIT > 1) {
+            float lo[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 128u + (uint32_t)c0, lo);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] += lo[i];
+        }
+        const int nb0 = n0 + c0;
+        if (P.epi == EPI_COS) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int n = nb0 + i;
+                float k;
+                if (m < P.M && n < P.N) {
+                    const float c = v[i] / (rn * __ldg(P.cn + (long long)b * P.scn + n) + P.eps);
+                    k = expf((c - 1.f) * P.inv_T);
+                    if (m == n && !P.no_diag) k += P.diag_add;
+                } else {
+                    k = (m == n && !P.no_diag) ? 1.f : 0.f;     // padding: identity block keeps the factorisation trivial there
+                }
+                v[i] = k;
+            }
+        }
+        if (Cb && m < P.store_m) {
+            float* crow = Cb + (long long)m * P.ldc + nb0;
+            if (nb0 + 32 <= P.store_n && (P.ldc & 3) == 0) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    float4 o = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+                    if (P.epi == EPI_SUB) {
+                        const float4 old = *reinterpret_cast<const float4*>(crow + i);
+                        o = make_float4(old.x - o.x, old.y - o.y, old.z - o.z, old.w - o.w);
+                        v[i] = o.x; v[i + 1] = o.y; v[i + 2] = o.z; v[i + 3] = o.w;
+                    }
+                    *reinterpret_cast<float4*>(crow + i) = o;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    if (nb0 + i < P.store_n) {
+                        if (P.epi == EPI_SUB) v[i] = crow[i] - v[i];
+                        crow[i] = v[i];
+                    }
+                }
+            }
+        }
+        if (Ctb && m < P.store_m) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (nb0 + i < P.store_n) Ctb[(long long)(nb0 + i) * P.ldct + m] = v[i];      // lanes -> consecutive m: coalesced
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------- kernel
 template <typename T, int SPLIT>
 __global__ void __launch_bounds__(kThreads, 2) gemm_nt_kernel(const Launch L) {
@@ -272,69 +343,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_nt_kernel(const Launch L) {
         tc_fence_after();
     }
 
-    // ---- epilogue: warp w drains lanes 32*(w&3).., columns 64*(w>>2).. ----
-    const int q = warp & 3, hf = warp >> 2;
-    const int m = m0 + q * 32 + lane;
-    float* Cb = P.C ? P.C + (long long)b * P.sC : nullptr;
-    float* Ctb = P.Ct ? P.Ct + (long long)b * P.sCt : nullptr;
-    float rn = 0.f;
-    if (P.epi == EPI_COS && m < P.M) rn = P.rn[(long long)b * P.srn + m];
-#pragma unroll 1
-    for (int cc = 0; cc < 2; ++cc) {
-        const int c0 = hf * 64 + cc * 32;
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-        if (SPLIT > 1) {
-            float lo[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 128u + (uint32_t)c0, lo);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] += lo[i];
-        }
-        const int nb0 = n0 + c0;
-        if (P.epi == EPI_COS) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const int n = nb0 + i;
-                float k;
-                if (m < P.M && n < P.N) {
-                    const float c = v[i] / (rn * __ldg(P.cn + (long long)b * P.scn + n) + P.eps);
-                    k = expf((c - 1.f) * P.inv_T);
-                    if (m == n && !P.no_diag) k += P.diag_add;
-                } else {
-                    k = (m == n && !P.no_diag) ? 1.f : 0.f;     // padding: identity block keeps the factorisation trivial there
-                }
-                v[i] = k;
-            }
-        }
-        if (Cb && m < P.store_m) {
-            float* crow = Cb + (long long)m * P.ldc + nb0;
-            if (nb0 + 32 <= P.store_n && (P.ldc & 3) == 0) {
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                    float4 o = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-                    if (P.epi == EPI_SUB) {
-                        const float4 old = *reinterpret_cast<const float4*>(crow + i);
-                        o = make_float4(old.x - o.x, old.y - o.y, old.z - o.z, old.w - o.w);
-                        v[i] = o.x; v[i + 1] = o.y; v[i + 2] = o.z; v[i + 3] = o.w;
-                    }
-                    *reinterpret_cast<float4*>(crow + i) = o;
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    if (nb0 + i < P.store_n) {
-                        if (P.epi == EPI_SUB) v[i] = crow[i] - v[i];
-                        crow[i] = v[i];
-                    }
-                }
-            }
-        }
-        if (Ctb && m < P.store_m) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-                if (nb0 + i < P.store_n) Ctb[(long long)(nb0 + i) * P.ldct + m] = v[i];      // lanes -> consecutive m: coalesced
-        }
-    }
+    tile_epilogue<SPLIT>(P, b, m0, n0, tmem_base, warp, lane);
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem_base, tmem_cols<SPLIT>());
@@ -352,6 +361,123 @@ static int launch_gemm_nt(const Launch& L, int batch, cudaStream_t st, const cha
     int tiles = L.tiles0 + (L.nprob > 1 ? L.p[1].tiles_m * L.p[1].tiles_n : 0);
     if (tiles <= 0 || batch <= 0) return ROMA_OK;
     gemm_nt_kernel<T, SPLIT><<<dim3(tiles, batch), kThreads, smem, st>>>(L);
+    return check_launch(what);
+}
+
+// ---------------------------------------------------------------------------------------------- TMA-fed main loop
+// 16-bit operands (bf16 / fp16 features as stored: the Gram matrices of the GP) need no conversion, so their
+// k-blocks go global -> shared by cp.async.bulk.tensor (3-D maps: K, rows, batch; SWIZZLE_128B lands them directly
+// in the UMMA K-major layout; rows / K beyond the tensor are zero-filled by the copy engine).  Warp-specialised:
+// lane 0 of warp 0 produces (waits `empty`, arms `full` with the byte count, issues the two box loads), lane 0 of
+// warp 1 issues tcgen05.mma and releases the stage with tcgen05.commit -> `empty`; all 8 warps run the epilogue.
+struct TmaMaps { CUtensorMap a[2], b[2]; };
+constexpr int kTmaStages = 3;                        // 3 x 32 KB: two CTAs per SM
+constexpr size_t kTmaSmem = (size_t)kTmaStages * 2 * kPlaneBytes + 1024;
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 2) gemm_nt_tma_kernel(const Launch L, const __grid_constant__ TmaMaps maps) {
+    extern __shared__ unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kTmaStages], empty_bar[kTmaStages], done_bar;
+    __shared__ uint32_t tmem_slot;
+
+    int t = blockIdx.x;
+    const int pi = (L.nprob > 1 && t >= L.tiles0) ? 1 : 0;
+    if (pi) t -= L.tiles0;
+    const Problem& P = L.p[pi];
+    const int tm = t / P.tiles_n, tn = t - tm * P.tiles_n;
+    if (P.lower_only && tn > tm) return;
+    const int b = blockIdx.y;
+    const int m0 = tm * BM, n0 = tn * BN;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int nkb = (P.K + BK - 1) / BK;
+    constexpr uint32_t kFmt = std::is_same<T, __half>::value ? 0u : 1u;
+    constexpr uint32_t idesc = instr_desc(kFmt);
+
+    if (warp == 0) tmem_alloc(&tmem_slot, 128);
+    if (tid == 0) {
+        for (int s = 0; s < kTmaStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&done_bar, 1);
+        fence_barrier_init();
+        tma::prefetch_map(&maps.a[pi]);
+        tma::prefetch_map(&maps.b[pi]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {                                         // ---- producer ----
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % kTmaStages;
+                if (kb >= kTmaStages) mbar_wait(&empty_bar[s], (uint32_t)((kb / kTmaStages - 1) & 1));
+                unsigned char* sa = smem + (size_t)s * 2 * kPlaneBytes;
+                tma::mbar_expect_tx(&full_bar[s], 2u * kPlaneBytes);
+                tma::load_3d(sa, &maps.a[pi], &full_bar[s], kb * BK, m0, b);
+                tma::load_3d(sa + kPlaneBytes, &maps.b[pi], &full_bar[s], kb * BK, n0, b);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {                                         // ---- MMA issuer ----
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % kTmaStages;
+                mbar_wait(&full_bar[s], (uint32_t)((kb / kTmaStages) & 1));
+                tc_fence_after();
+                const uint32_t a0 = smem_u32(smem + (size_t)s * 2 * kPlaneBytes), b0 = a0 + kPlaneBytes;
+#pragma unroll
+                for (int kk = 0; kk < BK / 16; ++kk)
+                    umma_f16(tmem_base, smem_desc_sw128(a0 + kk * 32), smem_desc_sw128(b0 + kk * 32), idesc, (kb | kk) ? 1u : 0u);
+                umma_commit(&empty_bar[s]);                      // stage reusable once these MMAs have read it
+            }
+            umma_commit(&done_bar);                              // accumulator complete
+        }
+        __syncwarp();
+    }
+    mbar_wait(&done_bar, 0);
+    tc_fence_after();
+    tile_epilogue<1>(P, b, m0, n0, tmem_base, warp, lane);
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, 128);
+}
+
+// Operand map: (K, rows, batch) with box (64, 128, 1).  Returns false when the operand cannot be described
+// (strides not multiples of 16 bytes, misaligned base): the caller then uses the register-staged kernel.
+template <typename T>
+static bool operand_map(CUtensorMap* map, const void* base, int rows, int K, int ld, long long batch_stride, int batch, int dtype) {
+    const uint64_t esz = sizeof(T);
+    if ((reinterpret_cast<uintptr_t>(base) & 15u) || ((uint64_t)ld * esz) % 16 || (batch > 1 && ((uint64_t)batch_stride * esz) % 16)) return false;
+    const uint64_t dims[3] = {(uint64_t)K, (uint64_t)rows, (uint64_t)batch};
+    const uint64_t strides[2] = {(uint64_t)ld * esz, (uint64_t)(batch > 1 ? batch_stride : (long long)rows * ld) * esz};
+    const uint32_t box[3] = {(uint32_t)BK, (uint32_t)BM, 1u};
+    return tma::encode_fn() && tma::encode_tiled(map, dtype, 3, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B) == 0;
+}
+
+extern std::atomic<int> g_tc_tma;      // 1 (default): TMA-fed main loop for 16-bit operands; 0: register-staged (testing aid)
+
+template <typename T>
+static int launch_gemm_nt_16(const Launch& L, int batch, cudaStream_t st, const char* what, int dtype) {
+    static_assert(sizeof(T) == 2, "16-bit operands");
+    int tiles = L.tiles0 + (L.nprob > 1 ? L.p[1].tiles_m * L.p[1].tiles_n : 0);
+    if (tiles <= 0 || batch <= 0) return ROMA_OK;
+    TmaMaps maps;
+    bool ok = g_tc_tma.load() != 0;
+    for (int i = 0; ok && i < L.nprob; ++i) {
+        const Problem& P = L.p[i];
+        ok = operand_map<T>(&maps.a[i], P.A, P.M, P.K, P.lda, P.sA, batch, dtype) &&
+             operand_map<T>(&maps.b[i], P.B, P.N, P.K, P.ldb, P.sB, batch, dtype);
+    }
+    if (!ok) return launch_gemm_nt<T, 1>(L, batch, st, what);
+    if (L.nprob < 2) { maps.a[1] = maps.a[0]; maps.b[1] = maps.b[0]; }
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_nt_tma_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmem);
+        if (e != cudaSuccess) return fail((int)e, "%s: smem opt-in (%zu B): %s", what, kTmaSmem, cudaGetErrorString(e));
+        configured = true;
+    }
+    gemm_nt_tma_kernel<T><<<dim3(tiles, batch), kThreads, kTmaSmem, st>>>(L, maps);
     return check_launch(what);
 }
 

@@ -204,12 +204,21 @@ def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2, path):
 @pytest.mark.parametrize("dtype,split,tol", [(torch.float32, 3, 2e-6), (torch.float32, 2, 2e-5), (torch.bfloat16, 1, 2e-6), (torch.float16, 1, 2e-6)])
 @pytest.mark.parametrize("batch,M,N,K", [(2, 300, 200, 136), (1, 128, 128, 64), (3, 129, 257, 520)])
 def test_tc_gemm_nt(ops, cuda, dtype, split, tol, batch, M, N, K):
-    """The tcgen05 building block on ragged shapes (row/column/K tails) against fp64."""
+    """The tcgen05 building block on ragged shapes (row/column/K tails) against fp64.  16-bit operands run the
+    TMA-fed warp-specialised main loop (default) and the register-staged one: identical results."""
+    from roma_b200 import _lib
     g = torch.Generator().manual_seed(5)
     a = torch.randn(batch, M, K, generator=g).to(dtype); b = torch.randn(batch, N, K, generator=g).to(dtype)
     want = a.double() @ b.double().mT
     got = ops.tc_gemm_nt(a.to(cuda), b.to(cuda), split)
     assert (got.double().cpu() - want).abs().max().item() < tol * want.abs().max().item()
+    if dtype != torch.float32:
+        try:
+            _lib.load().roma_tc_set_tma(0)
+            staged = ops.tc_gemm_nt(a.to(cuda), b.to(cuda), split)
+        finally:
+            _lib.load().roma_tc_set_tma(1)
+        assert torch.equal(staged, got)
 
 
 # --------------------------------------------------------------------------------------------- K3b
