@@ -242,6 +242,9 @@ int roma_refiner_out_conv(const void* x, const float* weight, const float* bias,
  */
 int roma_pointwise_narrow(const void* x, const float* weight, const float* bias, void* out,
                           long long npix, int C, int OUT, int dtype, void* stream);
+/* Testing aid: 0 (default) = 16-bit inputs with C <= 64 use warp-level tensor-core MMAs (weights rounded to the
+ * input dtype, as autocast does in the reference); 1 = always the fp32-weight FFMA2 kernel. */
+int roma_pointwise_narrow_set_simt(int on);
 /* Testing aid: 0 = automatic (TMA-tiled input when C * sizeof(dtype) is a multiple of 16 and x is 16-byte
  * aligned, per-thread cp.async staging otherwise), 1 = always the cp.async variant.  Results are identical. */
 int roma_dwconv_set_path(int path);

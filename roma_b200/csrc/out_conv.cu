@@ -11,13 +11,14 @@
 // grid-stride loop, two pixels in flight.  Partial sums are combined with xor-shuffles inside the group.
 // Output: fp32 (npix, 4) interleaved (dx, dy, dcert, 0) so that every pixel is one 16-byte store; the consumer
 // (`roma_flow_update_resample`) takes explicit strides.
+#include <atomic>
 #include "common.cuh"
 
 namespace roma {
 
 constexpr int kOutMax = 3;
 
-template <typename T, int NV>
+template <typename T, int NV, int PX>
 __global__ void __launch_bounds__(256)
 out_conv_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const float* __restrict__ bias, float4* __restrict__ out,
                 long long npix, int C, int OUT, int G, int gshift) {
@@ -36,43 +37,49 @@ out_conv_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const fl
     }
     const float b0 = OUT > 0 ? __ldg(bias + 0) : 0.f, b1 = OUT > 1 ? __ldg(bias + 1) : 0.f, b2 = OUT > 2 ? __ldg(bias + 2) : 0.f;
 
+    // PX pixels in flight per group (more for narrow rows, where one pixel is a single 16-byte load per lane)
     const long long groups_total = ((long long)gridDim.x * blockDim.x) >> gshift;
     // the trip count is uniform per warp (the shuffles below need all 32 lanes): a group past the end idles
     const long long warp_first = (((long long)blockIdx.x * blockDim.x + threadIdx.x) & ~31LL) >> gshift;
-    for (long long base = warp_first; base < npix; base += 2 * groups_total) {
-        const long long p = base + (lane >> gshift), p1 = p + groups_total;
-        const bool has0 = p < npix, has1 = p1 < npix;    // uniform inside the group
-        uint4 ra[NV], rb[NV];
+    for (long long base = warp_first; base < npix; base += PX * groups_total) {
+        const long long p0 = base + (lane >> gshift);
+        uint4 raw[PX][NV];
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-            const int v = gl + i * G;
-            ra[i] = (v < nvec && has0) ? ldg16(x + p * C + v * kVec) : make_uint4(0, 0, 0, 0);
-            rb[i] = (v < nvec && has1) ? ldg16(x + p1 * C + v * kVec) : make_uint4(0, 0, 0, 0);
+        for (int u = 0; u < PX; ++u) {
+            const long long p = p0 + u * groups_total;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const int v = gl + i * G;
+                raw[u][i] = (v < nvec && p < npix) ? ldg16(x + p * C + v * kVec) : make_uint4(0, 0, 0, 0);
+            }
         }
-        float sa[kOutMax] = {0.f, 0.f, 0.f}, sb[kOutMax] = {0.f, 0.f, 0.f};
+        float s[PX][kOutMax];
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-            float fa[kVec], fb[kVec];
-            unpack16<T>(ra[i], fa);
-            unpack16<T>(rb[i], fb);
+        for (int u = 0; u < PX; ++u) {
 #pragma unroll
-            for (int o = 0; o < kOutMax; ++o)
+            for (int o = 0; o < kOutMax; ++o) s[u][o] = 0.f;
 #pragma unroll
-                for (int k = 0; k < kVec; ++k) {
-                    sa[o] = fmaf(fa[k], wv[i][o][k], sa[o]);
-                    sb[o] = fmaf(fb[k], wv[i][o][k], sb[o]);
-                }
+            for (int i = 0; i < NV; ++i) {
+                float f[kVec];
+                unpack16<T>(raw[u][i], f);
+#pragma unroll
+                for (int o = 0; o < kOutMax; ++o)
+#pragma unroll
+                    for (int k = 0; k < kVec; ++k) s[u][o] = fmaf(f[k], wv[i][o][k], s[u][o]);
+            }
         }
         for (int off = G >> 1; off > 0; off >>= 1) {
 #pragma unroll
-            for (int o = 0; o < kOutMax; ++o) {
-                sa[o] += __shfl_xor_sync(0xffffffffu, sa[o], off);
-                sb[o] += __shfl_xor_sync(0xffffffffu, sb[o], off);
-            }
+            for (int u = 0; u < PX; ++u)
+#pragma unroll
+                for (int o = 0; o < kOutMax; ++o) s[u][o] += __shfl_xor_sync(0xffffffffu, s[u][o], off);
         }
-        if (gl == 0 && has0) {
-            out[p] = make_float4(sa[0] + b0, sa[1] + b1, sa[2] + b2, 0.f);
-            if (has1) out[p1] = make_float4(sb[0] + b0, sb[1] + b1, sb[2] + b2, 0.f);
+        if (gl == 0) {
+#pragma unroll
+            for (int u = 0; u < PX; ++u) {
+                const long long p = p0 + u * groups_total;
+                if (p < npix) out[p] = make_float4(s[u][0] + b0, s[u][1] + b1, s[u][2] + b2, 0.f);
+            }
         }
     }
 }
@@ -114,18 +121,19 @@ static int launch_out_conv(const void* x, const float* w, const float* b, float*
     int G = 1, gshift = 0;
     while (G < 32 && G < nvec) { G <<= 1; ++gshift; }
     const int nv = cdiv(nvec, G);
-    const long long groups_wanted = (npix + 1) / 2;
+    const int px = nv <= 1 ? 8 : nv <= 2 ? 4 : 2;
+    const long long groups_wanted = (npix + px - 1) / px;
     const int groups_per_block = 256 / G;
     long long blocks = (groups_wanted + groups_per_block - 1) / groups_per_block;
     const long long cap = (long long)sm_count() * 8;                   // grid-stride beyond 8 resident blocks per SM
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-#define ROMA_OUT_CONV(NVC) out_conv_kernel<T, NVC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, w, b, (float4*)out, npix, C, OUT, G, gshift)
-    if (nv <= 1) ROMA_OUT_CONV(1);
-    else if (nv <= 2) ROMA_OUT_CONV(2);
-    else if (nv <= 3) ROMA_OUT_CONV(3);
-    else if (nv <= 5) ROMA_OUT_CONV(5);
-    else if (nv <= 9) ROMA_OUT_CONV(9);
+#define ROMA_OUT_CONV(NVC, PXC) out_conv_kernel<T, NVC, PXC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, w, b, (float4*)out, npix, C, OUT, G, gshift)
+    if (nv <= 1) ROMA_OUT_CONV(1, 8);
+    else if (nv <= 2) ROMA_OUT_CONV(2, 4);
+    else if (nv <= 3) ROMA_OUT_CONV(3, 2);
+    else if (nv <= 5) ROMA_OUT_CONV(5, 2);
+    else if (nv <= 9) ROMA_OUT_CONV(9, 2);
     else {
         long long wb = (npix + 7) / 8;
         if (wb > cap) wb = cap;
@@ -170,6 +178,7 @@ extern "C" int roma_refiner_out_conv(const void* x, const float* weight, const f
 namespace roma {
 
 constexpr int kNarrowMaxOut = 32;
+static std::atomic<int> g_narrow_simt{0};     // testing aid: 1 forces the FFMA2 kernel for 16-bit inputs too
 
 template <typename T, int OUTP>
 __global__ void __launch_bounds__(128)
@@ -239,8 +248,138 @@ pointwise_narrow_kernel(const T* __restrict__ x, const float* __restrict__ wgt, 
     }
 }
 
+// ---- tensor-core variant (16-bit dtypes, C <= 64, OUT <= 32) -------------------------------------------------
+// The op is a GEMM with N, K <= 64 over millions of rows: memory-bound as soon as the 576 MACs per pixel leave the
+// FP32 pipe, so it runs on warp-level mma.sync m16n8k16 (fp32 accumulate) with the A fragments loaded straight
+// from global memory (a quad of lanes reads 16 contiguous bytes of one pixel), the weights converted once per
+// thread into B fragments and the C fragments stored as packed 16-bit pairs.  No shared memory, no barrier.
+// (tcgen05 would need the A tile staged in shared memory and a TMEM round trip for a kernel whose roofline is HBM.)
+template <typename T> __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <> __device__ __forceinline__ void mma16816<__nv_bfloat16>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <> __device__ __forceinline__ void mma16816<__half>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <typename T> __device__ __forceinline__ uint32_t pack2(float lo, float hi);
+template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float lo, float hi) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+template <> __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
+    const __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+constexpr int kMmaTiles = 2;           // 16-pixel tiles in flight per warp
+
+template <typename T, int KS, int NT>
+__global__ void __launch_bounds__(256)
+narrow_mma_kernel(const T* __restrict__ x, const float* __restrict__ wgt, const float* __restrict__ bias, T* __restrict__ out,
+                  long long npix, int C, int OUT) {
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    // B fragments: B[k][n] = W[n][k];  b0 = (k = 16 ks + 2t, +1 ; n = 8 nt + g), b1 = the same 8 further in k
+    uint32_t bf[KS][NT][2];
+    float bv[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        const int n = nt * 8 + g;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int k = ks * 16 + 2 * t + 8 * h;
+                const float w0 = (n < OUT && k < C) ? __ldg(wgt + (long long)n * C + k) : 0.f;
+                const float w1 = (n < OUT && k + 1 < C) ? __ldg(wgt + (long long)n * C + k + 1) : 0.f;
+                bf[ks][nt][h] = pack2<T>(w0, w1);
+            }
+        }
+        bv[nt][0] = nt * 8 + 2 * t < OUT ? __ldg(bias + nt * 8 + 2 * t) : 0.f;
+        bv[nt][1] = nt * 8 + 2 * t + 1 < OUT ? __ldg(bias + nt * 8 + 2 * t + 1) : 0.f;
+    }
+    const bool pair_store = (OUT & 1) == 0;            // 4-byte aligned channel pairs
+    const long long ntiles = (npix + 15) / 16;
+    const long long wstride = (((long long)gridDim.x * blockDim.x) >> 5) * kMmaTiles;
+    for (long long tile0 = ((((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5)) * kMmaTiles; tile0 < ntiles; tile0 += wstride) {
+        uint32_t a[kMmaTiles][KS][4];
+#pragma unroll
+        for (int u = 0; u < kMmaTiles; ++u) {
+            const long long plo = (tile0 + u) * 16 + g, phi = plo + 8;
+            const uint32_t* rlo = reinterpret_cast<const uint32_t*>(x + plo * C);
+            const uint32_t* rhi = reinterpret_cast<const uint32_t*>(x + phi * C);
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks) {
+                const int k0 = ks * 16 + 2 * t, k1 = k0 + 8;
+                a[u][ks][0] = (plo < npix && k0 < C) ? __ldg(rlo + (k0 >> 1)) : 0u;
+                a[u][ks][1] = (phi < npix && k0 < C) ? __ldg(rhi + (k0 >> 1)) : 0u;
+                a[u][ks][2] = (plo < npix && k1 < C) ? __ldg(rlo + (k1 >> 1)) : 0u;
+                a[u][ks][3] = (phi < npix && k1 < C) ? __ldg(rhi + (k1 >> 1)) : 0u;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kMmaTiles; ++u) {
+            const long long plo = (tile0 + u) * 16 + g, phi = plo + 8;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                float c[4] = {bv[nt][0], bv[nt][1], bv[nt][0], bv[nt][1]};
+#pragma unroll
+                for (int ks = 0; ks < KS; ++ks) mma16816<T>(c, a[u][ks], bf[ks][nt][0], bf[ks][nt][1]);
+                const int n = nt * 8 + 2 * t;
+                if (pair_store) {
+                    if (n < OUT) {
+                        if (plo < npix) *reinterpret_cast<uint32_t*>(out + plo * OUT + n) = pack2<T>(c[0], c[1]);
+                        if (phi < npix) *reinterpret_cast<uint32_t*>(out + phi * OUT + n) = pack2<T>(c[2], c[3]);
+                    }
+                } else {
+                    if (plo < npix) {
+                        if (n < OUT) out[plo * OUT + n] = Elem<T>::from_f(c[0]);
+                        if (n + 1 < OUT) out[plo * OUT + n + 1] = Elem<T>::from_f(c[1]);
+                    }
+                    if (phi < npix) {
+                        if (n < OUT) out[phi * OUT + n] = Elem<T>::from_f(c[2]);
+                        if (n + 1 < OUT) out[phi * OUT + n + 1] = Elem<T>::from_f(c[3]);
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <typename T, int KS>
+static void launch_narrow_mma_nt(const void* x, const float* w, const float* b, void* out, long long npix, int C, int OUT,
+                                 unsigned blocks, cudaStream_t st) {
+    const int nt = (OUT + 7) / 8;
+    switch (nt) {
+        case 1: narrow_mma_kernel<T, KS, 1><<<blocks, 256, 0, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
+        case 2: narrow_mma_kernel<T, KS, 2><<<blocks, 256, 0, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
+        case 3: narrow_mma_kernel<T, KS, 3><<<blocks, 256, 0, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
+        default: narrow_mma_kernel<T, KS, 4><<<blocks, 256, 0, st>>>((const T*)x, w, b, (T*)out, npix, C, OUT); break;
+    }
+}
+
+template <typename T>
+static bool launch_narrow_mma(const void* x, const float* w, const float* b, void* out, long long npix, int C, int OUT, cudaStream_t st) {
+    if constexpr (sizeof(T) != 2) return false;
+    else {
+        if (C > 64 || OUT > 32 || g_narrow_simt.load()) return false;
+        const long long warps = ((npix + 15) / 16 + kMmaTiles - 1) / kMmaTiles;
+        long long blocks = (warps + 7) / 8;
+        const long long cap = (long long)sm_count() * 16;
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        const int ks = (C + 15) / 16;
+        if (ks <= 1) launch_narrow_mma_nt<T, 1>(x, w, b, out, npix, C, OUT, (unsigned)blocks, st);
+        else if (ks <= 2) launch_narrow_mma_nt<T, 2>(x, w, b, out, npix, C, OUT, (unsigned)blocks, st);
+        else launch_narrow_mma_nt<T, 4>(x, w, b, out, npix, C, OUT, (unsigned)blocks, st);
+        return true;
+    }
+}
+
 template <typename T>
 static int launch_narrow(const void* x, const float* w, const float* b, void* out, long long npix, int C, int OUT, cudaStream_t st) {
+    if (launch_narrow_mma<T>(x, w, b, out, npix, C, OUT, st)) return 0;
     int outp = (OUT + 3) / 4 * 4;
     if (outp == 20) outp = 24;
     if (outp == 28) outp = 32;
@@ -262,6 +401,11 @@ static int launch_narrow(const void* x, const float* w, const float* b, void* ou
 }
 
 }  // namespace roma
+
+extern "C" int roma_pointwise_narrow_set_simt(int on) {
+    roma::g_narrow_simt.store(on ? 1 : 0);
+    return 0;
+}
 
 extern "C" int roma_pointwise_narrow(const void* x, const float* weight, const float* bias, void* out,
                                      long long npix, int C, int OUT, int dtype, void* stream) {

@@ -384,7 +384,8 @@ def test_maxpool2x2_bit_exact(ops, cuda, dtype, B, C, h, w):
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1e-2), (torch.float16, 2e-3)])
 @pytest.mark.parametrize("B,C,OUT,h,w", [(2, 64, 9, 17, 23), (1, 8, 1, 3, 5), (1, 128, 16, 4, 4), (3, 64, 9, 1, 1),
-                                         (2, 24, 24, 9, 11), (1, 32, 32, 5, 5), (1, 16, 20, 3, 3)])
+                                         (2, 24, 24, 9, 11), (1, 32, 32, 5, 5), (1, 16, 20, 3, 3), (1, 48, 7, 6, 7),
+                                         (1, 8, 3, 37, 1)])
 def test_pointwise_narrow(ops, cuda, dtype, tol, B, C, OUT, h, w):
     """proj["1"] (Conv 64 -> 9 + folded BN) as a streaming kernel vs F.conv2d in fp64 on the stored inputs."""
     g = torch.Generator().manual_seed(29)
@@ -392,9 +393,17 @@ def test_pointwise_narrow(ops, cuda, dtype, tol, B, C, OUT, h, w):
     wt = torch.randn(OUT, C, generator=g) / C ** 0.5
     bias = torch.randn(OUT, generator=g)
     want = torch.nn.functional.conv2d(x.double(), wt.double().view(OUT, C, 1, 1), bias.double()).float()
-    got = ops.pointwise_narrow(x.to(cuda).contiguous(memory_format=torch.channels_last), wt.to(cuda), bias.to(cuda))
+    from roma_b200 import _lib
+    xc = x.to(cuda).contiguous(memory_format=torch.channels_last)
+    got = ops.pointwise_narrow(xc, wt.to(cuda), bias.to(cuda))          # 16-bit: tensor-core path (weights in dtype)
     assert got.shape == want.shape and got.dtype == dtype
     assert err(got, want) < tol * max(1.0, want.abs().max().item())
+    try:
+        _lib.load().roma_pointwise_narrow_set_simt(1)
+        simt = ops.pointwise_narrow(xc, wt.to(cuda), bias.to(cuda))     # fp32-weight FFMA2 kernel
+    finally:
+        _lib.load().roma_pointwise_narrow_set_simt(0)
+    assert err(simt, want) < tol * max(1.0, want.abs().max().item())
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-6), (torch.bfloat16, 8e-3), (torch.float16, 1e-3)])

@@ -162,6 +162,36 @@ def main():
                  alg_MB=round(alg / 1e6, 1), GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4),
                  fp32_TFLOPs=round(2 * macs / ms / 1e9, 2))
 
+    if want("narrow"):
+        for name, Cin, Cout, side in (("pw24 s1u", 24, 24, 864), ("pw24 s1", 24, 24, 560), ("proj1 864", 64, 9, 864)):
+            x = torch.randn(B, side, side, Cin, device=dev, dtype=dt).permute(0, 3, 1, 2)
+            wt = torch.randn(Cout, Cin, device=dev) * 0.2
+            bs = torch.randn(Cout, device=dev)
+            alg = B * side * side * (Cin + Cout) * x.element_size()
+            ms = timeit(lambda: ops.pointwise_narrow(x, wt, bs), args.iters, flush)
+            emit(kernel="pointwise_narrow", case=name, batch=B, ms=round(ms, 4), alg_MB=round(alg / 1e6, 1),
+                 GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4))
+    if want("outconv"):
+        for name, Cp, side in (("s1u", 24, 864), ("s2u", 144, 432), ("s4u", 576, 216), ("s8u", 1144, 108)):
+            x = torch.randn(B, side, side, Cp, device=dev, dtype=dt).permute(0, 3, 1, 2)
+            wt = torch.randn(3, Cp, device=dev) * 0.1
+            bs = torch.randn(3, device=dev)
+            alg = B * side * side * (Cp * x.element_size() + 16)
+            ms = timeit(lambda: ops.refiner_out_conv(x, wt, bs), args.iters, flush)
+            emit(kernel="refiner_out_conv", case=name, batch=B, ms=round(ms, 4), alg_MB=round(alg / 1e6, 1),
+                 GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4))
+    if want("stream"):
+        x = torch.randn(B, 1601, 1024, device=dev, dtype=dt)
+        g1, b1 = torch.ones(1024, device=dev, dtype=dt), torch.zeros(1024, device=dev, dtype=dt)
+        alg = 2 * x.numel() * x.element_size()
+        ms = timeit(lambda: ops.layer_norm(x, g1, b1, 1e-6), args.iters, flush)
+        emit(kernel="layernorm", rows=B * 1601, D=1024, ms=round(ms, 4), GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4))
+        for C, side in ((64, 864), (128, 432), (256, 216)):
+            y = torch.randn(B, side, side, C, device=dev, dtype=dt).permute(0, 3, 1, 2)
+            alg = y.numel() * y.element_size() * 5 // 4
+            ms = timeit(lambda: ops.maxpool2x2(y), args.iters, flush)
+            emit(kernel="maxpool2x2", C=C, side=side, ms=round(ms, 4), GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4))
+
 
 if __name__ == "__main__":
     main()
