@@ -102,13 +102,14 @@ class ConvRefiner(nn.Module):
                 d = F.linear(d.permute(0, 2, 3, 1), w_pw, b_pw).permute(0, 3, 1, 2)   # NHWC GEMM, bias in the epilogue
         return ops.refiner_out_conv(d, w_out, b_out)                                  # matcher.py:141 (fp32 math)
 
-    def delta(self, x, y, flow, scale_factor: float = 1) -> torch.Tensor:
+    def delta(self, x, y, flow, scale_factor: float = 1, swap_halves: bool = False) -> torch.Tensor:
         """The (B,3,h,w) out_conv tensor (dx, dy, dcertainty) consumed by the fused update kernel."""
         # K2: x_hat = grid_sample(y, flow), disp_emb(40/32*scale_factor*(flow-grid)), local_correlation and the
         # concat of matcher.py:109-132 in one launch, written channels-last in the feature dtype.
         dw = self.disp_emb.weight if self.has_displacement_emb else None
         db = self.disp_emb.bias if self.has_displacement_emb else None
-        d = ops.refiner_inputs(x, y, flow, dw, db, 40 / 32 * scale_factor, self.local_corr_radius, pad_to=8)
+        d = ops.refiner_inputs(x, y, flow, dw, db, 40 / 32 * scale_factor, self.local_corr_radius, pad_to=8,
+                               swap_halves=swap_halves)
         return self._body(d)
 
     def forward(self, x, y, flow, scale_factor: float = 1, logits=None):
@@ -247,17 +248,17 @@ class Decoder(nn.Module):
             if new_scale in self.proj:
                 f1_s = self._project(new_scale, f1_s)
                 f2_s = None if swapped else self._project(new_scale, f2_s)
-            if swapped:
-                a, b = f1_s.chunk(2)
-                f2_s = torch.cat((b, a), dim=0)
-                if f1_s.dim() == 4 and f1_s.is_contiguous(memory_format=torch.channels_last):
-                    f2_s = f2_s.contiguous(memory_format=torch.channels_last)
             if ins in coarse_scales:
+                if swapped:      # the GP takes whole tensors: one small swapped copy at the coarsest scale only
+                    a, b = f1_s.chunk(2)
+                    f2_s = torch.cat((b, a), dim=0)
+                    if f1_s.is_contiguous(memory_format=torch.channels_last):
+                        f2_s = f2_s.contiguous(memory_format=torch.channels_last)
                 gp_posterior = self.gps[new_scale](f1_s, f2_s)                                  # K1
                 cls, certainty, _ = self.embedding_decoder(gp_posterior, f1_s, None, new_scale)
                 flow = ops.cls_to_flow_refine(cls).permute(0, 3, 1, 2)                          # (f-1)
             if new_scale in self.conv_refiner:
-                delta = self.conv_refiner[new_scale].delta(f1_s, f2_s, flow, scale_factor=scale_factor)
+                delta = self.conv_refiner[new_scale].delta(f1_s, f2_s, flow, scale_factor=scale_factor, swap_halves=swapped)
             else:
                 delta = None
             nxt = tuple(sizes[ins // 2]) if new_scale != "1" else None

@@ -102,9 +102,10 @@ def _f32(t: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------------------------------
 # K2
 # --------------------------------------------------------------------------------------------------
-def refiner_inputs(x: torch.Tensor, y: torch.Tensor, flow: torch.Tensor,
+def refiner_inputs(x: torch.Tensor, y: Optional[torch.Tensor], flow: torch.Tensor,
                    disp_w: Optional[torch.Tensor] = None, disp_b: Optional[torch.Tensor] = None,
-                   disp_scale: float = 1.0, local_corr_radius: Optional[int] = None, pad_to: int = 1) -> torch.Tensor:
+                   disp_scale: float = 1.0, local_corr_radius: Optional[int] = None, pad_to: int = 1,
+                   swap_halves: bool = False) -> torch.Tensor:
     """ConvRefiner input d = cat(x, x_hat, disp_emb, local_corr) in ONE kernel (matcher.py:105-132).
 
     x, y: (B,C,h,w) features of image A / B (any of fp32/fp16/bf16, same dtype); flow: (B,2,h,w) fp32 view.
@@ -112,8 +113,12 @@ def refiner_inputs(x: torch.Tensor, y: torch.Tensor, flow: torch.Tensor,
     channel count is rounded up to a multiple of pad_to and the extra channels are zero: rows become 16-byte
     aligned (pad_to=8 for 16-bit features), which is what the vectorised kernel path and the tensor-core GEMMs of
     the refiner body want; the caller pads its weights accordingly.
+    swap_halves=True (symmetric matching, matcher.py:459-463): y is x with the two halves of the batch exchanged;
+    no swapped copy is made — the kernel runs once per half on views (y may be None).
     """
     dev = _cuda(x, y, flow, disp_w, disp_b)
+    if swap_halves:
+        y = x
     if x.dtype != y.dtype or x.dtype not in _DT:
         raise ValueError(f"unsupported feature dtypes {x.dtype}/{y.dtype}")
     B, Cc, h, w = x.shape
@@ -130,11 +135,18 @@ def refiner_inputs(x: torch.Tensor, y: torch.Tensor, flow: torch.Tensor,
         dch = (dch + pad_to - 1) // pad_to * pad_to
     d = torch.empty((B, dch, h, w), device=dev, dtype=x.dtype, memory_format=torch.channels_last)
     lib = _lib.load()
-    _run("roma_refiner_gather", dict(B=B, C=Cc, h=h, w=w, r=r, E=E, esize=x.element_size()),
-         lambda: lib.roma_refiner_gather(
-             _ptr(x), _ptr(y), _ptr(flow), _s4(flow), _ptr(disp_w), _ptr(disp_b), float(disp_scale),
-             _ptr(d), dch, 0, Cc, (2 * Cc if E else -1), (2 * Cc + E if r > 0 else -1),
-             B, Cc, h, w, h1, w1, E, r, _DT[x.dtype], _stream(dev)))
+    if swap_halves:
+        if B % 2:
+            raise ValueError("swap_halves needs an even batch")
+        parts = [(x[:B // 2], x[B // 2:], flow[:B // 2], d[:B // 2]), (x[B // 2:], x[:B // 2], flow[B // 2:], d[B // 2:])]
+    else:
+        parts = [(x, y, flow, d)]
+    for xp, yp, fp_, dp in parts:
+        _run("roma_refiner_gather", dict(B=xp.shape[0], C=Cc, h=h, w=w, r=r, E=E, esize=x.element_size()),
+             lambda: lib.roma_refiner_gather(
+                 _ptr(xp), _ptr(yp), _ptr(fp_), _s4(fp_), _ptr(disp_w), _ptr(disp_b), float(disp_scale),
+                 _ptr(dp), dch, 0, Cc, (2 * Cc if E else -1), (2 * Cc + E if r > 0 else -1),
+                 xp.shape[0], Cc, h, w, h1, w1, E, r, _DT[x.dtype], _stream(dev)))
     return d
 
 
