@@ -214,12 +214,15 @@ __device__ __forceinline__ void tile_epilogue(const Problem& P, int b, int m0, i
         }
         const int nb0 = n0 + c0;
         if (P.epi == EPI_COS) {
+            // column norms of this 32-column group: one coalesced load, broadcast by shuffle
+            const float cn_lane = (nb0 + lane < P.N) ? __ldg(P.cn + (long long)b * P.scn + nb0 + lane) : 1.f;
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
                 const int n = nb0 + i;
+                const float cn_i = __shfl_sync(0xffffffffu, cn_lane, i);
                 float k;
                 if (m < P.M && n < P.N) {
-                    const float c = v[i] / (rn * __ldg(P.cn + (long long)b * P.scn + n) + P.eps);
+                    const float c = v[i] / (rn * cn_i + P.eps);
                     k = expf((c - 1.f) * P.inv_T);
                     if (m == n && !P.no_diag) k += P.diag_add;
                 } else {
@@ -371,11 +374,11 @@ static int launch_gemm_nt(const Launch& L, int batch, cudaStream_t st, const cha
 // lane 0 of warp 0 produces (waits `empty`, arms `full` with the byte count, issues the two box loads), lane 0 of
 // warp 1 issues tcgen05.mma and releases the stage with tcgen05.commit -> `empty`; all 8 warps run the epilogue.
 struct TmaMaps { CUtensorMap a[2], b[2]; };
-constexpr int kTmaStages = 3;                        // 3 x 32 KB: two CTAs per SM
+constexpr int kTmaStages = 2;                        // 2 x 32 KB: three CTAs per SM (the epilogue, not the main loop, bounds the Gram)
 constexpr size_t kTmaSmem = (size_t)kTmaStages * 2 * kPlaneBytes + 1024;
 
 template <typename T>
-__global__ void __launch_bounds__(kThreads, 2) gemm_nt_tma_kernel(const Launch L, const __grid_constant__ TmaMaps maps) {
+__global__ void __launch_bounds__(kThreads, 3) gemm_nt_tma_kernel(const Launch L, const __grid_constant__ TmaMaps maps) {
     extern __shared__ unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kTmaStages], empty_bar[kTmaStages], done_bar;
     __shared__ uint32_t tmem_slot;

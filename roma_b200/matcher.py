@@ -61,8 +61,16 @@ class RegressionMatcher(nn.Module):
         self.upsample_res = (14 * 16 * 6, 14 * 16 * 6)
         self.symmetric = symmetric
         self.sample_thresh = 0.05
+        self.overlap_encoder = True      # upsample-pass encoder on a side stream, concurrent with the coarse pass
+        self._streams = {}
 
     # ------------------------------------------------------------------------------------------ helpers
+    def _side_stream(self, device) -> "torch.cuda.Stream":
+        key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+        if key not in self._streams:
+            self._streams[key] = torch.cuda.Stream(device=device)
+        return self._streams[key]
+
     def get_output_resolution(self):
         return (self.h_resized, self.w_resized) if not self.upsample_preds else self.upsample_res
 
@@ -78,13 +86,13 @@ class RegressionMatcher(nn.Module):
         return self.encoder(x, upsample=upsample)
 
     def forward(self, batch, batched: bool = True, upsample: bool = False, scale_factor: float = 1):
-        pyr = self.extract_backbone_features(batch, upsample=upsample)
+        pyr = batch.get("pyramid") or self.extract_backbone_features(batch, upsample=upsample)
         f_q = {s: f.chunk(2)[0] for s, f in pyr.items()}
         f_s = {s: f.chunk(2)[1] for s, f in pyr.items()}
         return self.decoder(f_q, f_s, upsample=upsample, **(batch.get("corresps") or {}), scale_factor=scale_factor)
 
     def forward_symmetric(self, batch, batched: bool = True, upsample: bool = False, scale_factor: float = 1):
-        pyr = self.extract_backbone_features(batch, upsample=upsample)
+        pyr = batch.get("pyramid") or self.extract_backbone_features(batch, upsample=upsample)
         # support pyramid = query pyramid with the batch halves exchanged (matcher.py:459-463): the decoder swaps
         # after its projections instead of being handed a second, copied pyramid
         return self.decoder(pyr, None, upsample=upsample, **(batch.get("corresps") or {}), scale_factor=scale_factor,
@@ -128,8 +136,7 @@ class RegressionMatcher(nn.Module):
             coarse = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
                       "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
         symmetric = self.symmetric
-        corresps = self.forward_symmetric(coarse) if symmetric else self.forward(coarse)
-        cert16 = corresps[16]["certainty"] if self.attenuate_cert else None
+        fine, side = None, None
         if self.upsample_preds:
             hs, ws = self.upsample_res
             if tensor_in:
@@ -137,6 +144,24 @@ class RegressionMatcher(nn.Module):
             else:
                 fine = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
                         "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
+            if self.overlap_encoder:
+                # The VGG pyramid of the upsample pass does not depend on the coarse pass: run it on a second
+                # stream, started once the coarse ENCODER is enqueued, so its large convolutions fill the SMs the
+                # latency-bound coarse DECODER (GP solve chain, 40x40 / 70x70 refiners, 1600-token transformer)
+                # leaves idle.  Joined before the upsample decoder.
+                coarse["pyramid"] = self.extract_backbone_features(coarse, upsample=False)
+                cur = torch.cuda.current_stream(device)
+                side = self._side_stream(device)
+                side.wait_stream(cur)
+                with torch.cuda.stream(side):
+                    fine["pyramid"] = self.extract_backbone_features(fine, upsample=True)
+        corresps = self.forward_symmetric(coarse) if symmetric else self.forward(coarse)
+        cert16 = corresps[16]["certainty"] if self.attenuate_cert else None
+        if self.upsample_preds:
+            if side is not None:
+                cur.wait_stream(side)
+                for t in fine["pyramid"].values():
+                    t.record_stream(cur)               # allocated on the side stream, consumed (and freed) on this one
             scale_factor = math.sqrt(self.upsample_res[0] * self.upsample_res[1] / (self.w_resized * self.h_resized))
             fine["corresps"] = corresps[1]
             corresps = (self.forward_symmetric(fine, upsample=True, scale_factor=scale_factor) if symmetric

@@ -23,7 +23,7 @@ with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_sh
     for i in range(B):
         m.sample(warp[i], cert[i])
     torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=90))
+print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=160, max_name_column_width=90))
 
 if len(sys.argv) > 3 and sys.argv[3] == "shapes":
     with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof2:
