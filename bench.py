@@ -7,7 +7,7 @@
 
 One "step" = one pass of the hot path over one batch of synthetic input: `model.match(im_A, im_B, batched=True)`
 on `--batch` (default 8) pairs per GPU (BASELINE.json configs[1]; configs[2] is the same per-GPU micro-batch on
-2/4/8 GPUs) followed by `model.sample(warp, certainty, num=10000)` for every pair — the call sequence of the
+2/4/8 GPUs) followed by `model.sample_batch(warp, certainty, num=10000)` (= `sample` for every pair) — the call sequence of the
 reference's benchmarks.  Pairs are independent, so ranks shard them with no collective in the
 timed region ("weak" scaling: per-GPU work fixed); NCCL is used only for the barrier and the max-over-ranks time.
 
@@ -290,11 +290,11 @@ def main():
 
     def step(a, b, to_host: bool):
         warp, cert = model.match(a, b, batched=True, device=dev)
-        for i in range(args.batch):
-            m, c = model.sample(warp[i], cert[i], num=args.num, generator=gens[i])
-            if to_host:
-                out_host[i, :, :4].copy_(m, non_blocking=True)
-                out_host[i, :, 4].copy_(c, non_blocking=True)
+        ms, cs = model.sample_batch(warp, cert, num=args.num, generators=gens)      # `sample` for every pair
+        if to_host:
+            for i in range(args.batch):
+                out_host[i, :, :4].copy_(ms[i], non_blocking=True)
+                out_host[i, :, 4].copy_(cs[i], non_blocking=True)
 
     def barrier():
         torch.cuda.synchronize()

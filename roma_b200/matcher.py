@@ -71,6 +71,12 @@ class RegressionMatcher(nn.Module):
             self._streams[key] = torch.cuda.Stream(device=device)
         return self._streams[key]
 
+    def _second_stream(self, device) -> "torch.cuda.Stream":
+        key = ("b", torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device())
+        if key not in self._streams:
+            self._streams[key] = torch.cuda.Stream(device=device)
+        return self._streams[key]
+
     def get_output_resolution(self):
         return (self.h_resized, self.w_resized) if not self.upsample_preds else self.upsample_res
 
@@ -177,6 +183,30 @@ class RegressionMatcher(nn.Module):
         """matcher.py:468-495: threshold -> multinomial(4*num) -> kde -> multinomial(num)."""
         return ops.sample(matches, certainty, num=num, sample_thresh=self.sample_thresh,
                           sample_mode=self.sample_mode, generator=generator)
+
+    def sample_batch(self, matches, certainty, num: int = 10000, generators=None):
+        """`sample` for every pair of a batched `match` result: matches (B,H,W,4), certainty (B,H,W) ->
+        (list of (num,4), list of (num,)).  Same arithmetic and RNG consumption per pair as B calls of `sample`
+        (Philox offsets are assigned at enqueue time, in pair order); consecutive pairs alternate between two
+        streams so that one pair's latency-bound multinomial / top-k kernels run under another pair's kde."""
+        B = matches.shape[0]
+        dev = matches.device
+        cur = torch.cuda.current_stream(dev)
+        lanes = [self._side_stream(dev), self._second_stream(dev)]
+        for st in lanes:
+            st.wait_stream(cur)
+        ms, cs = [], []
+        for i in range(B):
+            with torch.cuda.stream(lanes[i % 2]):
+                m, c = ops.sample(matches[i], certainty[i], num=num, sample_thresh=self.sample_thresh,
+                                  sample_mode=self.sample_mode, generator=None if generators is None else generators[i])
+            ms.append(m)
+            cs.append(c)
+        for st in lanes:
+            cur.wait_stream(st)
+        for t in ms + cs:
+            t.record_stream(cur)
+        return ms, cs
 
     # ------------------------------------------------------------------------------------------ keypoints
     def match_keypoints(self, x_A, x_B, warp, certainty, return_tuple: bool = True, return_inds: bool = False):

@@ -226,3 +226,10 @@ def test_match_full_size_swap_symmetry(cuda):
     assert (c_ab[:, :, :864] - c_ba[:, :, 864:]).abs().max().item() < 5e-2
     m, c = model.sample(w_ab[0], c_ab[0], num=10000)
     assert m.shape == (10000, 4) and c.shape == (10000,)
+    # sample_batch == sample per pair with the same generators (two streams inside, same RNG consumption)
+    g1 = [torch.Generator(device=cuda).manual_seed(100 + i) for i in range(2)]
+    g2 = [torch.Generator(device=cuda).manual_seed(100 + i) for i in range(2)]
+    ms, cs = model.sample_batch(w_ab, c_ab, num=5000, generators=g1)
+    for i in range(2):
+        mi, ci = model.sample(w_ab[i], c_ab[i], num=5000, generator=g2[i])
+        assert torch.equal(ms[i], mi) and torch.equal(cs[i], ci)
