@@ -146,6 +146,11 @@ size_t roma_gp_workspace_bytes(int B, int Nx, int Ny, int C, int D);
 /* Testing / profiling aid: 0 = auto (tcgen05 tensor-core path when the shapes allow, default), 1 = force the fp32
  * SIMT path, 2 = require the tcgen05 path (ROMA_ERR_UNSUPPORTED from roma_gp_posterior when it cannot be used). */
 int roma_gp_set_path(int path);
+/* Schedule of the tcgen05 factorisation: 1 (default) = two lanes — the dependent chain diag -> panel -> syrk of the
+ * blocked Cholesky on a high-priority helper stream owned by the library (one per device), the block-column
+ * updates and all right-hand-side work one step behind on the caller's stream, ordered by events, forked from and
+ * joined to the caller's stream inside the call; 0 = every launch on the caller's stream (left-looking). */
+int roma_gp_set_lanes(int on);
 /* The tensor-core building block of K1, exposed for unit tests and timing: batched C = A * B^T with
  * A (batch, M, K), B (batch, N, K) row-major in `dtype`, C (batch, M, N) fp32.  fp32 operands are split on the
  * fly into `split` (2 or 3) bf16 planes (3 / 6 tcgen05.mma per k-step, fp32 TMEM accumulate); bf16 / fp16

@@ -104,6 +104,12 @@ extern "C" int roma_tc_set_tma(int on) {
 }
 namespace roma { namespace gp { static std::atomic<int> g_path{0}; } }   // 0 auto, 1 SIMT fp32, 2 tcgen05 (3-plane solve), 3 tcgen05 (2-plane solve)
 
+namespace roma { namespace gp { std::atomic<int> g_lanes{1}; } }
+extern "C" int roma_gp_set_lanes(int on) {
+    roma::gp::g_lanes.store(on ? 1 : 0);
+    return ROMA_OK;
+}
+
 extern "C" int roma_gp_set_path(int path) {
     if (path < 0 || path > 3) return roma::fail(ROMA_ERR_BAD_ARG, "roma_gp_set_path: path must be 0 (auto), 1 (simt) or 2 (tcgen05)");
     roma::gp::g_path.store(path);

@@ -26,6 +26,8 @@
 #pragma once
 #include "tc_gemm.cuh"
 #include "gp_simt.cuh"
+#include <atomic>
+#include <mutex>
 
 namespace roma {
 namespace gp {
@@ -206,6 +208,42 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
     }
 }
 
+// ---- two-lane schedule of the factorisation ---------------------------------------------------------
+// The dependent chain of the blocked Cholesky is  diag(k) -> panel_A(k) -> syrk(k) -> diag(k+1)  (small launches,
+// <= 12 x B tiles); everything else — the left-looking updates of the block column below the diagonal and ALL
+// right-hand-side work — only has to be finished one step later.  The chain therefore runs on a high-priority
+// helper stream owned by the library (one per device, created on first use, never destroyed) while the bulk stays
+// on the caller's stream; cudaEvents order the two lanes.  Fork/join are both on the caller's stream, so the call
+// is still "asynchronous on the passed stream" (and capturable into a CUDA graph).
+constexpr int kMaxLaneBlocks = 64;
+struct Lanes {
+    cudaStream_t chain = nullptr;
+    cudaEvent_t fork = nullptr, diag[kMaxLaneBlocks], upd[kMaxLaneBlocks], panel[kMaxLaneBlocks];
+    bool ok = false;
+};
+static Lanes* lanes_for_current_device() {
+    static std::mutex mu;
+    static Lanes* table[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    if (table[dev]) return table[dev]->ok ? table[dev] : nullptr;
+    Lanes* l = new Lanes();
+    table[dev] = l;
+    int least = 0, greatest = 0;
+    if (cudaDeviceGetStreamPriorityRange(&least, &greatest) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaStreamCreateWithPriority(&l->chain, cudaStreamNonBlocking, greatest) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    bool ok = cudaEventCreateWithFlags(&l->fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < kMaxLaneBlocks; ++i)
+        ok = cudaEventCreateWithFlags(&l->diag[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&l->upd[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&l->panel[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { cudaGetLastError(); return nullptr; }
+    l->ok = true;
+    return l;
+}
+extern std::atomic<int> g_lanes;         // 1 (default): two-lane schedule; 0: everything on the caller's stream, left-looking
+
 struct WorkspaceTC {
     float *xn, *yn, *A, *R, *Ld;
     int Mp, nb;
@@ -281,6 +319,63 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
         diag_cfg = true;
     }
 
+    Lanes* lanes = (g_lanes.load() != 0 && nb > 1 && nb <= kMaxLaneBlocks) ? lanes_for_current_device() : nullptr;
+    if (lanes) {
+        // 3'. two-lane schedule.  Diagonal tiles are kept up to date right-looking (syrk after every panel), the rest of
+        //     the block column and the right-hand sides left-looking, one step behind the chain.
+        //       chain (sc):  diag(k) . [wait upd(k)] panel_A(k) . syrk(k)
+        //       bulk  (st):  [wait panel(k-1)] update_off(k): A[k+1:, k] and R[:, k] . [wait diag(k)] panel_R(k)
+        cudaStream_t sc = lanes->chain;
+#define ROMA_CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail((int)e_, "gp lanes: %s", cudaGetErrorString(e_)); } while (0)
+        ROMA_CU(cudaEventRecord(lanes->fork, st));
+        ROMA_CU(cudaStreamWaitEvent(sc, lanes->fork, 0));
+        for (int k = 0; k < nb; ++k) {
+            const int k0 = k * kDB, rem = Mp - k0 - kDB;
+            const float* Lk = w.A + (long long)k0 * Mp;                 // L_{k,0:k}: 128 rows x k0
+            const float* Linv = w.Ld + (long long)k * kDB * kDB;
+            float* Ap = w.A + (long long)(k0 + kDB) * Mp + k0;          // block column k below the diagonal
+            diag_block_kernel<<<B, 256, kDiagSmem, sc>>>(w.A, w.Ld, Mp, k0, sA, sLd, k);
+            if ((rc = check_launch("gp diag"))) return rc;
+            ROMA_CU(cudaEventRecord(lanes->diag[k], sc));
+            if (k > 0) {
+                ROMA_CU(cudaStreamWaitEvent(st, lanes->panel[k - 1], 0));       // L[:, 0:k] complete
+                Launch L{};
+                int np = 0;
+                if (rem > 0) {
+                    L.p[np] = make_problem(Lk + (long long)kDB * Mp, Lk, Ap, rem, kDB, k0, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
+                    L.tiles0 = L.p[np].tiles_m;
+                    ++np;
+                }
+                L.p[np] = make_problem(w.R, Lk, w.R + k0, RR, kDB, k0, Mp, Mp, Mp, sR, sA, sR, EPI_SUB);
+                if (np == 0) L.tiles0 = L.p[0].tiles_m;
+                L.nprob = np + 1;
+                if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update"))) return rc;
+                ROMA_CU(cudaEventRecord(lanes->upd[k], st));
+            }
+            if (rem > 0) {
+                if (k > 0) ROMA_CU(cudaStreamWaitEvent(sc, lanes->upd[k], 0));
+                Launch L{};
+                L.p[0] = make_problem(Ap, Linv, Ap, rem, kDB, kDB, Mp, kDB, Mp, sA, sLd, sA, EPI_STORE);
+                L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
+                if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, sc, "gp panel A"))) return rc;
+                ROMA_CU(cudaEventRecord(lanes->panel[k], sc));
+                Launch S{};                                             // A_ii -= L_ik L_ik^T for every i > k
+                S.p[0] = make_problem(Ap, Ap, w.A + (long long)(k0 + kDB) * Mp + (k0 + kDB), rem, rem, kDB, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
+                S.p[0].diag_only = 1;
+                S.nprob = 1; S.tiles0 = S.p[0].tiles_m;
+                if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(S, B, sc, "gp syrk"))) return rc;
+            }
+            ROMA_CU(cudaStreamWaitEvent(st, lanes->diag[k], 0));
+            {
+                Launch L{};
+                L.p[0] = make_problem(w.R + k0, Linv, w.R + k0, RR, kDB, kDB, Mp, kDB, Mp, sR, sLd, sR, EPI_STORE);
+                L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
+                if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp panel R"))) return rc;
+            }
+        }
+#undef ROMA_CU
+        // the chain's last operation is diag(nb-1), which panel_R(nb-1) waited for: the lanes are joined
+    } else
     // 3. left-looking blocked Cholesky with the transposed right-hand sides riding along
     for (int k = 0; k < nb; ++k) {
         const int k0 = k * kDB, rows = Mp - k0, rem = rows - kDB;

@@ -39,6 +39,7 @@ struct Problem {
     int lda, ldb, ldc, ldct;
     int tiles_m, tiles_n;
     int lower_only;                      // skip tiles strictly above the diagonal (tn > tm)
+    int diag_only;                       // tile t is (t, t): only the diagonal tiles exist (tiles = tiles_m)
     int no_diag;                         // EPI_COS: no diag_add / identity padding (rectangular cross kernel)
     int epi;
     int store_m, store_n;                // store bounds (>= M, N when padded rows/cols must be written)
@@ -275,7 +276,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_nt_kernel(const Launch L) {
     const int pi = (L.nprob > 1 && t >= L.tiles0) ? 1 : 0;
     if (pi) t -= L.tiles0;
     const Problem& P = L.p[pi];
-    const int tm = t / P.tiles_n, tn = t - tm * P.tiles_n;
+    const int tm = P.diag_only ? t : t / P.tiles_n, tn = P.diag_only ? t : t - tm * P.tiles_n;
     if (P.lower_only && tn > tm) return;
     const int b = blockIdx.y;
     const int m0 = tm * BM, n0 = tn * BN;
@@ -361,7 +362,7 @@ static int launch_gemm_nt(const Launch& L, int batch, cudaStream_t st, const cha
         if (e != cudaSuccess) return fail((int)e, "%s: smem opt-in (%zu B): %s", what, smem, cudaGetErrorString(e));
         configured = true;
     }
-    int tiles = L.tiles0 + (L.nprob > 1 ? L.p[1].tiles_m * L.p[1].tiles_n : 0);
+    int tiles = L.tiles0 + (L.nprob > 1 ? (L.p[1].diag_only ? L.p[1].tiles_m : L.p[1].tiles_m * L.p[1].tiles_n) : 0);
     if (tiles <= 0 || batch <= 0) return ROMA_OK;
     gemm_nt_kernel<T, SPLIT><<<dim3(tiles, batch), kThreads, smem, st>>>(L);
     return check_launch(what);
@@ -387,7 +388,7 @@ __global__ void __launch_bounds__(kThreads, 3) gemm_nt_tma_kernel(const Launch L
     const int pi = (L.nprob > 1 && t >= L.tiles0) ? 1 : 0;
     if (pi) t -= L.tiles0;
     const Problem& P = L.p[pi];
-    const int tm = t / P.tiles_n, tn = t - tm * P.tiles_n;
+    const int tm = P.diag_only ? t : t / P.tiles_n, tn = P.diag_only ? t : t - tm * P.tiles_n;
     if (P.lower_only && tn > tm) return;
     const int b = blockIdx.y;
     const int m0 = tm * BM, n0 = tn * BN;
@@ -463,7 +464,7 @@ extern std::atomic<int> g_tc_tma;      // 1 (default): TMA-fed main loop for 16-
 template <typename T>
 static int launch_gemm_nt_16(const Launch& L, int batch, cudaStream_t st, const char* what, int dtype) {
     static_assert(sizeof(T) == 2, "16-bit operands");
-    int tiles = L.tiles0 + (L.nprob > 1 ? L.p[1].tiles_m * L.p[1].tiles_n : 0);
+    int tiles = L.tiles0 + (L.nprob > 1 ? (L.p[1].diag_only ? L.p[1].tiles_m : L.p[1].tiles_m * L.p[1].tiles_n) : 0);
     if (tiles <= 0 || batch <= 0) return ROMA_OK;
     TmaMaps maps;
     bool ok = g_tc_tma.load() != 0;
@@ -491,7 +492,7 @@ static inline Problem make_problem(const void* A, const void* B, float* C, int M
     p.sA = sA; p.sB = sB; p.sC = sC; p.sCt = 0;
     p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.ldct = 0;
     p.tiles_m = (M + BM - 1) / BM; p.tiles_n = (N + BN - 1) / BN;
-    p.lower_only = 0; p.no_diag = 0; p.epi = epi; p.store_m = M; p.store_n = N;
+    p.lower_only = 0; p.diag_only = 0; p.no_diag = 0; p.epi = epi; p.store_m = M; p.store_n = N;
     p.rn = p.cn = nullptr; p.srn = p.scn = 0; p.eps = 0.f; p.inv_T = 0.f; p.diag_add = 0.f;
     return p;
 }

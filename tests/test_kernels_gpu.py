@@ -201,6 +201,46 @@ def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2, path):
     assert err(got_tc, got_simt) < 5e-4
 
 
+@pytest.mark.parametrize("h1,w1,h2,w2,b", [(40, 40, 40, 40, 4), (13, 21, 19, 15, 2), (30, 30, 24, 16, 3)])
+def test_gp_two_lane_schedule(ops, cuda, h1, w1, h2, w2, b):
+    """The two-lane schedule (chain diag -> panel -> syrk on the library's helper stream, bulk updates one step
+    behind on the caller's stream) against the single-stream left-looking schedule and the fp64 oracle; repeated
+    calls on a non-default stream are bit-reproducible (no race between the lanes or between calls)."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(77)
+    C, D = 512, 512
+    base = O.bilinear_resize(torch.randn(b, C, 5, 5, generator=g), (h1, w1))
+    x = (base + 0.4 * torch.randn(b, C, h1, w1, generator=g)).to(torch.bfloat16)
+    y = (O.bilinear_resize(base, (h2, w2)) + 0.4 * torch.randn(b, C, h2, w2, generator=g)).to(torch.bfloat16)
+    pw = torch.randn(D, 2, generator=g) * 0.5; pb = torch.randn(D, generator=g) * 0.5
+    want = O.gp_posterior(x.float(), y.float(), pw, pb, dtype=torch.float64)
+    ref32 = O.gp_posterior(x.float(), y.float(), pw, pb)
+    xc, yc, pwc, pbc = x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda)
+    try:
+        assert lib.roma_gp_set_path(3) == 0
+        assert lib.roma_gp_set_lanes(0) == 0
+        single = ops.gp_posterior(xc, yc, pwc, pbc)
+        assert lib.roma_gp_set_lanes(1) == 0
+        lanes = ops.gp_posterior(xc, yc, pwc, pbc)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        reps = []
+        with torch.cuda.stream(side):
+            for _ in range(4):
+                reps.append(ops.gp_posterior(xc, yc, pwc, pbc))
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+    finally:
+        lib.roma_gp_set_lanes(1)
+        lib.roma_gp_set_path(0)
+    e_l, e_s, e_ref = err(lanes, want), err(single, want), err(ref32, want)
+    assert e_l < max(10 * e_ref, 2e-4), (e_l, e_s, e_ref)
+    assert err(lanes, single) < 2e-4
+    for r in reps:
+        assert torch.equal(r, lanes)
+
+
 @pytest.mark.parametrize("dtype,split,tol", [(torch.float32, 3, 2e-6), (torch.float32, 2, 2e-5), (torch.bfloat16, 1, 2e-6), (torch.float16, 1, 2e-6)])
 @pytest.mark.parametrize("batch,M,N,K", [(2, 300, 200, 136), (1, 128, 128, 64), (3, 129, 257, 520)])
 def test_tc_gemm_nt(ops, cuda, dtype, split, tol, batch, M, N, K):

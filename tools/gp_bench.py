@@ -35,16 +35,20 @@ N = side * side
 flops = B * (2.0 * N * N * C * 2 + N ** 3 / 3 + 2.0 * N * N * D + 2.0 * N * N * D)
 names = {1: "simt", 2: "tcgen05 split3", 3: "tcgen05 split2"}
 for path in paths:
-    lib.roma_gp_set_path(path)
-    for _ in range(2):
-        mu = ops.gp_posterior(xd, yd, pwd, pbd)
-    torch.cuda.synchronize()
-    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s.record()
-    for _ in range(5):
-        mu = ops.gp_posterior(xd, yd, pwd, pbd)
-    e.record(); torch.cuda.synchronize()
-    ms = s.elapsed_time(e) / 5
-    print(json.dumps({"path": names[path], "N": N, "B": B, "dtype": str(dt), "ms": round(ms, 3),
-                      "alg_TFLOPs": round(flops / ms / 1e9, 1), "err_vs_fp64": (mu[:1].cpu() - want).abs().max().item()}))
+    for lanes in ((1, 0) if path != 1 else (1,)):
+        lib.roma_gp_set_path(path)
+        lib.roma_gp_set_lanes(lanes)
+        for _ in range(2):
+            mu = ops.gp_posterior(xd, yd, pwd, pbd)
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(5):
+            mu = ops.gp_posterior(xd, yd, pwd, pbd)
+        e.record(); torch.cuda.synchronize()
+        ms = s.elapsed_time(e) / 5
+        print(json.dumps({"path": names[path], "schedule": "two-lane" if lanes else "single-stream", "N": N, "B": B, "dtype": str(dt),
+                          "ms": round(ms, 3), "alg_TFLOPs": round(flops / ms / 1e9, 1),
+                          "err_vs_fp64": (mu[:1].cpu() - want).abs().max().item()}))
 lib.roma_gp_set_path(0)
+lib.roma_gp_set_lanes(1)
