@@ -180,8 +180,11 @@ int roma_gp_posterior(const void* x, const void* y, const float* pos_w, const fl
  *   path; a smaller buffer of at least N floats is accepted and only reduces parallelism / disables the table).
  */
 size_t roma_kde_workspace_bytes(int N);
-/* Testing aid: 1 = evaluate the half-precision op chain directly per pair instead of through the (bit-identical)
- * lookup table of the chain's single half-valued argument; 0 = auto (default). */
+/* Half path selection.  0 = auto (default): the squared distance d2 = half(|a|^2 + |b|^2 - 2ab) of every pair comes
+ * from a warp-level tensor-core product over the 6-wide augmented half vectors (what ATen's _euclidean_dist feeds
+ * the GPU's HGEMM), the rest of the chain from a lookup table of its single half-valued argument.  Testing aids:
+ * 1 = evaluate the whole op chain directly per pair with sequential fp32 FMAs; 2 = table + sequential FMAs
+ * (bit-identical per pair to 1). */
 int roma_kde_set_direct(int direct);
 int roma_kde(const float* x, int N, int down, double std, int half,
              float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream);

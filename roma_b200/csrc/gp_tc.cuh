@@ -65,7 +65,7 @@ posenc_t_kernel(float* __restrict__ R, const float* __restrict__ pw, const float
 // S (lower) <- chol(A_kk); V <- S^-1 (lower).  L_kk is written back into A (lower part of the block; nothing
 // reads it again, it is kept for inspection) and V into Ld.
 constexpr int kDiagLd = kDB + 1;
-constexpr size_t kDiagSmem = (size_t)2 * kDB * kDiagLd * sizeof(float) + 32 * 33 * sizeof(float);
+constexpr size_t kDiagSmem = (size_t)2 * kDB * kDiagLd * sizeof(float) + 32 * 33 * sizeof(float) + kDB * sizeof(float);
 
 __global__ void __launch_bounds__(256)
 diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0, long long sA, long long sLd, int kblk) {
@@ -73,6 +73,7 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
     float (*S)[kDiagLd] = reinterpret_cast<float (*)[kDiagLd]>(dsm);
     float (*V)[kDiagLd] = reinterpret_cast<float (*)[kDiagLd]>(dsm + kDB * kDiagLd);
     float (*Tm)[33] = reinterpret_cast<float (*)[33]>(dsm + 2 * kDB * kDiagLd);
+    float* invd = dsm + 2 * kDB * kDiagLd + 32 * 33;                 // 1 / L_jj
     const int b = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     float* Ab = A + (long long)b * sA + (long long)k0 * ld + k0;
     float* Lo = Ld + (long long)b * sLd + (long long)kblk * kDB * kDB;
@@ -96,8 +97,12 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
             for (int c = 0; c < 32; ++c) a[c] = S[j0 + lane][j0 + c];
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-                const float d = sqrtf(__shfl_sync(0xffffffffu, a[j], j));
-                a[j] = (lane == j) ? d : a[j] / d;
+                // 1/sqrt once per column (MUFU.RSQ, 2 ulp) instead of an IEEE sqrt and 32 divisions on the critical path;
+                // the same reciprocal scales the column here, the panel rows below and the inverse further down
+                const float piv = __shfl_sync(0xffffffffu, a[j], j);
+                const float rinv = rsqrtf(piv);
+                a[j] = (lane == j) ? piv * rinv : a[j] * rinv;
+                if (lane == j) invd[j0 + j] = rinv;
 #pragma unroll
                 for (int k = j + 1; k < 32; ++k) {
                     const float lk = __shfl_sync(0xffffffffu, a[j], k);
@@ -120,7 +125,7 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
 #pragma unroll
                     for (int t = 0; t < 32; ++t)
                         if (t < c) s = fmaf(-x[t], S[j0 + c][j0 + t], s);
-                    x[c] = s / S[j0 + c][j0 + c];
+                    x[c] = s * invd[j0 + c];
                 }
 #pragma unroll
                 for (int c = 0; c < 32; ++c) S[r][j0 + c] = x[c];
@@ -167,7 +172,7 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
 #pragma unroll
             for (int t = 0; t < 32; ++t)
                 if (t < i) s = fmaf(-S[j0 + i][j0 + t], x[t], s);            // x[t] == 0 for t < lane
-            x[i] = (i >= lane) ? s / S[j0 + i][j0 + i] : 0.f;
+            x[i] = (i >= lane) ? s * invd[j0 + i] : 0.f;
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) V[j0 + i][j0 + lane] = x[i];

@@ -177,6 +177,111 @@ kde_partial_lut_kernel(const float* __restrict__ x, int N, int M, int down, cons
         if (i0 + u < N) partial[(long long)split * N + i0 + u] = acc[u];
 }
 
+// ---- half mode, table-driven, distances on the tensor cores ------------------------------------------------------
+// The reference's half cdist IS a matrix product (ATen _euclidean_dist: [-2a, |a|^2, 1] . [b, 1, |b|^2] over 6-wide
+// augmented half vectors, fp32 accumulate, rounded to half; on CUDA it runs as a tensor-core HGEMM).  Here the same
+// product is one warp-level mma.sync.m16n8k8 (f16 x f16 -> f32, K padded 6 -> 8 with zeros; every product is exact
+// in fp32) per 16 queries x 8 reference points: the 6 FMUL2/FFMA2/FADD2 per pair of the SIMT table kernel disappear
+// and what is left per pair is the half pack, the two 16-bit SIMD clamps, the table lookup and the fp32 add.
+// A warp keeps kKdeQT query tiles (A fragments) in registers and streams the reference points (B fragments, one
+// conflict-free LDS.32 per thread per 8 points) against all of them.  Only the fp32 summation order inside the
+// product differs from the sequential chain of kde_partial_kernel<true>: a pair can land on the neighbouring half
+// value of d2 when the fp32 sum is within an ulp of a rounding boundary (tests/test_kernels_gpu.py bounds the effect
+// on the densities: at most one half ulp on a small fraction of the rows).
+constexpr int kKdeQT = 8;                // 16-query tiles per warp: 128 queries per warp, 1024 per block
+
+__device__ __forceinline__ void mma_m16n8k8_f16(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%7, %7, %7, %7};"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3]) : "r"(a0), "r"(a1), "r"(b0), "f"(0.f));
+}
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
+    const __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+__global__ void __launch_bounds__(kKdeThreads)
+kde_partial_mma_kernel(const float* __restrict__ x, int N, int M, int down, const float* __restrict__ lut_g,
+                       int cutoff, float* __restrict__ partial, int nsplit) {
+    extern __shared__ float ksm[];
+    float* lut = ksm;                                               // [cutoff + 1]; every entry >= cutoff is 0
+    uint4* ref = reinterpret_cast<uint4*>(ksm + ((cutoff + 1 + 3) & ~3));      // [tile]: halves (x, y, z, w, 1, |r|^2, 0, 0)
+    for (int t = threadIdx.x; t <= cutoff; t += kKdeThreads) lut[t] = (t < cutoff) ? lut_g[t] : 0.f;
+
+    const int split = blockIdx.y;
+    const int per = (M + nsplit - 1) / nsplit;
+    const int j_begin = split * per, j_end = min(M, j_begin + per);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+    const int q0 = (blockIdx.x * (kKdeThreads / 32) + warp) * (16 * kKdeQT);
+
+    // A fragments: row g (a0) and g + 8 (a1) of each query tile, columns 2 t4, 2 t4 + 1 of (-2x, -2y, -2z, -2w, |q|^2, 1, 0, 0)
+    uint32_t a[kKdeQT][2];
+    float acc[kKdeQT][2];
+#pragma unroll
+    for (int qt = 0; qt < kKdeQT; ++qt) {
+#pragma unroll
+        for (int hr = 0; hr < 2; ++hr) {
+            const int q = q0 + qt * 16 + g + 8 * hr;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            float one = 0.f;
+            if (q < N) { v = reinterpret_cast<const float4*>(x)[q]; one = 1.f; }
+            v = make_float4(rh(v.x), rh(v.y), rh(v.z), rh(v.w));
+            const float n = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
+            const float lo = t4 == 0 ? -2.f * v.x : t4 == 1 ? -2.f * v.z : t4 == 2 ? n : 0.f;
+            const float hi = t4 == 0 ? -2.f * v.y : t4 == 1 ? -2.f * v.w : t4 == 2 ? one : 0.f;
+            a[qt][hr] = pack_h2(lo, hi);
+            acc[qt][hr] = 0.f;
+        }
+    }
+    const unsigned cut2 = (unsigned)cutoff | ((unsigned)cutoff << 16);
+    const uint32_t* refw = reinterpret_cast<const uint32_t*>(ref) + g * 4 + t4;     // word t4 of point g of a group of 8
+    for (int j0 = j_begin; j0 < j_end; j0 += kKdeTile) {
+        const int n = min(kKdeTile, j_end - j0);
+        const int groups = (n + 7) >> 3;
+        __syncthreads();
+        for (int t = threadIdx.x; t < groups * 8; t += kKdeThreads) {
+            uint4 pk;
+            if (t < n) {
+                float4 r = reinterpret_cast<const float4*>(x)[(long long)(j0 + t) * down];
+                r = make_float4(rh(r.x), rh(r.y), rh(r.z), rh(r.w));
+                const float rn = rh(rh(r.x * r.x) + rh(r.y * r.y) + rh(r.z * r.z) + rh(r.w * r.w));
+                pk = make_uint4(pack_h2(r.x, r.y), pack_h2(r.z, r.w), pack_h2(1.f, rn), 0u);
+            } else {
+                pk = make_uint4(0u, 0u, pack_h2(0.f, 60000.f), 0u);       // tail of the last group: far beyond the cutoff -> contributes 0
+            }
+            ref[t] = pk;
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int s = 0; s < groups; ++s) {
+            const uint32_t b0 = refw[s * 32];
+#pragma unroll
+            for (int qt = 0; qt < kKdeQT; ++qt) {
+                float d[4];
+                mma_m16n8k8_f16(d, a[qt][0], a[qt][1], b0);
+                // half bit patterns of d2; negative -> entry 0 (clamp_min(0)), beyond the table / inf -> `cutoff` (0)
+                unsigned u0 = __vminu2(__vmaxs2(pack_h2(d[0], d[1]), 0u), cut2);
+                unsigned u1 = __vminu2(__vmaxs2(pack_h2(d[2], d[3]), 0u), cut2);
+                acc[qt][0] += lut[u0 & 0xffffu];
+                acc[qt][1] += lut[u1 & 0xffffu];
+                acc[qt][0] += lut[u0 >> 16];
+                acc[qt][1] += lut[u1 >> 16];
+            }
+        }
+    }
+    // the four threads of a quad hold the columns of the same query rows: fixed-order butterfly, thread 0 stores
+#pragma unroll
+    for (int qt = 0; qt < kKdeQT; ++qt) {
+#pragma unroll
+        for (int hr = 0; hr < 2; ++hr) {
+            float v = acc[qt][hr];
+            v += __shfl_xor_sync(0xffffffffu, v, 1);
+            v += __shfl_xor_sync(0xffffffffu, v, 2);
+            const int q = q0 + qt * 16 + g + 8 * hr;
+            if (t4 == 0 && q < N) partial[(long long)split * N + q] = v;
+        }
+    }
+}
+
 __global__ void kde_finalize_kernel(const float* __restrict__ partial, int N, int nsplit, int half,
                                     float* __restrict__ density, float* __restrict__ p_out, const int* __restrict__ poison) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -217,9 +322,10 @@ extern "C" size_t roma_kde_workspace_bytes(int N) {
     return (size_t)64 * (size_t)N * sizeof(float) + roma::kKdeLutBytes;
 }
 
-// 0 = auto (table-driven half path when its table fits), 1 = always the direct op chain (testing aid)
+// 0 = auto (half: table-driven with the distances on the tensor cores, when the table fits), 1 = always the direct
+// op chain, 2 = table-driven with the SIMT FFMA2 distance chain (1 and 2 are testing aids)
 namespace roma { static int g_kde_direct = 0; }
-extern "C" int roma_kde_set_direct(int direct) { roma::g_kde_direct = direct ? 1 : 0; return ROMA_OK; }
+extern "C" int roma_kde_set_direct(int direct) { roma::g_kde_direct = (direct == 1 || direct == 2) ? direct : 0; return ROMA_OK; }
 
 extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
                            float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream) {
@@ -243,7 +349,7 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
     int* poison = nullptr;
     // table-driven half path: the cutoff is a property of std alone; evaluate it on the host with the same
     // half arithmetic (exp(-s/(2 std^2)) < 2^-25 rounds to 0) so no device round trip is needed to size smem.
-    bool use_lut = half && !g_kde_direct && workspace_bytes >= (size_t)N * sizeof(float) + kKdeLutBytes;
+    bool use_lut = half && g_kde_direct != 1 && workspace_bytes >= (size_t)N * sizeof(float) + kKdeLutBytes;
     int cutoff_bound = 0;
     if (use_lut) {
         // s beyond which exp underflows to 0 in half: exp(-s*inv) < 2^-25  <=>  s > 25 ln2 / inv ; +12.5% margin
@@ -265,12 +371,29 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
             if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
             cfg = true;
         }
-        const int qblocks = (N + kKdeThreads * kQPT - 1) / (kKdeThreads * kQPT);
-        int ns = (2 * 3 * sm_count() + qblocks - 1) / qblocks;
-        ns = ns < 1 ? 1 : (ns > nsplit ? nsplit : ns);
-        if (ns > (M + 255) / 256) ns = (M + 255) / 256;
-        nsplit = ns;
-        kde_partial_lut_kernel<<<dim3(qblocks, nsplit), kKdeThreads, smem, st>>>(x, N, M, down, lut, cutoff_bound, partial, nsplit);
+        if (g_kde_direct == 2) {
+            const int qblocks = (N + kKdeThreads * kQPT - 1) / (kKdeThreads * kQPT);
+            int ns = (2 * 3 * sm_count() + qblocks - 1) / qblocks;
+            ns = ns < 1 ? 1 : (ns > nsplit ? nsplit : ns);
+            if (ns > (M + 255) / 256) ns = (M + 255) / 256;
+            nsplit = ns;
+            kde_partial_lut_kernel<<<dim3(qblocks, nsplit), kKdeThreads, smem, st>>>(x, N, M, down, lut, cutoff_bound, partial, nsplit);
+        } else {
+            static bool cfg_mma = false;
+            if (!cfg_mma) {
+                cudaError_t e = cudaFuncSetAttribute(kde_partial_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((kLutMax + 4) * sizeof(float)) + kKdeTile * 16));
+                if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
+                cfg_mma = true;
+            }
+            const size_t smem_mma = ((size_t)(cutoff_bound + 1 + 3) & ~(size_t)3) * sizeof(float) + kKdeTile * sizeof(uint4);
+            const int qper = (kKdeThreads / 32) * 16 * kKdeQT;                  // queries per block
+            const int qblocks = (N + qper - 1) / qper;
+            int ns = (2 * 3 * sm_count() + qblocks - 1) / qblocks;              // >= 2 waves of 3 resident blocks per SM
+            ns = ns < 1 ? 1 : (ns > nsplit ? nsplit : ns);
+            if (ns > (M + 255) / 256) ns = (M + 255) / 256;
+            nsplit = ns;
+            kde_partial_mma_kernel<<<dim3(qblocks, nsplit), kKdeThreads, smem_mma, st>>>(x, N, M, down, lut, cutoff_bound, partial, nsplit);
+        }
         if ((rc = check_launch("roma_kde(lut)", 2))) return rc;
     } else {
         if (half) kde_partial_kernel<true><<<grid, kKdeThreads, 0, st>>>(x, N, M, down, inv_two_var, partial, nsplit);

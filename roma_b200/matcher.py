@@ -61,7 +61,8 @@ class RegressionMatcher(nn.Module):
         self.upsample_res = (14 * 16 * 6, 14 * 16 * 6)
         self.symmetric = symmetric
         self.sample_thresh = 0.05
-        self.overlap_encoder = True      # upsample-pass encoder on a side stream, concurrent with the coarse pass
+        self.overlap_encoder = True      # upsample-pass encoder concurrent with the coarse decoder (second stream)
+        self.decoder_priority = True     # ... with the coarse decoder on a high-priority stream
         self._streams = {}
 
     # ------------------------------------------------------------------------------------------ helpers
@@ -69,6 +70,12 @@ class RegressionMatcher(nn.Module):
         key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
         if key not in self._streams:
             self._streams[key] = torch.cuda.Stream(device=device)
+        return self._streams[key]
+
+    def _priority_stream(self, device) -> "torch.cuda.Stream":
+        key = ("hi", torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device())
+        if key not in self._streams:
+            self._streams[key] = torch.cuda.Stream(device=device, priority=-1)
         return self._streams[key]
 
     def _second_stream(self, device) -> "torch.cuda.Stream":
@@ -142,7 +149,7 @@ class RegressionMatcher(nn.Module):
             coarse = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
                       "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
         symmetric = self.symmetric
-        fine, side = None, None
+        fine, side, corresps = None, None, None
         if self.upsample_preds:
             hs, ws = self.upsample_res
             if tensor_in:
@@ -151,17 +158,33 @@ class RegressionMatcher(nn.Module):
                 fine = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
                         "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
             if self.overlap_encoder:
-                # The VGG pyramid of the upsample pass does not depend on the coarse pass: run it on a second
-                # stream, started once the coarse ENCODER is enqueued, so its large convolutions fill the SMs the
+                # The VGG pyramid of the upsample pass does not depend on the coarse pass: run the two concurrently,
+                # started once the coarse ENCODER is enqueued, so its large convolutions fill the SMs the
                 # latency-bound coarse DECODER (GP solve chain, 40x40 / 70x70 refiners, 1600-token transformer)
                 # leaves idle.  Joined before the upsample decoder.
                 coarse["pyramid"] = self.extract_backbone_features(coarse, upsample=False)
                 cur = torch.cuda.current_stream(device)
-                side = self._side_stream(device)
-                side.wait_stream(cur)
-                with torch.cuda.stream(side):
+                if self.decoder_priority:
+                    # the pyramid stays on the caller's stream (enqueued first: few, long kernels) and the coarse
+                    # decoder goes to a HIGH-PRIORITY stream: whenever thread blocks of a convolution retire, the
+                    # decoder's short dependent kernels are scheduled ahead of the convolution's next blocks
+                    hi = self._priority_stream(device)
+                    hi.wait_stream(cur)
                     fine["pyramid"] = self.extract_backbone_features(fine, upsample=True)
-        corresps = self.forward_symmetric(coarse) if symmetric else self.forward(coarse)
+                    with torch.cuda.stream(hi):
+                        corresps = self.forward_symmetric(coarse) if symmetric else self.forward(coarse)
+                    cur.wait_stream(hi)
+                    for sc in corresps.values():
+                        for t in sc.values():
+                            if torch.is_tensor(t):
+                                t.record_stream(cur)   # allocated on the priority stream, consumed (and freed) on this one
+                else:
+                    side = self._side_stream(device)
+                    side.wait_stream(cur)
+                    with torch.cuda.stream(side):
+                        fine["pyramid"] = self.extract_backbone_features(fine, upsample=True)
+        if corresps is None:
+            corresps = self.forward_symmetric(coarse) if symmetric else self.forward(coarse)
         cert16 = corresps[16]["certainty"] if self.attenuate_cert else None
         if self.upsample_preds:
             if side is not None:
