@@ -233,3 +233,54 @@ def test_match_full_size_swap_symmetry(cuda):
     for i in range(2):
         mi, ci = model.sample(w_ab[i], c_ab[i], num=5000, generator=g2[i])
         assert torch.equal(ms[i], mi) and torch.equal(cs[i], ci)
+
+
+# ------------------------------------------------------------------------------------------------ config 4 (672 -> 1344)
+def test_gp_config4_n2304_vs_fp64_oracle(ops, cuda):
+    """BASELINE config 4: the GP at 48 x 48 = 2304 tokens (18 diagonal blocks of the blocked Cholesky) against the
+    fp64 oracle, both schedules, fp32 and bf16 features."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(4)
+    base = O.bilinear_resize(torch.randn(1, 512, 6, 6, generator=g), (48, 48))
+    x32 = base + 0.5 * torch.randn(1, 512, 48, 48, generator=g)
+    y32 = base * 0.7 + 0.5 * torch.randn(1, 512, 48, 48, generator=g)
+    pw = torch.randn(512, 2, generator=g) * 0.5
+    pb = torch.randn(512, generator=g) * 0.5
+    for dt in (torch.bfloat16, torch.float32):
+        x, y = x32.to(dt), y32.to(dt)
+        want = O.gp_posterior(x.float(), y.float(), pw, pb, dtype=torch.float64)
+        try:
+            for lanes in (1, 0):
+                lib.roma_gp_set_lanes(lanes)
+                got = ops.gp_posterior(x.repeat(3, 1, 1, 1).to(cuda), y.repeat(3, 1, 1, 1).to(cuda), pw.to(cuda), pb.to(cuda))
+                assert got.shape == (3, 512, 48, 48)
+                assert (got[0].float().cpu() - want[0].float()).abs().max().item() < 1e-3, (dt, lanes)
+                assert torch.equal(got[1], got[0]) and torch.equal(got[2], got[0])
+        finally:
+            lib.roma_gp_set_lanes(1)
+
+
+@pytest.mark.parametrize("coarse,up", [((672, 672), (1344, 1344)), ((560, 560), (864, 1152))])
+def test_match_config4_and_nonsquare_swap_symmetry(cuda, coarse, up):
+    """BASELINE config 4 (672 -> 1344: local correlation at 168^2 / 336^2, gather-only at 672^2 / 1344^2) and the
+    reference demo's non-square upsample resolution (demo/demo_match.py:28: 864 x 1152), one pair in bf16:
+    shapes, ranges, the grid half of the warp, and (A, B) / (B, A) swap symmetry."""
+    import roma_b200
+    weights, dinov2 = roma_b200.random_init_weights(seed=0)
+    model = roma_b200.roma_outdoor(cuda, weights, dinov2, coarse_res=coarse, upsample_res=up, amp_dtype=torch.bfloat16)
+    H, W = up
+    g = torch.Generator().manual_seed(16)
+    A = (torch.rand(1, 3, H, W, generator=g) * 255).to(torch.uint8)
+    Bm = (torch.rand(1, 3, H, W, generator=g) * 255).to(torch.uint8)
+    w_ab, c_ab = model.match(A, Bm, batched=True, device=cuda)
+    w_ba, c_ba = model.match(Bm, A, batched=True, device=cuda)
+    assert w_ab.shape == (1, H, 2 * W, 4) and c_ab.shape == (1, H, 2 * W)
+    assert torch.isfinite(w_ab).all() and torch.isfinite(c_ab).all()
+    assert w_ab.abs().max().item() <= 1 and 0 <= c_ab.min().item() and c_ab.max().item() <= 1
+    grid = _grid(1, H, W, cuda).permute(0, 2, 3, 1)
+    assert (w_ab[:, :, :W, :2] - grid).abs().max().item() < 1e-6 and (w_ab[:, :, W:, 2:] - grid).abs().max().item() < 1e-6
+    assert (w_ab[:, :, :W, 2:] - w_ba[:, :, W:, :2]).abs().max().item() < 2e-2
+    assert (c_ab[:, :, :W] - c_ba[:, :, W:]).abs().max().item() < 5e-2
+    m, c = model.sample(w_ab[0], c_ab[0], num=5000)
+    assert m.shape == (5000, 4) and c.shape == (5000,)

@@ -92,3 +92,24 @@ def test_tiny_sample_gpu(golden, cuda):
     assert d.max().item() == 0.0
     kA, kB = model.to_pixel_coordinates(m, 200, 232, 200, 232)
     assert kA.shape == (2000, 2) and kB.shape == (2000, 2)
+
+
+@pytest.mark.gpu
+def test_tiny_config5_batch_independence(cuda):
+    """BASELINE config 5 shapes (480 x 640 pairs, coarse grid 60 x 80 = 4800 tokens per image): a batch of 8 pairs
+    built from 2 distinct pairs reproduces the 2 single-pair results element for element (the fused correlation +
+    soft-argmax kernel and the gathers treat batch elements independently), outputs finite and in range."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    model, _ = _build(cuda)
+    g = torch.Generator().manual_seed(4321)
+    A = torch.rand(2, 3, 480, 640, generator=g)
+    B = torch.rand(2, 3, 480, 640, generator=g)
+    w2, c2 = model.match(A.to(cuda), B.to(cuda), batched=True)
+    assert w2.shape == (2, 480, 640, 4) and c2.shape == (2, 480, 640)
+    assert torch.isfinite(w2).all() and torch.isfinite(c2).all()
+    w8, c8 = model.match(A.repeat(4, 1, 1, 1).to(cuda), B.repeat(4, 1, 1, 1).to(cuda), batched=True)
+    for i in range(8):
+        assert (w8[i] - w2[i % 2]).abs().max().item() < 1e-4 and (c8[i] - c2[i % 2]).abs().max().item() < 1e-4
+    m, c = model.sample(w8[3], c8[3], num=5000)
+    assert m.shape == (5000, 4) and c.shape == (5000,)
