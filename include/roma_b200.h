@@ -80,6 +80,10 @@ typedef struct roma_strides4 {
  * Zero padding: taps outside f1 contribute 0 (grid_sample padding_mode="zeros").
  * The correlation is sum_c f0[c] * f1_sampled[c] / sqrt(C).
  */
+/* Testing / profiling aid for the aligned 16-bit local-correlation case (C in {64, 128, 256, 512}): 0 (default) =
+ * neighbour dot products as warp-level tensor-core MMAs (mma.sync m16n8k16, fragments filled straight from 16-byte
+ * global loads), 1 = SIMT FMA dot products with shuffle reductions. */
+int roma_local_corr_set_path(int path);
 int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_strides4 flow_strides,
                         const float* disp_w, const float* disp_b, float disp_scale,
                         void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,

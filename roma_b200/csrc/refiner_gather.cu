@@ -17,6 +17,7 @@
 // transpose-reduction (1 shuffle per neighbour), results staged in shared memory per CTA tile and
 // written back as ONE contiguous, 16-byte-vectorised span (the rows of `d` are odd-sized, e.g.
 // 1377 channels, so per-row vector stores are impossible but the tile span is contiguous).
+#include <atomic>
 #include "common.cuh"
 
 namespace roma {
@@ -327,6 +328,161 @@ local_corr_v2_kernel(const GatherParams p) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Kernel A3 (default for the aligned case): the neighbour dot products on warp-level tensor-core MMAs.
+//
+// local_corr_v2 is bound by memory-level parallelism, not by bytes: a lane keeps 8 independent 16-byte loads in
+// flight and then spends ~130 issue slots per step on bf16 unpacks, FMAs and shuffles, with f0 held as 64 fp32
+// registers (coherent and incoherent flows take the same time, tools/kernel_bench.py).  Here one
+// mma.sync.m16n8k16 computes 16 neighbours x 16 channels: A = 16 neighbour rows (rows g and g + 8 of the
+// fragment), B = the pixel's own f0 vector repeated in the 8 columns, fp32 accumulate.  Fragments are filled
+// straight from 16-byte global loads — the K dimension is a sum, so its order is free: lane (g, t) takes
+// channels 32 kb + 8 t .. + 7 of its two rows and feeds them to two MMAs (.x/.y and .z/.w words), with the same
+// permutation applied to f0, which sits in shared memory (1 KB per warp, one broadcast LDS.128 per two MMAs).
+// Per 16 neighbours x 256 channels a lane issues 16 independent 16-byte loads (twice v2's bytes in flight at
+// half its registers) and 16 HMMAs; no unpack, no FMA, no shuffle.  Out-of-image neighbours load zeros.
+// ------------------------------------------------------------------------------------------------
+template <typename T> struct Mma16816;
+template <> struct Mma16816<__nv_bfloat16> {
+    static __device__ __forceinline__ void run(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                     : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+    }
+};
+template <> struct Mma16816<__half> {
+    static __device__ __forceinline__ void run(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                     : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+    }
+};
+template <> struct Mma16816<float> {
+    static __device__ __forceinline__ void run(float (&)[4], uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
+};
+
+template <typename T, int VPL>
+__global__ void __launch_bounds__(256, 2)
+local_corr_mma_kernel(const GatherParams p) {
+    static_assert(sizeof(T) == 2, "local_corr_mma is for 16-bit feature types");
+    constexpr int kMaxNN = 256;                  // (2r+2)^2 for r <= 7
+    constexpr int NB = 2 * VPL;                  // 32-channel blocks per row
+    constexpr int CH = NB < 8 ? NB : 8;          // blocks per load chunk: 16 uint4 in flight per lane
+    __shared__ float Dall[8][kMaxNN + 4];
+    __shared__ __align__(16) T f0s[8][64 * VPL];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t4 = lane & 3;
+    const int W2 = 2 * p.r + 2, NN = W2 * W2, K1 = 2 * p.r + 1, K = K1 * K1;
+    float* Dsm = Dall[warp];
+    T* f0w = f0s[warp];
+    const float inv_sqrt_c = rsqrtf((float)p.C);
+    const T* f0 = reinterpret_cast<const T*>(p.f0);
+    const T* f1 = reinterpret_cast<const T*>(p.f1);
+    T* dout = reinterpret_cast<T*>(p.d);
+    const int covered = p.covered;
+
+    const long long tile_start = (long long)blockIdx.x * p.tile_px;
+    int tile_n = p.tile_px;
+    if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
+
+    for (int lp = warp; lp < tile_n; lp += 8) {
+        const long long pix = tile_start + lp;
+        int b, y, x; float gx, gy;
+        pixel_coords(p, pix, b, y, x, gx, gy);
+        int x0, y0; float wx0, wx1, wy0, wy1;
+        sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+        T* row = dout + pix * p.dch;
+
+        // f0 row -> shared (B operand of every MMA of this pixel) and -> the x segment of d
+        const T* f0p = f0 + pix * p.C;
+#pragma unroll
+        for (int q = 0; q < (8 * VPL + 31) / 32; ++q) {
+            const int v = lane + 32 * q;
+            if (v < 8 * VPL) {
+                const uint4 raw = ldg16(f0p + v * 8);
+                *reinterpret_cast<uint4*>(f0w + v * 8) = raw;
+                if (p.off_x >= 0) *reinterpret_cast<uint4*>(row + p.off_x + v * 8) = raw;
+            }
+        }
+        __syncwarp();
+        const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
+        for (int n0 = 0; n0 < NN; n0 += 16) {
+            // rows g and g + 8 of the A fragment = neighbours n0 + g and n0 + g + 8
+            const T* src[2];
+#pragma unroll
+            for (int hr = 0; hr < 2; ++hr) {
+                const int n = n0 + g + 8 * hr;
+                const int j = n / W2, i = n - j * W2;
+                const int yy = y0 + j - p.r, xx = x0 + i - p.r;
+                const bool ok = n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+                src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + t4 * 8 : nullptr;
+            }
+            float dA[4] = {0.f, 0.f, 0.f, 0.f}, dB[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int c0 = 0; c0 < NB; c0 += CH) {
+                uint4 u[2][CH];
+#pragma unroll
+                for (int kb = 0; kb < CH; ++kb) {
+#pragma unroll
+                    for (int hr = 0; hr < 2; ++hr)
+                        u[hr][kb] = src[hr] ? ldg16(src[hr] + 32 * (c0 + kb)) : make_uint4(0u, 0u, 0u, 0u);
+                }
+#pragma unroll
+                for (int kb = 0; kb < CH; ++kb) {
+                    const uint4 fb = *reinterpret_cast<const uint4*>(f0w + 32 * (c0 + kb) + t4 * 8);
+                    Mma16816<T>::run(dA, u[0][kb].x, u[1][kb].x, u[0][kb].y, u[1][kb].y, fb.x, fb.y);
+                    Mma16816<T>::run(dB, u[0][kb].z, u[1][kb].z, u[0][kb].w, u[1][kb].w, fb.z, fb.w);
+                }
+            }
+            // every column of the accumulator tile holds the same dot products: column 0 (t4 == 0) stores rows g, g + 8
+            if (t4 == 0) {
+                if (n0 + g < NN) Dsm[n0 + g] = dA[0] + dB[0];
+                if (n0 + g + 8 < NN) Dsm[n0 + g + 8] = dA[2] + dB[2];
+            }
+        }
+        __syncwarp();
+        // x_hat: 4-tap blend of the centre neighbours, lanes over the row's 16-byte vectors (lines just loaded: L1 hits)
+        if (p.off_xhat >= 0) {
+#pragma unroll
+            for (int q = 0; q < (VPL + 3) / 4; ++q) {
+                const int v = lane + 32 * q;
+                if (v < 8 * VPL) {
+                    float xh[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) xh[e] = 0.f;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
+                        if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
+                            const float wgt = ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0);
+                            float f[8];
+                            unpack16<T>(ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C + v * 8), f);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) xh[e] = fmaf(wgt, f[e], xh[e]);
+                        }
+                    }
+                    *reinterpret_cast<uint4*>(row + p.off_xhat + v * 8) = pack16<T>(xh);
+                }
+            }
+        }
+        if (p.off_corr >= 0) {
+            for (int k = lane; k < K; k += 32) {
+                const int ky = k / K1, kx = k - ky * K1;
+                const float* D0 = Dsm + ky * W2 + kx;
+                const float c = wy0 * (wx0 * D0[0] + wx1 * D0[1]) + wy1 * (wx0 * D0[W2] + wx1 * D0[W2 + 1]);
+                row[p.off_corr + k] = Elem<T>::from_f(c * inv_sqrt_c);
+            }
+        }
+        if (p.off_emb >= 0 && p.E > 0) {
+            const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+            const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+            for (int e = lane; e < p.E; e += 32)
+                row[p.off_emb + e] = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx,
+                                                          fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
+        }
+        if (lane < p.dch - covered) row[covered + lane] = Elem<T>::from_f(0.f);      // zero the pitch padding (< 8 channels)
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Kernel C: r == 0 with rows that cannot be vectorised (C*sizeof(T) not a multiple of 16, e.g. the 9-channel
 // finest scale).  One thread per pixel computes its whole output row (x copy, x_hat, emb) into a shared-memory
 // stage; the CTA then writes the contiguous span of its 256 rows with 16-byte stores.
@@ -464,6 +620,8 @@ gather_only_kernel(const GatherParams p, long long nthreads, int cpp) {
     }
 }
 
+static std::atomic<int> g_local_corr_path{0};     // 0: tensor-core dot products (default), 1: SIMT FMA dot products (v2)
+
 template <typename T>
 static int launch_gather(GatherParams p, cudaStream_t st) {
     constexpr int kVec = Elem<T>::kVec;
@@ -482,6 +640,15 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
             p.tile_px = 32;
             const int grid = cdiv(p.npix, p.tile_px);
             if constexpr (sizeof(T) == 2) {
+                if (g_local_corr_path.load() == 0) {
+                    switch (p.C) {
+                        case 512: local_corr_mma_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
+                        case 256: local_corr_mma_kernel<T, 4><<<grid, 256, 0, st>>>(p); break;
+                        case 128: local_corr_mma_kernel<T, 2><<<grid, 256, 0, st>>>(p); break;
+                        default:  local_corr_mma_kernel<T, 1><<<grid, 256, 0, st>>>(p); break;
+                    }
+                    return check_launch("roma_refiner_gather(local_corr_mma)");
+                }
                 switch (p.C) {
                     case 512: local_corr_v2_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
                     case 256: local_corr_v2_kernel<T, 4><<<grid, 256, 0, st>>>(p); break;
@@ -538,6 +705,12 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
 }
 
 }  // namespace roma
+
+extern "C" int roma_local_corr_set_path(int path) {
+    if (path < 0 || path > 1) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 tensor-core, 1 SIMT)", path);
+    roma::g_local_corr_path.store(path);
+    return ROMA_OK;
+}
 
 extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_strides4 fs,
                                    const float* disp_w, const float* disp_b, float disp_scale,

@@ -83,6 +83,38 @@ def test_refiner_inputs_vs_oracle(ops, cuda, dtype, tol, C, E, r, h, w, flow_mod
     assert err(got, want) < tol * scale
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("C,r,h,w", [(512, 7, 12, 14), (512, 3, 23, 19), (256, 2, 31, 27), (128, 1, 17, 20), (64, 4, 16, 16)])
+@pytest.mark.parametrize("flow_mode", ["coherent", "incoherent"])
+def test_local_corr_tensor_core_vs_simt_and_oracle(ops, cuda, dtype, C, r, h, w, flow_mode):
+    """Aligned 16-bit local correlation: the tensor-core dot products (mma.sync m16n8k16, default) against the SIMT
+    FMA kernel and the fp32 oracle on the same rounded features — correlation channels agree to the rounding of the
+    16-bit output; the copied / gathered segments (x, x_hat) are bit-identical between the two kernels."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(31)
+    B = 3
+    x = torch.randn(B, C, h, w, generator=g).to(dtype)
+    y = (0.6 * x.roll(1, 3).float() + 0.8 * torch.randn(B, C, h, w, generator=g)).to(dtype)
+    flow = make_flow(g, B, h, w, flow_mode)
+    want = O.refiner_inputs(x.float(), y.float(), flow, None, None, 1.0, r)
+    try:
+        assert lib.roma_local_corr_set_path(1) == 0
+        simt = ops.refiner_inputs(x.to(cuda), y.to(cuda), flow.to(cuda), None, None, 1.0, r, pad_to=8)
+        assert lib.roma_local_corr_set_path(0) == 0
+        tc = ops.refiner_inputs(x.to(cuda), y.to(cuda), flow.to(cuda), None, None, 1.0, r, pad_to=8)
+    finally:
+        lib.roma_local_corr_set_path(0)
+    K = (2 * r + 1) ** 2
+    assert tc.shape == simt.shape and tc.shape[1] == (want.shape[1] + 7) // 8 * 8     # padded pitch: the aligned kernels
+    assert tc[:, want.shape[1]:].abs().max().item() == 0 if tc.shape[1] > want.shape[1] else True
+    assert torch.equal(tc[:, : 2 * C], simt[:, : 2 * C])
+    ulp = 2.0 ** (-10 if dtype == torch.float16 else -7)
+    scale = max(1.0, want[:, 2 * C: 2 * C + K].abs().max().item())
+    assert err(tc[:, 2 * C: 2 * C + K], want[:, 2 * C: 2 * C + K]) < 1.5 * ulp * scale
+    assert err(tc[:, 2 * C: 2 * C + K], simt[:, 2 * C: 2 * C + K]) < 1.5 * ulp * scale
+
+
 def test_refiner_inputs_strided_flow_and_nchw_features(ops, cuda):
     """Permuted flow views and NCHW-contiguous features are accepted (SURVEY §8a 'strided inputs')."""
     g = torch.Generator().manual_seed(3)
