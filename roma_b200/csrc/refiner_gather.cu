@@ -555,15 +555,32 @@ gather_rowstage_kernel(const GatherParams p) {
 // ------------------------------------------------------------------------------------------------
 // Kernel B: r == 0 (gather-only scales 2 and 1, Tiny-RoMa).  One thread per (pixel, VEC-channel chunk).
 // ------------------------------------------------------------------------------------------------
-template <typename T, int VEC>
+// IDX32: every index fits 32 bits (nthreads < 2^31): unsigned 32-bit divisions instead of the emulated 64-bit ones.
+template <typename T, int VEC, bool IDX32>
 __global__ void __launch_bounds__(256)
 gather_only_kernel(const GatherParams p, long long nthreads, int cpp) {
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= nthreads) return;
-    const long long pix = idx / cpp;
-    const int ch = (int)(idx - pix * cpp) * VEC;
-    int b, y, x; float gx, gy;
-    pixel_coords(p, pix, b, y, x, gx, gy);
+    long long pix;
+    int ch, b, y, x; float gx, gy;
+    if (IDX32) {
+        const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
+        if (idx >= (unsigned)nthreads) return;
+        const unsigned pix32 = idx / (unsigned)cpp;
+        ch = (int)(idx - pix32 * (unsigned)cpp) * VEC;
+        const unsigned hw = (unsigned)(p.h * p.w);
+        const unsigned bb = pix32 / hw, rem = pix32 - bb * hw;
+        const unsigned yy = rem / (unsigned)p.w;
+        b = (int)bb; y = (int)yy; x = (int)(rem - yy * (unsigned)p.w);
+        const float* f = p.flow + (long long)b * p.fs.b + (long long)y * p.fs.y + (long long)x * p.fs.x;
+        gx = __ldg(f);
+        gy = __ldg(f + p.fs.c);
+        pix = pix32;
+    } else {
+        const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        if (idx >= nthreads) return;
+        pix = idx / cpp;
+        ch = (int)(idx - pix * cpp) * VEC;
+        pixel_coords(p, pix, b, y, x, gx, gy);
+    }
     T* out = reinterpret_cast<T*>(p.d) + pix * p.dch + ch;
     const T* f0 = reinterpret_cast<const T*>(p.f0);
     const T* f1 = reinterpret_cast<const T*>(p.f1);
@@ -688,7 +705,8 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
     if (vec && seg_pad_ok) {
         const int cpp = p.dch / kVec;
         const long long n = p.npix * cpp;
-        gather_only_kernel<T, kVec><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);
+        if (n < (1ll << 31)) gather_only_kernel<T, kVec, true><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);
+        else gather_only_kernel<T, kVec, false><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);
     } else if ((size_t)256 * p.dch * sizeof(T) + 32 <= 96 * 1024 && p.C <= 64) {
         // small, unalignable rows (the 9-channel finest scale): one thread per pixel + staged span write
         const size_t smem = (size_t)256 * p.dch * sizeof(T) + 32;
@@ -699,7 +717,8 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
         gather_rowstage_kernel<T><<<cdiv(p.npix, 256), 256, smem, st>>>(p);
     } else {
         const long long n = p.npix * p.dch;
-        gather_only_kernel<T, 1><<<cdiv(n, 256), 256, 0, st>>>(p, n, p.dch);
+        if (n < (1ll << 31)) gather_only_kernel<T, 1, true><<<cdiv(n, 256), 256, 0, st>>>(p, n, p.dch);
+        else gather_only_kernel<T, 1, false><<<cdiv(n, 256), 256, 0, st>>>(p, n, p.dch);
     }
     return check_launch("roma_refiner_gather(gather_only)");
 }

@@ -60,9 +60,12 @@ def main():
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--only", default="")
+    ap.add_argument("--local-corr-path", type=int, default=0, help="0 tensor-core dot products (default), 1 SIMT")
     ap.add_argument("--scales", default="", help="comma list of refiner visits for --only gather (s16,s8,...,s1u)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
+    from roma_b200 import _lib
+    _lib.load().roma_local_corr_set_path(args.local_corr_path)
     dt = DT[args.dtype]
     es = torch.tensor([], dtype=dt).element_size()
     B = args.batch
