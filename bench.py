@@ -89,7 +89,7 @@ def alg_work(name: str, d: dict):
         return "hbm", 4 * n * (3 + 4 + 1 + (1 if d["logits"] else 0))
     if name == "roma_cls_to_flow_refine":
         return "hbm", d["B"] * d["H"] * d["W"] * (d["C"] * d["esize"] + 8)
-    if name == "roma_dwconv5x5_bias_act":                                   # one read + one write of the activation
+    if name in ("roma_dwconv5x5_bias_act", "roma_dwconv5x5_pointwise"):    # one read + one write of the activation
         return "hbm", 2 * d["B"] * d["h"] * d["w"] * d["C"] * d["esize"]
     if name == "roma_layernorm":
         return "hbm", 2 * d["rows"] * d["D"] * d["esize"]

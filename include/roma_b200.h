@@ -231,6 +231,14 @@ int roma_cls_to_flow_refine(const void* cls, roma_strides4 cls_strides, int dtyp
  */
 int roma_dwconv5x5_bias_act(const void* x, const float* weight, const float* bias, void* out,
                             int B, int h, int w, int C, int relu, int dtype, void* stream);
+/* One whole ConvRefiner block of the finest scale (hidden width 22 padded to 24): depthwise 5x5 + folded BatchNorm +
+ * ReLU immediately followed by the block's 1x1 convolution 24 -> 24 (matcher.py:77-103: conv1, norm, relu, conv2),
+ * the depthwise result staying in shared memory (two passes over the activation instead of four).
+ * x, out: (B, h, w, 24) channels-last fp16 / bf16; dw_weight fp32 (25, 24) tap-major, dw_bias fp32 (24);
+ * pw_weight fp32 (24, 24) [out][in], pw_bias fp32 (24).  Other widths: ROMA_ERR_UNSUPPORTED (use the two calls). */
+int roma_dwconv5x5_pointwise(const void* x, const float* dw_weight, const float* dw_bias, const float* pw_weight,
+                             const float* pw_bias, void* out, int B, int h, int w, int C, int relu, int dtype,
+                             void* stream);
 /* (f-2) ConvRefiner head: out[p, o] = bias[o] + sum_c weight[o, c] * x[p, c], o < OUT <= 3, fp32 accumulation.
  *
  * Replaces (reference): romatch/models/matcher.py:141 `self.out_conv(d.float())` (fp32 copy of the activation +

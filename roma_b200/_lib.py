@@ -51,6 +51,7 @@ SIGNATURES = {
     "roma_match_keypoints_workspace_bytes": (_sz, [_i, _i]),
     "roma_match_keypoints": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _i, _f, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
     "roma_dwconv5x5_bias_act": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "roma_dwconv5x5_pointwise": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "roma_dwconv_set_path": (_i, [_i]),
     "roma_tc_set_tma": (_i, [_i]),
     "roma_pointwise_narrow_set_simt": (_i, [_i]),

@@ -269,6 +269,170 @@ static int launch_dw_tma(const void* x, const float* weight, const float* bias, 
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------- fused block, Cp = 24
+// One ConvRefiner block of the finest scale in one pass: depthwise 5x5 + folded BN + ReLU (as above) followed by the
+// block's 1x1 convolution 24 -> 24 (matcher.py:77-103: conv1, norm, relu, conv2).  At 24 channels both halves are
+// memory-bound when run separately (four passes over a 573 MB activation at 864 x 864, B = 16); fused, the depthwise
+// result never leaves the SM: the 16 x 40-pixel tile is written as 16-bit pairs into shared memory, and after one
+// barrier the four warps run the 1x1 convolution as warp-level tensor-core MMAs (mma.sync m16n8k16, fp32 accumulate;
+// A fragments by conflict-free LDS.32 from the tile, the 24 x 24 weights held as B fragments in registers since
+// kernel start) and store the packed 16-bit result: two passes instead of four.  The rounding points are those of
+// the two-kernel path (16-bit activation between the convolutions, fp32 accumulation in both).
+constexpr int kPwC = 24, kPwPPB = 12, kPwRPB = 10;                 // channels, pairs and 4-column runs per block
+constexpr int kPwCols = kPwRPB * kDwTW;                            // 40 output columns per tile
+constexpr int kPwPixBytes = 2 * kPwPPB * 2, kPwRowBytes = (kPwCols + 4) * kPwPixBytes, kPwChunkBytes = 5 * kPwRowBytes;
+constexpr int kPwChunkStride = (kPwChunkBytes + 127) / 128 * 128;
+constexpr int kPwObufBytes = kDwRY * kPwCols * kPwC * 2;
+constexpr size_t kPwSmem = (size_t)kDwChunks * kPwChunkStride + 128 + kPwObufBytes + 128;
+
+template <typename T> __device__ __forceinline__ void dw_mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <> __device__ __forceinline__ void dw_mma16816<__nv_bfloat16>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <> __device__ __forceinline__ void dw_mma16816<__half>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <typename T> __device__ __forceinline__ uint32_t dw_pack2(float lo, float hi);
+template <> __device__ __forceinline__ uint32_t dw_pack2<__nv_bfloat16>(float lo, float hi) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+template <> __device__ __forceinline__ uint32_t dw_pack2<__half>(float lo, float hi) {
+    const __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kDwThreads, 3)
+dwconv5_pw24_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restrict__ wgt, const float* __restrict__ bias,
+                        const float* __restrict__ pw_w, const float* __restrict__ pw_b, T* __restrict__ out, int h, int w, int relu) {
+    static_assert(sizeof(T) == 2, "fused block: 16-bit activations");
+    extern __shared__ unsigned char dw_smem_raw[];
+    unsigned char* tile = dw_smem_raw + ((128u - (tma::saddr(dw_smem_raw) & 127u)) & 127u);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tile + kDwChunks * kPwChunkStride);
+    T* obuf = reinterpret_cast<T*>(tile + kDwChunks * kPwChunkStride + 128);          // [16 rows][40 cols][24 ch]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rg = blockIdx.x, b = blockIdx.z, y0 = blockIdx.y * kDwRY;
+    int nch = kDwChunks;
+    while (nch > 1 && y0 + 5 * (nch - 1) - 4 >= h) --nch;
+
+    if (tid == 0) {
+        tma::prefetch_map(&map);
+        for (int k = 0; k < nch; ++k) tma::mbar_init(&bars[k], 1);
+        tma::fence_barrier_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        for (int k = 0; k < nch; ++k) {
+            tma::mbar_expect_tx(&bars[k], (uint32_t)kPwChunkBytes);
+            tma::load_4d(tile + k * kPwChunkStride, &map, &bars[k], 0, rg * kPwCols - 2, y0 - 2 + 5 * k, b);
+        }
+    }
+
+    // B fragments of the 1x1 convolution: B[k][n] = W[n][k]; b0 = (k = 16 ks + 2t, +1; n = 8 nt + g), b1 = 8 further in k
+    const int g = lane >> 2, t4 = lane & 3;
+    uint32_t bf[2][3][2];
+    float bv[3][2];
+#pragma unroll
+    for (int nt = 0; nt < 3; ++nt) {
+        const int n = nt * 8 + g;
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                const int k = ks * 16 + 2 * t4 + 8 * hh;
+                const float w0 = k < kPwC ? __ldg(pw_w + n * kPwC + k) : 0.f;
+                const float w1 = k + 1 < kPwC ? __ldg(pw_w + n * kPwC + k + 1) : 0.f;
+                bf[ks][nt][hh] = dw_pack2<T>(w0, w1);
+            }
+        }
+        bv[nt][0] = __ldg(pw_b + nt * 8 + 2 * t4);
+        bv[nt][1] = __ldg(pw_b + nt * 8 + 2 * t4 + 1);
+    }
+
+    // ---- phase 1: depthwise 5x5 + bias + ReLU into the shared-memory tile --------------------------------------
+    const int runs = (w + kDwTW - 1) / kDwTW;
+    const int pair_l = tid % kPwPPB, run_l = tid / kPwPPB;
+    const int run = rg * kPwRPB + run_l;
+    if (run_l < kPwRPB && run < runs) {
+        const int c = pair_l * 2;
+        DwOut<T> o;
+        o.row_stride = kPwCols * kPwC;
+        o.col_stride = kPwC;
+        o.orow = obuf + run_l * kDwTW * kPwC + c;
+        o.storemask = (1u << kDwTW) - 1u;
+        o.full = true;
+        o.relu = relu != 0;
+        float2 wv[25];
+#pragma unroll
+        for (int k = 0; k < 25; ++k) wv[k] = __ldg(reinterpret_cast<const float2*>(wgt + k * kPwC + c));
+        const float2 bvv = __ldg(reinterpret_cast<const float2*>(bias + c));
+        const unsigned char* tb = tile + run_l * kDwTW * kPwPixBytes + pair_l * 4;
+        float2 acc[5][kDwTW];
+        tma::mbar_wait(&bars[0], 0);
+        dw_chunk_smem<T, true, false>(tb, kPwRowBytes, kPwPixBytes, o, y0 - 2, h, wv, bvv, acc);
+#pragma unroll 1
+        for (int ch = 1; ch < kDwChunks - 1; ++ch) {
+            if (ch < nch) {
+                tma::mbar_wait(&bars[ch], 0);
+                dw_chunk_smem<T, false, false>(tb + ch * kPwChunkStride, kPwRowBytes, kPwPixBytes, o, y0 - 2 + 5 * ch, h, wv, bvv, acc);
+            }
+        }
+        if (nch == kDwChunks) {
+            tma::mbar_wait(&bars[kDwChunks - 1], 0);
+            dw_chunk_smem<T, false, true>(tb + (kDwChunks - 1) * kPwChunkStride, kPwRowBytes, kPwPixBytes, o, y0 - 2 + 5 * (kDwChunks - 1), h,
+                                          wv, bvv, acc);
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 2: 1x1 convolution of the tile on tensor cores, 16 pixels per MMA tile --------------------------
+    const uint32_t* ob32 = reinterpret_cast<const uint32_t*>(obuf);
+    T* outb = out + (long long)b * h * w * kPwC;
+    const int x_base = rg * kPwCols;
+#pragma unroll 2
+    for (int mt = warp; mt < kDwRY * kPwCols / 16; mt += kDwThreads / 32) {
+        const int qlo = mt * 16 + g, qhi = qlo + 8;
+        uint32_t a0[4], a1[4];
+        a0[0] = ob32[qlo * 12 + t4];     a0[1] = ob32[qhi * 12 + t4];
+        a0[2] = ob32[qlo * 12 + 4 + t4]; a0[3] = ob32[qhi * 12 + 4 + t4];
+        a1[0] = ob32[qlo * 12 + 8 + t4]; a1[1] = ob32[qhi * 12 + 8 + t4];
+        a1[2] = 0u; a1[3] = 0u;                                       // k = 24..31 do not exist
+        const int ylo = y0 + qlo / kPwCols, xlo = x_base + qlo % kPwCols;
+        const int yhi = y0 + qhi / kPwCols, xhi = x_base + qhi % kPwCols;
+        const bool vlo = ylo < h && xlo < w, vhi = yhi < h && xhi < w;
+        T* plo = outb + ((long long)ylo * w + xlo) * kPwC + 2 * t4;
+        T* phi = outb + ((long long)yhi * w + xhi) * kPwC + 2 * t4;
+#pragma unroll
+        for (int nt = 0; nt < 3; ++nt) {
+            float c[4] = {bv[nt][0], bv[nt][1], bv[nt][0], bv[nt][1]};
+            dw_mma16816<T>(c, a0, bf[0][nt][0], bf[0][nt][1]);
+            dw_mma16816<T>(c, a1, bf[1][nt][0], bf[1][nt][1]);
+            if (vlo) *reinterpret_cast<uint32_t*>(plo + nt * 8) = dw_pack2<T>(c[0], c[1]);
+            if (vhi) *reinterpret_cast<uint32_t*>(phi + nt * 8) = dw_pack2<T>(c[2], c[3]);
+        }
+    }
+}
+
+template <typename T>
+static int launch_dw_pw24(const void* x, const float* weight, const float* bias, const float* pw_w, const float* pw_b, void* out,
+                          int B, int h, int w, int relu, int dtype, cudaStream_t st) {
+    const int runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRY - 1) / kDwRY;
+    CUtensorMap map;
+    const uint64_t dims[4] = {(uint64_t)kPwC, (uint64_t)w, (uint64_t)h, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)kPwC * 2, (uint64_t)w * kPwC * 2, (uint64_t)h * w * kPwC * 2};
+    const uint32_t box[4] = {(uint32_t)kPwC, (uint32_t)(kPwCols + 4), 5u, 1u};
+    if (int rc = tma::encode_tiled(&map, dtype, 4, x, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+    cudaError_t e = cudaFuncSetAttribute(dwconv5_pw24_tma_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPwSmem);
+    if (e != cudaSuccess) return fail((int)e, "roma_dwconv5x5_pointwise: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    const dim3 grid((unsigned)cdiv(runs, kPwRPB), (unsigned)strips, (unsigned)B);
+    dwconv5_pw24_tma_kernel<T><<<grid, kDwThreads, kPwSmem, st>>>(map, weight, bias, pw_w, pw_b, (T*)out, h, w, relu);
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------- cp.async variant
 // Asynchronous global -> shared copy of one channel pair; src_bytes = 0 zero-fills (image border).
 template <int BYTES>
@@ -426,4 +590,27 @@ extern "C" int roma_dwconv5x5_bias_act(const void* x, const float* weight, const
         default: return fail(ROMA_ERR_BAD_ARG, "roma_dwconv5x5_bias_act: unknown dtype %d", dtype);
     }
     return check_launch("roma_dwconv5x5_bias_act");
+}
+
+extern "C" int roma_dwconv5x5_pointwise(const void* x, const float* dw_weight, const float* dw_bias, const float* pw_weight,
+                                        const float* pw_bias, void* out, int B, int h, int w, int C, int relu, int dtype,
+                                        void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(x && dw_weight && dw_bias && pw_weight && pw_bias && out, ROMA_ERR_BAD_ARG, "roma_dwconv5x5_pointwise: null pointer");
+    ROMA_REQUIRE(B > 0 && h > 0 && w > 0, ROMA_ERR_BAD_ARG, "roma_dwconv5x5_pointwise: bad sizes");
+    ROMA_REQUIRE(C == kPwC && (dtype == ROMA_F16 || dtype == ROMA_BF16), ROMA_ERR_UNSUPPORTED,
+                 "roma_dwconv5x5_pointwise: the fused block exists for C = 24 in fp16 / bf16 (got C = %d, dtype %d); "
+                 "use roma_dwconv5x5_bias_act + a 1x1 convolution", C, dtype);
+    ROMA_REQUIRE(x != out, ROMA_ERR_BAD_ARG, "roma_dwconv5x5_pointwise: in-place operation is not supported");
+    ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0 &&
+                 ((reinterpret_cast<uintptr_t>(dw_weight) | reinterpret_cast<uintptr_t>(dw_bias)) & 7u) == 0,
+                 ROMA_ERR_ALIGNMENT, "roma_dwconv5x5_pointwise: misaligned pointer");
+    const int strips = (h + kDwRY - 1) / kDwRY;
+    ROMA_REQUIRE(B <= 65535 && strips <= 65535, ROMA_ERR_UNSUPPORTED, "roma_dwconv5x5_pointwise: batch / height too large");
+    ROMA_REQUIRE(tma::encode_fn() != nullptr, ROMA_ERR_UNSUPPORTED, "roma_dwconv5x5_pointwise: cuTensorMapEncodeTiled is not available");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    int rc = dtype == ROMA_F16 ? launch_dw_pw24<__half>(x, dw_weight, dw_bias, pw_weight, pw_bias, out, B, h, w, relu, dtype, st)
+                               : launch_dw_pw24<__nv_bfloat16>(x, dw_weight, dw_bias, pw_weight, pw_bias, out, B, h, w, relu, dtype, st);
+    if (rc) return rc;
+    return check_launch("roma_dwconv5x5_pointwise");
 }

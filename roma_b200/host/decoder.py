@@ -48,6 +48,7 @@ class ConvRefiner(nn.Module):
         self.in_dim, self.hidden_dim, self.kernel_size = in_dim, hidden_dim, kernel_size
         self._prep = None
         self._prep_key = None
+        self.fuse_narrow_block = True     # Cp = 24: depthwise + 1x1 convolution of a block in one kernel
 
     @staticmethod
     def _block(cin: int, cout: int, k: int, momentum: float) -> nn.Sequential:
@@ -94,7 +95,11 @@ class ConvRefiner(nn.Module):
         """d (B, Cp, h, w) channels-last -> (B, 3, h, w) fp32 out_conv output."""
         Cp, blocks, w_out, b_out = self._prepare(d.device, d.dtype)
         B, _, h, w = d.shape
+        fused = self.fuse_narrow_block and Cp == 24 and d.dtype in (torch.float16, torch.bfloat16)
         for w_dw, b_dw, w_pw, b_pw in blocks:
+            if fused:
+                d = ops.dwconv5x5_pointwise(d, w_dw, b_dw, w_pw, b_pw, relu=True)     # whole block in one pass
+                continue
             d = ops.dwconv5x5_bias_act(d, w_dw, b_dw, relu=True)                      # (f-2): dw conv + folded BN + ReLU
             if Cp <= 32:
                 d = ops.pointwise_narrow(d, w_pw, b_pw)                               # conv2, N = K = 24

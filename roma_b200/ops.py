@@ -403,6 +403,26 @@ def dwconv5x5_bias_act(x: torch.Tensor, weight_taps: torch.Tensor, bias: torch.T
     return out
 
 
+def dwconv5x5_pointwise(x: torch.Tensor, dw_weight_taps: torch.Tensor, dw_bias: torch.Tensor, pw_weight: torch.Tensor,
+                        pw_bias: torch.Tensor, relu: bool = True) -> torch.Tensor:
+    """One ConvRefiner block at the finest scale's padded width (C = 24, fp16 / bf16): depthwise 5x5 + bias + ReLU and the
+    1x1 convolution that follows it (matcher.py:77-103), fused — the depthwise result stays in shared memory.
+    x (B,24,h,w) channels-last; dw_weight_taps fp32 (25,24); pw_weight fp32 (24,24) [out][in]."""
+    dev = _cuda(x, dw_weight_taps, dw_bias, pw_weight, pw_bias)
+    if x.dtype not in (torch.float16, torch.bfloat16):
+        raise ValueError(f"unsupported dtype {x.dtype}")
+    B, Cc, h, w = x.shape
+    x = _nhwc(x)
+    pw_weight = pw_weight.reshape(Cc, Cc).float().contiguous()
+    pw_bias = pw_bias.float().contiguous()
+    out = torch.empty_like(x, memory_format=torch.channels_last)
+    lib = _lib.load()
+    _run("roma_dwconv5x5_pointwise", dict(B=B, C=Cc, h=h, w=w, esize=x.element_size()),
+         lambda: lib.roma_dwconv5x5_pointwise(_ptr(x), _ptr(dw_weight_taps), _ptr(dw_bias), _ptr(pw_weight), _ptr(pw_bias), _ptr(out),
+                                              B, h, w, Cc, int(bool(relu)), _DT[x.dtype], _stream(dev)))
+    return out
+
+
 def pointwise_narrow(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
     """1x1 convolution to OUT <= 16 channels in the dtype of x (roma_models.py:131-142, proj["1"] with its BatchNorm
     folded).  x (B,C,h,w) channels-last; weight fp32 (OUT,C); bias fp32 (OUT) -> (B,OUT,h,w) channels-last."""

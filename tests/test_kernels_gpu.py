@@ -518,3 +518,33 @@ def test_layer_norm(ops, cuda, dtype, tol, shape):
     got = ops.layer_norm(x.to(cuda), wt.to(cuda), bias.to(cuda), 1e-6)
     assert got.shape == x.shape and got.dtype == dtype
     assert err(got, want) < tol * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("B,h,w", [(2, 16, 40), (1, 37, 53), (3, 70, 81), (1, 5, 3), (2, 48, 200)])
+def test_dwconv_pointwise_fused_block(ops, cuda, dtype, B, h, w):
+    """The fused refiner block (C = 24): bit-identical to the depthwise kernel followed by the narrow 1x1 kernel (same
+    rounding points, same MMA sequence), and within 16-bit rounding of an fp64 evaluation of the two convolutions."""
+    g = torch.Generator().manual_seed(41)
+    C = 24
+    x = torch.randn(B, C, h, w, generator=g).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    w_dw = (torch.randn(25, C, generator=g) * 0.2).to(cuda)
+    b_dw = (torch.randn(C, generator=g) * 0.1).to(cuda)
+    w_pw = (torch.randn(C, C, generator=g) / C ** 0.5).to(cuda)
+    b_pw = (torch.randn(C, generator=g) * 0.1).to(cuda)
+    two = ops.pointwise_narrow(ops.dwconv5x5_bias_act(x, w_dw, b_dw, relu=True), w_pw, b_pw)
+    one = ops.dwconv5x5_pointwise(x, w_dw, b_dw, w_pw, b_pw, relu=True)
+    assert one.shape == two.shape == (B, C, h, w) and one.dtype == dtype
+    assert torch.equal(one, two)
+    mid = torch.nn.functional.conv2d(x.double(), w_dw.t().reshape(C, 1, 5, 5).double(), b_dw.double(), padding=2, groups=C).relu()
+    mid = mid.to(dtype).double()                                   # the 16-bit activation between the two convolutions
+    want = torch.nn.functional.conv2d(mid, w_pw.double().view(C, C, 1, 1), b_pw.double())
+    tol = (2.0 ** -9 if dtype == torch.float16 else 2.0 ** -6) * max(1.0, want.abs().max().item())
+    assert (one.double() - want).abs().max().item() < tol
+
+
+def test_dwconv_pointwise_rejects_other_widths(ops, cuda):
+    x = torch.zeros(1, 32, 8, 8, device=cuda, dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    with pytest.raises((RuntimeError, ValueError)):
+        ops.dwconv5x5_pointwise(x, torch.zeros(25, 32, device=cuda), torch.zeros(32, device=cuda), torch.zeros(32, 32, device=cuda),
+                                torch.zeros(32, device=cuda))
