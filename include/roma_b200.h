@@ -299,6 +299,14 @@ int roma_maxpool2x2_nhwc(const void* x, void* out, int B, int h, int w, int C, i
  */
 int roma_tiny_corr_posembed(const float* feat0, const float* feat1, float* out,
                             int B, int C, int H0, int W0, int H1, int W1, void* stream);
+/* The same op on tensor cores (default in the host wrapper when C % 4 == 0): scores = feat0 feat1^T / sqrt(C) as a
+ * tcgen05 / TMEM GEMM over fp32 features split on the fly into three bf16 planes (fp32-grade products), the arg-max
+ * and online-softmax reduction fused on the TMEM drain (one record per 64-column tile half and query), one merge
+ * kernel over the column tiles.  workspace: roma_tiny_corr_posembed_workspace_bytes(...) bytes, 16-byte aligned. */
+size_t roma_tiny_corr_posembed_workspace_bytes(int B, int H0, int W0, int H1, int W1);
+int roma_tiny_corr_posembed_tc(const float* feat0, const float* feat1, float* out,
+                               int B, int C, int H0, int W0, int H1, int W1,
+                               void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,7 @@
 // (f-1) cls_to_flow_refine (romatch/utils/utils.py:301-323) and
 // KT  Tiny-RoMa fused corr_volume + pos_embed (romatch/models/tiny.py:241-254, 178-199).
 #include "common.cuh"
+#include "tc_gemm.cuh"
 
 namespace roma {
 
@@ -125,6 +126,36 @@ tiny_corr_posembed_kernel(const float* __restrict__ f0, const float* __restrict_
     }
 }
 
+
+// Merge of the per-(tile half) records written by the EPI_TINY epilogue of the tcgen05 GEMM (tc_gemm.cuh): slots are
+// visited in ascending column order, so a strict comparison keeps the first maximum like torch.argmax; the online
+// softmax triples merge as in the warp merge above; then the index-as-logit term of tiny.py:196.
+__global__ void __launch_bounds__(256)
+tiny_merge_kernel(const float* __restrict__ part, float* __restrict__ out, int B, int n0, int slots, int H1, int W1) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)B * n0) return;
+    const int b = (int)(idx / n0), qi = (int)(idx - (long long)b * n0);
+    float best = -INFINITY; int bi = 0x7fffffff;
+    float m = -INFINITY, ssum = 0.f, sx = 0.f, sy = 0.f;
+    const float* rec = part + (long long)b * slots * 6 * n0 + qi;
+    for (int sl = 0; sl < slots; ++sl, rec += 6ll * n0) {
+        const float ov = rec[0];
+        const int oi = __float_as_int(rec[n0]);
+        if (ov > best) { best = ov; bi = oi; }
+        const float om = rec[2ll * n0], os = rec[3ll * n0], ox = rec[4ll * n0], oy = rec[5ll * n0];
+        const float nm = fmaxf(m, om);
+        const float a = (m == -INFINITY) ? 0.f : expf(m - nm), c = (om == -INFINITY) ? 0.f : expf(om - nm);
+        ssum = ssum * a + os * c; sx = sx * a + ox * c; sy = sy * a + oy * c; m = nm;
+    }
+    const float extra = (float)bi;
+    const float nm = fmaxf(m, extra);
+    const float a = (m == -INFINITY) ? 0.f : expf(m - nm), e = expf(extra - nm);
+    const int by = bi / W1, bx = bi - by * W1;
+    const float tot = ssum * a + e;
+    out[((long long)b * 2 + 0) * n0 + qi] = (sx * a + e * pixel_center(bx, W1)) / tot;
+    out[((long long)b * 2 + 1) * n0 + qi] = (sy * a + e * pixel_center(by, H1)) / tot;
+}
+
 }  // namespace roma
 
 extern "C" int roma_cls_to_flow_refine(const void* cls, roma_strides4 cs, int dtype,
@@ -166,4 +197,45 @@ extern "C" int roma_tiny_corr_posembed(const float* feat0, const float* feat1, f
         default: return fail(ROMA_ERR_UNSUPPORTED, "roma_tiny_corr_posembed: C=%d (supported: 16, 24, 32, 64)", C);
     }
     return check_launch("roma_tiny_corr_posembed");
+}
+
+// Tensor-core form of the same op: scores = f0 f1^T / sqrt(C) as a tcgen05 GEMM with the fp32 features split on the
+// fly into three bf16 planes (fp32-grade products, tc_gemm.cuh), the arg-max / online-softmax reduction fused on the
+// TMEM drain, one small merge kernel over the column tiles.  The (n0 x n1) volume is never written.
+extern "C" size_t roma_tiny_corr_posembed_workspace_bytes(int B, int H0, int W0, int H1, int W1) {
+    if (B <= 0 || H0 <= 0 || W0 <= 0 || H1 <= 0 || W1 <= 0) return 0;
+    const long long n0 = (long long)H0 * W0, n1 = (long long)H1 * W1;
+    const long long slots = 2 * ((n1 + roma::tc::BN - 1) / roma::tc::BN);
+    return (size_t)((long long)B * slots * 6 * n0) * sizeof(float);
+}
+
+extern "C" int roma_tiny_corr_posembed_tc(const float* feat0, const float* feat1, float* out,
+                                          int B, int C, int H0, int W0, int H1, int W1,
+                                          void* workspace, size_t workspace_bytes, void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(feat0 && feat1 && out && workspace, ROMA_ERR_BAD_ARG, "roma_tiny_corr_posembed_tc: null pointer");
+    ROMA_REQUIRE(B > 0 && H0 > 0 && W0 > 0 && H1 >= 4 && W1 >= 4 && C > 0, ROMA_ERR_BAD_ARG, "roma_tiny_corr_posembed_tc: bad sizes");
+    ROMA_REQUIRE(H1 % 4 == 0 && W1 % 4 == 0, ROMA_ERR_UNSUPPORTED,
+                 "roma_tiny_corr_posembed_tc: H1, W1 must be multiples of 4 (the reference's strided subset and grid_lr disagree otherwise)");
+    ROMA_REQUIRE(C % 4 == 0 && ((reinterpret_cast<uintptr_t>(feat0) | reinterpret_cast<uintptr_t>(feat1)) & 15u) == 0, ROMA_ERR_ALIGNMENT,
+                 "roma_tiny_corr_posembed_tc: features must be 16-byte aligned rows (C %% 4 == 0)");
+    ROMA_REQUIRE(workspace_bytes >= roma_tiny_corr_posembed_workspace_bytes(B, H0, W0, H1, W1), ROMA_ERR_WORKSPACE,
+                 "roma_tiny_corr_posembed_tc: workspace too small");
+    ROMA_REQUIRE(B <= 65535, ROMA_ERR_UNSUPPORTED, "roma_tiny_corr_posembed_tc: batch too large");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int n0 = H0 * W0, n1 = H1 * W1;
+    tc::Launch L{};
+    tc::Problem& P = L.p[0];
+    P = tc::make_problem(feat0, feat1, nullptr, n0, n1, C, C, C, 0, (long long)n0 * C, (long long)n1 * C, 0, tc::EPI_TINY);
+    const int down = 4, wl = W1 / down, hl = H1 / down;
+    P.part = reinterpret_cast<float*>(workspace);
+    P.scale = 1.0f / sqrtf((float)C);
+    P.w1 = W1;
+    P.lx0 = -1.f + (float)down / W1; P.ly0 = -1.f + (float)down / H1;
+    P.lxs = wl > 1 ? (2.f - 2.f * down / W1) / (wl - 1) : 0.f;
+    P.lys = hl > 1 ? (2.f - 2.f * down / H1) / (hl - 1) : 0.f;
+    L.nprob = 1; L.tiles0 = P.tiles_m * P.tiles_n;
+    if (int rc = tc::launch_gemm_nt<float, 3>(L, B, st, "roma_tiny_corr_posembed_tc(gemm)")) return rc;
+    tiny_merge_kernel<<<cdiv((long long)B * n0, 256), 256, 0, st>>>(P.part, out, B, n0, 2 * P.tiles_n, H1, W1);
+    return check_launch("roma_tiny_corr_posembed_tc(merge)");
 }

@@ -29,7 +29,7 @@ constexpr int kThreads = 256;
 constexpr int kPlaneBytes = BM * BK * 2;          // 16 KB: one bf16 plane of one operand k-block
 template <int SPLIT> constexpr int tmem_cols() { return SPLIT == 1 ? 128 : 256; }
 
-enum Epi : int { EPI_STORE = 0, EPI_SUB = 1, EPI_COS = 2 };
+enum Epi : int { EPI_STORE = 0, EPI_SUB = 1, EPI_COS = 2, EPI_TINY = 3 };
 
 struct Problem {
     const void* A; const void* B;
@@ -46,6 +46,11 @@ struct Problem {
     // EPI_COS: K = exp((acc / (rn[m]*cn[n] + eps) - 1) * inv_T) (+ diag_add on m == n); padding -> identity
     const float* rn; const float* cn; long long srn, scn;
     float eps, inv_T, diag_add;
+    // EPI_TINY (Tiny-RoMa corr_volume + pos_embed, tiny.py:178-199, 241-254): nothing is stored; every 64-column half
+    // of a tile reduces its scores s = acc * scale per row m to (max, argmax, online-softmax triple over the columns of
+    // the 4x4-strided subset) and writes the record to part[((b * slots + slot) * 6 + field) * M + m],
+    // slot = 2 * tn + half, slots = 2 * tiles_n.  Column n is pixel (n / w1, n % w1) of image 1.
+    float* part; float scale; int w1; float lx0, lxs, ly0, lys;
 };
 
 struct Launch {
@@ -200,6 +205,45 @@ __device__ __forceinline__ void tile_epilogue(const Problem& P, int b, int m0, i
     const int m = m0 + q * 32 + lane;
     float* Cb = P.C ? P.C + (long long)b * P.sC : nullptr;
     float* Ctb = P.Ct ? P.Ct + (long long)b * P.sCt : nullptr;
+    if (P.epi == EPI_TINY) {
+        float best = -INFINITY; int bi = 0x7fffffff;
+        float mx = -INFINITY, ssum = 0.f, sx = 0.f, sy = 0.f;
+#pragma unroll 1
+        for (int cc = 0; cc < 2; ++cc) {
+            const int c0 = hf * 64 + cc * 32;
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+            if (SPLIT > 1) {
+                float lo[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 128u + (uint32_t)c0, lo);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] += lo[i];
+            }
+            const int nb0 = n0 + c0;
+            int y1 = nb0 / P.w1, x1 = nb0 - y1 * P.w1;            // the same for every row: warp-uniform branches below
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                if (nb0 + i < P.N) {
+                    const float sj = v[i] * P.scale;
+                    if (sj > best) { best = sj; bi = nb0 + i; }        // columns ascend: the first maximum is kept
+                    if (((x1 | y1) & 3) == 0) {
+                        const float gx = P.lx0 + P.lxs * (float)(x1 >> 2), gy = P.ly0 + P.lys * (float)(y1 >> 2);
+                        if (sj > mx) { const float sc = expf(mx - sj); ssum *= sc; sx *= sc; sy *= sc; mx = sj; }
+                        const float e = expf(sj - mx);
+                        ssum += e; sx = fmaf(e, gx, sx); sy = fmaf(e, gy, sy);
+                    }
+                }
+                if (++x1 == P.w1) { x1 = 0; ++y1; }
+            }
+        }
+        if (m < P.M) {
+            const int slots = 2 * P.tiles_n, slot = 2 * (n0 / BN) + hf;
+            float* rec = P.part + ((long long)b * slots + slot) * 6 * P.M + m;
+            rec[0] = best; rec[(long long)P.M] = __int_as_float(bi); rec[2ll * P.M] = mx;
+            rec[3ll * P.M] = ssum; rec[4ll * P.M] = sx; rec[5ll * P.M] = sy;
+        }
+        return;
+    }
     float rn = 0.f;
     if (P.epi == EPI_COS && m < P.M) rn = P.rn[(long long)b * P.srn + m];
 #pragma unroll 1
@@ -494,6 +538,7 @@ static inline Problem make_problem(const void* A, const void* B, float* C, int M
     p.tiles_m = (M + BM - 1) / BM; p.tiles_n = (N + BN - 1) / BN;
     p.lower_only = 0; p.diag_only = 0; p.no_diag = 0; p.epi = epi; p.store_m = M; p.store_n = N;
     p.rn = p.cn = nullptr; p.srn = p.scn = 0; p.eps = 0.f; p.inv_T = 0.f; p.diag_add = 0.f;
+    p.part = nullptr; p.scale = 1.f; p.w1 = 1; p.lx0 = p.lxs = p.ly0 = p.lys = 0.f;
     return p;
 }
 

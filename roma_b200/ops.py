@@ -509,10 +509,14 @@ def cls_to_flow_refine(cls: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def tiny_corr_posembed(feat0: torch.Tensor, feat1: torch.Tensor) -> torch.Tensor:
+_tiny_ws = {}
+
+
+def tiny_corr_posembed(feat0: torch.Tensor, feat1: torch.Tensor, tensor_cores: Optional[bool] = None) -> torch.Tensor:
     """TinyRoMa.pos_embed(TinyRoMa.corr_volume(feat0, feat1)) (tiny.py:241-254 + 178-199), fused.
 
-    feat0 (B,C,H0,W0), feat1 (B,C,H1,W1) -> (B,2,H0,W0); the (B,H1,W1,H0,W0) volume is never formed."""
+    feat0 (B,C,H0,W0), feat1 (B,C,H1,W1) -> (B,2,H0,W0); the (B,H1,W1,H0,W0) volume is never formed.
+    tensor_cores: None = the tcgen05 path whenever the shapes allow (C % 4 == 0), False = the fp32 SIMT kernel."""
     dev = _cuda(feat0, feat1)
     B, Cc, H0, W0 = feat0.shape
     _, _, H1, W1 = feat1.shape
@@ -520,6 +524,19 @@ def tiny_corr_posembed(feat0: torch.Tensor, feat1: torch.Tensor) -> torch.Tensor
     f1 = _nhwc(feat1.float())
     out = torch.empty((B, 2, H0, W0), device=dev, dtype=torch.float32)
     lib = _lib.load()
+    if tensor_cores is None:
+        tensor_cores = Cc % 4 == 0
+    if tensor_cores:
+        need = lib.roma_tiny_corr_posembed_workspace_bytes(B, H0, W0, H1, W1)
+        key = (dev, torch.cuda.current_stream(dev).cuda_stream)
+        ws = _tiny_ws.get(key)
+        if ws is None or ws.numel() < need:
+            ws = torch.empty(need, device=dev, dtype=torch.uint8)
+            _tiny_ws[key] = ws
+        _run("roma_tiny_corr_posembed_tc", dict(B=B, C=Cc, n0=H0 * W0, n1=H1 * W1),
+             lambda: lib.roma_tiny_corr_posembed_tc(_ptr(f0), _ptr(f1), _ptr(out), B, Cc, H0, W0, H1, W1, _ptr(ws), ws.numel(),
+                                                    _stream(dev)))
+        return out
     _run("roma_tiny_corr_posembed", dict(B=B, C=Cc, n0=H0 * W0, n1=H1 * W1),
          lambda: lib.roma_tiny_corr_posembed(_ptr(f0), _ptr(f1), _ptr(out), B, Cc, H0, W0, H1, W1, _stream(dev)))
     return out

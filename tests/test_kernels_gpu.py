@@ -412,13 +412,31 @@ def test_cls_to_flow_golden_and_strided(ops, cuda, golden):
     assert err(got16, O.cls_to_flow_refine(out.half().float().permute(0, 2, 1).reshape(2, 4097, 6, 7)[:, :-1])) < 1e-5
 
 
-def test_tiny_golden_and_oracle(ops, cuda, golden):
+@pytest.mark.parametrize("tc", [True, False])
+def test_tiny_golden_and_oracle(ops, cuda, golden, tc):
+    """Fused corr_volume + pos_embed: the tcgen05 GEMM with the fused arg-max / online-softmax epilogue (tc=True,
+    fp32 features as three bf16 planes) and the fp32 SIMT kernel, against the reference's own output and the oracle."""
     g = golden("tiny")
-    assert err(ops.tiny_corr_posembed(g["feat0"].to(cuda), g["feat1"].to(cuda)), g["pos_embed"]) < 1e-5
+    assert err(ops.tiny_corr_posembed(g["feat0"].to(cuda), g["feat1"].to(cuda), tensor_cores=tc), g["pos_embed"]) < 1e-5
     gg = torch.Generator().manual_seed(6)
-    f0 = torch.randn(2, 64, 12, 16, generator=gg); f1 = torch.randn(2, 64, 12, 16, generator=gg)
-    want = torch.cat([O.tiny_pos_embed(O.tiny_corr_volume(f0[i:i + 1], f1[i:i + 1])) for i in range(2)])
-    assert err(ops.tiny_corr_posembed(f0.to(cuda), f1.to(cuda)), want) < 1e-5
+    for (h0, w0, h1, w1) in [(12, 16, 12, 16), (9, 15, 20, 28)]:          # ragged row / column tiles
+        f0 = torch.randn(2, 64, h0, w0, generator=gg); f1 = torch.randn(2, 64, h1, w1, generator=gg)
+        want = torch.cat([O.tiny_pos_embed(O.tiny_corr_volume(f0[i:i + 1], f1[i:i + 1])) for i in range(2)])
+        assert err(ops.tiny_corr_posembed(f0.to(cuda), f1.to(cuda), tensor_cores=tc), want) < 1e-5
+
+
+def test_tiny_corr_tensor_cores_config5_shape(ops, cuda):
+    """BASELINE config 5 shape (60 x 80 = 4800 tokens per image, C = 64): the tensor-core path against the SIMT kernel.
+    Outputs agree to 1e-5 wherever the two pick the same arg-max; a different pick needs two scores within fp32
+    rounding of each other, so at most a handful of the 14400 queries may differ."""
+    g = torch.Generator().manual_seed(12)
+    f0 = torch.randn(3, 64, 60, 80, generator=g).to(cuda)
+    f1 = (0.5 * f0.roll(3, 3) + torch.randn(3, 64, 60, 80, generator=g).to(cuda))
+    a = ops.tiny_corr_posembed(f0, f1, tensor_cores=True)
+    b = ops.tiny_corr_posembed(f0, f1, tensor_cores=False)
+    assert a.shape == b.shape == (3, 2, 60, 80) and torch.isfinite(a).all()
+    bad = ((a - b).abs().amax(dim=1) > 1e-5).float().mean().item()
+    assert bad < 1e-3, bad
 
 
 # --------------------------------------------------------------------------------------------- (f-2)
