@@ -333,13 +333,12 @@ local_corr_v2_kernel(const GatherParams p) {
 // local_corr_v2 is bound by memory-level parallelism, not by bytes: a lane keeps 8 independent 16-byte loads in
 // flight and then spends ~130 issue slots per step on bf16 unpacks, FMAs and shuffles, with f0 held as 64 fp32
 // registers (coherent and incoherent flows take the same time, tools/kernel_bench.py).  Here one
-// mma.sync.m16n8k16 computes 16 neighbours x 16 channels: A = 16 neighbour rows (rows g and g + 8 of the
-// fragment), B = the pixel's own f0 vector repeated in the 8 columns, fp32 accumulate.  Fragments are filled
-// straight from 16-byte global loads — the K dimension is a sum, so its order is free: lane (g, t) takes
-// channels 32 kb + 8 t .. + 7 of its two rows and feeds them to two MMAs (.x/.y and .z/.w words), with the same
-// permutation applied to f0, which sits in shared memory (1 KB per warp, one broadcast LDS.128 per two MMAs).
-// Per 16 neighbours x 256 channels a lane issues 16 independent 16-byte loads (twice v2's bytes in flight at
-// half its registers) and 16 HMMAs; no unpack, no FMA, no shuffle.  Out-of-image neighbours load zeros.
+// mma.sync.m16n8k16 computes 16 rows x 16 channels with fp32 accumulation, fragments filled straight from 16-byte
+// global loads (the K dimension is a sum, so its order is free: the same channel permutation is applied to f0,
+// which sits in shared memory, 1 KB per warp, one LDS.128 per two MMAs).  Per 8 neighbours x C channels a lane
+// issues 2 C/64 independent 16-byte loads (16 for C = 512: twice v2's bytes in flight at half its registers) and
+// as many HMMAs; no unpack, no FMA, one shuffle.  Row layout chosen for the L1: see the loop.  Out-of-image
+// neighbours load zeros.
 // ------------------------------------------------------------------------------------------------
 template <typename T> struct Mma16816;
 template <> struct Mma16816<__nv_bfloat16> {
@@ -363,8 +362,6 @@ __global__ void __launch_bounds__(256, 2)
 local_corr_mma_kernel(const GatherParams p) {
     static_assert(sizeof(T) == 2, "local_corr_mma is for 16-bit feature types");
     constexpr int kMaxNN = 256;                  // (2r+2)^2 for r <= 7
-    constexpr int NB = 2 * VPL;                  // 32-channel blocks per row
-    constexpr int CH = NB < 8 ? NB : 8;          // blocks per load chunk: 16 uint4 in flight per lane
     __shared__ float Dall[8][kMaxNN + 4];
     __shared__ __align__(16) T f0s[8][64 * VPL];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -403,38 +400,42 @@ local_corr_mma_kernel(const GatherParams p) {
         }
         __syncwarp();
         const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
-        for (int n0 = 0; n0 < NN; n0 += 16) {
-            // rows g and g + 8 of the A fragment = neighbours n0 + g and n0 + g + 8
+        for (int n0 = 0; n0 < NN; n0 += 8) {
+            // A-fragment rows 2j and 2j+1 are the two 64-byte halves of a 128-byte piece of neighbour n0 + j (rows
+            // 8.. : neighbour n0 + 4 + j), so the 8 lanes of a quarter-warp read ONE full line per 16-byte load
+            // (4 L1 wavefronts per instruction, not 8).  The B fragment carries the matching f0 channels in the
+            // column of the same parity: D[g][g & 1] is the partial dot product of row g, and the two halves meet
+            // with one shuffle.
             const T* src[2];
 #pragma unroll
             for (int hr = 0; hr < 2; ++hr) {
-                const int n = n0 + g + 8 * hr;
+                const int n = n0 + (g >> 1) + 4 * hr;
                 const int j = n / W2, i = n - j * W2;
                 const int yy = y0 + j - p.r, xx = x0 + i - p.r;
                 const bool ok = n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
-                src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + t4 * 8 : nullptr;
+                src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + 32 * (g & 1) + t4 * 8 : nullptr;
             }
             float dA[4] = {0.f, 0.f, 0.f, 0.f}, dB[4] = {0.f, 0.f, 0.f, 0.f};
+            uint4 u[2][VPL];
 #pragma unroll
-            for (int c0 = 0; c0 < NB; c0 += CH) {
-                uint4 u[2][CH];
+            for (int kb = 0; kb < VPL; ++kb) {
 #pragma unroll
-                for (int kb = 0; kb < CH; ++kb) {
-#pragma unroll
-                    for (int hr = 0; hr < 2; ++hr)
-                        u[hr][kb] = src[hr] ? ldg16(src[hr] + 32 * (c0 + kb)) : make_uint4(0u, 0u, 0u, 0u);
-                }
-#pragma unroll
-                for (int kb = 0; kb < CH; ++kb) {
-                    const uint4 fb = *reinterpret_cast<const uint4*>(f0w + 32 * (c0 + kb) + t4 * 8);
-                    Mma16816<T>::run(dA, u[0][kb].x, u[1][kb].x, u[0][kb].y, u[1][kb].y, fb.x, fb.y);
-                    Mma16816<T>::run(dB, u[0][kb].z, u[1][kb].z, u[0][kb].w, u[1][kb].w, fb.z, fb.w);
-                }
+                for (int hr = 0; hr < 2; ++hr)
+                    u[hr][kb] = src[hr] ? ldg16(src[hr] + 64 * kb) : make_uint4(0u, 0u, 0u, 0u);
             }
-            // every column of the accumulator tile holds the same dot products: column 0 (t4 == 0) stores rows g, g + 8
-            if (t4 == 0) {
-                if (n0 + g < NN) Dsm[n0 + g] = dA[0] + dB[0];
-                if (n0 + g + 8 < NN) Dsm[n0 + g + 8] = dA[2] + dB[2];
+#pragma unroll
+            for (int kb = 0; kb < VPL; ++kb) {
+                const uint4 fb = *reinterpret_cast<const uint4*>(f0w + 64 * kb + 32 * (g & 1) + t4 * 8);
+                Mma16816<T>::run(dA, u[0][kb].x, u[1][kb].x, u[0][kb].y, u[1][kb].y, fb.x, fb.y);
+                Mma16816<T>::run(dB, u[0][kb].z, u[1][kb].z, u[0][kb].w, u[1][kb].w, fb.z, fb.w);
+            }
+            float vlo = (g & 1) ? dA[1] + dB[1] : dA[0] + dB[0];
+            float vhi = (g & 1) ? dA[3] + dB[3] : dA[2] + dB[2];
+            vlo += __shfl_xor_sync(0xffffffffu, vlo, 4);
+            vhi += __shfl_xor_sync(0xffffffffu, vhi, 4);
+            if (t4 == 0 && (g & 1) == 0) {
+                if (n0 + (g >> 1) < NN) Dsm[n0 + (g >> 1)] = vlo;
+                if (n0 + 4 + (g >> 1) < NN) Dsm[n0 + 4 + (g >> 1)] = vhi;
             }
         }
         __syncwarp();
