@@ -12,6 +12,10 @@
  *  - the CALLER owns every buffer (outputs and workspaces); the library never
  *    allocates or frees device memory and keeps no pointer across calls.
  *  - asynchronous on `stream` (a cudaStream_t passed as void*); no hidden syncs.
+ *    One entry point (roma_gp_posterior, two-lane schedule) additionally uses a
+ *    high-priority helper stream and events owned by the library (one set per device,
+ *    created on first use): it forks from and joins back to `stream` inside the call,
+ *    so for the caller the call is still ordered on `stream` alone.
  *  - return 0 on success, a negative ROMA_ERR_* for bad arguments, a positive
  *    cudaError_t for a failed launch.  `roma_last_error_string()` describes the
  *    last failure on the calling thread.  Nothing throws across the ABI.
