@@ -68,6 +68,12 @@ constexpr int kDwThreads = 128;
 constexpr int kDwAhead = 4;   // input rows in flight per thread (cp.async groups)
 constexpr int kDwChunks = (kDwRY + 4) / 5;
 static_assert((kDwRY + 4) % 5 == 0 && kDwChunks >= 2, "strip height + halo must be a multiple of the accumulator ring");
+// TMA-tiled kernel: strips of 36 output rows = 8 five-row input chunks streamed through a ring of 4 shared-memory
+// slots (halo overhead 40/36 instead of 20/16, half as many cold starts per SM, same shared memory per block)
+constexpr int kDwRYL = 36;
+constexpr int kDwChunksL = (kDwRYL + 4) / 5;
+constexpr int kDwRing = 4;
+static_assert((kDwRYL + 4) % 5 == 0 && kDwChunksL > kDwRing, "long strips: whole chunks, more chunks than ring slots");
 
 // One input row (8 unpacked pixels of the thread's channel pair) scattered into the output rows it feeds.
 // Input row r = r0 + I feeds the five output rows r-2..r+2 (tap row dy = r - o + 2); the accumulators of those
@@ -173,34 +179,36 @@ dwconv5_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restr
     }
     extern __shared__ unsigned char dw_smem_raw[];
     unsigned char* tile = dw_smem_raw + ((128u - (tma::saddr(dw_smem_raw) & 127u)) & 127u);   // 128-byte aligned box destinations
-    uint64_t* bars = reinterpret_cast<uint64_t*>(tile + kDwChunks * p.chunk_stride);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tile + kDwRing * p.chunk_stride);
 
     const int tid = threadIdx.x;
     const int pg = blockIdx.x % pr.pair_groups, rg = blockIdx.x / pr.pair_groups;
-    const int b = blockIdx.z, y0 = blockIdx.y * kDwRY;
+    const int b = blockIdx.z, y0 = blockIdx.y * kDwRYL;
     const int h = pr.h, w = pr.w, Cp = pr.Cp;
     // chunk ch completes output rows y0 + 5 ch - 4 ...: it is needed only if the first of them is inside the image
-    int nch = kDwChunks;
+    int nch = kDwChunksL;
     while (nch > 1 && y0 + 5 * (nch - 1) - 4 >= h) --nch;
 
     if (tid == 0) {
         tma::prefetch_map(&map);
-        for (int k = 0; k < nch; ++k) tma::mbar_init(&bars[k], 1);
+        for (int k = 0; k < kDwRing; ++k) tma::mbar_init(&bars[k], 1);
         tma::fence_barrier_init();
     }
     __syncthreads();
+    auto issue = [&](int ch) {      // chunk ch -> ring slot ch % kDwRing (thread 0 only)
+        const int slot = ch % kDwRing;
+        tma::mbar_expect_tx(&bars[slot], (uint32_t)p.chunk_bytes);
+        tma::load_4d(tile + slot * p.chunk_stride, &map, &bars[slot], pg * p.ppb * 2, rg * p.rpb * kDwTW - 2, y0 - 2 + 5 * ch, b);
+    };
     if (tid == 0) {
-        for (int k = 0; k < nch; ++k) {
-            tma::mbar_expect_tx(&bars[k], (uint32_t)p.chunk_bytes);
-            tma::load_4d(tile + k * p.chunk_stride, &map, &bars[k], pg * p.ppb * 2, rg * p.rpb * kDwTW - 2, y0 - 2 + 5 * k, b);
-        }
+        for (int k = 0; k < kDwRing && k < nch; ++k) issue(k);
     }
 
     const int npairs = Cp >> 1, runs = (w + kDwTW - 1) / kDwTW;
     const int pair_l = tid % p.ppb, run_l = tid / p.ppb;
     const int pair = pg * p.ppb + pair_l, run = rg * p.rpb + run_l;
     const bool active = run_l < p.rpb && pair < npairs && run < runs;   // thread 0 (the issuer) is always active
-    if (!active) return;
+    if (!active) return;                                                // exited threads no longer count at the barriers below
     const int c = pair * 2, x0 = run * kDwTW;
     DwOut<T> o;
     o.row_stride = (long long)w * Cp;
@@ -219,25 +227,34 @@ dwconv5_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restr
 
     const unsigned char* tb = tile + run_l * kDwTW * p.pix_bytes + pair_l * (int)sizeof(typename Pair<T>::Raw);
     float2 acc[5][kDwTW];
+    // after a chunk has been consumed by every thread of the block its slot is refilled with the chunk kDwRing ahead
+    auto refill = [&](int ch) {
+        if (ch + kDwRing < nch) {
+            __syncthreads();
+            if (tid == 0) issue(ch + kDwRing);
+        }
+    };
     tma::mbar_wait(&bars[0], 0);
     dw_chunk_smem<T, true, false>(tb, p.row_bytes, p.pix_bytes, o, y0 - 2, h, wv, bv, acc);
+    refill(0);
 #pragma unroll 1
-    for (int ch = 1; ch < kDwChunks - 1; ++ch) {
+    for (int ch = 1; ch < kDwChunksL - 1; ++ch) {
         if (ch >= nch) return;
-        tma::mbar_wait(&bars[ch], 0);
-        dw_chunk_smem<T, false, false>(tb + ch * p.chunk_stride, p.row_bytes, p.pix_bytes, o, y0 - 2 + 5 * ch, h, wv, bv, acc);
+        tma::mbar_wait(&bars[ch % kDwRing], (uint32_t)((ch / kDwRing) & 1));
+        dw_chunk_smem<T, false, false>(tb + (ch % kDwRing) * p.chunk_stride, p.row_bytes, p.pix_bytes, o, y0 - 2 + 5 * ch, h, wv, bv, acc);
+        refill(ch);
     }
-    if (nch < kDwChunks) return;
-    tma::mbar_wait(&bars[kDwChunks - 1], 0);
-    dw_chunk_smem<T, false, true>(tb + (kDwChunks - 1) * p.chunk_stride, p.row_bytes, p.pix_bytes, o, y0 - 2 + 5 * (kDwChunks - 1), h,
-                                  wv, bv, acc);
+    if (nch < kDwChunksL) return;
+    tma::mbar_wait(&bars[(kDwChunksL - 1) % kDwRing], (uint32_t)(((kDwChunksL - 1) / kDwRing) & 1));
+    dw_chunk_smem<T, false, true>(tb + ((kDwChunksL - 1) % kDwRing) * p.chunk_stride, p.row_bytes, p.pix_bytes, o,
+                                  y0 - 2 + 5 * (kDwChunksL - 1), h, wv, bv, acc);
 }
 
 template <typename T>
 static int launch_dw_tma(const void* x, const float* weight, const float* bias, void* out, int B, int h, int w, int C, int relu,
                          int dtype, cudaStream_t st) {
     const int esz = (int)sizeof(T);
-    const int npairs = C / 2, runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRY - 1) / kDwRY;
+    const int npairs = C / 2, runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRYL - 1) / kDwRYL;
     const int pair_groups = cdiv(npairs, 32);
     const int gran = 16 / (2 * esz);                               // pairs per 16 bytes
     int ppb = cdiv(cdiv(npairs, pair_groups), gran) * gran;        // <= 32; box rows are whole 16-byte units
@@ -250,7 +267,7 @@ static int launch_dw_tma(const void* x, const float* weight, const float* bias, 
     p.row_bytes = tcols * p.pix_bytes;
     p.chunk_bytes = 5 * p.row_bytes;
     p.chunk_stride = (p.chunk_bytes + 127) / 128 * 128;
-    const size_t smem = (size_t)kDwChunks * p.chunk_stride + kDwChunks * sizeof(uint64_t) + 128;
+    const size_t smem = (size_t)kDwRing * p.chunk_stride + kDwRing * sizeof(uint64_t) + 128;
 
     CUtensorMap map;
     const uint64_t dims[4] = {(uint64_t)C, (uint64_t)w, (uint64_t)h, (uint64_t)B};
