@@ -254,6 +254,35 @@ class RegressionMatcher(nn.Module):
         in_th = ((coords - fb).norm(dim=-1) < th_n).float()
         return in_th if has_batch else in_th[0]
 
+    def visualize_warp(self, warp, certainty, im_A=None, im_B=None, im_A_path=None, im_B_path=None, device="cuda",
+                       symmetric: bool = True, save_path=None, unnormalize: bool = False):
+        """matcher.py:732-766, headless: each image is transferred through the other direction's warp (the K2 gather
+        kernel in gather-only mode), blended with white by the certainty; returns the (3, H, W') tensor and, when
+        `save_path` is given, writes it as an image file (no window / display involved)."""
+        H, W2, _ = warp.shape
+        W = W2 // 2 if symmetric else W2
+        dev = warp.device
+        if im_A is None:
+            im_A, im_B = _load_rgb(im_A_path), _load_rgb(im_B_path)
+        if not torch.is_tensor(im_A):
+            to_t = lambda im: torch.from_numpy(np.asarray(im.resize((W, H)), dtype=np.float32) / 255.0).to(dev).permute(2, 0, 1)
+            x_A, x_B = to_t(im_A), to_t(im_B)
+        else:
+            x_A, x_B = im_A.to(dev).float(), im_B.to(dev).float()
+        a_from_b = ops.grid_sample(x_B[None], warp[None, :, :W, 2:].float())[0]
+        if symmetric:
+            b_from_a = ops.grid_sample(x_A[None], warp[None, :, W:, :2].float())[0]
+            warp_im = torch.cat((a_from_b, b_from_a), dim=2)
+        else:
+            warp_im = a_from_b
+        vis = certainty * warp_im + (1 - certainty) * torch.ones_like(certainty)
+        if save_path is not None:
+            v = vis
+            if unnormalize:
+                v = v * torch.tensor(_STD, device=dev).view(3, 1, 1) + torch.tensor(_MEAN, device=dev).view(3, 1, 1)
+            Image.fromarray((v.clamp(0, 1).permute(1, 2, 0) * 255).round().to(torch.uint8).cpu().numpy()).save(save_path)
+        return vis
+
     # ------------------------------------------------------------------------------------------ coordinates
     def to_pixel_coordinates(self, coords, H_A, W_A, H_B=None, W_B=None):
         if coords.shape[-1] == 2:

@@ -78,3 +78,37 @@ def test_batched_uint8_tensor_inputs(case):
     w0, c0 = gpu.match(A[None], B[None], batched=True, device="cuda")
     assert warp.shape == (2, up[0], 2 * up[1], 4)
     assert (warp[0] - w0[0]).abs().max().item() < 1e-4 and (cert[0] - c0[0]).abs().max().item() < 1e-3
+
+
+def test_visualize_warp_and_fb_consistency_headless(tmp_path):
+    """§8(f)-4: `visualize_warp` (matcher.py:732-766) and `conf_from_fb_consistency` (:530-551) run on the K2 gather
+    kernel; checked against F.grid_sample on the CPU.  Headless: the visualisation is a tensor, optionally a file."""
+    import torch.nn.functional as F
+    from roma_b200.matcher import RegressionMatcher
+    dev = torch.device("cuda")
+    m = RegressionMatcher(torch.nn.Identity(), torch.nn.Identity(), h=24, w=32, symmetric=True)
+    g = torch.Generator().manual_seed(5)
+    H, W = 24, 32
+    warp = torch.rand(H, 2 * W, 4, generator=g) * 2.2 - 1.1
+    cert = torch.rand(H, 2 * W, generator=g)
+    xA, xB = torch.rand(3, H, W, generator=g), torch.rand(3, H, W, generator=g)
+    vis = m.visualize_warp(warp.to(dev), cert.to(dev), im_A=xA.to(dev), im_B=xB.to(dev), symmetric=True,
+                           save_path=str(tmp_path / "vis.png"))
+    a = F.grid_sample(xB[None], warp[None, :, :W, 2:], mode="bilinear", align_corners=False)[0]
+    b = F.grid_sample(xA[None], warp[None, :, W:, :2], mode="bilinear", align_corners=False)[0]
+    want = cert * torch.cat((a, b), dim=2) + (1 - cert)
+    assert vis.shape == (3, H, 2 * W) and (vis.cpu() - want).abs().max().item() < 1e-5
+    assert (tmp_path / "vis.png").exists()
+    vis1 = m.visualize_warp(warp[:, :W].to(dev), cert[:, :W].to(dev), im_A=xA.to(dev), im_B=xB.to(dev), symmetric=False)
+    assert (vis1.cpu() - (cert[:, :W] * a + (1 - cert[:, :W]))).abs().max().item() < 1e-5
+
+    fwd = torch.rand(2, H, W, 2, generator=g) * 2 - 1
+    bwd = torch.rand(2, H, W, 2, generator=g) * 2 - 1
+    got = m.conf_from_fb_consistency(fwd.to(dev), bwd.to(dev), th=6)
+    xs = torch.linspace(-1 + 1 / W, 1 - 1 / W, W); ys = torch.linspace(-1 + 1 / H, 1 - 1 / H, H)
+    coords = torch.stack((xs[None, :].expand(H, W), ys[:, None].expand(H, W)), dim=-1)
+    fb = F.grid_sample(bwd.permute(0, 3, 1, 2), fwd, mode="bilinear", align_corners=False).permute(0, 2, 3, 1)
+    dist = (coords - fb).norm(dim=-1)
+    want_mask = (dist < 2 * 6 / max(H, W)).float()
+    sure = (dist - 2 * 6 / max(H, W)).abs() > 1e-5                  # away from the threshold
+    assert got.shape == (2, H, W) and torch.equal(got.cpu()[sure], want_mask[sure])
