@@ -312,6 +312,19 @@ int roma_tiny_corr_posembed_tc(const float* feat0, const float* feat1, float* ou
                                int B, int C, int H0, int W0, int H1, int W1,
                                void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * (f-3)  Input path: uint8 RGB batch -> ImageNet-normalised fp32 images at a pass resolution.
+ *
+ * Replaces (reference): romatch/models/matcher.py:606-637, 667-676 with romatch/utils/utils.py:165-261
+ *   (resize, ToTensor, Normalize) in tensor form: (u8 / 255 - mean) / std, then — where (h, w) != (H, W) —
+ *   F.interpolate(mode="bicubic", antialias=True, align_corners=False) with ATen's weights and summation order.
+ * images : DEVICE uint8 (B, 3, H, W) planar, contiguous.   out : DEVICE fp32 (B, 3, h, w) planar.
+ * mean3, std3 : HOST pointers to 3 floats each (passed to the kernel by value).
+ * Downscale factors above 4 per dimension: ROMA_ERR_UNSUPPORTED.
+ */
+int roma_prepare_images(const unsigned char* images, float* out, int B, int H, int W, int h, int w,
+                        const float* mean3, const float* std3, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

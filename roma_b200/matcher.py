@@ -63,6 +63,7 @@ class RegressionMatcher(nn.Module):
         self.sample_thresh = 0.05
         self.overlap_encoder = True      # upsample-pass encoder concurrent with the coarse decoder (second stream)
         self.decoder_priority = True     # ... with the coarse decoder on a high-priority stream
+        self.native_image_prep = True    # uint8 tensors: normalise + antialiased bicubic resize in one kernel
         self._streams = {}
 
     # ------------------------------------------------------------------------------------------ helpers
@@ -136,13 +137,20 @@ class RegressionMatcher(nn.Module):
             if imA.dim() == 3:
                 imA, imB = imA[None], imB[None]
             assert imA.shape == imB.shape, "For batched images we assume same size"
-            if imA.dtype == torch.uint8:
-                imA, imB = self._normalise(imA), self._normalise(imB)
             full_A, full_B = imA, imB
+            if imA.dtype == torch.uint8 and self.native_image_prep and imA.shape[1] == 3:
+                # (f-3): normalisation + antialiased bicubic resize in one kernel per pass resolution, from the uint8 pixels
+                def at(res, t):
+                    if max(t.shape[-2] / res[0], t.shape[-1] / res[1]) > 4:          # beyond the kernel's tap budget
+                        return F.interpolate(self._normalise(t), size=tuple(res), mode="bicubic", antialias=True, align_corners=False)
+                    return ops.prepare_images(t, res)
+            else:
+                if imA.dtype == torch.uint8:
+                    full_A, full_B = self._normalise(imA), self._normalise(imB)
 
-            def at(res, t):
-                return t if tuple(t.shape[-2:]) == tuple(res) else F.interpolate(t, size=tuple(res), mode="bicubic",
-                                                                                 antialias=True, align_corners=False)
+                def at(res, t):
+                    return t if tuple(t.shape[-2:]) == tuple(res) else F.interpolate(t, size=tuple(res), mode="bicubic",
+                                                                                     antialias=True, align_corners=False)
             coarse = {"im_A": at((hs, ws), full_A), "im_B": at((hs, ws), full_B)}
         else:
             pilA, pilB = _load_rgb(im_A_input), _load_rgb(im_B_input)

@@ -509,6 +509,29 @@ def cls_to_flow_refine(cls: torch.Tensor) -> torch.Tensor:
     return out
 
 
+_MEAN3 = (C.c_float * 3)(0.485, 0.456, 0.406)
+_STD3 = (C.c_float * 3)(0.229, 0.224, 0.225)
+
+
+def prepare_images(images_u8: torch.Tensor, size_hw: Tuple[int, int], mean=None, std=None) -> torch.Tensor:
+    """uint8 (B,3,H,W) -> ImageNet-normalised fp32 (B,3,h,w): (u8/255 - mean)/std and, where the size differs, the
+    antialiased bicubic resize of F.interpolate(..., antialias=True) (utils.py:165-261 in tensor form), one kernel."""
+    dev = _cuda(images_u8)
+    if images_u8.dtype != torch.uint8 or images_u8.dim() != 4 or images_u8.shape[1] != 3:
+        raise ValueError("prepare_images expects a uint8 (B,3,H,W) tensor")
+    x = images_u8.contiguous()
+    B, _, H, W = x.shape
+    h, w = int(size_hw[0]), int(size_hw[1])
+    m = _MEAN3 if mean is None else (C.c_float * 3)(*[float(v) for v in mean])
+    s = _STD3 if std is None else (C.c_float * 3)(*[float(v) for v in std])
+    out = torch.empty((B, 3, h, w), device=dev, dtype=torch.float32)
+    lib = _lib.load()
+    _run("roma_prepare_images", dict(B=B, H=H, W=W, h=h, w=w),
+         lambda: lib.roma_prepare_images(_ptr(x), _ptr(out), B, H, W, h, w, C.cast(m, C.c_void_p), C.cast(s, C.c_void_p),
+                                         _stream(dev)))
+    return out
+
+
 _tiny_ws = {}
 
 

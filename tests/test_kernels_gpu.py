@@ -566,3 +566,29 @@ def test_dwconv_pointwise_rejects_other_widths(ops, cuda):
     with pytest.raises((RuntimeError, ValueError)):
         ops.dwconv5x5_pointwise(x, torch.zeros(25, 32, device=cuda), torch.zeros(32, device=cuda), torch.zeros(32, 32, device=cuda),
                                 torch.zeros(32, device=cuda))
+
+
+# --------------------------------------------------------------------------------------------- (f-3)
+@pytest.mark.parametrize("H,W,h,w", [(864, 864, 560, 560), (480, 640, 560, 560), (600, 1200, 224, 308), (64, 48, 64, 48),
+                                     (100, 75, 333, 290)])
+def test_prepare_images_vs_aten(ops, cuda, H, W, h, w):
+    """uint8 batch -> normalised (+ antialiased bicubic resize): against (u8/255 - mean)/std followed by
+    F.interpolate(antialias=True) evaluated by ATen on the CPU; the same-size case is bit-identical."""
+    import torch.nn.functional as F
+    g = torch.Generator().manual_seed(H * 7 + w)
+    img = (torch.rand(2, 3, H, W, generator=g) * 255).round().to(torch.uint8)
+    mean = torch.tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)
+    std = torch.tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
+    norm = (img.float() / 255.0 - mean) / std
+    got = ops.prepare_images(img.to(cuda), (h, w))
+    assert got.shape == (2, 3, h, w) and got.dtype == torch.float32
+    if (h, w) == (H, W):
+        assert torch.equal(got.cpu(), norm)
+    else:
+        want = F.interpolate(norm, size=(h, w), mode="bicubic", antialias=True, align_corners=False)
+        assert err(got, want) < 2e-5
+
+
+def test_prepare_images_rejects_large_downscale(ops, cuda):
+    with pytest.raises((RuntimeError, ValueError)):
+        ops.prepare_images(torch.zeros(1, 3, 900, 900, dtype=torch.uint8, device=cuda), (200, 200))
