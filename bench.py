@@ -253,6 +253,7 @@ def main():
     ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16", "float32"])
     ap.add_argument("--num", type=int, default=10000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sample-lanes", type=int, default=2, help="streams sample_batch spreads the pairs over")
     ap.add_argument("--decoder-priority", type=int, default=1, help="0: upsample-pass encoder on a side stream, coarse decoder on "
                     "the caller's; 1 (default): coarse decoder on a high-priority stream")
     ap.add_argument("--ref-budget", type=float, default=200.0, help="wall-clock cap (s) of the CPU reference arm")
@@ -285,6 +286,7 @@ def main():
     model = roma_b200.roma_outdoor(dev, weights, dinov2, coarse_res=args.coarse, upsample_res=args.upsample, amp_dtype=amp)
 
     model.decoder_priority = bool(args.decoder_priority)
+    model.sample_lanes = args.sample_lanes
     A8, B8 = synthetic_pairs(args.batch, args.upsample, 1234 + rank)
     A_host, B_host = A8.pin_memory(), B8.pin_memory()
     A_dev, B_dev = A8.to(dev), B8.to(dev)

@@ -284,6 +284,11 @@ int roma_dwconv_set_path(int path);
  */
 int roma_layernorm(const void* x, const void* gamma, const void* beta, void* out,
                    long long rows, int D, float eps, int dtype, void* stream);
+/* LayerNorm(x + shift) with shift fp32 (D), added in fp32 in front of the statistics.  Lets a pre-norm transformer keep
+ * its residual stream without the bias vectors of its residual branches (each branch = one GEMM accumulating in place),
+ * the accumulated bias re-entering at every norm.  Otherwise as roma_layernorm. */
+int roma_layernorm_shift(const void* x, const float* shift, const void* gamma, const void* beta, void* out,
+                         long long rows, int D, float eps, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Encoder: 2x2 / stride-2 max pooling, channels-last (floor semantics: odd trailing row / column dropped).

@@ -12,8 +12,8 @@ namespace roma {
 
 template <typename T, int NV>
 __global__ void __launch_bounds__(256)
-layernorm_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* __restrict__ beta, T* __restrict__ out,
-                 long long rows, int D, float eps) {
+layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const T* __restrict__ gamma, const T* __restrict__ beta,
+                 T* __restrict__ out, long long rows, int D, float eps) {
     constexpr int kVec = Elem<T>::kVec;
     const int lane = threadIdx.x & 31;
     const int nvec = D / kVec;
@@ -27,6 +27,10 @@ layernorm_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* 
             const int vi = lane + 32 * i;
             if (vi < nvec) {
                 unpack16<T>(ldg16(xr + vi * kVec), v[i]);
+                if (shift) {                     // residual stream stored without its accumulated bias vector (see header)
+#pragma unroll
+                    for (int k = 0; k < kVec; ++k) v[i][k] += __ldg(shift + vi * kVec + k);
+                }
 #pragma unroll
                 for (int k = 0; k < kVec; ++k) s += v[i][k];
             } else {
@@ -61,13 +65,13 @@ layernorm_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* 
 }
 
 template <typename T>
-static int launch_layernorm(const void* x, const void* g, const void* b, void* out, long long rows, int D, float eps, cudaStream_t st) {
+static int launch_layernorm(const void* x, const float* shift, const void* g, const void* b, void* out, long long rows, int D, float eps, cudaStream_t st) {
     constexpr int kVec = Elem<T>::kVec;
     const int nv = cdiv(D / kVec, 32);
     long long blocks = (rows + 7) / 8;
     const long long cap = (long long)sm_count() * 16;
     if (blocks > cap) blocks = cap;
-#define ROMA_LN(NVC) layernorm_kernel<T, NVC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, (const T*)g, (const T*)b, (T*)out, rows, D, eps)
+#define ROMA_LN(NVC) layernorm_kernel<T, NVC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, shift, (const T*)g, (const T*)b, (T*)out, rows, D, eps)
     if (nv <= 1) ROMA_LN(1);
     else if (nv <= 2) ROMA_LN(2);
     else if (nv <= 4) ROMA_LN(4);
@@ -79,23 +83,38 @@ static int launch_layernorm(const void* x, const void* g, const void* b, void* o
 
 }  // namespace roma
 
-extern "C" int roma_layernorm(const void* x, const void* gamma, const void* beta, void* out,
-                              long long rows, int D, float eps, int dtype, void* stream) {
+static int layernorm_entry(const char* who, const void* x, const float* shift, const void* gamma, const void* beta, void* out,
+                           long long rows, int D, float eps, int dtype, void* stream) {
     using namespace roma;
-    ROMA_REQUIRE(x && gamma && beta && out, ROMA_ERR_BAD_ARG, "roma_layernorm: null pointer");
-    ROMA_REQUIRE(rows > 0 && D > 0, ROMA_ERR_BAD_ARG, "roma_layernorm: bad sizes");
+    ROMA_REQUIRE(x && gamma && beta && out, ROMA_ERR_BAD_ARG, "%s: null pointer", who);
+    ROMA_REQUIRE(rows > 0 && D > 0, ROMA_ERR_BAD_ARG, "%s: bad sizes", who);
     const int kvec = dtype == ROMA_F32 ? 4 : 8;
-    ROMA_REQUIRE(D % kvec == 0, ROMA_ERR_UNSUPPORTED, "roma_layernorm: D = %d must be a multiple of %d", D, kvec);
+    ROMA_REQUIRE(D % kvec == 0, ROMA_ERR_UNSUPPORTED, "%s: D = %d must be a multiple of %d", who, D, kvec);
     ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(gamma) |
-                   reinterpret_cast<uintptr_t>(beta)) & 15u) == 0, ROMA_ERR_ALIGNMENT, "roma_layernorm: pointers must be 16-byte aligned");
+                   reinterpret_cast<uintptr_t>(beta)) & 15u) == 0, ROMA_ERR_ALIGNMENT, "%s: pointers must be 16-byte aligned", who);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     int rc;
     switch (dtype) {
-        case ROMA_F32:  rc = launch_layernorm<float>(x, gamma, beta, out, rows, D, eps, st); break;
-        case ROMA_F16:  rc = launch_layernorm<__half>(x, gamma, beta, out, rows, D, eps, st); break;
-        case ROMA_BF16: rc = launch_layernorm<__nv_bfloat16>(x, gamma, beta, out, rows, D, eps, st); break;
-        default: return fail(ROMA_ERR_BAD_ARG, "roma_layernorm: unknown dtype %d", dtype);
+        case ROMA_F32:  rc = launch_layernorm<float>(x, shift, gamma, beta, out, rows, D, eps, st); break;
+        case ROMA_F16:  rc = launch_layernorm<__half>(x, shift, gamma, beta, out, rows, D, eps, st); break;
+        case ROMA_BF16: rc = launch_layernorm<__nv_bfloat16>(x, shift, gamma, beta, out, rows, D, eps, st); break;
+        default: return fail(ROMA_ERR_BAD_ARG, "%s: unknown dtype %d", who, dtype);
     }
     if (rc) return rc;
-    return check_launch("roma_layernorm");
+    return check_launch(who);
+}
+
+extern "C" int roma_layernorm(const void* x, const void* gamma, const void* beta, void* out,
+                              long long rows, int D, float eps, int dtype, void* stream) {
+    return layernorm_entry("roma_layernorm", x, nullptr, gamma, beta, out, rows, D, eps, dtype, stream);
+}
+
+// LayerNorm(x + shift), shift fp32 (D): the residual stream of a pre-norm transformer can be kept WITHOUT the bias
+// vectors of its residual branches (x' = x - sum of the biases so far), so that every branch is one GEMM accumulating
+// in place (beta = 1, no separate residual add and no bias pass); the accumulated bias re-enters here, in fp32, in
+// front of the statistics.
+extern "C" int roma_layernorm_shift(const void* x, const float* shift, const void* gamma, const void* beta, void* out,
+                                    long long rows, int D, float eps, int dtype, void* stream) {
+    ROMA_REQUIRE(shift, ROMA_ERR_BAD_ARG, "roma_layernorm_shift: null shift");
+    return layernorm_entry("roma_layernorm_shift", x, shift, gamma, beta, out, rows, D, eps, dtype, stream);
 }

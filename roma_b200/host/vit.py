@@ -20,13 +20,16 @@ import torch.nn.functional as F
 class RowNorm(nn.LayerNorm):
     """nn.LayerNorm (same parameters / state_dict keys) that runs `roma_layernorm` on CUDA at inference."""
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def native(self, x: torch.Tensor) -> bool:
         D = self.normalized_shape[0]
-        if (x.is_cuda and not self.training and x.dtype in (torch.float16, torch.bfloat16, torch.float32)
-                and D % 8 == 0 and D <= (1024 if x.dtype == torch.float32 else 2048)):
+        return (x.is_cuda and not self.training and x.dtype in (torch.float16, torch.bfloat16, torch.float32)
+                and D % 8 == 0 and D <= (1024 if x.dtype == torch.float32 else 2048))
+
+    def forward(self, x: torch.Tensor, shift: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if self.native(x):
             from .. import ops
-            return ops.layer_norm(x, self.weight, self.bias, self.eps)
-        return super().forward(x)
+            return ops.layer_norm(x, self.weight, self.bias, self.eps, shift=shift)
+        return super().forward(x if shift is None else (x.float() + shift).to(x.dtype))
 
 
 class SelfAttention(nn.Module):
@@ -93,6 +96,22 @@ class Block(nn.Module):
                               (ps[3].float() * g2[:, None]).to(dt), (ps[4].float() * g2).to(dt))
             self._fold_key = key
         return self._fold
+
+    def foldable(self, x) -> bool:
+        return (not self.training and x.is_cuda and isinstance(self.ls1, ChannelScale) and self.attn.proj.bias is not None
+                and self.norm1.native(x))
+
+    def forward_unbiased(self, x, shift):
+        """x is the residual stream WITHOUT the bias vectors accumulated so far (`shift`, fp32 (D)): both residual
+        branches are GEMMs accumulating into x in place (beta = 1: no separate add, no bias pass); the bias re-enters in
+        fp32 inside the next LayerNorm (`roma_layernorm_shift`).  Returns (x, shift + b1 + b2); x is modified in place."""
+        w1, b1, w2, b2 = self._folded()
+        B, N, D = x.shape
+        x2 = x.view(B * N, D)
+        x2.addmm_(self.attn.attend(self.norm1(x, shift)).reshape(B * N, D), w1.t())
+        shift = shift + b1.float()
+        x2.addmm_(F.gelu(self.mlp.fc1(self.norm2(x, shift))).reshape(B * N, -1), w2.t())
+        return x, shift + b2.float()
 
     def forward(self, x):
         if not self.training and x.is_cuda and isinstance(self.ls1, ChannelScale) and self.attn.proj.bias is not None:
@@ -163,6 +182,7 @@ class DinoViT(nn.Module):
                         nn.init.zeros_(m.bias)
         self.requires_grad_(False)
         self._pos_cache = {}
+        self.unbiased_residual = True    # residual branches as in-place accumulating GEMMs (Block.forward_unbiased)
 
     def _pos(self, hp: int, wp: int, dtype) -> torch.Tensor:
         """Position table resampled to an hp x wp patch grid (dinov2.py:166-191: bicubic, +0.1 scale nudge)."""
@@ -188,6 +208,11 @@ class DinoViT(nn.Module):
         t = self.patch_embed(x)
         t = torch.cat((self.cls_token.expand(B, -1, -1).to(t.dtype), t), dim=1)
         t = t + self._pos(H // self.patch_size, W // self.patch_size, t.dtype)
+        if self.unbiased_residual and t.is_contiguous() and all(blk.foldable(t) for blk in self.blocks):
+            shift = torch.zeros(t.shape[-1], device=t.device, dtype=torch.float32)
+            for blk in self.blocks:
+                t, shift = blk.forward_unbiased(t, shift)
+            return self.norm(t, shift)[:, 1:]
         for blk in self.blocks:
             t = blk(t)
         return self.norm(t)[:, 1:]

@@ -64,6 +64,7 @@ class RegressionMatcher(nn.Module):
         self.overlap_encoder = True      # upsample-pass encoder concurrent with the coarse decoder (second stream)
         self.decoder_priority = True     # ... with the coarse decoder on a high-priority stream
         self.native_image_prep = True    # uint8 tensors: normalise + antialiased bicubic resize in one kernel
+        self.sample_lanes = 2            # streams sample_batch spreads the pairs over
         self._streams = {}
 
     # ------------------------------------------------------------------------------------------ helpers
@@ -224,11 +225,16 @@ class RegressionMatcher(nn.Module):
         dev = matches.device
         cur = torch.cuda.current_stream(dev)
         lanes = [self._side_stream(dev), self._second_stream(dev)]
+        for k in range(2, max(2, int(self.sample_lanes))):
+            key = ("lane", k, dev.index if dev.index is not None else torch.cuda.current_device())
+            if key not in self._streams:
+                self._streams[key] = torch.cuda.Stream(device=dev)
+            lanes.append(self._streams[key])
         for st in lanes:
             st.wait_stream(cur)
         ms, cs = [], []
         for i in range(B):
-            with torch.cuda.stream(lanes[i % 2]):
+            with torch.cuda.stream(lanes[i % len(lanes)]):
                 m, c = ops.sample(matches[i], certainty[i], num=num, sample_thresh=self.sample_thresh,
                                   sample_mode=self.sample_mode, generator=None if generators is None else generators[i])
             ms.append(m)

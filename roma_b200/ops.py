@@ -442,9 +442,11 @@ def pointwise_narrow(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor) 
     return out.permute(0, 3, 1, 2)
 
 
-def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float) -> torch.Tensor:
-    """F.layer_norm(x, (D,), weight, bias, eps) over the last dimension (block.py:88-101, dinov2.py:236)."""
-    dev = _cuda(x, weight, bias)
+def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float,
+               shift: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """F.layer_norm(x [+ shift], (D,), weight, bias, eps) over the last dimension (block.py:88-101, dinov2.py:236).
+    shift: optional fp32 (D) vector added in fp32 in front of the statistics (`roma_layernorm_shift`)."""
+    dev = _cuda(x, weight, bias, shift)
     if x.dtype not in _DT:
         raise ValueError(f"unsupported dtype {x.dtype}")
     D = x.shape[-1]
@@ -453,6 +455,12 @@ def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: f
     out = torch.empty_like(x)
     rows = x.numel() // D
     lib = _lib.load()
+    if shift is not None:
+        shift = shift.reshape(D).float().contiguous()
+        _run("roma_layernorm", dict(rows=rows, D=D, esize=x.element_size()),
+             lambda: lib.roma_layernorm_shift(_ptr(x), _ptr(shift), _ptr(weight), _ptr(bias), _ptr(out), rows, D, float(eps),
+                                              _DT[x.dtype], _stream(dev)))
+        return out
     _run("roma_layernorm", dict(rows=rows, D=D, esize=x.element_size()),
          lambda: lib.roma_layernorm(_ptr(x), _ptr(weight), _ptr(bias), _ptr(out), rows, D, float(eps), _DT[x.dtype], _stream(dev)))
     return out

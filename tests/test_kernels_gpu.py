@@ -592,3 +592,40 @@ def test_prepare_images_vs_aten(ops, cuda, H, W, h, w):
 def test_prepare_images_rejects_large_downscale(ops, cuda):
     with pytest.raises((RuntimeError, ValueError)):
         ops.prepare_images(torch.zeros(1, 3, 900, 900, dtype=torch.uint8, device=cuda), (200, 200))
+
+
+# --------------------------------------------------------------------------------------------- encoder side
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 3e-2), (torch.float16, 4e-3)])
+def test_layernorm_shift(ops, cuda, dtype, tol):
+    """LayerNorm(x + shift) with the shift added in fp32 inside the kernel vs F.layer_norm on the fp32 sum."""
+    g = torch.Generator().manual_seed(17)
+    x = (torch.randn(3, 37, 1024, generator=g) * 2 + 0.5).to(dtype)
+    shift = torch.randn(1024, generator=g) * 0.7
+    w = (1 + 0.1 * torch.randn(1024, generator=g)).to(dtype); b = (0.1 * torch.randn(1024, generator=g)).to(dtype)
+    want = torch.nn.functional.layer_norm(x.float() + shift, (1024,), w.float(), b.float(), 1e-6)
+    got = ops.layer_norm(x.to(cuda), w.to(cuda), b.to(cuda), 1e-6, shift=shift.to(cuda))
+    assert got.dtype == dtype and err(got, want) < tol
+    assert torch.equal(ops.layer_norm(x.to(cuda), w.to(cuda), b.to(cuda), 1e-6, shift=torch.zeros(1024, device=cuda)),
+                       ops.layer_norm(x.to(cuda), w.to(cuda), b.to(cuda), 1e-6))
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 6e-2)])
+def test_vit_unbiased_residual_stream(cuda, dtype, tol):
+    """DinoViT with the residual branches as in-place accumulating GEMMs (biases carried as an fp32 shift into the
+    LayerNorms) vs the plain block formulation, same weights with NON-zero biases and LayerScale."""
+    from roma_b200.host.vit import DinoViT
+    torch.manual_seed(3)
+    vit = DinoViT(img_size=70, patch_size=14, embed_dim=128, depth=3, num_heads=4, init_values=0.7)
+    with torch.no_grad():
+        for m in vit.modules():
+            if isinstance(m, torch.nn.Linear):
+                m.bias.normal_(std=0.3)
+    vit = vit.to(cuda).to(dtype).eval()
+    x = torch.randn(2, 3, 70, 84, device=cuda).to(dtype)
+    with torch.inference_mode():
+        vit.unbiased_residual = True
+        a = vit.patch_tokens(x)
+        vit.unbiased_residual = False
+        b = vit.patch_tokens(x)
+    assert a.shape == b.shape == (2, 30, 128)
+    assert err(a, b) < tol
