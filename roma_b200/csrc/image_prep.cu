@@ -30,69 +30,123 @@ __device__ __forceinline__ float cubic_aa(float x) {
     return 0.f;
 }
 
-// weights of output index i along one dimension; returns the first input index, n = number of taps
-__device__ __forceinline__ int aa_weights(int i, int in_size, float scale, float support, float (&wt)[kPrepMaxTaps], int& n) {
-    const float center = scale * ((float)i + 0.5f);
-    const int xmin = max((int)(center - support + 0.5f), 0);
-    n = min((int)(center + support + 0.5f), in_size) - xmin;
-    n = min(n, kPrepMaxTaps);
-    const float invscale = scale >= 1.f ? 1.f / scale : 1.f;
-    const float xmc = (float)xmin - center;
-    float total = 0.f;
-#pragma unroll
-    for (int j = 0; j < kPrepMaxTaps; ++j) {
-        float wv = 0.f;
-        if (j < n) { wv = cubic_aa(((float)j + xmc + 0.5f) * invscale); total += wv; }
-        wt[j] = wv;
-    }
-    if (total != 0.f) {
-#pragma unroll
-        for (int j = 0; j < kPrepMaxTaps; ++j) wt[j] = wt[j] / total;
-    }
-    return xmin;
+constexpr int kPrepTile = 16;         // output tile of a block: 16 x 16 pixels, all three channels
+constexpr int kPrepThreads = kPrepTile * kPrepTile;
+
+// geometry of output index i along one dimension (the integer arithmetic of ATen's weight computation)
+struct AaSpan { float center; int lo, n; };
+__device__ __forceinline__ AaSpan aa_span(int i, int in_size, float scale, float support) {
+    AaSpan s;
+    s.center = scale * ((float)i + 0.5f);
+    s.lo = max((int)(s.center - support + 0.5f), 0);
+    s.n = min(min((int)(s.center + support + 0.5f), in_size) - s.lo, kPrepMaxTaps);
+    return s;
 }
 
-__global__ void __launch_bounds__(256)
+// Resize: a block owns a 16 x 16 output tile of all three channels and works in four phases out of shared memory.
+//   1. weights: thread (o, j) evaluates the raw cubic taps j and j + 16 of column ox0 + o and of row oy0 + o; after a
+//      barrier it sums its vector's taps in ascending order (ATen's `total`) and divides its own taps by it;
+//   2. stage: the union of the input spans of the tile (the spans are monotonic in the output index, so the first and
+//      last column / row bound it) is loaded once, coalesced along x, as NORMALISED fp32 values (table lookup per byte);
+//   3. horizontal: tmp[c][y][ox] = sum_i tile[c][y][x0(ox) + i] * wx[ox][i], ascending i - ATen's inner sum, which
+//      does not depend on the output row, so it is evaluated once per input row instead of once per (row, tap);
+//   4. vertical: out[c][oy][ox] = sum_j tmp[c][y0(oy) + j][ox] * wy[oy][j], ascending j.
+// Same products and the same summation order as the direct double loop, 2.3x fewer of them at scale 1.54.
+__global__ void __launch_bounds__(kPrepThreads)
 prepare_images_kernel(const unsigned char* __restrict__ src, float* __restrict__ out, int B, int H, int W, int h, int w,
-                      float m0, float m1, float m2, float s0, float s1, float s2) {
+                      float m0, float m1, float m2, float s0, float s1, float s2, int tile_w, int tile_h) {
+    extern __shared__ float prep_smem[];
+    __shared__ float lut[3][256];
+    __shared__ float wraw[2][kPrepTile][kPrepMaxTaps], wn[2][kPrepTile][kPrepMaxTaps];
+    __shared__ int first[2][kPrepTile], taps[2][kPrepTile];
+    float* tile = prep_smem;                                          // [3][tile_h][tile_w]
+    float* tmp = prep_smem + 3 * tile_h * tile_w;                     // [3][tile_h][16]
+    const int tid = threadIdx.x, o = tid / kPrepTile, jj = tid % kPrepTile;
+    const int b = blockIdx.z;
+    const int ox0 = blockIdx.x * kPrepTile, oy0 = blockIdx.y * kPrepTile;
+    const float sc[2] = {(float)W / (float)w, (float)H / (float)h};
+    const int in_size[2] = {W, H}, out_size[2] = {w, h}, o0[2] = {ox0, oy0};
+    {
+        const float f = (float)tid / 255.f;
+        lut[0][tid] = (f - m0) / s0; lut[1][tid] = (f - m1) / s1; lut[2][tid] = (f - m2) / s2;
+    }
+#pragma unroll
+    for (int d = 0; d < 2; ++d) {
+        const float support = sc[d] >= 1.f ? 2.f * sc[d] : 2.f, invscale = sc[d] >= 1.f ? 1.f / sc[d] : 1.f;
+        const int i = min(o0[d] + o, out_size[d] - 1);                // columns / rows past the edge repeat the last one
+        const AaSpan sp = aa_span(i, in_size[d], sc[d], support);
+        const float xmc = (float)sp.lo - sp.center;
+        for (int j = jj; j < kPrepMaxTaps; j += kPrepTile)
+            wraw[d][o][j] = j < sp.n ? cubic_aa(((float)j + xmc + 0.5f) * invscale) : 0.f;
+        if (jj == 0) { first[d][o] = sp.lo; taps[d][o] = sp.n; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int d = 0; d < 2; ++d) {
+        float total = 0.f;
+        const int n = taps[d][o];
+        for (int j = 0; j < n; ++j) total += wraw[d][o][j];
+        for (int j = jj; j < kPrepMaxTaps; j += kPrepTile)
+            wn[d][o][j] = total != 0.f ? wraw[d][o][j] / total : wraw[d][o][j];
+    }
+    const int last = kPrepTile - 1;
+    const int xlo = first[0][0], ylo = first[1][0];
+    const int tw = min(first[0][last] + taps[0][last] - xlo, tile_w), th = min(first[1][last] + taps[1][last] - ylo, tile_h);
+    const unsigned char* sb = src + (long long)b * 3 * H * W;
+    for (int r = tid / 32; r < 3 * th; r += kPrepThreads / 32) {
+        const int c = r / th, y = r - c * th;
+        const unsigned char* srow = sb + ((long long)c * H + ylo + y) * W + xlo;
+        float* trow = tile + (c * tile_h + y) * tile_w;
+        for (int x = tid % 32; x < tw; x += 32) trow[x] = lut[c][srow[x]];
+    }
+    __syncthreads();
+    {
+        const int ox = jj, x0 = first[0][ox] - xlo, nx = taps[0][ox];
+        const float* wx = wn[0][ox];
+        for (int r = o; r < 3 * th; r += kPrepTile) {
+            const int c = r / th, y = r - c * th;
+            const float* row = tile + (c * tile_h + y) * tile_w + x0;
+            float acc = 0.f;
+            for (int i = 0; i < nx; ++i) acc += row[i] * wx[i];
+            tmp[(c * tile_h + y) * kPrepTile + ox] = acc;
+        }
+    }
+    __syncthreads();
+    const int ox = ox0 + jj, oy = oy0 + o;
+    if (ox >= w || oy >= h) return;
+    const int y0 = first[1][o] - ylo, ny = taps[1][o];
+    const float* wy = wn[1][o];
+    float* ob = out + (long long)b * 3 * h * w + (long long)oy * w + ox;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float* col = tmp + (c * tile_h + y0) * kPrepTile + jj;
+        float acc = 0.f;
+        for (int j = 0; j < ny; ++j) acc += col[j * kPrepTile] * wy[j];
+        ob[(long long)c * h * w] = acc;
+    }
+}
+
+// Same resolution: pure table lookup, 4 pixels per thread where the row length allows (uchar4 in, float4 out).
+__global__ void __launch_bounds__(256)
+normalise_images_kernel(const unsigned char* __restrict__ src, float* __restrict__ out, long long plane, long long total,
+                        float m0, float m1, float m2, float s0, float s1, float s2, int vec) {
     __shared__ float lut[3][256];
     {
-        const int v = threadIdx.x;                                    // blockDim.x == 256
+        const int v = threadIdx.x;
         const float f = (float)v / 255.f;
         lut[0][v] = (f - m0) / s0; lut[1][v] = (f - m1) / s1; lut[2][v] = (f - m2) / s2;
     }
     __syncthreads();
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)B * h * w) return;
-    const int ox = (int)(idx % w);
-    const int oy = (int)((idx / w) % h);
-    const int b = (int)(idx / ((long long)w * h));
-    const unsigned char* sb = src + (long long)b * 3 * H * W;
-    float* ob = out + (long long)b * 3 * h * w + (long long)oy * w + ox;
-    if (h == H && w == W) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c) ob[(long long)c * h * w] = lut[c][sb[((long long)c * H + oy) * W + ox]];
-        return;
-    }
-    const float sx = (float)W / (float)w, sy = (float)H / (float)h;
-    const float supx = sx >= 1.f ? 2.f * sx : 2.f, supy = sy >= 1.f ? 2.f * sy : 2.f;
-    float wx[kPrepMaxTaps], wy[kPrepMaxTaps];
-    int nx, ny;
-    const int x0 = aa_weights(ox, W, sx, supx, wx, nx);
-    const int y0 = aa_weights(oy, H, sy, supy, wy, ny);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const unsigned char* sc = sb + (long long)c * H * W;
-        float acc = 0.f;
-        for (int j = 0; j < ny; ++j) {
-            const unsigned char* row = sc + (long long)(y0 + j) * W + x0;
-            float r = 0.f;
-#pragma unroll
-            for (int i = 0; i < kPrepMaxTaps; ++i)
-                if (i < nx) r += lut[c][row[i]] * wx[i];
-            acc += r * wy[j];
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (vec) {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i * 4 < total; i += stride) {
+            const int c = (int)((i * 4 / plane) % 3);
+            const uchar4 u = reinterpret_cast<const uchar4*>(src)[i];
+            reinterpret_cast<float4*>(out)[i] = make_float4(lut[c][u.x], lut[c][u.y], lut[c][u.z], lut[c][u.w]);
         }
-        ob[(long long)c * h * w] = acc;
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
+            out[i] = lut[(int)((i / plane) % 3)][src[i]];
     }
 }
 
@@ -109,8 +163,25 @@ extern "C" int roma_prepare_images(const unsigned char* images, float* out, int 
     ROMA_REQUIRE(smax <= 4.f, ROMA_ERR_UNSUPPORTED,                  // taps per dimension <= 4 * scale + 1 <= 17
                  "roma_prepare_images: downscale factor %.2f > 4 is not supported (resize in two steps)", smax);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    const long long n = (long long)B * h * w;
-    prepare_images_kernel<<<cdiv(n, 256), 256, 0, st>>>(images, out, B, H, W, h, w, mean3[0], mean3[1], mean3[2],
-                                                        std3[0], std3[1], std3[2]);
+    if (h == H && w == W) {
+        const long long plane = (long long)H * W, total = 3ll * B * plane;
+        const int vec = plane % 4 == 0 && ((reinterpret_cast<uintptr_t>(images) & 3u) | (reinterpret_cast<uintptr_t>(out) & 15u)) == 0;
+        long long blocks = ((vec ? total / 4 : total) + 255) / 256;
+        const long long cap = (long long)sm_count() * 16;
+        if (blocks > cap) blocks = cap;
+        normalise_images_kernel<<<(unsigned)blocks, 256, 0, st>>>(images, out, plane, total, mean3[0], mean3[1], mean3[2],
+                                                                 std3[0], std3[1], std3[2], vec);
+        return check_launch("roma_prepare_images");
+    }
+    ROMA_REQUIRE(B <= 65535, ROMA_ERR_UNSUPPORTED, "roma_prepare_images: batch too large");
+    // input span of 16 consecutive outputs: <= 15 * scale + 2 * support + 2
+    auto span = [](float sc) { const float sup = sc >= 1.f ? 2.f * sc : 2.f; return (int)ceilf(15.f * sc + 2.f * sup) + 3; };
+    const int tile_w = span(sx), tile_h = span(sy);
+    const size_t smem = (size_t)(3 * tile_w * tile_h + 3 * tile_h * kPrepTile) * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(prepare_images_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail((int)e, "roma_prepare_images: smem opt-in (%zu B): %s", smem, cudaGetErrorString(e));
+    const dim3 grid((unsigned)cdiv(w, kPrepTile), (unsigned)cdiv(h, kPrepTile), (unsigned)B);
+    prepare_images_kernel<<<grid, kPrepThreads, smem, st>>>(images, out, B, H, W, h, w, mean3[0], mean3[1], mean3[2],
+                                                                     std3[0], std3[1], std3[2], tile_w, tile_h);
     return check_launch("roma_prepare_images");
 }
