@@ -330,6 +330,25 @@ int roma_tiny_corr_posembed_tc(const float* feat0, const float* feat1, float* ou
 int roma_prepare_images(const unsigned char* images, float* out, int B, int H, int W, int h, int w,
                         const float* mean3, const float* std3, void* stream);
 
+/* (f-3)  Input path with the reference's OWN resize: PIL `Image.resize((w, h), Image.BICUBIC)` of an 8-bit RGB image,
+ * then ToTensor and Normalize — bit-exact integer arithmetic.
+ *
+ * Replaces (reference): romatch/utils/utils.py:223-232 (TupleResize -> PIL resize), :234-239 (ToTensorScaled, / 255),
+ *   :254-261 (Normalize) as applied by romatch/models/matcher.py:628-634 and :667-676 to file / PIL inputs.  The resize
+ *   arithmetic is Pillow's (third-party, libImaging/Resample.c, 8 bits per channel): double-precision bicubic
+ *   coefficients quantised to 22 fractional bits, horizontal then vertical pass, each rounded and clipped to 8 bits;
+ *   a dimension that does not change is passed through.
+ * images : DEVICE uint8, B images of 3 channels, addressed images[b*stride_b + c*stride_c + y*stride_y + x*stride_x]
+ *          (strides in bytes: (H, W, 3) interleaved as decoded by PIL = {H*W*3, 1, W*3, 3}; planar = {3*H*W, H*W, W, 1}).
+ * out    : DEVICE fp32 (B, 3, h, w) planar = (resized / 255 - mean) / std, or NULL.
+ * out_u8 : DEVICE uint8 (B, 3, h, w) planar = the resized 8-bit image, or NULL (at least one output is required).
+ * mean3, std3 : HOST pointers to 3 floats each (required with `out`).
+ * Downscale factors above 4 per dimension: ROMA_ERR_UNSUPPORTED.
+ */
+int roma_prepare_images_pil(const unsigned char* images, float* out, unsigned char* out_u8, int B, int H, int W,
+                            int h, int w, long long stride_b, long long stride_c, long long stride_y,
+                            long long stride_x, const float* mean3, const float* std3, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

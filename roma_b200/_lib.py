@@ -62,6 +62,8 @@ SIGNATURES = {
     "roma_refiner_out_conv": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
     "roma_cls_to_flow_refine": (_i, [_vp, Strides4, _i, _vp, _i, _i, _i, _i, _vp]),
     "roma_prepare_images": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "roma_prepare_images_pil": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, C.c_longlong, C.c_longlong, C.c_longlong,
+                                     C.c_longlong, _vp, _vp, _vp]),
     "roma_tiny_corr_posembed": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "roma_tiny_corr_posembed_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "roma_tiny_corr_posembed_tc": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),

@@ -150,6 +150,116 @@ normalise_images_kernel(const unsigned char* __restrict__ src, float* __restrict
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// PIL semantics: `Image.resize(size, Image.BICUBIC)` of an 8-bit image (Pillow, libImaging/Resample.c), which is what the
+// reference applies to every file / PIL input (utils/utils.py:223-232), followed by ToTensor and Normalize.  Integer
+// arithmetic, bit-exact: coefficients in double precision (explicit round-to-nearest intrinsics, so that no FMA
+// contraction changes a rounding), quantised to 22 fractional bits half away from zero; horizontal pass then vertical
+// pass, each producing 8-bit pixels `clip8((2^21 + sum u8 * k) >> 22)`; a dimension that does not change is passed
+// through (coefficient 2^22 on the pixel itself gives the pixel back exactly).
+// Same block structure as above: 16 x 16 output tile, coefficients once per tile, input span staged once (as bytes),
+// horizontal pass into an 8-bit intermediate in shared memory, vertical pass from it.
+constexpr int kPilBits = 32 - 8 - 2;
+
+__device__ __forceinline__ double pil_bicubic(double x) {
+    if (x < 0.0) x = -x;
+    if (x < 1.0) return __dadd_rn(__dmul_rn(__dmul_rn(__dsub_rn(__dmul_rn(1.5, x), 2.5), x), x), 1.0);
+    if (x < 2.0) return __dmul_rn(__dsub_rn(__dmul_rn(__dadd_rn(__dmul_rn(__dsub_rn(x, 5.0), x), 8.0), x), 4.0), -0.5);
+    return 0.0;
+}
+
+__global__ void __launch_bounds__(kPrepThreads)
+prepare_images_pil_kernel(const unsigned char* __restrict__ src, float* __restrict__ out, unsigned char* __restrict__ out_u8,
+                          int H, int W, int h, int w, long long sb, long long sc, long long sy, long long sx,
+                          float m0, float m1, float m2, float s0, float s1, float s2, int tile_w, int tile_h) {
+    extern __shared__ unsigned char pil_smem[];
+    __shared__ float lut[3][256];
+    __shared__ double wraw[2][kPrepTile][kPrepMaxTaps];
+    __shared__ int kq[2][kPrepTile][kPrepMaxTaps];
+    __shared__ int first[2][kPrepTile], taps[2][kPrepTile];
+    unsigned char* tile = pil_smem;                                   // [3][tile_h][tile_w]
+    unsigned char* tmp = pil_smem + 3 * tile_h * tile_w;              // [3][tile_h][16]
+    const int tid = threadIdx.x, o = tid / kPrepTile, jj = tid % kPrepTile;
+    const int b = blockIdx.z;
+    const int ox0 = blockIdx.x * kPrepTile, oy0 = blockIdx.y * kPrepTile;
+    const int in_size[2] = {W, H}, out_size[2] = {w, h}, o0[2] = {ox0, oy0};
+    if (out) {
+        const float f = (float)tid / 255.f;
+        lut[0][tid] = (f - m0) / s0; lut[1][tid] = (f - m1) / s1; lut[2][tid] = (f - m2) / s2;
+    }
+#pragma unroll
+    for (int d = 0; d < 2; ++d) {
+        const int i = min(o0[d] + o, out_size[d] - 1);
+        if (in_size[d] == out_size[d]) {                              // pass skipped by PIL: identity coefficient
+            for (int j = jj; j < kPrepMaxTaps; j += kPrepTile) wraw[d][o][j] = j == 0 ? 1.0 : 0.0;
+            if (jj == 0) { first[d][o] = i; taps[d][o] = 1; }
+            continue;
+        }
+        const double scale = __ddiv_rn((double)in_size[d], (double)out_size[d]);
+        const double filterscale = scale < 1.0 ? 1.0 : scale;
+        const double support = __dmul_rn(2.0, filterscale), ss = __ddiv_rn(1.0, filterscale);
+        const double center = __dmul_rn(__dadd_rn((double)i, 0.5), scale);
+        int xmin = (int)__dadd_rn(__dsub_rn(center, support), 0.5);
+        if (xmin < 0) xmin = 0;
+        int xmax = (int)__dadd_rn(__dadd_rn(center, support), 0.5);
+        if (xmax > in_size[d]) xmax = in_size[d];
+        const int n = min(xmax - xmin, kPrepMaxTaps);
+        for (int j = jj; j < kPrepMaxTaps; j += kPrepTile)
+            wraw[d][o][j] = j < n ? pil_bicubic(__dmul_rn(__dadd_rn(__dsub_rn((double)(j + xmin), center), 0.5), ss)) : 0.0;
+        if (jj == 0) { first[d][o] = xmin; taps[d][o] = n; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int d = 0; d < 2; ++d) {
+        double ww = 0.0;
+        const int n = taps[d][o];
+        for (int j = 0; j < n; ++j) ww = __dadd_rn(ww, wraw[d][o][j]);
+        for (int j = jj; j < kPrepMaxTaps; j += kPrepTile) {
+            double wv = wraw[d][o][j];
+            if (ww != 0.0) wv = __ddiv_rn(wv, ww);
+            const double q = __dmul_rn(wv, (double)(1 << kPilBits));
+            kq[d][o][j] = wv < 0.0 ? (int)__dadd_rn(-0.5, q) : (int)__dadd_rn(0.5, q);
+        }
+    }
+    const int last = kPrepTile - 1;
+    const int xlo = first[0][0], ylo = first[1][0];
+    const int tw = min(first[0][last] + taps[0][last] - xlo, tile_w), th = min(first[1][last] + taps[1][last] - ylo, tile_h);
+    const unsigned char* sbp = src + (long long)b * sb;
+    for (int r = tid / 32; r < 3 * th; r += kPrepThreads / 32) {
+        const int c = r / th, y = r - c * th;
+        const unsigned char* srow = sbp + c * sc + (long long)(ylo + y) * sy + (long long)xlo * sx;
+        unsigned char* trow = tile + (c * tile_h + y) * tile_w;
+        for (int x = tid % 32; x < tw; x += 32) trow[x] = srow[x * sx];
+    }
+    __syncthreads();
+    {
+        const int ox = jj, x0 = first[0][ox] - xlo, nx = taps[0][ox];
+        const int* kx = kq[0][ox];
+        for (int r = o; r < 3 * th; r += kPrepTile) {
+            const int c = r / th, y = r - c * th;
+            const unsigned char* row = tile + (c * tile_h + y) * tile_w + x0;
+            int acc = 1 << (kPilBits - 1);
+            for (int i = 0; i < nx; ++i) acc += (int)row[i] * kx[i];
+            tmp[(c * tile_h + y) * kPrepTile + ox] = (unsigned char)min(max(acc >> kPilBits, 0), 255);
+        }
+    }
+    __syncthreads();
+    const int ox = ox0 + jj, oy = oy0 + o;
+    if (ox >= w || oy >= h) return;
+    const int y0 = first[1][o] - ylo, ny = taps[1][o];
+    const int* ky = kq[1][o];
+    const long long obase = (long long)b * 3 * h * w + (long long)oy * w + ox;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const unsigned char* col = tmp + (c * tile_h + y0) * kPrepTile + jj;
+        int acc = 1 << (kPilBits - 1);
+        for (int j = 0; j < ny; ++j) acc += (int)col[j * kPrepTile] * ky[j];
+        const int v = min(max(acc >> kPilBits, 0), 255);
+        if (out) out[obase + (long long)c * h * w] = lut[c][v];
+        if (out_u8) out_u8[obase + (long long)c * h * w] = (unsigned char)v;
+    }
+}
+
 }  // namespace roma
 
 extern "C" int roma_prepare_images(const unsigned char* images, float* out, int B, int H, int W, int h, int w,
@@ -184,4 +294,30 @@ extern "C" int roma_prepare_images(const unsigned char* images, float* out, int 
     prepare_images_kernel<<<grid, kPrepThreads, smem, st>>>(images, out, B, H, W, h, w, mean3[0], mean3[1], mean3[2],
                                                                      std3[0], std3[1], std3[2], tile_w, tile_h);
     return check_launch("roma_prepare_images");
+}
+
+extern "C" int roma_prepare_images_pil(const unsigned char* images, float* out, unsigned char* out_u8, int B, int H, int W,
+                                       int h, int w, long long stride_b, long long stride_c, long long stride_y,
+                                       long long stride_x, const float* mean3, const float* std3, void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(images && (out || out_u8), ROMA_ERR_BAD_ARG, "roma_prepare_images_pil: null pointer");
+    ROMA_REQUIRE(!out || (mean3 && std3), ROMA_ERR_BAD_ARG, "roma_prepare_images_pil: mean / std required for the fp32 output");
+    ROMA_REQUIRE(B > 0 && B <= 65535 && H > 0 && W > 0 && h > 0 && w > 0, ROMA_ERR_BAD_ARG, "roma_prepare_images_pil: bad sizes");
+    ROMA_REQUIRE(!out || (std3[0] != 0.f && std3[1] != 0.f && std3[2] != 0.f), ROMA_ERR_BAD_ARG, "roma_prepare_images_pil: zero std");
+    const double sx = (double)W / w, sy = (double)H / h;
+    ROMA_REQUIRE(sx <= 4.0 && sy <= 4.0, ROMA_ERR_UNSUPPORTED,       // taps per dimension <= 4 * scale + 1 <= 17
+                 "roma_prepare_images_pil: downscale factor %.2f > 4 is not supported", sx > sy ? sx : sy);
+    // input span of 16 consecutive outputs: <= 15 * scale + 2 * support + 1 (a skipped pass: 16)
+    auto span = [](double sc) { const double sup = sc >= 1.0 ? 2.0 * sc : 2.0; return (int)ceil(15.0 * sc + 2.0 * sup) + 3; };
+    const int tile_w = W == w ? kPrepTile : span(sx), tile_h = H == h ? kPrepTile : span(sy);
+    const size_t smem = (size_t)(3 * tile_w * tile_h + 3 * tile_h * kPrepTile);
+    cudaError_t e = cudaFuncSetAttribute(prepare_images_pil_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail((int)e, "roma_prepare_images_pil: smem opt-in (%zu B): %s", smem, cudaGetErrorString(e));
+    const float zero3[3] = {0.f, 0.f, 0.f}, one3[3] = {1.f, 1.f, 1.f};
+    const float* m = out ? mean3 : zero3;
+    const float* sd = out ? std3 : one3;
+    const dim3 grid((unsigned)cdiv(w, kPrepTile), (unsigned)cdiv(h, kPrepTile), (unsigned)B);
+    prepare_images_pil_kernel<<<grid, kPrepThreads, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
+        images, out, out_u8, H, W, h, w, stride_b, stride_c, stride_y, stride_x, m[0], m[1], m[2], sd[0], sd[1], sd[2], tile_w, tile_h);
+    return check_launch("roma_prepare_images_pil");
 }

@@ -155,8 +155,16 @@ class RegressionMatcher(nn.Module):
             coarse = {"im_A": at((hs, ws), full_A), "im_B": at((hs, ws), full_B)}
         else:
             pilA, pilB = _load_rgb(im_A_input), _load_rgb(im_B_input)
-            coarse = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
-                      "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
+            # (f-3): the decoded 8-bit pixels go to the device once; PIL's bicubic resize (bit-exact), / 255 and the
+            # normalisation run there in one kernel per pass resolution.  Beyond the kernel's tap budget: PIL on the host.
+            devA = torch.from_numpy(np.array(pilA)).to(device, non_blocking=True) if self.native_image_prep else None
+            devB = torch.from_numpy(np.array(pilB)).to(device, non_blocking=True) if self.native_image_prep else None
+
+            def at_pil(res, pil, dev_u8):
+                if dev_u8 is None or max(pil.size[1] / res[0], pil.size[0] / res[1]) > 4:
+                    return self._normalise(_pil_to_tensor(pil, res)[None].to(device))
+                return ops.prepare_images_pil(dev_u8, res, channels_last=True)
+            coarse = {"im_A": at_pil((hs, ws), pilA, devA), "im_B": at_pil((hs, ws), pilB, devB)}
         symmetric = self.symmetric
         fine, side, corresps = None, None, None
         if self.upsample_preds:
@@ -164,8 +172,7 @@ class RegressionMatcher(nn.Module):
             if tensor_in:
                 fine = {"im_A": at((hs, ws), full_A), "im_B": at((hs, ws), full_B)}
             else:
-                fine = {"im_A": self._normalise(_pil_to_tensor(pilA, (hs, ws))[None].to(device)),
-                        "im_B": self._normalise(_pil_to_tensor(pilB, (hs, ws))[None].to(device))}
+                fine = {"im_A": at_pil((hs, ws), pilA, devA), "im_B": at_pil((hs, ws), pilB, devB)}
             if self.overlap_encoder:
                 # The VGG pyramid of the upsample pass does not depend on the coarse pass: run the two concurrently,
                 # started once the coarse ENCODER is enqueued, so its large convolutions fill the SMs the

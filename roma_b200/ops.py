@@ -540,6 +540,37 @@ def prepare_images(images_u8: torch.Tensor, size_hw: Tuple[int, int], mean=None,
     return out
 
 
+def prepare_images_pil(images_u8: torch.Tensor, size_hw: Tuple[int, int], mean=None, std=None, channels_last: bool = False,
+                       normalise: bool = True):
+    """PIL `Image.resize((w, h), Image.BICUBIC)` of 8-bit RGB images on the device, bit-exact (utils.py:223-232), fused with
+    ToTensor + Normalize (utils.py:234-261).
+
+    images_u8: uint8 (B,3,H,W), or (B,H,W,3) / (H,W,3) as decoded by PIL with `channels_last=True`; any strides.
+    Returns fp32 (B,3,h,w) normalised, or — `normalise=False` — the resized uint8 (B,3,h,w) itself."""
+    dev = _cuda(images_u8)
+    x = images_u8
+    if x.dtype != torch.uint8:
+        raise ValueError("prepare_images_pil expects uint8 pixels")
+    if channels_last:
+        if x.dim() == 3:
+            x = x[None]
+        x = x.permute(0, 3, 1, 2)
+    if x.dim() != 4 or x.shape[1] != 3:
+        raise ValueError("prepare_images_pil expects 3-channel images: (B,3,H,W), or (B,H,W,3) with channels_last=True")
+    B, _, H, W = x.shape
+    h, w = int(size_hw[0]), int(size_hw[1])
+    m = _MEAN3 if mean is None else (C.c_float * 3)(*[float(v) for v in mean])
+    s = _STD3 if std is None else (C.c_float * 3)(*[float(v) for v in std])
+    out = torch.empty((B, 3, h, w), device=dev, dtype=torch.float32 if normalise else torch.uint8)
+    sb, sc, sy, sx = x.stride()
+    lib = _lib.load()
+    _run("roma_prepare_images_pil", dict(B=B, H=H, W=W, h=h, w=w),
+         lambda: lib.roma_prepare_images_pil(_ptr(x), _ptr(out) if normalise else None, None if normalise else _ptr(out),
+                                             B, H, W, h, w, sb, sc, sy, sx, C.cast(m, C.c_void_p), C.cast(s, C.c_void_p),
+                                             _stream(dev)))
+    return out
+
+
 _tiny_ws = {}
 
 

@@ -41,6 +41,22 @@ def test_match_paths_vs_reference_golden(case, tmp_path):
     assert (cert[::2, ::2].cpu() - g["certainty"]).abs().max().item() < LOGIT_TOL   # probabilities: tighter than logits
 
 
+def test_match_paths_device_resize_is_pil_exact(case, tmp_path):
+    """File inputs: PIL's resize + ToTensor + Normalize on the device (roma_prepare_images_pil) feed the encoder the very
+    same pixels as the host PIL path, so the whole match is bit-identical between the two."""
+    g, _, gpu, _, _ = case
+    Image.fromarray(g["im_A"].numpy()).save(tmp_path / "A.png")
+    Image.fromarray(g["im_B"].numpy()).save(tmp_path / "B.png")
+    assert gpu.native_image_prep
+    warp, cert = gpu.match(str(tmp_path / "A.png"), str(tmp_path / "B.png"), device="cuda")
+    gpu.native_image_prep = False
+    try:
+        warp_h, cert_h = gpu.match(str(tmp_path / "A.png"), str(tmp_path / "B.png"), device="cuda")
+    finally:
+        gpu.native_image_prep = True
+    assert torch.equal(warp, warp_h) and torch.equal(cert, cert_h)
+
+
 def test_match_tensors_vs_oracle_logits(case):
     g, cpu, gpu, coarse, up = case
     prep = lambda im, res: cpu._normalise(_pil_to_tensor(Image.fromarray(im.numpy()), tuple(res))[None])

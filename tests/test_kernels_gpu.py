@@ -595,6 +595,47 @@ def test_prepare_images_vs_aten(ops, cuda, H, W, h, w):
         assert err(got, want_cpu) < 5e-4
 
 
+PIL_CASES = [((48, 64), (35, 40)), ((480, 640), (560, 560)), ((618, 640), (864, 864)), ((100, 75), (333, 290)),
+             ((600, 1200), (224, 308)), ((37, 53), (37, 80)), ((64, 48), (20, 48)), ((30, 30), (30, 30)),
+             ((1120, 896), (280, 224)), ((5, 7), (16, 3))]
+
+
+@pytest.mark.parametrize("src,dst", PIL_CASES)
+@pytest.mark.parametrize("kind", ["noise", "edges"])
+def test_prepare_images_pil_bit_exact(ops, cuda, src, dst, kind):
+    """PIL bicubic resize of 8-bit images on the device: equal, byte for byte, to Pillow itself and to the restatement
+    in oracle/pil_resample_oracle.py; interleaved (as decoded) and planar inputs; the normalised fp32 output equals
+    the reference's ToTensor + Normalize applied to Pillow's result, bit for bit."""
+    import numpy as np
+    from PIL import Image
+    from oracle import pil_resample_oracle as P
+    g = np.random.default_rng(src[0] * 31 + dst[1])
+    if kind == "noise":
+        imgs = [g.integers(0, 256, size=(*src, 3), dtype=np.uint8) for _ in range(2)]
+    else:
+        imgs = [np.kron(g.integers(0, 2, size=(src[0] // 4 + 1, src[1] // 4 + 1, 3)) * 255,
+                        np.ones((4, 4, 1)))[: src[0], : src[1]].astype(np.uint8) for _ in range(2)]
+    want = np.stack([np.asarray(Image.fromarray(im).resize((dst[1], dst[0]), resample=Image.BICUBIC)) for im in imgs])
+    assert np.array_equal(want[0], P.resize_bicubic_u8(imgs[0], dst))
+    hwc = torch.from_numpy(np.stack(imgs)).to(cuda)
+    got = ops.prepare_images_pil(hwc, dst, channels_last=True, normalise=False)
+    assert got.shape == (2, 3, *dst) and got.dtype == torch.uint8
+    assert np.array_equal(got.permute(0, 2, 3, 1).cpu().numpy(), want)
+    planar = hwc.permute(0, 3, 1, 2).contiguous()
+    assert torch.equal(ops.prepare_images_pil(planar, dst, normalise=False), got)
+    mean = torch.tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)
+    std = torch.tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
+    ref = (torch.from_numpy(want.astype(np.float32).transpose(0, 3, 1, 2) / 255.0) - mean) / std      # utils.py:234-261
+    assert torch.equal(ops.prepare_images_pil(hwc, dst, channels_last=True).cpu(), ref)
+
+
+def test_prepare_images_pil_rejects(ops, cuda):
+    with pytest.raises((RuntimeError, ValueError)):
+        ops.prepare_images_pil(torch.zeros(1, 3, 900, 900, dtype=torch.uint8, device=cuda), (200, 200))
+    with pytest.raises((RuntimeError, ValueError)):
+        ops.prepare_images_pil(torch.zeros(1, 3, 90, 90, device=cuda), (20, 20))
+
+
 def test_prepare_images_rejects_large_downscale(ops, cuda):
     with pytest.raises((RuntimeError, ValueError)):
         ops.prepare_images(torch.zeros(1, 3, 900, 900, dtype=torch.uint8, device=cuda), (200, 200))
