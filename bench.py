@@ -93,6 +93,10 @@ def alg_work(name: str, d: dict):
         return "hbm", 2 * d["B"] * d["h"] * d["w"] * d["C"] * d["esize"]
     if name == "roma_layernorm":
         return "hbm", 2 * d["rows"] * d["D"] * d["esize"]
+    if name == "roma_gelu":
+        return "hbm", 2 * d["n"] * d["esize"]
+    if name in ("roma_prepare_images", "roma_prepare_images_pil"):
+        return "hbm", d["B"] * 3 * (d["H"] * d["W"] + 4 * d["h"] * d["w"])
     if name == "roma_pointwise_narrow":
         return "hbm", d["B"] * d["h"] * d["w"] * (d["C"] + d["OUT"]) * d["esize"]
     if name == "roma_maxpool2x2_nhwc":

@@ -290,6 +290,13 @@ int roma_layernorm(const void* x, const void* gamma, const void* beta, void* out
 int roma_layernorm_shift(const void* x, const float* shift, const void* gamma, const void* beta, void* out,
                          long long rows, int D, float eps, int dtype, void* stream);
 
+/* Exact (erf) GELU over a flat tensor of n elements (n % 8 == 0 for 16-bit, % 4 for fp32; 16-byte aligned; in place allowed).
+ * Replaces (reference): nn.GELU() of every transformer MLP, romatch/models/transformer/layers/mlp.py:23, 31, 37.
+ * x * Phi(x) with Phi(-|x|) = erfc(|x| / sqrt 2) / 2 from a relative-accuracy erfc fit (< 1.2e-7 fractional error), so the
+ * 16-bit output is the correctly rounded exact GELU (ATen's 0.5 * x * (1 + erf) form loses relative accuracy in the negative
+ * tail: the two differ by one unit in the last place in ~2-3 % of the elements, all with |y| < 0.05). */
+int roma_gelu(const void* x, void* out, long long n, int dtype, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Encoder: 2x2 / stride-2 max pooling, channels-last (floor semantics: odd trailing row / column dropped).
  *

@@ -50,6 +50,16 @@ class SelfAttention(nn.Module):
         return self.proj(self.attend(x))
 
 
+def gelu_(h: torch.Tensor) -> torch.Tensor:
+    """nn.GELU() (mlp.py:37) on a fresh fc1 output: 16-bit CUDA tensors go through `roma_gelu` in place (one streaming
+    pass at HBM speed; correctly rounded exact GELU), everything else through ATen."""
+    if (h.is_cuda and h.dtype in (torch.bfloat16, torch.float16) and h.is_contiguous() and h.numel() % 8 == 0
+            and not (torch.is_grad_enabled() and h.requires_grad)):
+        from .. import ops
+        return ops.gelu(h, inplace=True)
+    return F.gelu(h)
+
+
 class FeedForward(nn.Module):
     def __init__(self, dim: int, hidden: int, bias: bool = True):
         super().__init__()
@@ -57,7 +67,7 @@ class FeedForward(nn.Module):
         self.fc2 = nn.Linear(hidden, dim, bias=bias)
 
     def forward(self, x):
-        return self.fc2(F.gelu(self.fc1(x)))
+        return self.fc2(gelu_(self.fc1(x)))
 
 
 class ChannelScale(nn.Module):
@@ -110,14 +120,14 @@ class Block(nn.Module):
         x2 = x.view(B * N, D)
         x2.addmm_(self.attn.attend(self.norm1(x, shift)).reshape(B * N, D), w1.t())
         shift = shift + b1.float()
-        x2.addmm_(F.gelu(self.mlp.fc1(self.norm2(x, shift))).reshape(B * N, -1), w2.t())
+        x2.addmm_(gelu_(self.mlp.fc1(self.norm2(x, shift))).reshape(B * N, -1), w2.t())
         return x, shift + b2.float()
 
     def forward(self, x):
         if not self.training and x.is_cuda and isinstance(self.ls1, ChannelScale) and self.attn.proj.bias is not None:
             w1, b1, w2, b2 = self._folded()
             x = x + F.linear(self.attn.attend(self.norm1(x)), w1, b1)
-            return x + F.linear(F.gelu(self.mlp.fc1(self.norm2(x))), w2, b2)
+            return x + F.linear(gelu_(self.mlp.fc1(self.norm2(x))), w2, b2)
         x = x + self.ls1(self.attn(self.norm1(x)))
         return x + self.ls2(self.mlp(self.norm2(x)))
 

@@ -466,6 +466,19 @@ def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: f
     return out
 
 
+def gelu(x: torch.Tensor, inplace: bool = False) -> torch.Tensor:
+    """nn.GELU() (exact, erf form; mlp.py:37) as one streaming kernel; `inplace` overwrites x (a fresh GEMM output)."""
+    dev = _cuda(x)
+    if x.dtype not in _DT:
+        raise ValueError(f"unsupported dtype {x.dtype}")
+    x = x if x.is_contiguous() else x.contiguous()
+    out = x if inplace else torch.empty_like(x)
+    lib = _lib.load()
+    _run("roma_gelu", dict(n=x.numel(), esize=x.element_size()),
+         lambda: lib.roma_gelu(_ptr(x), _ptr(out), x.numel(), _DT[x.dtype], _stream(dev)))
+    return out
+
+
 def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
     """nn.MaxPool2d(2, 2) on a channels-last (B,C,h,w) tensor (encoders.py:57-66); returns channels-last."""
     dev = _cuda(x)

@@ -656,6 +656,37 @@ def test_layernorm_shift(ops, cuda, dtype, tol):
                        ops.layer_norm(x.to(cuda), w.to(cuda), b.to(cuda), 1e-6))
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+def test_gelu_erf(ops, cuda, dtype):
+    """roma_gelu against the exact GELU x * Phi(x) in fp64 (erfc form): fp32 to 4e-7 absolute and 1e-5 relative
+    including the negative tail; 16-bit outputs equal to the correctly rounded exact value; at most one unit in the
+    last place from ATen's GELU; in place == out of place; special values."""
+    g = torch.Generator().manual_seed(5)
+    x = torch.cat([torch.randn(1 << 20, generator=g) * 2.5, torch.linspace(-9, 9, 1 << 16),
+                   torch.tensor([0.0, -0.0, 1e-30, -1e-30, 30.0, -30.0, 1e4, -1e4])]).to(dtype)
+    xd = x.double()
+    exact = 0.5 * xd * torch.erfc(-xd / 2 ** 0.5)
+    got = ops.gelu(x.to(cuda))
+    assert got.dtype == dtype and got.shape == x.shape
+    if dtype == torch.float32:
+        d = (got.cpu().double() - exact).abs()
+        assert d.max().item() < 4e-7
+        m = (exact.abs() > 1e-30) & (xd.abs() < 6)
+        assert (d[m] / exact[m].abs()).max().item() < 1e-5                       # relative accuracy in the negative tail
+        m = (exact.abs() > 1e-30) & (xd.abs() < 9.01)
+        assert (d[m] / exact[m].abs()).max().item() < 5e-5                       # exp argument ~ -60: its own rounding
+    else:
+        assert (got.cpu() != exact.to(dtype)).float().mean().item() < 1e-4          # correctly rounded almost everywhere
+        aten = torch.nn.functional.gelu(x.to(cuda))
+        ulp = torch.finfo(dtype).eps * aten.float().abs().clamp_min(torch.finfo(dtype).tiny)
+        assert ((got.float() - aten.float()).abs() <= 1.01 * ulp + 5e-7).all()        # 5e-7: ATen's cancellation in 1 + erf
+    assert torch.isfinite(got).all()
+    y = x.to(cuda).clone()
+    assert ops.gelu(y, inplace=True).data_ptr() == y.data_ptr() and torch.equal(y, got)
+    with pytest.raises((RuntimeError, ValueError)):
+        ops.gelu(torch.zeros(7, device=cuda, dtype=dtype))
+
+
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 6e-2)])
 def test_vit_unbiased_residual_stream(cuda, dtype, tol):
     """DinoViT with the residual branches as in-place accumulating GEMMs (biases carried as an fp32 shift into the
