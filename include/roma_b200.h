@@ -192,7 +192,10 @@ size_t roma_kde_workspace_bytes(int N);
  * from a warp-level tensor-core product over the 6-wide augmented half vectors (what ATen's _euclidean_dist feeds
  * the GPU's HGEMM), the rest of the chain from a lookup table of its single half-valued argument.  Testing aids:
  * 1 = evaluate the whole op chain directly per pair with sequential fp32 FMAs; 2 = table + sequential FMAs
- * (bit-identical per pair to 1). */
+ * (bit-identical per pair to 1); 3 = as 0 but without the symmetric evaluation below.
+ * Symmetric evaluation (mode 0, down == 1, N <= 65536): the kernel value of a pair is the same for (i, j) and (j, i),
+ * so every pair is evaluated once and added to the row sum of i and to a per-warp-range column sum of j
+ * (ceil(N / 128) x N fp32 partials in the workspace, fixed summation order, no atomics: deterministic). */
 int roma_kde_set_direct(int direct);
 int roma_kde(const float* x, int N, int down, double std, int half,
              float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream);

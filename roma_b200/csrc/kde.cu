@@ -201,15 +201,18 @@ __device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
 
 __global__ void __launch_bounds__(kKdeThreads)
 kde_partial_mma_kernel(const float* __restrict__ x, int N, int M, int down, const float* __restrict__ lut_g,
-                       int cutoff, float* __restrict__ partial, int nsplit) {
+                       int cutoff, float* __restrict__ partial, int per, int sym, float* __restrict__ colpart) {
     extern __shared__ float ksm[];
     float* lut = ksm;                                               // [cutoff + 1]; every entry >= cutoff is 0
     uint4* ref = reinterpret_cast<uint4*>(ksm + ((cutoff + 1 + 3) & ~3));      // [tile]: halves (x, y, z, w, 1, |r|^2, 0, 0)
-    for (int t = threadIdx.x; t <= cutoff; t += kKdeThreads) lut[t] = (t < cutoff) ? lut_g[t] : 0.f;
-
+    // Symmetric mode (reference points = the queries): k(i, j) = k(j, i) exactly (the tensor core sums the same six exact
+    // products), so a warp owning rows [q0, q0 + 128) evaluates only j >= q0: the square on the diagonal as before
+    // (row sums only) and, for j >= q0 + 128, every value is added to its row sum AND to a column sum that is written,
+    // per warp range and without atomics, to colpart[q0 / 128][j]; kde_finalize adds the column sums of the ranges above.
     const int split = blockIdx.y;
-    const int per = (M + nsplit - 1) / nsplit;
-    const int j_begin = split * per, j_end = min(M, j_begin + per);
+    const int j_begin = split * per, j_end = min(M, j_begin + per);       // per is a multiple of 8
+    if (sym && j_end <= (int)(blockIdx.x * (kKdeThreads / 32)) * (16 * kKdeQT)) return;   // whole chunk below the diagonal
+    for (int t = threadIdx.x; t <= cutoff; t += kKdeThreads) lut[t] = (t < cutoff) ? lut_g[t] : 0.f;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
     const int q0 = (blockIdx.x * (kKdeThreads / 32) + warp) * (16 * kKdeQT);
 
@@ -225,7 +228,8 @@ kde_partial_mma_kernel(const float* __restrict__ x, int N, int M, int down, cons
             float one = 0.f;
             if (q < N) { v = reinterpret_cast<const float4*>(x)[q]; one = 1.f; }
             v = make_float4(rh(v.x), rh(v.y), rh(v.z), rh(v.w));
-            const float n = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
+            float n = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
+            if (q >= N) n = 60000.f;                                  // rows past the end: beyond the cutoff, contribute 0
             const float lo = t4 == 0 ? -2.f * v.x : t4 == 1 ? -2.f * v.z : t4 == 2 ? n : 0.f;
             const float hi = t4 == 0 ? -2.f * v.y : t4 == 1 ? -2.f * v.w : t4 == 2 ? one : 0.f;
             a[qt][hr] = pack_h2(lo, hi);
@@ -251,8 +255,12 @@ kde_partial_mma_kernel(const float* __restrict__ x, int N, int M, int down, cons
             ref[t] = pk;
         }
         __syncthreads();
+        // groups of 8 reference points: [0, s_skip) lie below this warp's rows (symmetric mode: left to the column sums of
+        // the warp ranges above), [s_skip, s_sym) meet the diagonal square (row sums only), [s_sym, groups) are symmetric
+        const int s_skip = sym ? min(max((q0 - j0) >> 3, 0), groups) : 0;
+        const int s_sym = sym ? min(max((q0 + 16 * kKdeQT - j0) >> 3, 0), groups) : groups;
 #pragma unroll 2
-        for (int s = 0; s < groups; ++s) {
+        for (int s = s_skip; s < s_sym; ++s) {
             const uint32_t b0 = refw[s * 32];
 #pragma unroll
             for (int qt = 0; qt < kKdeQT; ++qt) {
@@ -265,6 +273,34 @@ kde_partial_mma_kernel(const float* __restrict__ x, int N, int M, int down, cons
                 acc[qt][1] += lut[u1 & 0xffffu];
                 acc[qt][0] += lut[u0 >> 16];
                 acc[qt][1] += lut[u1 >> 16];
+            }
+        }
+        for (int s = s_sym; s < groups; ++s) {
+            const uint32_t b0 = refw[s * 32];
+            float c0 = 0.f, c1 = 0.f;                                 // columns 2 t4, 2 t4 + 1 of the group, rows g and g + 8 of all tiles
+#pragma unroll
+            for (int qt = 0; qt < kKdeQT; ++qt) {
+                float d[4];
+                mma_m16n8k8_f16(d, a[qt][0], a[qt][1], b0);
+                unsigned u0 = __vminu2(__vmaxs2(pack_h2(d[0], d[1]), 0u), cut2);
+                unsigned u1 = __vminu2(__vmaxs2(pack_h2(d[2], d[3]), 0u), cut2);
+                const float v00 = lut[u0 & 0xffffu], v10 = lut[u1 & 0xffffu], v01 = lut[u0 >> 16], v11 = lut[u1 >> 16];
+                acc[qt][0] += v00;
+                acc[qt][1] += v10;
+                acc[qt][0] += v01;
+                acc[qt][1] += v11;
+                c0 += v00; c0 += v10;
+                c1 += v01; c1 += v11;
+            }
+            // the eight row groups of the warp hold the same two columns: fixed-order butterfly over g
+            c0 += __shfl_xor_sync(0xffffffffu, c0, 4);  c1 += __shfl_xor_sync(0xffffffffu, c1, 4);
+            c0 += __shfl_xor_sync(0xffffffffu, c0, 8);  c1 += __shfl_xor_sync(0xffffffffu, c1, 8);
+            c0 += __shfl_xor_sync(0xffffffffu, c0, 16); c1 += __shfl_xor_sync(0xffffffffu, c1, 16);
+            if (g == 0) {
+                const int j = j0 + s * 8 + 2 * t4;
+                float* cp = colpart + (long long)(q0 / (16 * kKdeQT)) * N + j;
+                if (j < N) cp[0] = c0;
+                if (j + 1 < N) cp[1] = c1;
             }
         }
     }
@@ -282,12 +318,24 @@ kde_partial_mma_kernel(const float* __restrict__ x, int N, int M, int down, cons
     }
 }
 
+// sym_per > 0: symmetric tensor-core mode with sym_per reference points per split and qper queries per block: the row
+// partial of split k exists only if its chunk reaches the block's rows, and the column sums of the warp ranges above
+// row i (colpart[w][i], w < i / 128) complete the density; fixed summation order, no atomics anywhere.
 __global__ void kde_finalize_kernel(const float* __restrict__ partial, int N, int nsplit, int half,
-                                    float* __restrict__ density, float* __restrict__ p_out, const int* __restrict__ poison) {
+                                    float* __restrict__ density, float* __restrict__ p_out, const int* __restrict__ poison,
+                                    int sym_per, int qper, const float* __restrict__ colpart) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     float s = 0.f;
-    for (int k = 0; k < nsplit; ++k) s += partial[(long long)k * N + i];
+    if (sym_per > 0) {
+        const int qb = (i / qper) * qper;
+        for (int k = 0; k < nsplit; ++k)
+            if (min(N, (k + 1) * sym_per) > qb) s += partial[(long long)k * N + i];
+        const int nw = i / (16 * kKdeQT);
+        for (int w = 0; w < nw; ++w) s += colpart[(long long)w * N + i];
+    } else {
+        for (int k = 0; k < nsplit; ++k) s += partial[(long long)k * N + i];
+    }
     if (poison && *poison) s = __int_as_float(0x7fc00000);
     if (half) s = rh(s);
     density[i] = s;
@@ -317,15 +365,23 @@ namespace roma {
 constexpr size_t kKdeLutBytes = 32768 * sizeof(float) + 256;      // table + cutoff word, at the END of the workspace
 }
 
+namespace roma {
+constexpr int kKdeSymMaxN = 65536;       // symmetric mode keeps ceil(N / 128) x N column partials: 134 MB at the limit
+static size_t kde_colpart_bytes(int N) {
+    return N <= kKdeSymMaxN ? (size_t)((N + 16 * kKdeQT - 1) / (16 * kKdeQT)) * (size_t)N * sizeof(float) : 0;
+}
+}  // namespace roma
+
 extern "C" size_t roma_kde_workspace_bytes(int N) {
     if (N <= 0) return 0;
-    return (size_t)64 * (size_t)N * sizeof(float) + roma::kKdeLutBytes;
+    return (size_t)64 * (size_t)N * sizeof(float) + roma::kde_colpart_bytes(N) + roma::kKdeLutBytes;
 }
 
-// 0 = auto (half: table-driven with the distances on the tensor cores, when the table fits), 1 = always the direct
-// op chain, 2 = table-driven with the SIMT FFMA2 distance chain (1 and 2 are testing aids)
+// 0 = auto (half: table-driven with the distances on the tensor cores, when the table fits; every pair evaluated once
+// when the reference points are the queries), 1 = always the direct op chain, 2 = table-driven with the SIMT FFMA2
+// distance chain, 3 = as 0 but every (i, j) AND (j, i) evaluated (1, 2 and 3 are testing aids)
 namespace roma { static int g_kde_direct = 0; }
-extern "C" int roma_kde_set_direct(int direct) { roma::g_kde_direct = (direct == 1 || direct == 2) ? direct : 0; return ROMA_OK; }
+extern "C" int roma_kde_set_direct(int direct) { roma::g_kde_direct = (direct >= 1 && direct <= 3) ? direct : 0; return ROMA_OK; }
 
 extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
                            float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream) {
@@ -347,6 +403,8 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
     dim3 grid((N + kKdeThreads - 1) / kKdeThreads, nsplit);
     int rc;
     int* poison = nullptr;
+    int sym_per = 0, sym_qper = 0;
+    float* colpart = nullptr;
     // table-driven half path: the cutoff is a property of std alone; evaluate it on the host with the same
     // half arithmetic (exp(-s/(2 std^2)) < 2^-25 rounds to 0) so no device round trip is needed to size smem.
     bool use_lut = half && g_kde_direct != 1 && workspace_bytes >= (size_t)N * sizeof(float) + kKdeLutBytes;
@@ -388,11 +446,24 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
             const size_t smem_mma = ((size_t)(cutoff_bound + 1 + 3) & ~(size_t)3) * sizeof(float) + kKdeTile * sizeof(uint4);
             const int qper = (kKdeThreads / 32) * 16 * kKdeQT;                  // queries per block
             const int qblocks = (N + qper - 1) / qper;
-            int ns = (2 * 3 * sm_count() + qblocks - 1) / qblocks;              // >= 2 waves of 3 resident blocks per SM
-            ns = ns < 1 ? 1 : (ns > nsplit ? nsplit : ns);
+            // symmetric mode: half of the (block, split) pairs exit at once, so twice the splits keep the same number of waves
+            const bool sym = down == 1 && g_kde_direct != 3 && N <= kKdeSymMaxN &&
+                             workspace_bytes >= (size_t)64 * N * sizeof(float) + kde_colpart_bytes(N) + kKdeLutBytes;
+            // >= 4 waves of 3 resident blocks per SM (uniform blocks: the tail of the last wave is what is lost)
+            const size_t avail = workspace_bytes - kKdeLutBytes - (sym ? kde_colpart_bytes(N) : 0);
+            int cap = (int)(avail / ((size_t)N * sizeof(float)));
+            if (cap > 64) cap = 64;
+            int ns = ((sym ? 8 : 4) * 3 * sm_count() + qblocks - 1) / qblocks;
+            ns = ns < 1 ? 1 : (ns > cap ? cap : ns);
             if (ns > (M + 255) / 256) ns = (M + 255) / 256;
-            nsplit = ns;
-            kde_partial_mma_kernel<<<dim3(qblocks, nsplit), kKdeThreads, smem_mma, st>>>(x, N, M, down, lut, cutoff_bound, partial, nsplit);
+            const int per = ((M + ns - 1) / ns + 7) & ~7;                       // reference points per split, a multiple of 8
+            nsplit = (M + per - 1) / per;
+            if (sym) {
+                sym_per = per; sym_qper = qper;
+                colpart = partial + (size_t)64 * N;
+            }
+            kde_partial_mma_kernel<<<dim3(qblocks, nsplit), kKdeThreads, smem_mma, st>>>(x, N, M, down, lut, cutoff_bound, partial, per,
+                                                                                     sym ? 1 : 0, colpart);
         }
         if ((rc = check_launch("roma_kde(lut)", 2))) return rc;
     } else {
@@ -400,6 +471,6 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
         else      kde_partial_kernel<false><<<grid, kKdeThreads, 0, st>>>(x, N, M, down, inv_two_var, partial, nsplit);
         if ((rc = check_launch("roma_kde(partial)"))) return rc;
     }
-    kde_finalize_kernel<<<(N + 255) / 256, 256, 0, st>>>(partial, N, nsplit, half, density, p_out, poison);
+    kde_finalize_kernel<<<(N + 255) / 256, 256, 0, st>>>(partial, N, nsplit, half, density, p_out, poison, sym_per, sym_qper, colpart);
     return check_launch("roma_kde(finalize)");
 }

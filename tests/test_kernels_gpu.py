@@ -321,6 +321,35 @@ def test_kde_lut_equals_direct(ops, cuda, N, down, mode):
     assert (diff <= ulp).all() and (diff > 0).float().mean().item() < (2e-3 if mode == 2 else 1e-2)
 
 
+@pytest.mark.parametrize("N", [40000, 5003, 1023, 130, 37])
+def test_kde_symmetric_evaluation(ops, cuda, N):
+    """Mode 0 evaluates every pair once (row sum of i + column sum of j); mode 3 evaluates (i, j) and (j, i): the same
+    terms in another fp32 order, so the half densities agree up to the final rounding of a few rows; the symmetric
+    path is deterministic run to run (no atomics) and permutation-covariant."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(N)
+    centres = torch.rand(9, 4, generator=g) * 1.6 - 0.8
+    x = (centres[torch.randint(0, 9, (N,), generator=g)] + 0.06 * torch.randn(N, 4, generator=g)).clamp(-1, 1).to(cuda)
+    try:
+        lib.roma_kde_set_direct(3)
+        d_full = ops.kde(x, half=True).float()
+        lib.roma_kde_set_direct(0)
+        d_sym = ops.kde(x, half=True).float()
+        d_sym2 = ops.kde(x, half=True).float()
+    finally:
+        lib.roma_kde_set_direct(0)
+    assert torch.equal(d_sym, d_sym2)
+    diff = (d_full - d_sym).abs()
+    assert (diff <= d_full.clamp(min=1.0) * 2.0 ** -10).all() and (diff > 0).float().mean().item() < 1e-2
+    if N >= 1000:
+        assert d_full.max().item() > 20
+    perm = torch.randperm(N, generator=g).to(cuda)
+    d_perm = ops.kde(x[perm], half=True).float()
+    dp = (d_perm - d_sym[perm]).abs()
+    assert (dp <= d_sym[perm].clamp(min=1.0) * 2.0 ** -10).all()
+
+
 def test_kde_tensor_core_distances_fp32_sums(ops, cuda):
     """Before the final half rounding: the fp32 row sums of the tensor-core path and of the direct chain agree to
     1e-5 relative (a pair moving to the neighbouring table entry changes its term by ~1e-3 of itself)."""

@@ -61,6 +61,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--only", default="")
     ap.add_argument("--local-corr-path", type=int, default=0, help="0 tensor-core dot products (default), 1 SIMT")
+    ap.add_argument("--kde-mode", type=int, default=0, help="roma_kde_set_direct: 0 default (symmetric tensor-core), 3 every pair twice")
     ap.add_argument("--scales", default="", help="comma list of refiner visits for --only gather (s16,s8,...,s1u)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -130,6 +131,8 @@ def main():
                  TFLOPs=round(flops / ms / 1e9, 2), frac_tensor=round(flops / ms / 1e9 / PEAKS["bf16_tflops"], 5))
 
     if want("kde"):
+        from roma_b200 import _lib as _l
+        _l.load().roma_kde_set_direct(args.kde_mode)
         for N in (20000, 40000):
             x = (torch.rand(N, 4, generator=g) * 2 - 1).to(dev)
             for half in (True, False):
