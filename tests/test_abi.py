@@ -51,3 +51,25 @@ def test_ops_refuse_cpu_tensors():
         ops.kde(torch.zeros(10, 4))
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         ops.gp_posterior(torch.zeros(1, 8, 2, 2), torch.zeros(1, 8, 2, 2), torch.zeros(4, 2), torch.zeros(4))
+
+
+def test_late_entry_points_validate_and_refuse_cpu():
+    """The input-path, GELU and LayerNorm-shift entry points: argument checks before any CUDA call; wrappers refuse
+    CPU tensors (there is no CPU path); the kde workspace covers the column partials of the symmetric evaluation."""
+    import torch
+    from roma_b200 import _lib, ops
+    lib = _lib.load()
+    assert lib.roma_prepare_images_pil(None, None, None, 1, 8, 8, 4, 4, 192, 64, 8, 1, None, None, None) == -1
+    assert b"null" in lib.roma_last_error_string()
+    assert lib.roma_prepare_images(None, None, 1, 8, 8, 4, 4, None, None, None) == -1
+    assert lib.roma_gelu(None, None, 8, 1, None) == -1
+    assert lib.roma_layernorm_shift(None, None, None, None, None, 1, 8, 1e-6, 1, None) == -1
+    N = 40000
+    assert lib.roma_kde_workspace_bytes(N) >= 64 * N * 4 + ((N + 127) // 128) * N * 4
+    assert lib.roma_kde_workspace_bytes(200000) < 64 * 200000 * 4 + (1 << 20)        # beyond the symmetric limit: row partials only
+    for call in (lambda: ops.gelu(torch.zeros(16, dtype=torch.bfloat16)),
+                 lambda: ops.prepare_images(torch.zeros(1, 3, 8, 8, dtype=torch.uint8), (4, 4)),
+                 lambda: ops.prepare_images_pil(torch.zeros(1, 3, 8, 8, dtype=torch.uint8), (4, 4)),
+                 lambda: ops.layer_norm(torch.zeros(2, 8), torch.ones(8), torch.zeros(8), 1e-6, shift=torch.zeros(8))):
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            call()
