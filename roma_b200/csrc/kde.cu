@@ -332,7 +332,8 @@ __global__ void kde_finalize_kernel(const float* __restrict__ partial, int N, in
         for (int k = 0; k < nsplit; ++k)
             if (min(N, (k + 1) * sym_per) > qb) s += partial[(long long)k * N + i];
         const int nw = i / (16 * kKdeQT);
-        for (int w = 0; w < nw; ++w) s += colpart[(long long)w * N + i];
+#pragma unroll 8
+        for (int w = 0; w < nw; ++w) s += colpart[(long long)w * N + i];      // independent loads, fixed summation order
     } else {
         for (int k = 0; k < nsplit; ++k) s += partial[(long long)k * N + i];
     }
@@ -471,6 +472,6 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
         else      kde_partial_kernel<false><<<grid, kKdeThreads, 0, st>>>(x, N, M, down, inv_two_var, partial, nsplit);
         if ((rc = check_launch("roma_kde(partial)"))) return rc;
     }
-    kde_finalize_kernel<<<(N + 255) / 256, 256, 0, st>>>(partial, N, nsplit, half, density, p_out, poison, sym_per, sym_qper, colpart);
+    kde_finalize_kernel<<<(N + 127) / 128, 128, 0, st>>>(partial, N, nsplit, half, density, p_out, poison, sym_per, sym_qper, colpart);
     return check_launch("roma_kde(finalize)");
 }
