@@ -44,17 +44,25 @@ def test_match_paths_vs_reference_golden(case, tmp_path):
 def test_match_paths_device_resize_is_pil_exact(case, tmp_path):
     """File inputs: PIL's resize + ToTensor + Normalize on the device (roma_prepare_images_pil) feed the encoder the very
     same pixels as the host PIL path, so the whole match is bit-identical between the two."""
-    g, _, gpu, _, _ = case
+    from roma_b200 import ops
+    g, _, gpu, coarse, up = case
     Image.fromarray(g["im_A"].numpy()).save(tmp_path / "A.png")
     Image.fromarray(g["im_B"].numpy()).save(tmp_path / "B.png")
     assert gpu.native_image_prep
+    for name in ("A.png", "B.png"):                      # the encoder inputs themselves: bit for bit
+        pil = Image.open(tmp_path / name).convert("RGB")
+        u8 = torch.from_numpy(np.array(pil)).cuda()
+        for res in (coarse, up):
+            host = gpu._normalise(_pil_to_tensor(pil, tuple(res))[None].cuda())
+            assert torch.equal(ops.prepare_images_pil(u8, tuple(res), channels_last=True), host)
     warp, cert = gpu.match(str(tmp_path / "A.png"), str(tmp_path / "B.png"), device="cuda")
     gpu.native_image_prep = False
     try:
         warp_h, cert_h = gpu.match(str(tmp_path / "A.png"), str(tmp_path / "B.png"), device="cuda")
     finally:
         gpu.native_image_prep = True
-    assert torch.equal(warp, warp_h) and torch.equal(cert, cert_h)
+    # identical inputs through the same kernels: equal up to the run-to-run reproducibility of the library convolutions
+    assert (warp - warp_h).abs().max().item() <= 1e-6 and (cert - cert_h).abs().max().item() <= 1e-6
 
 
 def test_match_tensors_vs_oracle_logits(case):
