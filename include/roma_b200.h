@@ -200,6 +200,14 @@ int roma_kde_set_direct(int direct);
 int roma_kde(const float* x, int N, int down, double std, int half,
              float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Testing aids for the exact half path (tests/test_kde_exact_gpu.py): d2(i, j) = half(x1_[i] . x2_[j]) of ATen's
+ * _euclidean_dist for ALL pairs of a small point set (N <= 16384) by one candidate arithmetic form — 0 = sequential fp32
+ * FMAs, 1 = mma.sync m16n8k8, 2 = mma.sync m16n8k16, 3 / 4 = 2 / 1 with the operand roles exchanged — written as half
+ * bit patterns to out_half_bits (N x N uint16); and the 31745-entry table of the rest of the chain (clamp_min(0), sqrt,
+ * **2, neg, / (2 std^2), exp, each rounded to half) as fp32 values indexed by the half bit pattern of d2 (lut: 32768 floats). */
+int roma_kde_debug_d2(const float* x, int N, int variant, void* out_half_bits, void* stream);
+int roma_kde_debug_lut(float* lut, double std, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * K3c  match_keypoints: warp keypoints of A into B, mutual nearest neighbours.
  *
