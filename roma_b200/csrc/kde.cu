@@ -351,6 +351,313 @@ __global__ void kde_finalize_kernel(const float* __restrict__ partial, int N, in
 
 }  // namespace roma
 
+
+namespace roma {
+// =====================================================================================================================
+// Exact half mode: the density is BIT-IDENTICAL to the reference's CUDA chain
+//     (-torch.cdist(x, x)**2 / (2 * std**2)).exp().sum(dim=-1)          romatch/utils/kde.py:4-12, x half
+// on this GPU / torch build (pinned on the B200 by tests/test_kde_exact_gpu.py against the unmodified chain):
+//   * d2: ATen's _euclidean_dist runs x1_ @ x2_^T (6-wide augmented half vectors) as cuBLAS'
+//     cutlass_80_tensorop_f16_s16816gemm (HMMA m16n8k16, fp32 accumulate).  One warp-level mma.sync over the same six
+//     products gives the same fp32 value for every pair (67 M pairs compared, 0 differences; the sequential-FMA form of
+//     mode 1 differs on 0.05 % of them) — kde_partial_mma_kernel already used it.
+//   * clamp_min(0), sqrt, **2, neg, * (1 / (2 std^2)), exp: elementwise half ops = the table (0 differences over all
+//     31745 non-negative half values).
+//   * sum(dim=-1): ATen's reduce kernel (ATen/native/cuda/Reduce.cuh, sum_functor<Half, float, Half>) accumulates in
+//     fp32 in a FIXED order that depends only on the row length M and the row's alignment: block (bw, bh) = (32, 16);
+//     for M >= 128 every thread keeps 8 accumulators over aligned 16-byte vectors (input_vec_size 8 for 16-bit types),
+//     vector index idx = tl, tl + T, ... with T = 512 cooperating threads per row when ceil(M / 32) >= 256 (else T = 32,
+//     one warp per row), unaligned head and tail elements go to accumulator 0 of the threads tx < 8, the 8 accumulators
+//     are combined left to right, then a shuffle-down tree over tx (16, 8, 4, 2, 1) and a shared-memory tree over ty
+//     (8, 4, 2, 1); the fp32 result is rounded to half once.  fp32 addition is not associative, so the kernels below
+//     add the same terms in the same order:
+//       - kde_exact_fused_kernel (M % 8 == 0, T = 512: the sizes sample() produces, N = 4 * num): accumulators
+//         (row, tl, c) live in registers — a column group of 8 of the MMA tile IS one aligned vector — and the
+//         512 per-thread values of a row go to the workspace; kde_exact_tree_kernel applies the two trees.
+//       - any other shape: kde_scores_kernel writes the half scores of a chunk of rows to the workspace and
+//         kde_aten_sum_kernel is a literal restatement of ATen's thread_reduce / block_x_reduce / block_y_reduce.
+// =====================================================================================================================
+struct AtenSumCfg { int vectorized, bw, bh, split; };
+
+// points -> the two 8-wide half operand rows of the GEMM (zero padded): q = x1_ = (-2a, |a|^2, 1), r = x2_ = (a, 1, |a|^2)
+__global__ void kde_pack_kernel(const float* __restrict__ x, int N, int M, int down, uint4* __restrict__ qpack, uint4* __restrict__ rpack) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) {
+        float4 v = reinterpret_cast<const float4*>(x)[i];
+        v = make_float4(rh(v.x), rh(v.y), rh(v.z), rh(v.w));
+        const float n = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
+        qpack[i] = make_uint4(pack_h2(-2.f * v.x, -2.f * v.y), pack_h2(-2.f * v.z, -2.f * v.w), pack_h2(n, 1.f), 0u);
+    }
+    if (i < M) {
+        float4 v = reinterpret_cast<const float4*>(x)[(long long)i * down];
+        v = make_float4(rh(v.x), rh(v.y), rh(v.z), rh(v.w));
+        const float n = rh(rh(v.x * v.x) + rh(v.y * v.y) + rh(v.z * v.z) + rh(v.w * v.w));
+        rpack[i] = make_uint4(pack_h2(v.x, v.y), pack_h2(v.z, v.w), pack_h2(1.f, n), 0u);
+    }
+}
+
+// ---- fused: T = 512 threads per row, rows 16-byte aligned (M % 8 == 0) ----------------------------------------------
+// Work item = (block of 8 x 16 rows, set of kFusedTL consecutive tl values): warp w owns rows [rb*128 + 16 w, +16) and, for
+// every k, the column groups G = 512 k + tl0 + u (u < kFusedTL) — i.e. all terms of the accumulators (row, tl0 + u, c).
+// Per group one m16n8k8 MMA (A = the warp's query rows, held in registers; B = 8 reference points, one coalesced
+// 4-byte load per lane from the packed operands: the 8 warps of the block read the same line, L1 hits), two packs, the
+// clamps, four table lookups and four fp32 adds in k order.  No shared-memory tile, no barrier in the main loop.
+constexpr int kFusedTL = 16;            // tl values per work item: 64 accumulators per thread
+
+__global__ void __launch_bounds__(kKdeThreads, 2)
+kde_exact_fused_kernel(const uint4* __restrict__ qpack, const uint4* __restrict__ rpack, int N, int M,
+                       const float* __restrict__ lut_g, int cutoff, float* __restrict__ V, int nrb, int nitems) {
+    extern __shared__ float ksm[];
+    float* lut = ksm;
+    for (int t = threadIdx.x; t <= cutoff; t += kKdeThreads) lut[t] = (t < cutoff) ? lut_g[t] : 0.f;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+    const unsigned cut2 = (unsigned)cutoff | ((unsigned)cutoff << 16);
+    const int ngroups = M >> 3;                                   // column groups (aligned vectors) per row
+    const uint32_t* rw = reinterpret_cast<const uint32_t*>(rpack) + g * 4 + t4;   // word t4 of point g of a group
+    for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        const int rb = item % nrb, ts = item / nrb;               // consecutive blocks share the reference columns
+        const int row0 = rb * 128 + warp * 16;
+        if (row0 >= N) continue;
+        const int tl0 = ts * kFusedTL;
+        uint32_t a0 = 0u, a1 = 0u;
+        {
+            const int q0 = row0 + g, q1 = row0 + g + 8;
+            const uint32_t far = t4 == 2 ? pack_h2(60000.f, 0.f) : 0u;          // rows past the end: beyond the cutoff
+            a0 = q0 < N ? reinterpret_cast<const uint32_t*>(qpack + q0)[t4] : far;
+            a1 = q1 < N ? reinterpret_cast<const uint32_t*>(qpack + q1)[t4] : far;
+        }
+        float acc[kFusedTL][4];
+#pragma unroll
+        for (int u = 0; u < kFusedTL; ++u) { acc[u][0] = acc[u][1] = acc[u][2] = acc[u][3] = 0.f; }
+        for (int G0 = tl0; G0 < ngroups; G0 += 512) {             // k = G0 / 512: ascending = ATen's loop order
+            uint32_t b[kFusedTL];
+#pragma unroll
+            for (int u = 0; u < kFusedTL; ++u) b[u] = (G0 + u < ngroups) ? __ldg(rw + (long long)(G0 + u) * 32) : 0xffffffffu;
+#pragma unroll
+            for (int u = 0; u < kFusedTL; ++u) {
+                if (G0 + u < ngroups) {                               // warp-uniform
+                    float d[4];
+                    mma_m16n8k8_f16(d, a0, a1, b[u]);
+                    const unsigned u0 = __vminu2(__vmaxs2(pack_h2(d[0], d[1]), 0u), cut2);
+                    const unsigned u1 = __vminu2(__vmaxs2(pack_h2(d[2], d[3]), 0u), cut2);
+                    acc[u][0] += lut[u0 & 0xffffu];               // (row g,     c = 2 t4)
+                    acc[u][1] += lut[u0 >> 16];                   // (row g,     c = 2 t4 + 1)
+                    acc[u][2] += lut[u1 & 0xffffu];               // (row g + 8, c = 2 t4)
+                    acc[u][3] += lut[u1 >> 16];                   // (row g + 8, c = 2 t4 + 1)
+                }
+            }
+        }
+        // combine the 8 accumulators of (row, tl) left to right: ((((((v0 + v1) + v2) + v3) + v4) + v5) + v6) + v7,
+        // v(2 t4), v(2 t4 + 1) held by lane t4 of the quad: the running sum walks through the quad
+#pragma unroll
+        for (int u = 0; u < kFusedTL; ++u) {
+#pragma unroll
+            for (int hr = 0; hr < 2; ++hr) {
+                const float e0 = acc[u][2 * hr], e1 = acc[u][2 * hr + 1];
+                float s = e0 + e1;                                 // lane t4 = 0: v0 + v1
+#pragma unroll
+                for (int step = 1; step < 4; ++step) {
+                    const float prev = __shfl_up_sync(0xffffffffu, s, 1);
+                    if (t4 == step) s = (prev + e0) + e1;
+                }
+                const int q = row0 + g + 8 * hr;
+                if (t4 == 3 && q < N && tl0 + u < 512) V[(long long)q * 512 + tl0 + u] = s;
+            }
+        }
+    }
+}
+
+// the two trees of ATen's reduce over the 512 per-thread values of a row (one warp per row: lane = tx, v[ty])
+__global__ void __launch_bounds__(256)
+kde_exact_tree_kernel(const float* __restrict__ V, int N, float* __restrict__ density, float* __restrict__ p_out,
+                      const int* __restrict__ poison) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= N) return;
+    float v[16];
+#pragma unroll
+    for (int ty = 0; ty < 16; ++ty) v[ty] = V[(long long)row * 512 + ty * 32 + lane];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+        for (int ty = 0; ty < 16; ++ty) v[ty] = v[ty] + __shfl_down_sync(0xffffffffu, v[ty], off);
+    }
+#pragma unroll
+    for (int off = 8; off > 0; off >>= 1) {
+#pragma unroll
+        for (int ty = 0; ty < 8; ++ty) if (ty < off) v[ty] = v[ty] + v[ty + off];
+    }
+    if (lane != 0) return;
+    float s = v[0];
+    if (poison && *poison) s = __int_as_float(0x7fc00000);
+    s = rh(s);
+    density[row] = s;
+    if (p_out) { float p = rh(1.f / rh(s + 1.f)); if (s < 10.f) p = rh(1e-7f); p_out[row] = p; }
+}
+
+// ---- generic: scores of a chunk of rows to the workspace, then ATen's reduction restated literally ------------------
+// E[(r - r0) * pitch + j] = half bits of exp(...) for rows [r0, r0 + rows) x all M columns; 16-bit table in shared memory
+__global__ void __launch_bounds__(kKdeThreads)
+kde_scores_kernel(const uint4* __restrict__ qpack, const uint4* __restrict__ rpack, int N, int M, int r0, int rows,
+                  const float* __restrict__ lut_g, int cutoff, unsigned short* __restrict__ E, int pitch, int gper) {
+    extern __shared__ unsigned short lut16[];                                // table as half bits (28 KB at std = 0.1)
+    for (int t = threadIdx.x; t <= cutoff; t += kKdeThreads)
+        lut16[t] = (t < cutoff) ? __half_as_ushort(__float2half_rn(lut_g[t])) : (unsigned short)0;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+    const int lr0 = (blockIdx.x * (kKdeThreads / 32) + warp) * 16;          // first local row of this warp
+    if (lr0 >= rows) return;
+    const unsigned cut2 = (unsigned)cutoff | ((unsigned)cutoff << 16);
+    const int q0 = r0 + lr0 + g, q1 = q0 + 8;
+    const bool ok0 = lr0 + g < rows && q0 < N, ok1 = lr0 + g + 8 < rows && q1 < N;
+    const uint32_t a0 = ok0 ? reinterpret_cast<const uint32_t*>(qpack + q0)[t4] : 0u;
+    const uint32_t a1 = ok1 ? reinterpret_cast<const uint32_t*>(qpack + q1)[t4] : 0u;
+    const int ngroups = (M + 7) >> 3;
+    const int G_begin = blockIdx.y * gper, G_end = min(ngroups, G_begin + gper);
+    for (int G = G_begin; G < G_end; ++G) {
+        const int jr = G * 8 + g;                                            // reference point of this lane's B row
+        const uint32_t b0 = jr < M ? __ldg(reinterpret_cast<const uint32_t*>(rpack + jr) + t4) : 0u;
+        float d[4];
+        mma_m16n8k8_f16(d, a0, a1, b0);
+        const unsigned u0 = __vminu2(__vmaxs2(pack_h2(d[0], d[1]), 0u), cut2);
+        const unsigned u1 = __vminu2(__vmaxs2(pack_h2(d[2], d[3]), 0u), cut2);
+        const int j = G * 8 + 2 * t4;
+        if (ok0) {
+            unsigned short* e = E + (long long)(lr0 + g) * pitch + j;
+            if (j < M) e[0] = lut16[u0 & 0xffffu];
+            if (j + 1 < M) e[1] = lut16[u0 >> 16];
+        }
+        if (ok1) {
+            unsigned short* e = E + (long long)(lr0 + g + 8) * pitch + j;
+            if (j < M) e[0] = lut16[u1 & 0xffffu];
+            if (j + 1 < M) e[1] = lut16[u1 >> 16];
+        }
+    }
+}
+
+// ATen's ReduceOp::run for a contiguous inner-dimension sum of halfs with fp32 accumulation (Reduce.cuh: thread_reduce
+// with input_vectorized_thread_reduce_impl / thread_reduce_impl, block_x_reduce, block_y_reduce), same block shape,
+// same per-thread element order; `rowM` = the row length in the REFERENCE's matrix (decides the alignment shift of row
+// r: (r * M) % 8 elements), E rows here are pitch-strided and always aligned (the shift is applied arithmetically).
+__global__ void kde_aten_sum_kernel(const unsigned short* __restrict__ E, int pitch, int r0, int rows, int N, int M,
+                                    AtenSumCfg cfg, float* __restrict__ density, float* __restrict__ p_out,
+                                    const int* __restrict__ poison) {
+    extern __shared__ float red[];
+    const int tx = threadIdx.x, ty = threadIdx.y, bw = blockDim.x, bh = blockDim.y;
+    const int lrow = cfg.split ? (int)blockIdx.x : (int)blockIdx.x * bh + ty;
+    const bool live = lrow < rows && r0 + lrow < N;
+    const int T = cfg.split ? bw * bh : bw;                       // threads cooperating on one row
+    const int tl = cfg.split ? tx + ty * bw : tx;                 // config.input_idx()
+    const bool tail_thread = !cfg.split || ty == 0;               // should_reduce_tail()
+    const unsigned short* data = E + (long long)lrow * pitch;
+    auto at = [&](int j) { return __half2float(__ushort_as_half(data[j])); };
+    float value = 0.f;
+    if (live) {
+        if (cfg.vectorized) {
+            int end = M, base = 0;                                // data + base is the (virtually) aligned start
+            float head = 0.f;
+            const int shift0 = (int)(((long long)(r0 + lrow) * M) & 7);
+            if (shift0 > 0) {
+                // data -= shift; end += shift; threads shift <= tx < 8 take element tx - shift; then skip one vector
+                if (tx >= shift0 && tx < 8 && tail_thread) head = head + at(tx - shift0);
+                end = M + shift0 - 8;
+                base = 8 - shift0;
+            }
+            float vl[8];
+            vl[0] = head;
+#pragma unroll
+            for (int c = 1; c < 8; ++c) vl[c] = 0.f;
+            int idx = tl;
+            while (idx * 8 + 7 < end) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) vl[c] = vl[c] + at(base + idx * 8 + c);
+                idx += T;
+            }
+            const int tail_start = end - (end & 7);               // end may be negative only when M < 8: not vectorized then
+            if (tail_thread) {
+                const int j = tail_start + tx;
+                if (j < end) vl[0] = vl[0] + at(base + j);
+            }
+#pragma unroll
+            for (int c = 1; c < 8; ++c) vl[0] = vl[0] + vl[c];
+            value = vl[0];
+        } else {
+            // thread_reduce_impl, vt0 = 4: four accumulators over idx, idx + T, idx + 2T, idx + 3T
+            float vl[4] = {0.f, 0.f, 0.f, 0.f};
+            int idx = tl;
+            while (idx + 3 * T < M) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) vl[i] = vl[i] + at(idx + i * T);
+                idx += 4 * T;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (idx >= M) break;
+                vl[i] = vl[i] + at(idx);
+                idx += T;
+            }
+            value = ((vl[0] + vl[1]) + vl[2]) + vl[3];
+        }
+    }
+    // block_x_reduce (always: the reduction runs along x)
+    int dim_x = bw;
+    if (dim_x > 32) {
+        const int address_base = tx + ty * bw;
+        red[address_base] = value;
+        for (int offset = dim_x / 2; offset >= 32; offset >>= 1) {
+            __syncthreads();
+            if (tx < offset && tx + offset < bw) {
+                value = value + red[address_base + offset];
+                red[address_base] = value;
+            }
+        }
+        dim_x = 32;
+    }
+    __syncthreads();
+    for (int offset = dim_x >> 1; offset > 0; offset >>= 1) value = value + __shfl_down_sync(0xffffffffu, value, offset);
+    if (cfg.split) {                                              // block_y_reduce
+        red[tx + ty * bw] = value;
+        for (int offset = bh / 2; offset > 0; offset >>= 1) {
+            __syncthreads();
+            if (ty < offset && ty + offset < bh) {
+                value = value + red[tx + (ty + offset) * bw];
+                red[tx + ty * bw] = value;
+            }
+        }
+    }
+    if (live && tx == 0 && (!cfg.split || ty == 0)) {
+        float s = value;
+        if (poison && *poison) s = __int_as_float(0x7fc00000);
+        s = rh(s);
+        density[r0 + lrow] = s;
+        if (p_out) { float p = rh(1.f / rh(s + 1.f)); if (s < 10.f) p = rh(1e-7f); p_out[r0 + lrow] = p; }
+    }
+}
+
+}  // namespace roma
+
+namespace roma {
+static int last_pow2(int n) {
+    n |= n >> 1; n |= n >> 2; n |= n >> 4; n |= n >> 8; n |= n >> 16;
+    const int r = n - (n >> 1);
+    return r < 1 ? 1 : r;
+}
+// setReduceConfig (Reduce.cuh) for sum(dim=-1) of a contiguous (rows, M) half matrix, input_vec_size = 8, 512 threads max
+static AtenSumCfg aten_sum_config(int rows, int M) {
+    AtenSumCfg c;
+    c.vectorized = M >= 128 ? 1 : 0;
+    const int dim0 = c.vectorized ? M / 8 : M, dim1 = rows;
+    const int d0 = dim0 < 512 ? last_pow2(dim0) : 512, d1 = dim1 < 512 ? last_pow2(dim1) : 512;
+    c.bw = d0 < 32 ? d0 : 32;
+    c.bh = d1 < 512 / c.bw ? d1 : 512 / c.bw;
+    c.bw = d0 < 512 / c.bh ? d0 : 512 / c.bh;
+    const int vpt = (M + c.bw - 1) / c.bw;
+    const int thr = c.bh * 16 < 256 ? c.bh * 16 : 256;
+    c.split = vpt >= thr ? 1 : 0;
+    return c;
+}
+}  // namespace roma
+
 namespace roma {
 static int kde_nsplit(int N) {
     // enough CTAs for >= 2 waves of 148 SMs x 4 resident CTAs
@@ -373,16 +680,102 @@ static size_t kde_colpart_bytes(int N) {
 }
 }  // namespace roma
 
+namespace roma {
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+// workspace of the exact mode: [qpack N x 16][rpack M x 16][table 32768 f + flag][main: V (N x 512 f) or a chunk of scores]
+static size_t kde_exact_fixed_bytes(int N) { return align256((size_t)N * 32) + align256(kKdeLutBytes); }
+}  // namespace roma
+
 extern "C" size_t roma_kde_workspace_bytes(int N) {
     if (N <= 0) return 0;
-    return (size_t)64 * (size_t)N * sizeof(float) + roma::kde_colpart_bytes(N) + roma::kKdeLutBytes;
+    const size_t legacy = (size_t)64 * (size_t)N * sizeof(float) + roma::kde_colpart_bytes(N) + roma::kKdeLutBytes;
+    const size_t exact = roma::kde_exact_fixed_bytes(N) + (size_t)N * 512 * sizeof(float) + 4096;   // V, or >= 1024 rows of scores
+    return legacy > exact ? legacy : exact;
 }
 
-// 0 = auto (half: table-driven with the distances on the tensor cores, when the table fits; every pair evaluated once
-// when the reference points are the queries), 1 = always the direct op chain, 2 = table-driven with the SIMT FFMA2
-// distance chain, 3 = as 0 but every (i, j) AND (j, i) evaluated (1, 2 and 3 are testing aids)
+// 0 (default) = exact: bit-identical to the reference's CUDA op chain (tensor-core distances, table, ATen's summation
+// order).  Testing / opt-in: 1 = the op chain per pair with sequential fp32 FMAs, 2 = table + sequential FMAs, 3 = tensor-core
+// distances + table, every (i, j) and (j, i), free summation order, 4 = as 3 with every pair evaluated once (fastest; the
+// density may differ from the reference's in the last half bit on ~0.03 % of the rows)
 namespace roma { static int g_kde_direct = 0; }
-extern "C" int roma_kde_set_direct(int direct) { roma::g_kde_direct = (direct >= 1 && direct <= 3) ? direct : 0; return ROMA_OK; }
+extern "C" int roma_kde_set_direct(int direct) { roma::g_kde_direct = (direct >= 1 && direct <= 4) ? direct : 0; return ROMA_OK; }
+
+namespace roma {
+static int kde_exact(const float* x, int N, int M, int down, float inv_two_var, float* density, float* p_out,
+                     void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    const size_t fixed = kde_exact_fixed_bytes(N);
+    const int pitch = (M + 7) & ~7;
+    ROMA_REQUIRE(workspace_bytes >= fixed + (size_t)16 * pitch * 2, ROMA_ERR_WORKSPACE,
+                 "roma_kde: workspace too small for the exact half mode (%zu bytes, see roma_kde_workspace_bytes)", workspace_bytes);
+    ROMA_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15u) == 0, ROMA_ERR_ALIGNMENT, "roma_kde: workspace must be 16-byte aligned");
+    char* base = reinterpret_cast<char*>(workspace);
+    uint4* qpack = reinterpret_cast<uint4*>(base);
+    uint4* rpack = qpack + N;
+    float* lut = reinterpret_cast<float*>(base + align256((size_t)N * 32));
+    int* poison = reinterpret_cast<int*>(lut + 32768);
+    char* mainbuf = base + fixed;
+    const size_t main_bytes = workspace_bytes - fixed;
+    // table: entries >= cutoff are exactly 0 (exp underflows in half); host-side estimate, verified on the device (poison)
+    int cutoff = 0x7C00;
+    {
+        const float s_max = 1.125f * 17.33f / inv_two_var;
+        if (s_max < 60000.f) {
+            const int cb = (int)__half_as_ushort(__float2half_rn(s_max)) + 2;
+            if (cb < cutoff) cutoff = cb;
+        }
+    }
+    int rc;
+    cudaMemsetAsync(poison, 0, sizeof(int), st);
+    kde_lut_kernel<<<(0x7C00 + 256) / 256, 256, 0, st>>>(lut, poison, inv_two_var, cutoff < 0x7C00 ? cutoff : 0x7C01);
+    kde_pack_kernel<<<cdiv(N, 256), 256, 0, st>>>(x, N, M, down, qpack, rpack);
+    if ((rc = check_launch("roma_kde(exact: table, pack)", 2))) return rc;
+    const AtenSumCfg cfg = aten_sum_config(N, M);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    static bool cfg_done[64] = {false};
+    if (dev >= 0 && dev < 64 && !cfg_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kde_exact_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((kLutMax + 4) * sizeof(float)));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kde_scores_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(0x7C04 * sizeof(unsigned short)));
+        if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
+        cfg_done[dev] = true;
+    }
+    const bool fused = cfg.vectorized && cfg.split && cfg.bw == 32 && cfg.bh == 16 && (M & 7) == 0 && cutoff <= kLutMax &&
+                       main_bytes >= (size_t)N * 512 * sizeof(float);
+    if (fused) {
+        float* V = reinterpret_cast<float*>(mainbuf);
+        const int nrb = cdiv(N, 128), nitems = nrb * (512 / kFusedTL);
+        int grid = 2 * sm_count();
+        if (grid > nitems) grid = nitems;
+        const size_t smem = ((size_t)(cutoff + 1 + 3) & ~(size_t)3) * sizeof(float);
+        kde_exact_fused_kernel<<<grid, kKdeThreads, smem, st>>>(qpack, rpack, N, M, lut, cutoff, V, nrb, nitems);
+        kde_exact_tree_kernel<<<cdiv(N, 8), 256, 0, st>>>(V, N, density, p_out, poison);
+        return check_launch("roma_kde(exact, fused)", 2);
+    }
+    // generic: chunks of rows through the workspace
+    long long chunk = (long long)(main_bytes / ((size_t)pitch * 2));
+    chunk = chunk > N ? N : chunk;
+    if (chunk < N) chunk &= ~15ll;
+    ROMA_REQUIRE(chunk >= 1, ROMA_ERR_WORKSPACE, "roma_kde: workspace too small for one chunk of scores");
+    unsigned short* E = reinterpret_cast<unsigned short*>(mainbuf);
+    const int ngroups = (M + 7) >> 3;
+    const size_t smem_scores = (size_t)(cutoff + 2) * sizeof(unsigned short);
+    for (long long r0 = 0; r0 < N; r0 += chunk) {
+        const int rows = (int)((N - r0) < chunk ? (N - r0) : chunk);
+        const int rblocks = cdiv(cdiv(rows, 16), kKdeThreads / 32);
+        int csplit = cdiv(4 * sm_count(), rblocks);
+        if (csplit > ngroups) csplit = ngroups;
+        if (csplit < 1) csplit = 1;
+        const int gper = cdiv(ngroups, csplit);
+        csplit = cdiv(ngroups, gper);
+        kde_scores_kernel<<<dim3(rblocks, csplit), kKdeThreads, smem_scores, st>>>(qpack, rpack, N, M, (int)r0, rows, lut, cutoff, E, pitch, gper);
+        const int sblocks = cfg.split ? rows : cdiv(rows, cfg.bh);
+        kde_aten_sum_kernel<<<sblocks, dim3(cfg.bw, cfg.bh), (size_t)cfg.bw * cfg.bh * sizeof(float), st>>>(
+            E, pitch, (int)r0, rows, N, M, cfg, density, p_out, poison);
+        if ((rc = check_launch("roma_kde(exact, generic)", 2))) return rc;
+    }
+    return ROMA_OK;
+}
+}  // namespace roma
 
 extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
                            float* density, float* p_out, void* workspace, size_t workspace_bytes, void* stream) {
@@ -400,6 +793,8 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
     const float two_var = (float)(2.0 * std * std);
     const float inv_two_var = 1.0f / two_var;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (half && g_kde_direct == 0) return kde_exact(x, N, M, down, inv_two_var, density, p_out, workspace, workspace_bytes, st);
+    const int legacy = g_kde_direct;                    // 1, 2, 3, 4 (half) — or anything for fp32
     float* partial = reinterpret_cast<float*>(workspace);
     dim3 grid((N + kKdeThreads - 1) / kKdeThreads, nsplit);
     int rc;
@@ -408,7 +803,7 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
     float* colpart = nullptr;
     // table-driven half path: the cutoff is a property of std alone; evaluate it on the host with the same
     // half arithmetic (exp(-s/(2 std^2)) < 2^-25 rounds to 0) so no device round trip is needed to size smem.
-    bool use_lut = half && g_kde_direct != 1 && workspace_bytes >= (size_t)N * sizeof(float) + kKdeLutBytes;
+    bool use_lut = half && legacy != 1 && workspace_bytes >= (size_t)N * sizeof(float) + kKdeLutBytes;
     int cutoff_bound = 0;
     if (use_lut) {
         // s beyond which exp underflows to 0 in half: exp(-s*inv) < 2^-25  <=>  s > 25 ln2 / inv ; +12.5% margin
@@ -430,7 +825,7 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
             if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
             cfg = true;
         }
-        if (g_kde_direct == 2) {
+        if (legacy == 2) {
             const int qblocks = (N + kKdeThreads * kQPT - 1) / (kKdeThreads * kQPT);
             int ns = (2 * 3 * sm_count() + qblocks - 1) / qblocks;
             ns = ns < 1 ? 1 : (ns > nsplit ? nsplit : ns);
@@ -448,7 +843,7 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
             const int qper = (kKdeThreads / 32) * 16 * kKdeQT;                  // queries per block
             const int qblocks = (N + qper - 1) / qper;
             // symmetric mode: half of the (block, split) pairs exit at once, so twice the splits keep the same number of waves
-            const bool sym = down == 1 && g_kde_direct != 3 && N <= kKdeSymMaxN &&
+            const bool sym = down == 1 && legacy == 4 && N <= kKdeSymMaxN &&
                              workspace_bytes >= (size_t)64 * N * sizeof(float) + kde_colpart_bytes(N) + kKdeLutBytes;
             // >= 4 waves of 3 resident blocks per SM (uniform blocks: the tail of the last wave is what is lost)
             const size_t avail = workspace_bytes - kKdeLutBytes - (sym ? kde_colpart_bytes(N) : 0);

@@ -66,7 +66,8 @@ def test_late_entry_points_validate_and_refuse_cpu():
     assert lib.roma_layernorm_shift(None, None, None, None, None, 1, 8, 1e-6, 1, None) == -1
     N = 40000
     assert lib.roma_kde_workspace_bytes(N) >= 64 * N * 4 + ((N + 127) // 128) * N * 4
-    assert lib.roma_kde_workspace_bytes(200000) < 64 * 200000 * 4 + (1 << 20)        # beyond the symmetric limit: row partials only
+    assert lib.roma_kde_workspace_bytes(N) >= N * 512 * 4 + N * 32 + 32768 * 4          # exact mode: per-thread row sums + packed operands + table
+    assert lib.roma_kde_workspace_bytes(200000) < 200000 * 512 * 4 + (16 << 20)        # beyond the symmetric limit: no column partials
     for call in (lambda: ops.gelu(torch.zeros(16, dtype=torch.bfloat16)),
                  lambda: ops.prepare_images(torch.zeros(1, 3, 8, 8, dtype=torch.uint8), (4, 4)),
                  lambda: ops.prepare_images_pil(torch.zeros(1, 3, 8, 8, dtype=torch.uint8), (4, 4)),

@@ -1,0 +1,222 @@
+"""north_star's integer criterion on the B200: `roma_kde(half)` is BIT-IDENTICAL to the reference's CUDA op chain
+(romatch/utils/kde.py:4-12) and `sample()` returns the SAME rows as the reference class under one seeded CUDA generator
+(romatch/models/matcher.py:468-495, romatch/models/tiny.py:297-327).
+
+The comparand is the unmodified reference from baseline/_ref when it travelled with the snapshot (oracle/reference.py);
+its kde is four ATen calls, restated verbatim below so the test also runs where the reference is absent.
+CUDA <-> CUDA only: the CPU generator and the CPU half kernels differ from the CUDA ones."""
+import ctypes as C
+import types
+
+import pytest
+import torch
+
+from oracle import reference as R
+
+pytestmark = pytest.mark.gpu
+
+
+def aten_chain_kde(x, std=0.1, half=True, down=None):
+    """romatch/utils/kde.py:4-12, the same four ATen calls (used when baseline/_ref is not on the machine)."""
+    if half:
+        x = x.half()
+    if down is not None:
+        scores = (-torch.cdist(x, x[::down]) ** 2 / (2 * std ** 2)).exp()
+    else:
+        scores = (-torch.cdist(x, x) ** 2 / (2 * std ** 2)).exp()
+    return scores.sum(dim=-1)
+
+
+def reference_kde():
+    if R.available():
+        R.import_reference()
+        from romatch.utils.kde import kde
+        return kde, "baseline/_ref romatch.utils.kde.kde"
+    return aten_chain_kde, "ATen chain restated (reference not on this machine)"
+
+
+def warp_rows(N, seed, dev):
+    """N rows (xA, yA, xB, yB) as sample() draws them from a symmetric warp: dense clusters + a smooth correspondence field."""
+    g = torch.Generator().manual_seed(seed)
+    a = torch.rand(N, 2, generator=g) * 2 - 1
+    k = N // 3
+    a[:k] = (torch.randn(k, 2, generator=g) * 0.05 + torch.tensor([0.3, -0.2])).clamp(-1, 1)
+    b = (a + 0.1 * torch.sin(3 * a.flip(1)) + 0.002 * torch.randn(N, 2, generator=g)).clamp(-1, 1)
+    return torch.cat((a, b), dim=1).to(dev)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from roma_b200 import ops as _ops
+    return _ops
+
+
+def bits(t):
+    return t.contiguous().view(torch.int16)
+
+
+def test_distance_arithmetic_is_the_tensor_core_product(ops, cuda):
+    """What makes the default mode exact: for every pair the half GEMM of ATen's _euclidean_dist equals ONE warp-level
+    mma.sync over the same six products (k8 or k16, either operand order); the sequential-FMA form (mode 1) does not."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    N = 4096
+    x = warp_rows(N, 1, cuda)
+    xh = x.half()
+    n = xh.pow(2).sum(-1, keepdim=True)
+    one = torch.ones_like(n)
+    x1, x2 = torch.cat((xh.mul(-2), n, one), -1), torch.cat((xh, one, n), -1)
+    ref = x1[None].matmul(x2[None].mT)[0]                                    # cdist_impl runs it as a batch of one
+    assert torch.equal(bits(ref.clone().clamp_min_(0).sqrt_()), bits(torch.cdist(xh, xh)))
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    xf = x.float().contiguous()
+    counts = {}
+    for var in range(5):
+        buf = torch.empty((N, N), dtype=torch.int16, device=cuda)
+        assert lib.roma_kde_debug_d2(C.c_void_p(xf.data_ptr()), N, var, C.c_void_p(buf.data_ptr()), st) == 0
+        counts[var] = int((buf != bits(ref)).sum().item())
+    print("d2 mismatches vs cuBLAS half GEMM over", N * N, "pairs:", counts)
+    assert counts[1] == counts[2] == counts[3] == counts[4] == 0
+    assert counts[0] > 0                                                      # the op-for-op FMA chain is NOT what cuBLAS computes
+
+
+def test_table_equals_aten_half_chain_on_every_value(cuda):
+    from roma_b200 import _lib
+    lib = _lib.load()
+    lut = torch.empty(32768, dtype=torch.float32, device=cuda)
+    assert lib.roma_kde_debug_lut(C.c_void_p(lut.data_ptr()), 0.1, C.c_void_p(torch.cuda.current_stream().cuda_stream)) == 0
+    d2 = torch.arange(0, 0x7C01, dtype=torch.int32, device=cuda).to(torch.int16).view(torch.float16)
+    r = d2.clone().clamp_min_(0).sqrt_()
+    e = (-r ** 2 / (2 * 0.1 ** 2)).exp()
+    assert torch.equal(bits(lut[:0x7C01].half()), bits(e))
+
+
+# fused path: N % 8 == 0 and N >= 8161; everything else (unaligned rows, one warp per row, non-vectorised, down) is the
+# generic path.  8160 / 8161 / 8168 straddle ATen's switch from one warp per row to 512 threads per row; 127 / 128 its switch
+# to vectorised loads; 1023 has a different alignment shift on every row.
+@pytest.mark.parametrize("N,down", [(40000, None), (20000, None), (8192, None), (8168, None), (8161, None), (8160, None),
+                                    (4000, None), (1023, None), (130, None), (128, None), (127, None), (100, None),
+                                    (37, None), (20000, 1), (20000, 8), (24001, 8), (8163, 3)])
+def test_kde_half_bit_exact_vs_reference_chain(ops, cuda, N, down):
+    kde_ref, what = reference_kde()
+    x = warp_rows(N, N, cuda)
+    want = kde_ref(x, std=0.1, half=True, down=down)
+    got = ops.kde(x, std=0.1, half=True, down=down)
+    assert got.dtype == want.dtype == torch.float16 and got.shape == want.shape
+    bad = int((bits(got) != bits(want)).sum().item())
+    print(f"kde N={N} down={down}: {bad} of {N} densities differ from {what}; max density {want.float().max().item():.0f}")
+    assert bad == 0
+    if N >= 4000:
+        assert want.float().max().item() > 50                                   # a non-trivial density field
+
+
+def test_kde_mismatch_count_of_every_mode(ops, cuda):
+    """Reported for the record: only the default (0) is exact; the opt-in fast mode (4) and the testing aids are not."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    kde_ref, what = reference_kde()
+    out = {}
+    for N in (20000, 40000):
+        x = warp_rows(N, 4, cuda)
+        want = kde_ref(x)
+        for mode in (0, 1, 2, 3, 4):
+            try:
+                lib.roma_kde_set_direct(mode)
+                got = ops.kde(x, half=True)
+            finally:
+                lib.roma_kde_set_direct(0)
+            out[(N, mode)] = int((bits(got) != bits(want)).sum().item())
+    print("densities differing from the reference chain, (N, mode) -> count:", out)
+    assert out[(20000, 0)] == 0 and out[(40000, 0)] == 0
+
+
+def _symmetric_field(H, W, seed, dev):
+    """(H, 2W, 4) warp and (H, 2W) certainty like match() returns: smooth correspondence + an uncertain region."""
+    g = torch.Generator().manual_seed(seed)
+    ys = torch.linspace(-1 + 1 / H, 1 - 1 / H, H)
+    xs = torch.linspace(-1 + 1 / W, 1 - 1 / W, W)
+    grid = torch.stack((xs[None, :].expand(H, W), ys[:, None].expand(H, W)), dim=-1)
+    low = torch.randn(2, 2, 6, 6, generator=g) * 0.15
+    disp = torch.nn.functional.interpolate(low, size=(H, W), mode="bicubic", align_corners=False).permute(0, 2, 3, 1)
+    ab, ba = (grid + disp[0]).clamp(-1, 1), (grid + disp[1]).clamp(-1, 1)
+    warp = torch.cat((torch.cat((grid, ab), dim=-1), torch.cat((ba, grid), dim=-1)), dim=1)
+    blob = torch.nn.functional.interpolate(torch.rand(1, 1, 9, 18, generator=g), size=(H, 2 * W), mode="bicubic", align_corners=False)[0, 0]
+    cert = (blob.clamp(0, 1) ** 2) * (torch.rand(H, 2 * W, generator=g) < 0.9)
+    return warp.to(dev).contiguous(), cert.to(dev).contiguous()
+
+
+def _reference_sample(kind):
+    """The reference's own sample() (unbound) on a stand-in `self` carrying the two attributes it reads."""
+    self = types.SimpleNamespace(sample_mode="threshold_balanced", sample_thresh=0.05)
+    if R.available():
+        R.import_reference()
+        if kind == "roma":
+            from romatch.models.matcher import RegressionMatcher
+            return lambda m, c, num: RegressionMatcher.sample(self, m, c, num=num), "baseline/_ref RegressionMatcher.sample"
+        from romatch.models.tiny import TinyRoMa
+        return lambda m, c, num: TinyRoMa.sample(self, m, c, num=num), "baseline/_ref TinyRoMa.sample"
+    from oracle import roma_oracle as O
+
+    def run(m, c, num):
+        return O.sample(m, c, num=num, kde_fn=lambda x, std: aten_chain_kde(x, std=std))
+    return run, "oracle sample() over the restated ATen chain (reference not on this machine)"
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_sample_rows_identical_to_reference(ops, cuda, seed):
+    """matcher.py:468-495 at the benchmark size: 864 x 1728 field, num = 10000 -> kde on 40000 candidates."""
+    import roma_b200
+    ref_sample, what = _reference_sample("roma")
+    warp, cert = _symmetric_field(864, 864, seed, cuda)
+    model = types.SimpleNamespace(sample_thresh=0.05, sample_mode="threshold_balanced")
+    cert0 = cert.clone()
+    torch.cuda.manual_seed(1000 + seed)
+    m_ref, c_ref = ref_sample(warp, cert, 10000)
+    torch.cuda.manual_seed(1000 + seed)
+    m, c, idx = ops.sample(warp, cert, num=10000, sample_thresh=model.sample_thresh, sample_mode=model.sample_mode, return_indices=True)
+    assert torch.equal(cert, cert0)                                             # neither implementation writes into the caller's tensor
+    assert idx.dtype == torch.int64 and m.shape == (10000, 4)
+    same = int((m == m_ref).all(dim=1).sum().item())
+    print(f"sample seed {seed}: {same} of 10000 rows identical to {what}")
+    assert torch.equal(m, m_ref) and torch.equal(c, c_ref)
+    assert torch.equal(warp.reshape(-1, 4)[idx], m_ref)                         # the integer indices reproduce the reference's rows
+    # RegressionMatcher.sample is the same call
+    mm = roma_b200.RegressionMatcher(torch.nn.Identity(), torch.nn.Identity())
+    torch.cuda.manual_seed(1000 + seed)
+    m2, c2 = mm.sample(warp, cert, num=10000)
+    assert torch.equal(m2, m_ref) and torch.equal(c2, c_ref)
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_tiny_sample_rows_identical_to_reference(cuda, seed):
+    """tiny.py:297-327: num = 5000, kde(half=True, down=1) on CUDA, on a 480 x 640 field."""
+    from roma_b200.host.tiny import TinyRoMa
+    ref_sample, what = _reference_sample("tiny")
+    warp, cert = _symmetric_field(480, 320, seed + 10, cuda)                     # (480, 640, 4)
+    ours = types.SimpleNamespace(sample_mode="threshold_balanced", sample_thresh=0.05)
+    torch.cuda.manual_seed(77 + seed)
+    m_ref, c_ref = ref_sample(warp, cert, 5000)
+    torch.cuda.manual_seed(77 + seed)
+    m, c = TinyRoMa.sample(ours, warp, cert, num=5000)
+    print(f"tiny sample seed {seed}: {int((m == m_ref).all(dim=1).sum().item())} of 5000 rows identical to {what}")
+    assert torch.equal(m, m_ref) and torch.equal(c, c_ref)
+
+
+def test_sample_num_above_candidate_count(ops, cuda):
+    """matcher.py:484,493: min(...) — asking for more than there is returns every candidate once, same rows as the reference."""
+    ref_sample, _ = _reference_sample("roma")
+    warp, cert = _symmetric_field(24, 20, 5, cuda)                               # 960 candidates < 4 * 10000
+    cert = cert.clamp(min=0.2)                                                  # every weight positive (else multinomial cannot fill)
+    torch.cuda.manual_seed(5)
+    m_ref, c_ref = ref_sample(warp, cert, 10000)
+    torch.cuda.manual_seed(5)
+    m, c = ops.sample(warp, cert, num=10000)
+    assert m.shape == (960, 4) and torch.equal(m, m_ref) and torch.equal(c, c_ref)
+
+
+def test_sample_all_zero_certainty_raises_like_the_reference(ops, cuda):
+    """All-zero weights make torch.multinomial raise in the reference; the drop-in keeps that behaviour."""
+    warp, cert = _symmetric_field(16, 16, 6, cuda)
+    with pytest.raises(RuntimeError):
+        ops.sample(warp, torch.zeros_like(cert), num=100)
+        torch.cuda.synchronize()

@@ -212,7 +212,16 @@ def current_modes(N):
     return out
 
 
+def sum_only():
+    """all rows, so that wrong summation orders show (~0.1 % of the rows move by one half ulp)"""
+    for N in (4000, 8160, 8192, 20000):
+        res[f"sumall_{N}"] = sum_candidates(N, rows=N)
+        print("sum(all rows)", N, {k: v for k, v in res[f"sumall_{N}"].items()})
+
+
 def main():
+    if "--sum-only" in sys.argv:
+        return sum_only()
     torch.manual_seed(0)
     print("device", torch.cuda.get_device_name(0), "torch", torch.__version__, "cublas", torch.backends.cuda.preferred_blas_library())
     res["allow_fp16_reduced_precision_reduction"] = torch.backends.cuda.matmul.allow_fp16_reduced_precision_reduction
@@ -233,6 +242,7 @@ def main():
         res[f"modes_{N}"] = current_modes(N)
         print("modes", N, res[f"modes_{N}"])
     (OUT / "kde_explore.json").write_text(json.dumps(res, indent=1))
+    sum_only()
 
 
 if __name__ == "__main__":
@@ -240,5 +250,5 @@ if __name__ == "__main__":
     try:
         main()
     finally:
-        (OUT / "kde_explore.json").write_text(json.dumps(res, indent=1))
+        (OUT / ("kde_explore_sum.json" if "--sum-only" in sys.argv else "kde_explore.json")).write_text(json.dumps(res, indent=1))
         print("elapsed", time.time() - t0)
