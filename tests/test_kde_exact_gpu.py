@@ -214,9 +214,27 @@ def test_sample_num_above_candidate_count(ops, cuda):
     assert m.shape == (960, 4) and torch.equal(m, m_ref) and torch.equal(c, c_ref)
 
 
-def test_sample_all_zero_certainty_raises_like_the_reference(ops, cuda):
-    """All-zero weights make torch.multinomial raise in the reference; the drop-in keeps that behaviour."""
-    warp, cert = _symmetric_field(16, 16, 6, cuda)
-    with pytest.raises(RuntimeError):
-        ops.sample(warp, torch.zeros_like(cert), num=100)
-        torch.cuda.synchronize()
+def test_sample_all_zero_certainty_raises_like_the_reference():
+    """All-zero weights make torch.multinomial raise in the reference; the drop-in keeps that behaviour.
+    On CUDA the raise is ATen's `_assert_async` — a device-side assert that poisons the CUDA context for good — so the
+    case runs in a process of its own, for the reference's sample() and for ours."""
+    import subprocess
+    import sys
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    code = (
+        "import sys, types, torch\n"
+        f"sys.path.insert(0, {str(R.ROOT)!r})\n"
+        "from tests.test_kde_exact_gpu import _symmetric_field, _reference_sample\n"
+        "from roma_b200 import ops\n"
+        "warp, cert = _symmetric_field(16, 16, 6, torch.device('cuda:0'))\n"
+        "fn = (lambda: ops.sample(warp, torch.zeros_like(cert), num=100)) if sys.argv[1] == 'ours' else "
+        "(lambda: _reference_sample('roma')[0](warp, torch.zeros_like(cert), 100))\n"
+        "try:\n"
+        "    fn(); torch.cuda.synchronize()\n"
+        "except RuntimeError as e:\n"
+        "    print('RAISED', type(e).__name__); sys.exit(0)\n"
+        "print('NO RAISE'); sys.exit(0)\n")
+    for who in ("reference", "ours"):
+        res = subprocess.run([sys.executable, "-c", code, who], capture_output=True, text=True, timeout=600)
+        assert "RAISED" in res.stdout, f"{who}: {res.stdout[-500:]} {res.stderr[-2000:]}"
