@@ -226,6 +226,22 @@ int roma_match_keypoints(const float* x_A, int Na, const float* x_B, int Nb,
                          float thresh, int64_t* inds_A, int64_t* inds_B, int capacity, int* count,
                          void* workspace, size_t workspace_bytes, void* stream);
 
+/* roma_match_keypoints_static: the same computation and outputs as roma_match_keypoints, but the call ALLOCATES
+ * NOTHING and takes no workspace: its scratch is a file-scope `static __device__` array inside the library.
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Limit: Na, Nb <= roma_match_keypoints_static_max_points() (16384 keypoints per image; 512 KiB of device memory per
+ * GPU that loads the library, held until the process exits).  Larger sizes: ROMA_ERR_UNSUPPORTED with a message —
+ * use roma_match_keypoints with a caller workspace.  Launches on the CURRENT device (the one the pointers live on).
+ * Every call on a device shares the one array: calls that overlap on the GPU (two streams, two host threads) RACE;
+ * serialise them on one stream.  Nothing in the array needs clearing between calls (every entry is written before
+ * it is read within a call); it keeps the last call's contents. */
+int roma_match_keypoints_static_max_points(void);
+int roma_match_keypoints_static(const float* x_A, int Na, const float* x_B, int Nb,
+                                const float* warp, const float* certainty, int H, int Wp,
+                                float thresh, int64_t* inds_A, int64_t* inds_B, int capacity, int* count,
+                                void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * (f-1) cls_to_flow_refine: softmax over res^2 bins, argmax, 5-tap weighted mean.
  *

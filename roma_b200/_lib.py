@@ -52,6 +52,8 @@ SIGNATURES = {
     "roma_kde_debug_lut": (_i, [_vp, C.c_double, _vp]),
     "roma_match_keypoints_workspace_bytes": (_sz, [_i, _i]),
     "roma_match_keypoints": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _i, _f, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
+    "roma_match_keypoints_static_max_points": (_i, []),
+    "roma_match_keypoints_static": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _i, _f, _vp, _vp, _i, _vp, _vp]),
     "roma_dwconv5x5_bias_act": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "roma_dwconv5x5_pointwise": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "roma_dwconv_set_path": (_i, [_i]),

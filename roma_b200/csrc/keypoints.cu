@@ -4,6 +4,8 @@
 // expression, so the equality tests D == rowmin and D == colmin of the reference are exact here too.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace roma {
 namespace kp {
 
@@ -149,4 +151,72 @@ extern "C" int roma_match_keypoints(const float* x_A, int Na, const float* x_B, 
     kp::scan_kernel<<<1, 1024, 0, st>>>(w.cnt, Na, count);
     kp::mutual_kernel<true><<<cdiv(Na, 256), 256, 0, st>>>(w.xab, w.certa, Na, x_B, Nb, w.rowmin, w.colmin, thresh, w.cnt, inds_A, inds_B, capacity);
     return check_launch("roma_match_keypoints", 6);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// roma_match_keypoints_static: the same six launches with the scratch in a file-scope device array — for callers
+// that may not allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// The array is per device (every GPU that loads the library holds ROMA_KP_STATIC_BYTES until exit); its device
+// address is resolved ONCE per device, with that device current, by cudaGetSymbolAddress: in host code the
+// symbol's name is a host-side stand-in, not a device pointer.
+// ---------------------------------------------------------------------------------------------------------------
+#define ROMA_KP_STATIC_MAX_POINTS 16384
+#define ROMA_KP_STATIC_BYTES (512 * 1024)
+
+static __device__ __align__(256) unsigned char g_kp_static_scratch[ROMA_KP_STATIC_BYTES];
+
+namespace roma {
+namespace kp {
+static void* g_static_addr[64] = {};
+static std::mutex g_static_mu;
+
+// device address of g_kp_static_scratch on the CURRENT device (resolved once per device); nullptr + *err on failure
+static void* static_scratch(int* device, cudaError_t* err) {
+    *err = cudaGetDevice(device);
+    if (*err != cudaSuccess) return nullptr;
+    if (*device < 0 || *device >= 64) { *err = cudaErrorInvalidDevice; return nullptr; }
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_addr[*device]) {
+        void* p = nullptr;
+        *err = cudaGetSymbolAddress(&p, g_kp_static_scratch);
+        if (*err != cudaSuccess) return nullptr;
+        g_static_addr[*device] = p;
+    }
+    return g_static_addr[*device];
+}
+}  // namespace kp
+}  // namespace roma
+
+extern "C" int roma_match_keypoints_static_max_points(void) { return ROMA_KP_STATIC_MAX_POINTS; }
+
+extern "C" int roma_match_keypoints_static(const float* x_A, int Na, const float* x_B, int Nb,
+                                           const float* warp, const float* certainty, int H, int Wp,
+                                           float thresh, int64_t* inds_A, int64_t* inds_B, int capacity, int* count,
+                                           void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(x_A && x_B && warp && certainty && inds_A && inds_B && count, ROMA_ERR_BAD_ARG, "roma_match_keypoints_static: null pointer");
+    ROMA_REQUIRE(Na > 0 && Nb > 0 && H > 0 && Wp > 0 && capacity >= 0, ROMA_ERR_BAD_ARG, "roma_match_keypoints_static: bad sizes");
+    ROMA_REQUIRE(Na <= ROMA_KP_STATIC_MAX_POINTS && Nb <= ROMA_KP_STATIC_MAX_POINTS, ROMA_ERR_UNSUPPORTED,
+                 "roma_match_keypoints_static: Na = %d / Nb = %d exceed the static scratch limit of %d keypoints per image "
+                 "(use roma_match_keypoints with a caller workspace)", Na, Nb, ROMA_KP_STATIC_MAX_POINTS);
+    ROMA_REQUIRE((reinterpret_cast<uintptr_t>(warp) & 15u) == 0 && (reinterpret_cast<uintptr_t>(x_A) & 7u) == 0 &&
+                 (reinterpret_cast<uintptr_t>(x_B) & 7u) == 0,
+                 ROMA_ERR_ALIGNMENT, "roma_match_keypoints_static: warp needs 16-byte, keypoints 8-byte alignment");
+    int device = -1;
+    cudaError_t err = cudaSuccess;
+    void* scratch = kp::static_scratch(&device, &err);
+    ROMA_REQUIRE(scratch != nullptr, ROMA_ERR_UNSUPPORTED, "roma_match_keypoints_static: cudaGetSymbolAddress failed on device %d: %s",
+                 device, cudaGetErrorString(err));
+    kp::Ws w = kp::carve(scratch, Na, Nb);
+    ROMA_REQUIRE(w.bytes <= (size_t)ROMA_KP_STATIC_BYTES, ROMA_ERR_WORKSPACE, "roma_match_keypoints_static: %zu scratch bytes > %d", w.bytes, ROMA_KP_STATIC_BYTES);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // every scratch entry read below is written first by an earlier launch of THIS call (xab, certa, rowmin, colmin,
+    // cnt[0..Na]); nothing relies on the array's previous contents, so no clearing is needed between calls.
+    kp::warp_points_kernel<<<cdiv(Na, 256), 256, 0, st>>>(x_A, Na, warp, certainty, H, Wp, w.xab, w.certa);
+    kp::min_dist_kernel<<<cdiv(Na, 256), 256, 0, st>>>(w.xab, Na, x_B, Nb, w.rowmin);
+    kp::min_dist_kernel<<<cdiv(Nb, 256), 256, 0, st>>>(x_B, Nb, w.xab, Na, w.colmin);
+    kp::mutual_kernel<false><<<cdiv(Na, 256), 256, 0, st>>>(w.xab, w.certa, Na, x_B, Nb, w.rowmin, w.colmin, thresh, w.cnt, nullptr, nullptr, 0);
+    kp::scan_kernel<<<1, 1024, 0, st>>>(w.cnt, Na, count);
+    kp::mutual_kernel<true><<<cdiv(Na, 256), 256, 0, st>>>(w.xab, w.certa, Na, x_B, Nb, w.rowmin, w.colmin, thresh, w.cnt, inds_A, inds_B, capacity);
+    return check_launch("roma_match_keypoints_static", 6);
 }
