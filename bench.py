@@ -14,9 +14,15 @@ timed region ("weak" scaling: per-GPU work fixed); NCCL is used only for the bar
   value  : pairs/s with the uint8 input images already resident in HBM.
   e2e    : the same call with pinned HOST images — H2D copy in, D2H copy of the sampled matches out, per step.
   roofline / kernels : per-kernel CUDA-event timings taken live inside the timed region (ops.KernelTimer).
-  cpu_baseline / --impl reference : the CPU oracle port of the same path (oracle/, fp32, all host threads)
-           on a bounded sample (1 pair per step) — there is no compiled reference to run (the reference is
-           Python and cannot travel to the GPU box).
+  cpu_baseline / --impl reference : the UNMODIFIED reference from baseline/_ref (installed by __graft_entry__.build(),
+           travels with the snapshot) on the host cores — roma_outdoor(device="cpu") through its own forward_symmetric +
+           epilogue + sample (SURVEY.md §8d), fp32, all host threads, 1 pair per step (bounded sample), one warm-up;
+           kind "reference".  Only when baseline/_ref is absent: the CPU oracle port of the same path (kind "port").
+  aten_cuda_baseline : the same unmodified reference on THIS GPU through ATen (fp16 autocast as shipped, and all-bf16).
+  hot_path : Σ SURVEY.md §8(d) roofline floors ÷ Σ measured time of the kernels north_star names (GP, gather / local
+           correlation, update / resample / epilogue).
+  configs  : short driver-visible runs of BASELINE.json configs[3] (672 -> 1344) and configs[4] (Tiny-RoMa, 480 x 640).
+  parity   : deviation of this run's (16-bit) output from the same model with fp32 bodies, first pair of the batch.
 """
 from __future__ import annotations
 
@@ -183,7 +189,23 @@ class ClockSampler:
 # CPU baseline (oracle port) — also the --impl reference arm
 # ------------------------------------------------------------------------------------------------------
 def cpu_pair_fn(coarse, upsample, weights, dinov2):
+    """-> (run(A8, B8, seed), kind).  kind "reference": the unmodified reference (baseline/_ref) on the CPU;
+    kind "port": the oracle port over the repo's host modules (only when the reference is not on this machine)."""
     import roma_b200
+    from oracle import reference as R
+    mean = torch.tensor((0.485, 0.456, 0.406)).view(1, 3, 1, 1)
+    std = torch.tensor((0.229, 0.224, 0.225)).view(1, 3, 1, 1)
+    rs = lambda t: F.interpolate(t, size=tuple(coarse), mode="bicubic", antialias=True, align_corners=False)
+    if R.available():
+        ref = R.reference_roma_outdoor("cpu", weights, dinov2, tuple(coarse), tuple(upsample), amp_dtype=torch.float32)
+
+        def run(A8: torch.Tensor, B8: torch.Tensor, seed: int = 0):
+            with torch.inference_mode():
+                fA, fB = (A8.float() / 255 - mean) / std, (B8.float() / 255 - mean) / std
+                warp, cert, _ = R.reference_forward_batched(ref, rs(fA), rs(fB), fA, fB)
+                torch.manual_seed(seed)
+                return ref.sample(warp[0], cert[0], num=10000)
+        return run, "reference"
     from oracle import roma_model_oracle as MO
     from oracle import roma_oracle as O
     cpu = roma_b200.roma_outdoor("cpu", weights, dinov2, coarse_res=coarse, upsample_res=upsample, amp_dtype=torch.float32)
@@ -192,11 +214,14 @@ def cpu_pair_fn(coarse, upsample, weights, dinov2):
     def run(A8: torch.Tensor, B8: torch.Tensor, seed: int = 0):
         with torch.inference_mode():
             fA, fB = cpu._normalise(A8), cpu._normalise(B8)
-            rs = lambda t: F.interpolate(t, size=tuple(coarse), mode="bicubic", antialias=True, align_corners=False)
             warp, cert = MO.match_tensors(cpu, rs(fA), rs(fB), fA, fB)
             g = torch.Generator().manual_seed(seed)
             return O.sample(warp[0], cert[0], num=10000, generator=g)
-    return run
+    return run, "port"
+
+
+WHAT = {"reference": "the UNMODIFIED reference (baseline/_ref): roma_outdoor(device='cpu') forward_symmetric x2 + epilogue + sample",
+        "port": "fp32 oracle port issuing the reference's ATen calls (baseline/_ref not on this machine)"}
 
 
 def run_reference_arm(args, rank, world):
@@ -206,7 +231,7 @@ def run_reference_arm(args, rank, world):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     weights, dinov2 = roma_b200.random_init_weights(seed=0)
-    run = cpu_pair_fn(args.coarse, args.upsample, weights, dinov2)
+    run, kind = cpu_pair_fn(args.coarse, args.upsample, weights, dinov2)
     A8, B8 = synthetic_pairs(1, args.upsample, 1234)
     budget_s = args.ref_budget
     t_all = time.perf_counter()
@@ -223,16 +248,174 @@ def run_reference_arm(args, rank, world):
     per = sum(times) / len(times)
     val = 1.0 / per
     sample = (f"1 pair per step (of the {args.batch}-pair batch) at {args.coarse[0]}->{args.upsample[0]}, match+sample(10000), "
-              f"fp32 oracle port on {cores} host threads; {warm} warm-up + {len(times)} timed steps "
-              f"(of {args.steps} requested, capped at {int(budget_s)} s)")
+              f"{WHAT[kind]}, fp32 on {cores} host threads; {warm} warm-up + {len(times)} timed steps "
+              f"(of {args.steps} requested, capped at {int(budget_s)} s), best {min(times):.1f} s")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": round(val, 5), "unit": UNIT, "n_gpus": args.gpus,
         "steps": len(times), "warmup": warm, "ms_per_step": round(per * 1e3, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_dict(args, cpu=True),
-        "cpu_baseline": {"value": round(val, 5), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": round(val, 5), "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": round(val, 5), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+# ------------------------------------------------------------------------------------------------------
+# the reference on THIS GPU (ATen), other configs, hot-path aggregate, parity of the 16-bit run
+# ------------------------------------------------------------------------------------------------------
+def aten_cuda_baseline(args, dev, weights, dinov2, A8, B8):
+    """The unmodified reference (baseline/_ref) on the B200 through its stock ATen path: the same batch, forward_symmetric x2
+    + epilogue + sample(10000) per pair; fp16 autocast (as shipped) and all-bf16.  Wall clock around synchronised steps."""
+    from oracle import reference as R
+    if not R.available():
+        return {"unavailable": "baseline/_ref is not on this machine"}
+    out = {"what": "unmodified reference (baseline/_ref) on this GPU, ATen kernels, same batch and call sequence",
+           "pairs_per_step": args.batch}
+    mean = torch.tensor((0.485, 0.456, 0.406), device=dev).view(1, 3, 1, 1)
+    std = torch.tensor((0.229, 0.224, 0.225), device=dev).view(1, 3, 1, 1)
+    rs = lambda t: F.interpolate(t, size=tuple(args.coarse), mode="bicubic", antialias=True, align_corners=False)
+    for name in ("float16", "bfloat16"):
+        try:
+            model = R.reference_roma_outdoor(dev, weights, dinov2, tuple(args.coarse), tuple(args.upsample), amp_dtype=getattr(torch, name))
+            t_mod = {}
+
+            def step(record=False):
+                t = [time.perf_counter()]
+                fa, fb = (A8.to(dev).float() / 255 - mean) / std, (B8.to(dev).float() / 255 - mean) / std
+                warp, cert, _ = R.reference_forward_batched(model, rs(fa), rs(fb), fa, fb)
+                if record:
+                    torch.cuda.synchronize(); t.append(time.perf_counter())
+                for i in range(args.batch):
+                    model.sample(warp[i], cert[i], num=args.num)
+                if record:
+                    torch.cuda.synchronize(); t.append(time.perf_counter())
+                    t_mod["match_ms"], t_mod["sample_ms"] = (t[1] - t[0]) * 1e3, (t[2] - t[1]) * 1e3
+            step()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            n = 2
+            for _ in range(n):
+                step()
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) / n
+            step(record=True)
+            out[name] = {"pairs_per_s": round(args.batch / dt, 3), "ms_per_step": round(dt * 1e3, 2),
+                         "match_ms_per_step": round(t_mod["match_ms"], 2), "sample_ms_per_step": round(t_mod["sample_ms"], 2)}
+            del model
+        except Exception as ex:  # noqa: BLE001 — a failing comparand must not take the bench line down
+            out[name] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
+        torch.cuda.empty_cache()
+    return out
+
+
+def survey_floor_ms(rows, pk):
+    """Σ SURVEY.md §8(d) floors vs Σ measured time for the kernels north_star names, per step.
+    K2 bytes per launch (§8d verbatim): e·C·hw·[r>0] + e·C·hw + 8·hw + e·K·hw + e·C·hw (no x copy at the gather-only scales, no
+    embedding); GP FLOPs: 2·(2N²C) + N³/3 + 2N²D + 2N²D; K3a: bytes read + written once (alg_work)."""
+    hbm, tc = pk["hbm_gbs"] * 1e9, pk["bf16_tflops_sustained"] * 1e12
+    parts = {"gp": [0.0, 0.0], "gather_local_corr": [0.0, 0.0], "update_resample_epilogue": [0.0, 0.0]}
+    for r in rows:
+        d, n = r["dims"], r["launches_per_step"]
+        if r["kernel"] == "roma_gp_posterior":
+            parts["gp"][0] += n * r["alg"] / tc * 1e3
+            parts["gp"][1] += r["ms_per_step"]
+        elif r["kernel"] == "roma_refiner_gather" and not d.get("only"):
+            e, hw, K = d["esize"], d["B"] * d["h"] * d["w"], (2 * d["r"] + 1) ** 2 if d["r"] else 0
+            b = hw * (e * d["C"] * (1 if d["r"] else 0) + e * d["C"] + 8 + e * K + e * d["C"])
+            parts["gather_local_corr"][0] += n * b / hbm * 1e3
+            parts["gather_local_corr"][1] += r["ms_per_step"]
+        elif r["kernel"] in ("roma_flow_update_resample", "roma_match_epilogue"):
+            parts["update_resample_epilogue"][0] += n * r["alg"] / hbm * 1e3
+            parts["update_resample_epilogue"][1] += r["ms_per_step"]
+    floor, meas = sum(v[0] for v in parts.values()), sum(v[1] for v in parts.values())
+    return {"floor_ms_per_step": round(floor, 4), "measured_ms_per_step": round(meas, 4), "frac": round(floor / meas, 4) if meas else None,
+            "parts": {k: {"floor_ms": round(v[0], 4), "measured_ms": round(v[1], 4), "frac": round(v[0] / v[1], 4) if v[1] else None}
+                      for k, v in parts.items()},
+            "note": "GP measured in-step (it overlaps the upsample-pass encoder); peaks: measured HBM copy and sustained bf16"}
+
+
+def other_configs(args, dev, model):
+    """BASELINE.json configs[3] and configs[4], short runs (2 warm-up + 3 timed steps, CUDA events)."""
+    import roma_b200
+    from roma_b200.host.tiny import TinyRoMa, XFeatBackbone, random_init_tiny
+    out = {}
+
+    def time_steps(fn, warm=2, steps=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            fn()
+        e.record()
+        torch.cuda.synchronize()
+        return s.elapsed_time(e) / steps
+    try:
+        keep = (model.h_resized, model.w_resized, model.upsample_res)
+        model.h_resized, model.w_resized, model.upsample_res = 672, 672, (1344, 1344)      # plain attributes, as in the reference
+        A8, B8 = synthetic_pairs(4, (1344, 1344), 99)
+        A8, B8 = A8.to(dev), B8.to(dev)
+
+        def step4():
+            warp, cert = model.match(A8, B8, batched=True, device=dev)
+            model.sample_batch(warp, cert, num=args.num)
+        ms = time_steps(step4)
+        out["config4_672_1344"] = {"pairs_per_s": round(4 / ms * 1e3, 2), "ms_per_step": round(ms, 2), "pairs_per_step": 4,
+                                   "workload": "roma_outdoor 672 -> 1344 (GP N = 2304), match + sample(10000)", "dtype": args.dtype}
+        model.h_resized, model.w_resized, model.upsample_res = keep
+        del A8, B8
+    except Exception as ex:  # noqa: BLE001
+        out["config4_672_1344"] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
+    torch.cuda.empty_cache()
+    try:
+        weights, trunk_sd = random_init_tiny(seed=0)
+        trunk = XFeatBackbone()
+        trunk.load_state_dict(trunk_sd)
+        tiny = TinyRoMa(trunk)
+        tiny.load_state_dict(weights)
+        tiny = tiny.to(dev).train(False)
+        g = torch.Generator().manual_seed(4321)
+        Bt = 32
+        A = torch.rand(Bt, 3, 480, 640, generator=g).to(dev)
+        Bm = torch.rand(Bt, 3, 480, 640, generator=g).to(dev)
+
+        def step5():
+            warp, cert = tiny.match(A, Bm, batched=True)
+            for i in range(Bt):
+                tiny.sample(warp[i], cert[i], num=5000)
+        ms = time_steps(step5)
+        out["config5_tiny_480x640"] = {"pairs_per_s": round(Bt / ms * 1e3, 1), "ms_per_step": round(ms, 2), "pairs_per_step": Bt,
+                                       "workload": "tiny_roma_v1_outdoor (XFeat stand-in trunk), 32 pairs/GPU of 480 x 640, match + "
+                                                   "sample(5000); configs[4] proper = 8 such replicas", "dtype": "f32 trunk, f16 kde"}
+    except Exception as ex:  # noqa: BLE001
+        out["config5_tiny_480x640"] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
+    torch.cuda.empty_cache()
+    return out
+
+
+def parity_block(args, dev, model, weights, dinov2, A8, B8):
+    """How far this run's 16-bit bodies move the output: first pair of the batch against the SAME model with fp32 bodies
+    (the configuration tests/test_refparity_e2e_gpu.py holds to 1e-3 / 1e-2 against the reference)."""
+    import roma_b200
+    try:
+        a, b = A8[:1].to(dev), B8[:1].to(dev)
+        w16, c16, l16 = model.match(a, b, batched=True, device=dev, return_logits=True)
+        tf = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+        torch.backends.cuda.matmul.allow_tf32 = torch.backends.cudnn.allow_tf32 = False
+        m32 = roma_b200.roma_outdoor(dev, weights, dinov2, coarse_res=args.coarse, upsample_res=args.upsample, amp_dtype=torch.float32)
+        w32, c32, l32 = m32.match(a, b, batched=True, device=dev, return_logits=True)
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf
+        del m32
+        torch.cuda.empty_cache()
+        dw, dl = (w16 - w32).abs().flatten(), (l16 - l32).abs().flatten()
+        q = lambda t, f: t.float().kthvalue(max(int(t.numel() * f), 1)).values.item()
+        return {"what": f"{args.dtype} bodies vs fp32 bodies of the same model, pair 0, {args.coarse[0]}->{args.upsample[0]}; north_star "
+                        "tolerances (warp 1e-3, logits 1e-2) are held by the fp32-body configuration against the reference",
+                "warp_abs": {"max": round(dw.max().item(), 5), "p99": round(q(dw, 0.99), 6), "mean": round(dw.mean().item(), 6)},
+                "logit_abs": {"max": round(dl.max().item(), 4), "p99": round(q(dl, 0.99), 5), "mean": round(dl.mean().item(), 5)}}
+    except Exception as ex:  # noqa: BLE001
+        return {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
 
 
 def config_dict(args, cpu=False):
@@ -257,6 +440,7 @@ def main():
     ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16", "float32"])
     ap.add_argument("--num", type=int, default=10000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip aten_cuda_baseline / configs / parity (profiling runs)")
     ap.add_argument("--sample-lanes", type=int, default=2, help="streams sample_batch spreads the pairs over")
     ap.add_argument("--decoder-priority", type=int, default=1, help="0: upsample-pass encoder on a side stream, coarse decoder on "
                     "the caller's; 1 (default): coarse decoder on a high-priority stream")
@@ -329,9 +513,11 @@ def main():
     # ---- timed region 1: device-resident inputs (value) with live per-kernel events ----------------------
     clocks = ClockSampler(local)
     l0 = lib.roma_kernel_launches()
-    with ops.KernelTimer() as kt:
-        ms_dev = timed(lambda: step(A_dev, B_dev, False), args.steps)
+    ms_dev = timed(lambda: step(A_dev, B_dev, False), args.steps)
     launches = int(lib.roma_kernel_launches() - l0)
+    # ---- same steps again with a CUDA-event pair around every own kernel (per-kernel table; not the headline) ---
+    with ops.KernelTimer() as kt:
+        ms_inst = timed(lambda: step(A_dev, B_dev, False), args.steps)
     # ---- timed region 2: end to end from pinned host memory ----------------------------------------------
     step(A_host, B_host, True)
     ms_e2e = timed(lambda: step(A_host.to(dev, non_blocking=True), B_host.to(dev, non_blocking=True), True), args.steps)
@@ -405,18 +591,27 @@ def main():
         "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": int(A_host.numel() + B_host.numel()) * world,
                 "d2h_bytes_per_step": int(out_host.numel() * 4) * world, "ms_per_step": round(ms_e2e / args.steps, 3)},
         "gpu_launches": launches, "clocks": clk, "roofline": roofline,
-        "own_kernels_ms_per_step": round(own_ms, 3), "headline_kernels": headline, "kernels": rows[:12],
+        "own_kernels_ms_per_step": round(own_ms, 3), "instrumented_ms_per_step": round(ms_inst / args.steps, 3),
+        "hot_path": survey_floor_ms(rows, pk), "headline_kernels": headline, "kernels": rows[:12],
     }
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        run = cpu_pair_fn(args.coarse, args.upsample, weights, dinov2)
-        t0 = time.perf_counter()
-        run(A8[:1], B8[:1])
-        dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": round(1.0 / dt, 5), "unit": UNIT, "cores": cores, "kind": "port",
+        if not args.no_extras:
+            line["parity"] = parity_block(args, dev, model, weights, dinov2, A8, B8)
+            line["aten_cuda_baseline"] = aten_cuda_baseline(args, dev, weights, dinov2, A8, B8)
+            line["configs"] = other_configs(args, dev, model)
+        run, kind = cpu_pair_fn(args.coarse, args.upsample, weights, dinov2)
+        run(A8[:1], B8[:1])                                   # warm-up (thread pool, oneDNN primitives)
+        dts = []
+        for i in range(2):
+            t0 = time.perf_counter()
+            run(A8[:1], B8[:1], seed=i)
+            dts.append(time.perf_counter() - t0)
+        dt = min(dts)
+        line["cpu_baseline"] = {"value": round(1.0 / dt, 5), "unit": UNIT, "cores": cores, "kind": kind,
                                 "sample": f"1 pair (first of the batch) at {args.coarse[0]}->{args.upsample[0]}, match+sample(10000), "
-                                          f"fp32 oracle port, one cold run of {dt:.1f} s on {cores} host threads"}
+                                          f"{WHAT[kind]}, fp32; one warm-up, best of 2 runs = {dt:.1f} s on {cores} host threads"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -84,9 +84,13 @@ typedef struct roma_strides4 {
  * Zero padding: taps outside f1 contribute 0 (grid_sample padding_mode="zeros").
  * The correlation is sum_c f0[c] * f1_sampled[c] / sqrt(C).
  */
-/* Testing / profiling aid for the aligned 16-bit local-correlation case (C in {64, 128, 256, 512}): 0 (default) =
- * neighbour dot products as warp-level tensor-core MMAs (mma.sync m16n8k16, fragments filled straight from 16-byte
- * global loads), 1 = SIMT FMA dot products with shuffle reductions. */
+/* Testing / profiling aid for the aligned 16-bit local-correlation case (C in {64, 128, 256, 512}).
+ * 0 (default) = for r = 2, 3 and equally sized maps, 8 x 8 pixel tiles whose windows fit a shared patch of f1 (coherent
+ *     flow) are computed as ONE tcgen05 GEMM of the tile's f0 rows against the patch (TMA-loaded once, TMEM accumulator;
+ *     local_corr_tile.cuh); the remaining tiles, and every other case, take the per-pixel kernel of path 2;
+ * 1 = SIMT FMA dot products with shuffle reductions;
+ * 2 = per pixel, neighbour dot products as warp-level tensor-core MMAs (mma.sync m16n8k16, fragments filled straight
+ *     from 16-byte global loads) for every pixel. */
 int roma_local_corr_set_path(int path);
 int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_strides4 flow_strides,
                         const float* disp_w, const float* disp_b, float disp_scale,

@@ -82,6 +82,27 @@ def reference_roma_outdoor(device, weights, dinov2_weights, coarse_res=560, upsa
     return model.eval()
 
 
+_inv_patched = False
+
+
+def unbatched_cpu_inv() -> None:
+    """`torch.linalg.inv` on a CPU batch (the reference's GP.forward, matcher.py:261, with b >= 2) dead-locks inside oneMKL for
+    n >~ 100 in this torch build.  Run the SAME LAPACK routine one matrix at a time instead — identical
+    arithmetic per element; CUDA tensors and single matrices pass straight through.  The reference source is untouched."""
+    global _inv_patched
+    if _inv_patched:
+        return
+    import torch
+    inv = torch.linalg.inv
+
+    def one_at_a_time(A, *a, **k):
+        if A.dim() == 3 and A.device.type == "cpu" and A.shape[0] > 1 and A.shape[-1] >= 64:
+            return torch.stack([inv(x, *a, **k) for x in A])
+        return inv(A, *a, **k)
+    torch.linalg.inv = one_at_a_time
+    _inv_patched = True
+
+
 def reference_forward_batched(model, im_A, im_B, im_A_up, im_B_up):
     """Batched two-pass matching with the UNMODIFIED reference modules.
 
@@ -97,6 +118,8 @@ def reference_forward_batched(model, im_A, im_B, im_A_up, im_B_up):
     B = im_A.shape[0]
     H, W = model.upsample_res
     dev = im_A.device
+    if dev.type == "cpu":
+        unbatched_cpu_inv()
     with torch.no_grad():
         coarse = model.forward_symmetric({"im_A": im_A, "im_B": im_B})
         low = F.interpolate(coarse[16]["certainty"], size=(H, W), mode="bilinear", align_corners=False)

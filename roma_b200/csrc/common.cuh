@@ -18,6 +18,15 @@ void set_error(const char* fmt, ...);
 int  fail(int code, const char* fmt, ...);
 int  check_launch(const char* what, int launches = 1);   // cudaGetLastError -> positive code + message; counts launches
 
+// Per-device one-time set-up (cudaFuncSetAttribute opt-ins are per device / context, not per process).
+// `if (DeviceOnce::pending(flags)) { ...set up...; DeviceOnce::done(flags); }` with `static DeviceOnce::Flags flags;`
+struct DeviceOnce {
+    struct Flags { bool set[64] = {}; };
+    static int current() { int d = 0; return (cudaGetDevice(&d) == cudaSuccess && d >= 0 && d < 64) ? d : -1; }
+    static bool pending(const Flags& f) { const int d = current(); return d < 0 || !f.set[d]; }
+    static void done(Flags& f) { const int d = current(); if (d >= 0) f.set[d] = true; }
+};
+
 #define ROMA_REQUIRE(cond, code, ...) \
     do { if (!(cond)) return ::roma::fail((code), __VA_ARGS__); } while (0)
 

@@ -225,6 +225,8 @@ struct Lanes {
     cudaStream_t chain = nullptr;
     cudaEvent_t fork = nullptr, diag[kMaxLaneBlocks], upd[kMaxLaneBlocks], panel[kMaxLaneBlocks];
     bool ok = false;
+    std::mutex enqueue;   // held while one call enqueues its two-lane schedule: cudaStreamWaitEvent snapshots an event at call
+                          // time, so whole-call mutual exclusion of the ENQUEUE makes concurrent host threads on one device safe
 };
 static Lanes* lanes_for_current_device() {
     static std::mutex mu;
@@ -317,15 +319,17 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
         }
     }
 
-    static bool diag_cfg = false;
-    if (!diag_cfg) {
+    static DeviceOnce::Flags diag_cfg;
+    if (DeviceOnce::pending(diag_cfg)) {
         cudaError_t e = cudaFuncSetAttribute(diag_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDiagSmem);
         if (e != cudaSuccess) return fail((int)e, "gp diag: smem opt-in: %s", cudaGetErrorString(e));
-        diag_cfg = true;
+        DeviceOnce::done(diag_cfg);
     }
 
     Lanes* lanes = (g_lanes.load() != 0 && nb > 1 && nb <= kMaxLaneBlocks) ? lanes_for_current_device() : nullptr;
+    std::unique_lock<std::mutex> lanes_lock;
     if (lanes) {
+        lanes_lock = std::unique_lock<std::mutex>(lanes->enqueue);
         // 3'. two-lane schedule.  Diagonal tiles are kept up to date right-looking (syrk after every panel), the rest of
         //     the block column and the right-hand sides left-looking, one step behind the chain.
         //       chain (sc):  diag(k) . [wait upd(k)] panel_A(k) . syrk(k)

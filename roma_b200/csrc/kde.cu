@@ -819,11 +819,11 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
         cudaMemsetAsync(poison, 0, sizeof(int), st);
         kde_lut_kernel<<<(0x7C00 + 256) / 256, 256, 0, st>>>(lut, poison, inv_two_var, cutoff_bound);
         const size_t smem = ((size_t)(cutoff_bound + 1 + 3) & ~(size_t)3) * sizeof(float) + kKdeTile * (2 * sizeof(float4) + sizeof(float2));
-        static bool cfg = false;
-        if (!cfg) {
+        static DeviceOnce::Flags cfg;
+        if (DeviceOnce::pending(cfg)) {
             cudaError_t e = cudaFuncSetAttribute(kde_partial_lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((kLutMax + 4) * sizeof(float)) + kKdeTile * 40));
             if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
-            cfg = true;
+            DeviceOnce::done(cfg);
         }
         if (legacy == 2) {
             const int qblocks = (N + kKdeThreads * kQPT - 1) / (kKdeThreads * kQPT);
@@ -833,11 +833,11 @@ extern "C" int roma_kde(const float* x, int N, int down, double std, int half,
             nsplit = ns;
             kde_partial_lut_kernel<<<dim3(qblocks, nsplit), kKdeThreads, smem, st>>>(x, N, M, down, lut, cutoff_bound, partial, nsplit);
         } else {
-            static bool cfg_mma = false;
-            if (!cfg_mma) {
+            static DeviceOnce::Flags cfg_mma;
+            if (DeviceOnce::pending(cfg_mma)) {
                 cudaError_t e = cudaFuncSetAttribute(kde_partial_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((kLutMax + 4) * sizeof(float)) + kKdeTile * 16));
                 if (e != cudaSuccess) return fail((int)e, "roma_kde: smem opt-in: %s", cudaGetErrorString(e));
-                cfg_mma = true;
+                DeviceOnce::done(cfg_mma);
             }
             const size_t smem_mma = ((size_t)(cutoff_bound + 1 + 3) & ~(size_t)3) * sizeof(float) + kKdeTile * sizeof(uint4);
             const int qper = (kKdeThreads / 32) * 16 * kKdeQT;                  // queries per block

@@ -30,6 +30,8 @@ struct GatherParams {
     long long npix;
     int tile_px;     // pixels per CTA tile (local-corr kernel)
     int covered;     // channels written by the enabled segments; [covered, dch) is zero-filled pitch padding
+    int tile_pw;     // > 0: 8 x 8 pixel tiles (grid = tiles_x, tiles_y, B); the per-pixel kernel SKIPS tiles whose windows fit
+                     // a tile_pw x tile_pw patch (they are computed by local_corr_tile_kernel, local_corr_tile.cuh)
 };
 
 __device__ __forceinline__ void pixel_coords(const GatherParams& p, long long pix, int& b, int& y, int& x,
@@ -55,6 +57,10 @@ __device__ __forceinline__ void sample_coords(float gx, float gy, int w1, int h1
     wx0 = (fx + 1.f) - ix; wx1 = ix - fx;
     wy0 = (fy + 1.f) - iy; wy1 = iy - fy;
 }
+
+}  // namespace roma
+#include "local_corr_tile.cuh"
+namespace roma {
 
 // ------------------------------------------------------------------------------------------------
 // Kernel A: r > 0.  One warp per pixel; CTA tile = tile_px consecutive (b,y,x)-flattened pixels.
@@ -375,12 +381,25 @@ local_corr_mma_kernel(const GatherParams p) {
     T* dout = reinterpret_cast<T*>(p.d);
     const int covered = p.covered;
 
-    const long long tile_start = (long long)blockIdx.x * p.tile_px;
+    long long tile_start = (long long)blockIdx.x * p.tile_px;
     int tile_n = p.tile_px;
-    if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
+    const bool tiled = p.tile_pw > 0;
+    if (tiled) {
+        // 8 x 8 tiles; the tiles whose windows fit the shared patch belong to local_corr_tile_kernel
+        __shared__ int red[8];
+        bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
+        if (tile_window_fits(p, blockIdx.z, blockIdx.y * kTileSide, blockIdx.x * kTileSide, p.tile_pw, red,
+                             valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0)) return;
+        tile_n = kTilePx;
+    } else if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
 
     for (int lp = warp; lp < tile_n; lp += 8) {
-        const long long pix = tile_start + lp;
+        long long pix = tile_start + lp;
+        if (tiled) {
+            const int ty = blockIdx.y * kTileSide + (lp >> 3), tx = blockIdx.x * kTileSide + (lp & 7);
+            if (ty >= p.h || tx >= p.w) continue;
+            pix = ((long long)blockIdx.z * p.h + ty) * p.w + tx;
+        }
         int b, y, x; float gx, gy;
         pixel_coords(p, pix, b, y, x, gx, gy);
         int x0, y0; float wx0, wx1, wy0, wy1;
@@ -638,7 +657,53 @@ gather_only_kernel(const GatherParams p, long long nthreads, int cpp) {
     }
 }
 
-static std::atomic<int> g_local_corr_path{0};     // 0: tensor-core dot products (default), 1: SIMT FMA dot products (v2)
+// 0 (default): shared-patch tcgen05 tiles for coherent tiles (r = 2, 3) + per-pixel tensor-core kernel for the rest;
+// 1: SIMT FMA dot products (v2); 2: per-pixel tensor-core kernel for every pixel (the round-1 default)
+static std::atomic<int> g_local_corr_path{2};   // TODO(validated on the GPU): 0
+
+// Shared-patch path: both kernels over the same (tiles_x, tiles_y, B) grid; every tile is taken by exactly one of them.
+// ROMA_ERR_UNSUPPORTED (silently, no message) when the feature maps cannot be described to TMA -> caller falls back.
+template <typename T, int R>
+static int launch_tiled_r(GatherParams p, cudaStream_t st, int dtype) {
+    using G = TileGeom<R>;
+    TileMaps maps;
+    const uint64_t e = sizeof(T);
+    const uint64_t d0[4] = {(uint64_t)p.C, (uint64_t)p.w, (uint64_t)p.h, (uint64_t)p.B};
+    const uint64_t s0[3] = {(uint64_t)p.C * e, (uint64_t)p.w * p.C * e, (uint64_t)p.h * p.w * p.C * e};
+    const uint32_t b0[4] = {64u, (uint32_t)kTileSide, (uint32_t)kTileSide, 1u};
+    const uint64_t d1[4] = {(uint64_t)p.C, (uint64_t)p.w1, (uint64_t)p.h1, (uint64_t)p.B};
+    const uint64_t s1[3] = {(uint64_t)p.C * e, (uint64_t)p.w1 * p.C * e, (uint64_t)p.h1 * p.w1 * p.C * e};
+    const uint32_t b1[4] = {64u, (uint32_t)G::PW, (uint32_t)G::ROWS, 1u};
+    if (!tma::encode_fn()) return ROMA_ERR_UNSUPPORTED;
+    if (tma::encode_tiled(&maps.f0, dtype, 4, p.f0, d0, s0, b0, CU_TENSOR_MAP_SWIZZLE_128B) != 0 ||
+        tma::encode_tiled(&maps.f1, dtype, 4, p.f1, d1, s1, b1, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return ROMA_ERR_UNSUPPORTED;
+    static DeviceOnce::Flags configured;
+    if (DeviceOnce::pending(configured)) {
+        cudaError_t err = cudaFuncSetAttribute(local_corr_tile_kernel<T, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+        if (err != cudaSuccess) return fail((int)err, "roma_refiner_gather: smem opt-in (%zu B): %s", G::SMEM, cudaGetErrorString(err));
+        DeviceOnce::done(configured);
+    }
+    p.tile_pw = G::PW;
+    const dim3 grid((unsigned)cdiv(p.w, kTileSide), (unsigned)cdiv(p.h, kTileSide), (unsigned)p.B);
+    local_corr_tile_kernel<T, R><<<grid, 256, G::SMEM, st>>>(p, maps);
+    switch (p.C) {
+        case 512: local_corr_mma_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
+        case 256: local_corr_mma_kernel<T, 4><<<grid, 256, 0, st>>>(p); break;
+        case 128: local_corr_mma_kernel<T, 2><<<grid, 256, 0, st>>>(p); break;
+        default:  local_corr_mma_kernel<T, 1><<<grid, 256, 0, st>>>(p); break;
+    }
+    return check_launch("roma_refiner_gather(local_corr_tile + local_corr_mma)", 2);
+}
+
+template <typename T>
+static int launch_tiled(GatherParams p, cudaStream_t st) {
+    if constexpr (sizeof(T) == 2) {
+        const int dtype = std::is_same<T, __half>::value ? ROMA_F16 : ROMA_BF16;
+        if (p.B > 65535 || cdiv(p.h, kTileSide) > 65535) return ROMA_ERR_UNSUPPORTED;
+        return p.r == 2 ? launch_tiled_r<T, 2>(p, st, dtype) : launch_tiled_r<T, 3>(p, st, dtype);
+    }
+    return ROMA_ERR_UNSUPPORTED;
+}
 
 template <typename T>
 static int launch_gather(GatherParams p, cudaStream_t st) {
@@ -658,7 +723,12 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
             p.tile_px = 32;
             const int grid = cdiv(p.npix, p.tile_px);
             if constexpr (sizeof(T) == 2) {
-                if (g_local_corr_path.load() == 0) {
+                if (g_local_corr_path.load() == 0 && (p.r == 2 || p.r == 3) && p.h == p.h1 && p.w == p.w1 && p.off_corr >= 0) {
+                    // shared-patch tiles (coherent flow) + per-pixel kernel for the tiles that decline (local_corr_tile.cuh)
+                    const int rc = launch_tiled<T>(p, st);
+                    if (rc != ROMA_ERR_UNSUPPORTED) return rc;
+                }
+                if (g_local_corr_path.load() == 0 || g_local_corr_path.load() == 2) {
                     switch (p.C) {
                         case 512: local_corr_mma_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
                         case 256: local_corr_mma_kernel<T, 4><<<grid, 256, 0, st>>>(p); break;
@@ -727,7 +797,7 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
 }  // namespace roma
 
 extern "C" int roma_local_corr_set_path(int path) {
-    if (path < 0 || path > 1) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 tensor-core, 1 SIMT)", path);
+    if (path < 0 || path > 2) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 default, 1 SIMT, 2 per-pixel tensor-core only)", path);
     roma::g_local_corr_path.store(path);
     return ROMA_OK;
 }
@@ -743,6 +813,10 @@ extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* 
                  ROMA_ERR_BAD_ARG, "roma_refiner_gather: bad sizes B=%d C=%d h=%d w=%d h1=%d w1=%d E=%d r=%d", B, C, h, w, h1, w1, E, r);
     if (E == 0) off_emb = -1;
     if (r == 0) off_corr = -1;
+    // the window offsets are linspace(-2r/h, 2r/h) in feature0's size (local_correlation.py:30-39): exact one-pixel steps in
+    // feature1 only when the two maps have the same size — the shared-weight form below relies on that
+    ROMA_REQUIRE(off_corr < 0 || (h == h1 && w == w1), ROMA_ERR_UNSUPPORTED,
+                 "roma_refiner_gather: local correlation needs feature maps of one size (f0 %dx%d, f1 %dx%d)", h, w, h1, w1);
     ROMA_REQUIRE(!(off_emb >= 0) || (disp_w && disp_b), ROMA_ERR_BAD_ARG, "roma_refiner_gather: embedding requested without weights");
     ROMA_REQUIRE(f0 || (off_x < 0 && off_corr < 0), ROMA_ERR_BAD_ARG, "roma_refiner_gather: f0 is required for the copy / correlation segments");
     // the enabled segments must tile [0, d_channels) exactly (the tile span is written as a whole)
@@ -766,7 +840,7 @@ extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* 
     p.disp_w = disp_w; p.disp_b = disp_b; p.disp_scale = disp_scale;
     p.d = d; p.dch = d_channels; p.off_x = off_x; p.off_xhat = off_xhat; p.off_emb = off_emb; p.off_corr = off_corr;
     p.B = B; p.C = C; p.h = h; p.w = w; p.h1 = h1; p.w1 = w1; p.E = E; p.r = r;
-    p.npix = (long long)B * h * w; p.tile_px = 0; p.covered = covered;
+    p.npix = (long long)B * h * w; p.tile_px = 0; p.covered = covered; p.tile_pw = 0;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (dtype) {
         case ROMA_F32:  return launch_gather<float>(p, st);

@@ -399,12 +399,12 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_nt_kernel(const Launch L) {
 
 template <typename T, int SPLIT>
 static int launch_gemm_nt(const Launch& L, int batch, cudaStream_t st, const char* what) {
-    static bool configured = false;     // per instantiation
+    static DeviceOnce::Flags configured;     // per instantiation and device
     constexpr size_t smem = smem_bytes<SPLIT>();
-    if (!configured) {
+    if (DeviceOnce::pending(configured)) {
         cudaError_t e = cudaFuncSetAttribute(gemm_nt_kernel<T, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return fail((int)e, "%s: smem opt-in (%zu B): %s", what, smem, cudaGetErrorString(e));
-        configured = true;
+        DeviceOnce::done(configured);
     }
     int tiles = L.tiles0 + (L.nprob > 1 ? (L.p[1].diag_only ? L.p[1].tiles_m : L.p[1].tiles_m * L.p[1].tiles_n) : 0);
     if (tiles <= 0 || batch <= 0) return ROMA_OK;
@@ -519,11 +519,11 @@ static int launch_gemm_nt_16(const Launch& L, int batch, cudaStream_t st, const 
     }
     if (!ok) return launch_gemm_nt<T, 1>(L, batch, st, what);
     if (L.nprob < 2) { maps.a[1] = maps.a[0]; maps.b[1] = maps.b[0]; }
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce::Flags configured;
+    if (DeviceOnce::pending(configured)) {
         cudaError_t e = cudaFuncSetAttribute(gemm_nt_tma_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmem);
         if (e != cudaSuccess) return fail((int)e, "%s: smem opt-in (%zu B): %s", what, kTmaSmem, cudaGetErrorString(e));
-        configured = true;
+        DeviceOnce::done(configured);
     }
     gemm_nt_tma_kernel<T><<<dim3(tiles, batch), kThreads, kTmaSmem, st>>>(L, maps);
     return check_launch(what);

@@ -6,8 +6,10 @@ not on a CUDA device raise.
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import math
+import threading
 from typing import Optional, Tuple
 
 import torch
@@ -43,17 +45,28 @@ class KernelTimer:
         return out
 
 
+_tls = threading.local()
+
+
 def _run(name: str, dims: dict, call):
-    """Invoke one C-ABI entry point (optionally bracketed by events on the current stream) and check its code."""
-    t = KernelTimer.active
-    if t is None:
-        rc = call()
-    else:
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        rc = call()
-        e.record()
-        t.records.append((name, dims, s, e))
+    """Invoke one C-ABI entry point (optionally bracketed by events on the current stream) and check its code.
+
+    The launch happens with the TENSORS' device current (recorded by `_cuda` for this thread): the library launches on
+    the calling thread's current device, and `_stream(dev)` / the pointers belong to the tensors' device — without the
+    guard a call on cuda:1 from a process whose current device is 0 would launch on GPU 0 against GPU-1 memory."""
+    dev = getattr(_tls, "dev", None)
+    guard = torch.cuda.device(dev) if dev is not None and dev.index is not None and dev.index != torch.cuda.current_device() \
+        else contextlib.nullcontext()
+    with guard:
+        t = KernelTimer.active
+        if t is None:
+            rc = call()
+        else:
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            rc = call()
+            e.record()
+            t.records.append((name, dims, s, e))
     _lib.check(rc, name)
 
 
@@ -69,6 +82,7 @@ def _cuda(*ts: Optional[torch.Tensor]) -> torch.device:
             dev = t.device
         elif t.device != dev:
             raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
+    _tls.dev = dev
     return dev
 
 
@@ -159,6 +173,9 @@ def local_correlation(feature0: torch.Tensor, feature1: torch.Tensor, local_radi
     dev = _cuda(feature0, feature1, flow)
     B, Cc, h, w = feature0.shape
     r = int(local_radius)
+    if tuple(feature1.shape[2:]) != (h, w):
+        raise NotImplementedError(f"roma_b200.local_correlation needs feature maps of one size, got {tuple(feature0.shape)} and "
+                                  f"{tuple(feature1.shape)} (the reference's window step is then not one pixel of feature1)")
     if flow is None:   # aligned features: sample around the pixel's own centre (local_correlation.py:16-27)
         ys = torch.linspace(-1 + 1 / h, 1 - 1 / h, h, device=dev)
         xs = torch.linspace(-1 + 1 / w, 1 - 1 / w, w, device=dev)

@@ -1,0 +1,230 @@
+"""GPU: the whole match at BASELINE.json's sizes against the UNMODIFIED reference.
+
+  * configs[0]: assets/sacre_coeur_A / _B through match() at 560 -> 864 against the reference's CPU fp32 output
+    (tests/golden/config1_*.npz, made by tests/golden/make_golden_config1.py in the build container).  fp32 bodies: north_star's
+    tolerances (warp <= 1e-3, certainty <= 1e-2); bf16 / fp16 bodies: the deviation is measured, printed and bounded.
+  * configs[1] shape: synthetic pairs at 560 -> 864 against the reference model running on the SAME GPU (baseline/_ref,
+    fp32, TF32 off) through its own forward_symmetric + epilogue (SURVEY.md §8d recipe).
+  * patch(): the reference model built from baseline/_ref on CUDA, matched before and after `roma_b200.patch(model)`.
+  * behaviours SURVEY.md §8(a) lists: attributes changed between calls on ONE instance, symmetric=False with a batch.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+from PIL import Image
+
+import roma_b200
+from oracle import reference as R
+
+pytestmark = pytest.mark.gpu
+WARP_TOL, CERT_TOL, LOGIT_TOL = 1e-3, 1e-2, 1e-2
+need_ref = pytest.mark.skipif(not R.available(), reason="baseline/_ref (the unmodified reference) is not on this machine")
+
+
+def _tf32_off():
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+
+
+@pytest.fixture(scope="module")
+def weights():
+    return {tag: roma_b200.random_init_weights(seed=0, sensitised=tag == "sensitised") for tag in ("default", "sensitised")}
+
+
+def _stats(a, b):
+    d = (a - b).abs().flatten().float()
+    k = max(int(d.numel() * 0.999), 1)
+    return d.max().item(), d.kthvalue(k).values.item(), d.mean().item()
+
+
+# ------------------------------------------------------------------------------------------------ configs[0]
+@pytest.mark.parametrize("tag", ["default", "sensitised"])
+def test_config1_sacre_coeur_560_864_vs_reference_cpu_golden(golden, cuda, weights, tag, capsys):
+    _tf32_off()
+    g, im = golden(f"config1_{tag}"), golden("config1_images")
+    w, dino = weights[tag]
+    assert roma_b200.state_digest(w) == bytes(g["digest"].numpy().astype(np.uint8)).decode()
+    sub = int(g["sub"])
+    pA, pB = Image.fromarray(im["im_A"].numpy()), Image.fromarray(im["im_B"].numpy())
+    report = {}
+    for name, dt in (("fp32", torch.float32), ("bf16", torch.bfloat16), ("fp16", torch.float16)):
+        model = roma_b200.roma_outdoor(cuda, w, dino, coarse_res=560, upsample_res=864, amp_dtype=dt)
+        warp, cert = model.match(pA, pB, device="cuda")
+        assert warp.shape == (864, 1728, 4) and cert.shape == (864, 1728)
+        report[name] = (_stats(warp[::sub, ::sub].cpu(), g["warp"]), _stats(cert[::sub, ::sub].cpu(), g["certainty"]))
+        del model
+        torch.cuda.empty_cache()
+    with capsys.disabled():
+        for name, (ws, cs) in report.items():
+            print(f"\nconfig 1 [{tag}] {name} bodies vs reference CPU fp32: warp max {ws[0]:.2e} p99.9 {ws[1]:.2e} mean {ws[2]:.2e}; "
+                  f"certainty max {cs[0]:.2e} p99.9 {cs[1]:.2e} mean {cs[2]:.2e}", end="")
+    assert report["fp32"][0][0] < WARP_TOL and report["fp32"][1][0] < CERT_TOL
+    # 16-bit bodies (the reference ships fp16 autocast): the stated budget — max over the field, both inits
+    for name in ("bf16", "fp16"):
+        assert report[name][0][2] < 2e-2 and report[name][1][2] < 5e-2, f"{name} mean deviation out of the documented budget"
+
+
+# ------------------------------------------------------------------------------------------------ configs[1] shape
+def _synthetic_pairs(B, dev, seed=1234):
+    """torch.rand images at 864, ImageNet-normalised; the coarse pass sees the same content at 560."""
+    g = torch.Generator().manual_seed(seed)
+    im = torch.rand(2, B, 3, 864, 864, generator=g).to(dev)
+    mean = torch.tensor([0.485, 0.456, 0.406], device=dev)[:, None, None]
+    std = torch.tensor([0.229, 0.224, 0.225], device=dev)[:, None, None]
+    fA, fB = (im[0] - mean) / std, (im[1] - mean) / std
+    down = lambda t: F.interpolate(t, size=(560, 560), mode="bicubic", antialias=True, align_corners=False)
+    return down(fA), down(fB), fA, fB
+
+
+@need_ref
+@pytest.mark.parametrize("tag", ["default", "sensitised"])
+def test_match_560_864_vs_reference_on_the_same_gpu(cuda, weights, tag, capsys):
+    _tf32_off()
+    w, dino = weights[tag]
+    B = 2
+    cA, cB, fA, fB = _synthetic_pairs(B, cuda)
+    ref = R.reference_roma_outdoor(cuda, w, dino, 560, 864, amp_dtype=torch.float32)
+    warp_r, cert_r, logit_r = R.reference_forward_batched(ref, cA, cB, fA, fB)
+    del ref
+    torch.cuda.empty_cache()
+    rows = []
+    for name, dt in (("fp32", torch.float32), ("bf16", torch.bfloat16), ("fp16", torch.float16)):
+        model = roma_b200.roma_outdoor(cuda, w, dino, coarse_res=560, upsample_res=864, amp_dtype=dt)
+        warp, cert, logits = model.match(fA, fB, batched=True, device="cuda", return_logits=True)
+        assert warp.shape == (B, 864, 1728, 4)
+        rows.append((name, _stats(warp, warp_r), _stats(logits, logit_r), _stats(cert, cert_r)))
+        del model
+        torch.cuda.empty_cache()
+    with capsys.disabled():
+        for name, ws, ls, cs in rows:
+            print(f"\n560->864 x{B} pairs [{tag}] {name} bodies vs reference fp32 on CUDA: warp max {ws[0]:.2e} p99.9 {ws[1]:.2e}; "
+                  f"logits max {ls[0]:.2e} p99.9 {ls[1]:.2e}; certainty max {cs[0]:.2e}", end="")
+    assert rows[0][1][0] < WARP_TOL and rows[0][2][0] < LOGIT_TOL
+
+
+@need_ref
+def test_reference_16bit_autocast_deviation_for_the_record(cuda, weights, capsys):
+    """How far the REFERENCE's own shipped mode (fp16 autocast) and its all-bf16 mode are from its fp32 run on this GPU —
+    the yardstick for the 16-bit rows printed above (same weights, same inputs)."""
+    _tf32_off()
+    w, dino = weights["sensitised"]
+    cA, cB, fA, fB = _synthetic_pairs(1, cuda)
+    outs = {}
+    for name, dt in (("fp32", torch.float32), ("fp16", torch.float16), ("bf16", torch.bfloat16)):
+        ref = R.reference_roma_outdoor(cuda, w, dino, 560, 864, amp_dtype=dt)
+        outs[name] = R.reference_forward_batched(ref, cA, cB, fA, fB)
+        del ref
+        torch.cuda.empty_cache()
+    with capsys.disabled():
+        for name in ("fp16", "bf16"):
+            ws, ls = _stats(outs[name][0], outs["fp32"][0]), _stats(outs[name][2].float(), outs["fp32"][2])
+            print(f"\nreference {name} autocast vs reference fp32 (sensitised, 1 pair): warp max {ws[0]:.2e} mean {ws[2]:.2e}; "
+                  f"logits max {ls[0]:.2e} mean {ls[2]:.2e}", end="")
+
+
+# ------------------------------------------------------------------------------------------------ patch()
+@need_ref
+def test_patch_on_the_real_reference_model(cuda, weights, golden, tmp_path, capsys):
+    """INTEGRATION.md §2 executed: reference roma_outdoor on CUDA (fp32 everywhere) -> match(paths) -> patch(model) -> match
+    again; then sample() and match_keypoints() of the patched model."""
+    _tf32_off()
+    im = golden("config1_images")
+    Image.fromarray(im["im_A"].numpy()).save(tmp_path / "A.png")
+    Image.fromarray(im["im_B"].numpy()).save(tmp_path / "B.png")
+    w, dino = weights["sensitised"]
+    ref = R.reference_roma_outdoor(cuda, w, dino, 560, 864, amp_dtype=torch.float32)
+    import romatch.models.matcher as M
+    import romatch.models.tiny as T
+    saved = (M.local_correlation, M.kde, M.cls_to_flow_refine, T.kde)
+    try:
+        warp0, cert0 = ref.match(str(tmp_path / "A.png"), str(tmp_path / "B.png"), device=cuda)
+        from roma_b200 import _lib
+        n0 = _lib.load().roma_kernel_launches()
+        roma_b200.patch(ref)
+        warp1, cert1 = ref.match(str(tmp_path / "A.png"), str(tmp_path / "B.png"), device=cuda)
+        launched = _lib.load().roma_kernel_launches() - n0
+        ws, cs = _stats(warp1, warp0), _stats(cert1, cert0)
+        torch.cuda.manual_seed(3)
+        m, c = ref.sample(warp1, cert1, num=5000)
+        x = torch.rand(1500, 2, device=cuda) * 2 - 1
+        ia, ib = ref.match_keypoints(x, x.flip(0).contiguous(), warp1, cert1, return_inds=True)
+    finally:
+        M.local_correlation, M.kde, M.cls_to_flow_refine, T.kde = saved
+    with capsys.disabled():
+        print(f"\npatched reference vs unpatched (fp32, 560->864): warp max {ws[0]:.2e}, certainty max {cs[0]:.2e}; "
+              f"{launched} kernels of libroma_b200 launched by the patched match", end="")
+    assert launched >= 20
+    assert ws[0] < WARP_TOL and cs[0] < CERT_TOL
+    assert m.shape == (5000, 4) and c.shape == (5000,) and ia.dtype == torch.int64 and ia.shape == ib.shape
+
+
+@need_ref
+def test_patch_on_the_real_reference_tiny_model(cuda, capsys):
+    _tf32_off()
+    R.import_reference()
+    from romatch.models.tiny import TinyRoMa as RefTiny
+    import romatch.models.tiny as T
+    from roma_b200.host.tiny import XFeatBackbone, random_init_tiny
+    weights, trunk_sd = random_init_tiny(seed=0)
+    trunk = XFeatBackbone()
+    trunk.load_state_dict(trunk_sd)
+    ref = RefTiny(xfeat=trunk)
+    ref.load_state_dict(weights)
+    ref = ref.to(cuda).train(False)
+    g = torch.Generator().manual_seed(4321)
+    imA, imB = torch.rand(1, 3, 480, 640, generator=g).to(cuda), torch.rand(1, 3, 480, 640, generator=g).to(cuda)
+    saved = T.kde
+    try:
+        with torch.inference_mode():
+            warp0, cert0 = ref.match(imA, imB, batched=True)
+            roma_b200.patch(ref)
+            warp1, cert1 = ref.match(imA, imB, batched=True)
+            torch.cuda.manual_seed(5)
+            m, c = ref.sample(warp1[0], cert1[0], num=2000)
+    finally:
+        T.kde = saved
+    ws, cs = _stats(warp1, warp0), _stats(cert1, cert0)
+    with capsys.disabled():
+        print(f"\npatched reference TinyRoMa vs unpatched (480x640): warp max {ws[0]:.2e}, certainty max {cs[0]:.2e}", end="")
+    assert ws[0] < WARP_TOL and cs[0] < CERT_TOL and m.shape == (2000, 4)
+
+
+# ------------------------------------------------------------------------------------------------ behaviours of §8(a)
+def test_attributes_changed_between_calls_on_one_instance(cuda, weights):
+    """README.md:55-61 of the reference: w_resized / h_resized / upsample_res are plain attributes set AFTER construction;
+    nothing may be baked at build time.  One instance re-targeted twice equals fresh instances built at those sizes."""
+    _tf32_off()
+    w, dino = weights["sensitised"]
+    g = torch.Generator().manual_seed(9)
+    A = (torch.rand(3, 300, 400, generator=g) * 255).to(torch.uint8)
+    Bm = (torch.rand(3, 300, 400, generator=g) * 255).to(torch.uint8)
+    one = roma_b200.roma_outdoor(cuda, w, dino, coarse_res=(224, 224), upsample_res=(336, 336), amp_dtype=torch.float32)
+    first = one.match(A, Bm, device="cuda")
+    for coarse, up in (((280, 336), (420, 504)), ((224, 224), (336, 336))):
+        one.h_resized, one.w_resized = coarse
+        one.upsample_res = up
+        got = one.match(A, Bm, device="cuda")
+        fresh = roma_b200.roma_outdoor(cuda, w, dino, coarse_res=coarse, upsample_res=up, amp_dtype=torch.float32)
+        want = fresh.match(A, Bm, device="cuda")
+        assert got[0].shape == (1, up[0], 2 * up[1], 4) or got[0].shape == (up[0], 2 * up[1], 4)
+        assert (got[0] - want[0]).abs().max().item() < 1e-5 and (got[1] - want[1]).abs().max().item() < 1e-5
+    assert (got[0] - first[0]).abs().max().item() < 1e-5                        # back at the first setting: the first result
+    one.upsample_preds = False                                                  # single pass: output at the coarse resolution
+    assert one.match(A, Bm, device="cuda")[0].shape[-3:] == (224, 448, 4)
+
+
+def test_asymmetric_batch(cuda, weights):
+    """demo/demo_3D_effect.py:27: symmetric=False; with a batch the output is (B, H, W, 4) and equals the A->B half of the
+    symmetric result."""
+    _tf32_off()
+    w, dino = weights["sensitised"]
+    g = torch.Generator().manual_seed(10)
+    A = (torch.rand(3, 3, 224, 224, generator=g) * 255).to(torch.uint8)
+    Bm = (torch.rand(3, 3, 224, 224, generator=g) * 255).to(torch.uint8)
+    model = roma_b200.roma_outdoor(cuda, w, dino, coarse_res=(224, 224), upsample_res=(336, 336), amp_dtype=torch.float32)
+    ws, cs = model.match(A, Bm, batched=True, device="cuda")
+    model.symmetric = False
+    wa, ca = model.match(A, Bm, batched=True, device="cuda")
+    assert wa.shape == (3, 336, 336, 4) and ca.shape == (3, 336, 336)
+    assert (wa - ws[:, :, :336]).abs().max().item() < 1e-4 and (ca - cs[:, :, :336]).abs().max().item() < 1e-3
