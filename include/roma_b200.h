@@ -163,6 +163,11 @@ int roma_gp_set_path(int path);
  * updates and all right-hand-side work one step behind on the caller's stream, ordered by events, forked from and
  * joined to the caller's stream inside the call; 0 = every launch on the caller's stream (left-looking). */
 int roma_gp_set_lanes(int on);
+/* 1: the finished panels of the factorisation (L and the solved right-hand sides) are ALSO written as bf16 hi / lo planes
+ * by the panel kernels' epilogue, and the update / syrk / posterior GEMMs read those planes through TMA with no conversion
+ * in their main loop (gemm_planes_kernel: 3-stage ring, three plane pairs per k-block); 0: fp32 operands re-split on the
+ * fly at every visit (the round-1 form).  Needs the two-lane schedule and the 2-plane solve; same products either way. */
+int roma_gp_set_planes(int on);
 /* The tensor-core building block of K1, exposed for unit tests and timing: batched C = A * B^T with
  * A (batch, M, K), B (batch, N, K) row-major in `dtype`, C (batch, M, N) fp32.  fp32 operands are split on the
  * fly into `split` (2 or 3) bf16 planes (3 / 6 tcgen05.mma per k-step, fp32 TMEM accumulate); bf16 / fp16

@@ -41,6 +41,7 @@ SIGNATURES = {
     "roma_gp_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "roma_gp_set_path": (_i, [_i]),
     "roma_gp_set_lanes": (_i, [_i]),
+    "roma_gp_set_planes": (_i, [_i]),
     "roma_local_corr_set_path": (_i, [_i]),
     "roma_tc_gemm_nt": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "roma_gp_posterior": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,

@@ -253,6 +253,7 @@ extern std::atomic<int> g_lanes;         // 1 (default): two-lane schedule; 0: e
 
 struct WorkspaceTC {
     float *xn, *yn, *A, *R, *Ld;
+    uint16_t *Ah, *Al, *Rh, *Rl;         // bf16 hi / lo planes of the finished panels of A (= L) and R (= [Z^T ; W^T])
     int Mp, nb;
     size_t bytes;
 };
@@ -272,9 +273,16 @@ static inline WorkspaceTC carve_tc(void* base, int B, int Nx, int Ny, int D) {
     w.A = take((size_t)B * w.Mp * w.Mp);
     w.R = take((size_t)B * (D + Nx) * w.Mp);
     w.Ld = take((size_t)B * w.nb * kDB * kDB);
+    w.Ah = reinterpret_cast<uint16_t*>(take(((size_t)B * w.Mp * w.Mp + 1) / 2));
+    w.Al = reinterpret_cast<uint16_t*>(take(((size_t)B * w.Mp * w.Mp + 1) / 2));
+    w.Rh = reinterpret_cast<uint16_t*>(take(((size_t)B * (D + Nx) * w.Mp + 1) / 2));
+    w.Rl = reinterpret_cast<uint16_t*>(take(((size_t)B * (D + Nx) * w.Mp + 1) / 2));
     w.bytes = off;
     return w;
 }
+
+extern std::atomic<int> g_planes;        // 1: finished panels are kept as bf16 hi / lo planes and the update / syrk / posterior
+                                         // GEMMs read them through TMA (gemm_planes_kernel); 0: fp32 operands re-split on the fly
 
 // The solve, all as "X * Y^T with both operands K-major" tcgen05 GEMMs.  R = [f^T ; K_xy] ((D + Nx) x Mp) is the
 // TRANSPOSED right-hand side block: forward substitution turns it into [Z^T ; W^T] = [f^T ; K_xy] L^-T, and
@@ -327,6 +335,7 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
     }
 
     Lanes* lanes = (g_lanes.load() != 0 && nb > 1 && nb <= kMaxLaneBlocks) ? lanes_for_current_device() : nullptr;
+    const bool planes = lanes != nullptr && SOLVE_SPLIT == 2 && g_planes.load() != 0 && w.Ah != nullptr;
     std::unique_lock<std::mutex> lanes_lock;
     if (lanes) {
         lanes_lock = std::unique_lock<std::mutex>(lanes->enqueue);
@@ -358,13 +367,28 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
                 L.p[np] = make_problem(w.R, Lk, w.R + k0, RR, kDB, k0, Mp, Mp, Mp, sR, sA, sR, EPI_SUB);
                 if (np == 0) L.tiles0 = L.p[0].tiles_m;
                 L.nprob = np + 1;
-                if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update"))) return rc;
+                bool done = false;
+                if (planes) {
+                    // operands from the planes: L[k0+128:, 0:k0] / R[:, 0:k0] against L[k0:k0+128, 0:k0]
+                    const long long offL = (long long)k0 * Mp;
+                    int q = 0;
+                    if (rem > 0) {
+                        L.p[q].Ah = w.Ah + offL + (long long)kDB * Mp; L.p[q].Al = w.Al + offL + (long long)kDB * Mp;
+                        L.p[q].Bh = w.Ah + offL; L.p[q].Bl = w.Al + offL;
+                        ++q;
+                    }
+                    L.p[q].Ah = w.Rh; L.p[q].Al = w.Rl; L.p[q].Bh = w.Ah + offL; L.p[q].Bl = w.Al + offL;
+                    if ((rc = launch_gemm_planes(L, B, st, "gp update (planes)", &done))) return rc;
+                }
+                if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update"))) return rc;
                 ROMA_CU(cudaEventRecord(lanes->upd[k], st));
             }
             if (rem > 0) {
                 if (k > 0) ROMA_CU(cudaStreamWaitEvent(sc, lanes->upd[k], 0));
                 Launch L{};
                 L.p[0] = make_problem(Ap, Linv, Ap, rem, kDB, kDB, Mp, kDB, Mp, sA, sLd, sA, EPI_STORE);
+                const long long offP = (long long)(k0 + kDB) * Mp + k0;
+                if (planes) { L.p[0].Ph = w.Ah + offP; L.p[0].Pl = w.Al + offP; }      // the finished panel, split once
                 L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
                 if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, sc, "gp panel A"))) return rc;
                 ROMA_CU(cudaEventRecord(lanes->panel[k], sc));
@@ -372,12 +396,18 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
                 S.p[0] = make_problem(Ap, Ap, w.A + (long long)(k0 + kDB) * Mp + (k0 + kDB), rem, rem, kDB, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
                 S.p[0].diag_only = 1;
                 S.nprob = 1; S.tiles0 = S.p[0].tiles_m;
-                if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(S, B, sc, "gp syrk"))) return rc;
+                bool done = false;
+                if (planes) {
+                    S.p[0].Ah = S.p[0].Bh = w.Ah + offP; S.p[0].Al = S.p[0].Bl = w.Al + offP;
+                    if ((rc = launch_gemm_planes(S, B, sc, "gp syrk (planes)", &done))) return rc;
+                }
+                if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(S, B, sc, "gp syrk"))) return rc;
             }
             ROMA_CU(cudaStreamWaitEvent(st, lanes->diag[k], 0));
             {
                 Launch L{};
                 L.p[0] = make_problem(w.R + k0, Linv, w.R + k0, RR, kDB, kDB, Mp, kDB, Mp, sR, sLd, sR, EPI_STORE);
+                if (planes) { L.p[0].Ph = w.Rh + k0; L.p[0].Pl = w.Rl + k0; }
                 L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
                 if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp panel R"))) return rc;
             }
@@ -416,7 +446,12 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
         Launch L{};
         L.p[0] = make_problem(Kxy, w.R, mu, Nx, D, Ny, Mp, Mp, D, sR, sR, (long long)Nx * D, EPI_STORE);
         L.nprob = 1; L.tiles0 = L.p[0].tiles_m * L.p[0].tiles_n;
-        if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp posterior"))) return rc;
+        bool done = false;
+        if (planes) {
+            L.p[0].Ah = w.Rh + (long long)D * Mp; L.p[0].Al = w.Rl + (long long)D * Mp; L.p[0].Bh = w.Rh; L.p[0].Bl = w.Rl;
+            if ((rc = launch_gemm_planes(L, B, st, "gp posterior (planes)", &done))) return rc;
+        }
+        if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp posterior"))) return rc;
     }
     return ROMA_OK;
 }

@@ -431,6 +431,45 @@ kde_exact_fused_kernel(const uint4* __restrict__ qpack, const uint4* __restrict_
 #pragma unroll
         for (int u = 0; u < kFusedTL; ++u) { acc[u][0] = acc[u][1] = acc[u][2] = acc[u][3] = 0.f; }
         for (int G0 = tl0; G0 < ngroups; G0 += 512) {             // k = G0 / 512: ascending = ATen's loop order
+            if (G0 + kFusedTL <= ngroups) {
+                // all kFusedTL groups exist (every iteration but possibly the last): straight-line code, so the 16 MMAs,
+                // packs, clamps, table loads and adds of one iteration interleave freely (a branch per group — the tail form
+                // below — exposes the HMMA and LDS latency once per group: measured 0.80 -> see DESIGN.md at N = 40000)
+                uint32_t b[kFusedTL];
+#pragma unroll
+                for (int u = 0; u < kFusedTL; ++u) b[u] = __ldg(rw + (long long)(G0 + u) * 32);
+#pragma unroll
+                for (int u0 = 0; u0 < kFusedTL; u0 += 4) {
+                    float d[4][4];
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) mma_m16n8k8_f16(d[v], a0, a1, b[u0 + v]);
+                    unsigned ix[4][2];
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        // clamp to [0, cutoff] (half bit patterns of non-negative values order like integers), then x 4 in
+                        // the packed domain: 4 * cutoff < 2^16, so each half becomes the BYTE offset of its table entry
+                        ix[v][0] = __vminu2(__vmaxs2(pack_h2(d[v][0], d[v][1]), 0u), cut2) << 2;
+                        ix[v][1] = __vminu2(__vmaxs2(pack_h2(d[v][2], d[v][3]), 0u), cut2) << 2;
+                    }
+                    const char* lutb = reinterpret_cast<const char*>(lut);
+                    float e[4][4];
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        e[v][0] = *reinterpret_cast<const float*>(lutb + (ix[v][0] & 0xffffu));
+                        e[v][1] = *reinterpret_cast<const float*>(lutb + (ix[v][0] >> 16));
+                        e[v][2] = *reinterpret_cast<const float*>(lutb + (ix[v][1] & 0xffffu));
+                        e[v][3] = *reinterpret_cast<const float*>(lutb + (ix[v][1] >> 16));
+                    }
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        acc[u0 + v][0] += e[v][0];               // (row g,     c = 2 t4)
+                        acc[u0 + v][1] += e[v][1];               // (row g,     c = 2 t4 + 1)
+                        acc[u0 + v][2] += e[v][2];               // (row g + 8, c = 2 t4)
+                        acc[u0 + v][3] += e[v][3];               // (row g + 8, c = 2 t4 + 1)
+                    }
+                }
+                continue;
+            }
             uint32_t b[kFusedTL];
 #pragma unroll
             for (int u = 0; u < kFusedTL; ++u) b[u] = (G0 + u < ngroups) ? __ldg(rw + (long long)(G0 + u) * 32) : 0xffffffffu;

@@ -191,38 +191,80 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
             if (pass == 0) mbar_arrive(&free_bar);
         }
     } else {                                                      // ---- streaming segments: warps 2, 3, 6, 7 ----
-        const int sw = (warp & 1) + ((warp >> 2) << 1);             // 0..3
+        // 16 pixels per warp, items = (pixel, 16-byte vector) pairs spread over the lanes and processed FOUR AT A TIME: all
+        // the loads of a group (4 x f0 or 16 x f1 taps) are issued before any is used — one L2 round trip per group instead of
+        // one per pixel (the first version handled a pixel at a time: 2/3 of the CTA's life was these four warps waiting)
+        const int sw = (warp & 1) + ((warp >> 2) << 1);             // 0..3: pixels [16 sw, 16 sw + 16)
         const int nvec = p.C / 8;
-        for (int m = sw; m < kTilePx; m += 4) {
-            if (s_x0[m] == INT_MIN) continue;
-            const int y = ty0 + (m >> 3), x = tx0 + (m & 7);
-            const long long pix = ((long long)b * p.h + y) * p.w + x;
-            T* row = dout + pix * p.dch;
-            if (p.off_x >= 0) {
-                const T* f0p = f0 + pix * p.C;
-                for (int v = lane; v < nvec; v += 32) *reinterpret_cast<uint4*>(row + p.off_x + v * 8) = ldg16(f0p + v * 8);
+        const int nitems = 16 * nvec;
+        const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
+        const long long rowpix0 = (long long)b * p.h;
+        auto pixel_of = [&](int m, long long& pix) -> bool {
+            if (s_x0[m] == INT_MIN) return false;
+            pix = (rowpix0 + ty0 + (m >> 3)) * p.w + tx0 + (m & 7);
+            return true;
+        };
+        if (p.off_x >= 0) {
+            for (int q0 = lane; q0 < nitems; q0 += 128) {
+                uint4 v[4]; T* dst[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int q = q0 + 32 * u;
+                    dst[u] = nullptr;
+                    long long pix;
+                    if (q < nitems && pixel_of(16 * sw + q / nvec, pix)) {
+                        const int vv = q % nvec;
+                        v[u] = ldg16(f0 + pix * p.C + vv * 8);
+                        dst[u] = dout + pix * p.dch + p.off_x + vv * 8;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) if (dst[u]) *reinterpret_cast<uint4*>(dst[u]) = v[u];
             }
-            if (p.off_xhat >= 0) {
-                const int px0 = s_x0[m], py0 = s_y0[m];
-                const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
-                for (int v = lane; v < nvec; v += 32) {
+        }
+        if (p.off_xhat >= 0) {
+            for (int q0 = lane; q0 < nitems; q0 += 128) {
+                uint4 tap[4][4]; float wgt[4][4]; T* dst[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int q = q0 + 32 * u;
+                    dst[u] = nullptr;
+                    long long pix;
+                    const int m = 16 * sw + (q < nitems ? q / nvec : 0);
+                    if (q < nitems && pixel_of(m, pix)) {
+                        const int vv = q % nvec, px0 = s_x0[m], py0 = s_y0[m];
+                        dst[u] = dout + pix * p.dch + p.off_xhat + vv * 8;
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            const int yy = py0 + (t >> 1), xx = px0 + (t & 1);
+                            const bool in = yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+                            wgt[u][t] = in ? s_w[m][2 + (t >> 1)] * s_w[m][t & 1] : 0.f;
+                            tap[u][t] = in ? ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C + vv * 8) : make_uint4(0u, 0u, 0u, 0u);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (!dst[u]) continue;
                     float xh[8];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) xh[e] = 0.f;
 #pragma unroll
                     for (int t = 0; t < 4; ++t) {
-                        const int yy = py0 + (t >> 1), xx = px0 + (t & 1);
-                        if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
-                            const float wgt = s_w[m][2 + (t >> 1)] * s_w[m][t & 1];
-                            float f[8];
-                            unpack16<T>(ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C + v * 8), f);
+                        float f[8];                       // out-of-image taps: weight 0 x value 0 leaves the sum unchanged
+                        unpack16<T>(tap[u][t], f);
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) xh[e] = fmaf(wgt, f[e], xh[e]);
-                        }
+                        for (int e = 0; e < 8; ++e) xh[e] = fmaf(wgt[u][t], f[e], xh[e]);
                     }
-                    *reinterpret_cast<uint4*>(row + p.off_xhat + v * 8) = pack16<T>(xh);
+                    *reinterpret_cast<uint4*>(dst[u]) = pack16<T>(xh);
                 }
             }
+        }
+        for (int m = 16 * sw; m < 16 * sw + 16; ++m) {
+            long long pix;
+            if (!pixel_of(m, pix)) continue;
+            const int y = ty0 + (m >> 3), x = tx0 + (m & 7);
+            T* row = dout + pix * p.dch;
             if (p.off_emb >= 0 && p.E > 0) {
                 const float dx = p.disp_scale * (s_g[m].x - pixel_center(x, p.w));
                 const float dy = p.disp_scale * (s_g[m].y - pixel_center(y, p.h));

@@ -82,7 +82,8 @@ def test_tile_kernel_vs_per_pixel_kernel_and_oracle(ops, cuda, C, r, h, w, E, dt
     ct, cp = d_tile[:, 2 * C + E:2 * C + E + K].float(), d_px[:, 2 * C + E:2 * C + E + K].float()
     ct, cp = torch.where(finite, ct, torch.zeros_like(ct)), torch.where(finite, cp, torch.zeros_like(cp))
     eps = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
-    tol = 1.5 * eps * torch.maximum(cp.abs(), torch.full_like(cp, 2.0 ** -4)) + 1e-6
+    ulp = 2 * eps * torch.exp2(torch.floor(torch.log2(torch.maximum(cp.abs(), torch.full_like(cp, 2.0 ** -4)))))   # of the 16-bit output
+    tol = 1.5 * ulp + 1e-6
     bad = int(((ct - cp).abs() > tol).sum().item())
     assert bad == 0, f"{bad} correlations further than 1.5 output ulps from the per-pixel kernel; max {(ct - cp).abs().max().item():.3e}"
     assert d_tile[:, 2 * C + E + K:].abs().max().item() == 0 if d_tile.shape[1] > 2 * C + E + K else True

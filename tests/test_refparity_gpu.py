@@ -112,11 +112,15 @@ def test_refiner_inputs_teacher_forced_vs_reference(ops, ref, cuda, visit, dtype
                 want = local_correlation(xf[sl].contiguous(), yf[sl].contiguous(), local_radius=r, flow=flow[sl], sample_mode="bilinear")
             got = d[sl, 2 * C + E:2 * C + E + K].float()
             err = (got - want).abs()
-            # the reference's own fp32 result carries ~sqrt(C) * 2^-24 * |terms| of summation noise: atol 1e-4 at |corr| ~ 1
-            assert bool((err <= _bound(want, dtype, 1e-4)).all()), f"corr max err {err.max().item():.3e} at {name} {kind}"
+            # atol: the reference un-normalises every window tap separately (flow + k * 2 / w, rounded in fp32, then * w / 2), so
+            # its 4 bilinear weights differ from tap to tap by ~1e-5 and a tap within that of a pixel boundary switches
+            # neighbours; the kernel uses the centre's weights for all taps.  Measured max over 18 M values: 1.5e-4
+            assert bool((err <= _bound(want, dtype, 3e-4)).all()), f"corr max err {err.max().item():.3e} at {name} {kind}"
             e_corr = torch.maximum(e_corr, err.max())
             if dtype != torch.float32 and b0 == 0:                   # for the record: the reference's own 16-bit chain vs its fp32 one
-                with torch.no_grad():
+                # as ConvRefiner.forward runs it: under autocast, where grid_sample is on the fp32 list (16-bit features are
+                # up-cast for the sampling, the products and the sum; the result is stored in the feature dtype)
+                with torch.no_grad(), torch.autocast("cuda", dtype=dtype):
                     own = local_correlation(x[sl].contiguous(), y[sl].contiguous(), local_radius=r, flow=flow[sl], sample_mode="bilinear")
                 e_own = (own.float() - want).abs().max()
         msg += f" corr {e_corr.item():.2e}" + (f" (reference's own {str(dtype)[6:]} chain vs its fp32: {e_own.item():.2e})" if dtype != torch.float32 else "")

@@ -14,6 +14,7 @@ dt = getattr(torch, sys.argv[3]) if len(sys.argv) > 3 else torch.bfloat16
 paths = tuple(int(p) for p in sys.argv[4].split(",")) if len(sys.argv) > 4 else (2, 3, 1)
 real = len(sys.argv) > 5 and sys.argv[5] == "real"
 lib = _lib.load()
+PLANES_DEFAULT = 0
 dev = torch.device("cuda:0")
 g = torch.Generator().manual_seed(3)
 C = D = 512
@@ -35,9 +36,10 @@ N = side * side
 flops = B * (2.0 * N * N * C * 2 + N ** 3 / 3 + 2.0 * N * N * D + 2.0 * N * N * D)
 names = {1: "simt", 2: "tcgen05 split3", 3: "tcgen05 split2"}
 for path in paths:
-    for lanes in ((1, 0) if path != 1 else (1,)):
+    for lanes, planes in (((1, 1), (1, 0), (0, 0)) if path == 3 else ((1, 0), (0, 0)) if path != 1 else ((1, 0),)):
         lib.roma_gp_set_path(path)
         lib.roma_gp_set_lanes(lanes)
+        lib.roma_gp_set_planes(planes)
         for _ in range(2):
             mu = ops.gp_posterior(xd, yd, pwd, pbd)
         torch.cuda.synchronize()
@@ -47,8 +49,9 @@ for path in paths:
             mu = ops.gp_posterior(xd, yd, pwd, pbd)
         e.record(); torch.cuda.synchronize()
         ms = s.elapsed_time(e) / 5
-        print(json.dumps({"path": names[path], "schedule": "two-lane" if lanes else "single-stream", "N": N, "B": B, "dtype": str(dt),
+        print(json.dumps({"path": names[path], "schedule": ("two-lane" if lanes else "single-stream") + (" + bf16 planes via TMA" if planes else ""), "N": N, "B": B, "dtype": str(dt),
                           "ms": round(ms, 3), "alg_TFLOPs": round(flops / ms / 1e9, 1),
                           "err_vs_fp64": (mu[:1].cpu() - want).abs().max().item()}))
 lib.roma_gp_set_path(0)
 lib.roma_gp_set_lanes(1)
+lib.roma_gp_set_planes(PLANES_DEFAULT)

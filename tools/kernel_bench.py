@@ -60,8 +60,8 @@ def main():
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--only", default="")
-    ap.add_argument("--local-corr-path", type=int, default=0, help="0 tensor-core dot products (default), 1 SIMT")
-    ap.add_argument("--kde-mode", type=int, default=0, help="roma_kde_set_direct: 0 default (symmetric tensor-core), 3 every pair twice")
+    ap.add_argument("--local-corr-path", type=int, default=0, help="0 shared-patch tiles + per-pixel tensor-core kernel, 1 SIMT, 2 per-pixel tensor-core kernel only")
+    ap.add_argument("--kde-mode", type=int, default=0, help="roma_kde_set_direct: 0 exact (default), 3 tensor-core every pair twice, 4 every pair once")
     ap.add_argument("--scales", default="", help="comma list of refiner visits for --only gather (s16,s8,...,s1u)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -134,7 +134,12 @@ def main():
         from roma_b200 import _lib as _l
         _l.load().roma_kde_set_direct(args.kde_mode)
         for N in (20000, 40000):
-            x = (torch.rand(N, 4, generator=g) * 2 - 1).to(dev)
+            # rows (xA, yA, xB, yB) as sample() draws them from a symmetric warp: a third in a dense cluster, a smooth
+            # correspondence field (the points lie near a 2-D manifold of [-1, 1]^4, like real candidates)
+            a = torch.rand(N, 2, generator=g) * 2 - 1
+            a[:N // 3] = (torch.randn(N // 3, 2, generator=g) * 0.05 + torch.tensor([0.3, -0.2])).clamp(-1, 1)
+            x = torch.cat((a, (a + 0.1 * torch.sin(3 * a.flip(1)) + 0.002 * torch.randn(N, 2, generator=g)).clamp(-1, 1)), dim=1)
+            x = x[torch.randperm(N, generator=g)].contiguous().to(dev)
             for half in (True, False):
                 ms = timeit(lambda: ops.kde(x, half=half), max(3, args.iters // 4), flush)
                 emit(kernel="kde", N=N, half=half, ms=round(ms, 3), Gpairs_per_s=round(N * N / ms / 1e6, 1))
