@@ -695,6 +695,107 @@ static int launch_tiled_r(GatherParams p, cudaStream_t st, int dtype) {
     return check_launch("roma_refiner_gather(local_corr_tile + local_corr_mma)", 2);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Kernel B2: r == 0, 16-bit features, C = 8 * NJ with NJ a power of two (the 64-channel scale-2 visits, Tiny-RoMa's
+// coarse features).  Kernel B spends one thread per 16-byte chunk of d and repeats the pixel decode, the two flow loads
+// and sample_coords for each of a pixel's 18 chunks: measured issue-bound (issue slots 69 % busy at 21 % of the DRAM
+// peak).  Here a thread owns chunk j of the x segment AND of the x_hat segment of its pixel (+ a share of the embedding /
+// padding chunks), so the per-pixel work is done C / 8 times instead of dch / 8 times, the four taps are loaded before
+// any is used, and the blend runs as packed fp32 FMAs (fma.rn.f32x2: the two halves of a 32-bit word ride one
+// instruction).  Same products and order per element as Kernel B: bit-identical output.
+// ------------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float2 unpack_pair(uint32_t w);
+template <> __device__ __forceinline__ float2 unpack_pair<__nv_bfloat16>(uint32_t w) {
+    return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+template <> __device__ __forceinline__ float2 unpack_pair<__half>(uint32_t w) {
+    return __half22float2(*reinterpret_cast<const __half2*>(&w));
+}
+template <> __device__ __forceinline__ float2 unpack_pair<float>(uint32_t) { return make_float2(0.f, 0.f); }
+
+template <typename T, int NJ>
+__global__ void __launch_bounds__(256)
+gather_only_v2_kernel(const GatherParams p, unsigned nthreads) {
+    static_assert(sizeof(T) == 2, "16-bit features");
+    const unsigned idx = blockIdx.x * 256u + threadIdx.x;
+    if (idx >= nthreads) return;
+    const unsigned pix = idx / NJ;
+    const int j = (int)(idx % NJ);
+    const unsigned hw = (unsigned)(p.h * p.w);
+    const unsigned bb = pix / hw, rem = pix - bb * hw;
+    const unsigned yy0 = rem / (unsigned)p.w;
+    const int b = (int)bb, y = (int)yy0, x = (int)(rem - yy0 * (unsigned)p.w);
+    const float* fl = p.flow + (long long)b * p.fs.b + (long long)y * p.fs.y + (long long)x * p.fs.x;
+    const float gx = __ldg(fl), gy = __ldg(fl + p.fs.c);
+    T* row = reinterpret_cast<T*>(p.d) + (long long)pix * p.dch;
+    const T* f0 = reinterpret_cast<const T*>(p.f0);
+    const T* f1 = reinterpret_cast<const T*>(p.f1);
+
+    uint4 xv = make_uint4(0u, 0u, 0u, 0u);
+    if (p.off_x >= 0) xv = ldg16(f0 + (long long)pix * p.C + j * 8);
+    if (p.off_xhat >= 0) {
+        int x0, y0; float wx0, wx1, wy0, wy1;
+        sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+        const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C + j * 8;
+        uint4 tap[4]; float wgt[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
+            const bool in = yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+            wgt[t] = in ? ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0) : 0.f;
+            tap[t] = in ? ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        float2 acc[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[i] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {                       // out-of-image taps: weight 0 x value 0 leaves the sums unchanged
+            const uint32_t w[4] = {tap[t].x, tap[t].y, tap[t].z, tap[t].w};
+            const float2 ww = make_float2(wgt[t], wgt[t]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[i] = __ffma2_rn(ww, unpack_pair<T>(w[i]), acc[i]);
+        }
+        const float o[8] = {acc[0].x, acc[0].y, acc[1].x, acc[1].y, acc[2].x, acc[2].y, acc[3].x, acc[3].y};
+        *reinterpret_cast<uint4*>(row + p.off_xhat + j * 8) = pack16<T>(o);
+    }
+    if (p.off_x >= 0) *reinterpret_cast<uint4*>(row + p.off_x + j * 8) = xv;
+    const int nE = (p.off_emb >= 0) ? p.E >> 3 : 0, nP = (p.dch - p.covered) >> 3;
+    for (int e = j; e < nE + nP; e += NJ) {
+        if (e < nE) {
+            const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+            const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                v[k] = fmaf(__ldg(p.disp_w + 2 * (8 * e + k)), dx, fmaf(__ldg(p.disp_w + 2 * (8 * e + k) + 1), dy, __ldg(p.disp_b + 8 * e + k)));
+            *reinterpret_cast<uint4*>(row + p.off_emb + 8 * e) = pack16<T>(v);
+        } else {
+            *reinterpret_cast<uint4*>(row + p.covered + 8 * (e - nE)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+    }
+}
+
+template <typename T>
+static bool launch_gather_v2(const GatherParams& p, cudaStream_t st) {
+    if constexpr (sizeof(T) == 2) {
+        const int nj = p.C / 8;
+        if (p.C % 8 || (nj & (nj - 1)) || nj > 64 || p.npix * nj >= (1ll << 32) || p.npix >= (1ll << 31)) return false;
+        const unsigned n = (unsigned)(p.npix * nj);
+        const unsigned grid = (n + 255u) / 256u;
+        switch (nj) {
+            case 1:  gather_only_v2_kernel<T, 1><<<grid, 256, 0, st>>>(p, n); break;
+            case 2:  gather_only_v2_kernel<T, 2><<<grid, 256, 0, st>>>(p, n); break;
+            case 4:  gather_only_v2_kernel<T, 4><<<grid, 256, 0, st>>>(p, n); break;
+            case 8:  gather_only_v2_kernel<T, 8><<<grid, 256, 0, st>>>(p, n); break;
+            case 16: gather_only_v2_kernel<T, 16><<<grid, 256, 0, st>>>(p, n); break;
+            case 32: gather_only_v2_kernel<T, 32><<<grid, 256, 0, st>>>(p, n); break;
+            default: gather_only_v2_kernel<T, 64><<<grid, 256, 0, st>>>(p, n); break;
+        }
+        return true;
+    }
+    return false;
+}
+
 template <typename T>
 static int launch_tiled(GatherParams p, cudaStream_t st) {
     if constexpr (sizeof(T) == 2) {
@@ -773,7 +874,9 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
     const bool vec = ptr16 && d16 && p.C % kVec == 0 && p.dch % kVec == 0 &&
                      seg_ok(p.off_x, p.C) && seg_ok(p.off_xhat, p.C) && seg_ok(p.off_emb, p.E);
     auto seg_pad_ok = p.covered % kVec == 0;
-    if (vec && seg_pad_ok) {
+    if (vec && seg_pad_ok && g_local_corr_path.load() != 1 && launch_gather_v2<T>(p, st)) {
+        return check_launch("roma_refiner_gather(gather_only_v2)");
+    } else if (vec && seg_pad_ok) {
         const int cpp = p.dch / kVec;
         const long long n = p.npix * cpp;
         if (n < (1ll << 31)) gather_only_kernel<T, kVec, true><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);

@@ -109,3 +109,31 @@ def test_tile_kernel_takes_the_coherent_tiles(ops, cuda):
     d_tile, d_px = _both_paths(ops, x, y, flow, None, None, r)
     assert not torch.equal(d_tile, d_px)                  # a different fp32 summation order shows in some last bits
     assert (d_tile.float() - d_px.float()).abs().max().item() < 0.05
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("C,E,h,w", [(64, 16, 53, 47), (8, 0, 9, 11), (128, 8, 16, 16), (512, 64, 10, 12)])
+def test_gather_only_v2_is_bit_identical_to_the_chunk_per_thread_kernel(ops, cuda, C, E, h, w, dtype):
+    """r = 0 visits (scale 2, Tiny-RoMa): gather_only_v2_kernel (a thread per (pixel, x / x_hat chunk pair), packed fp32
+    FMAs) against gather_only_kernel (a thread per 16-byte chunk; roma_local_corr_set_path(1) keeps it): same bits."""
+    from roma_b200 import _lib
+    lib = _lib.load()
+    B = 3
+    g = torch.Generator(device="cuda").manual_seed(C + h)
+    x = torch.randn(B, h, w, C, device=cuda, generator=g).to(dtype).permute(0, 3, 1, 2)
+    y = torch.randn(B, h, w, C, device=cuda, generator=g).to(dtype).permute(0, 3, 1, 2)
+    dw = torch.randn(E, 2, 1, 1, device=cuda, generator=g) if E else None
+    db = torch.randn(E, device=cuda, generator=g) if E else None
+    for kind in ("coherent", "incoherent", "shifted"):
+        flow = _flow(kind, B, h, w, cuda, g)
+        try:
+            lib.roma_local_corr_set_path(DEFAULT_PATH)
+            d2 = ops.refiner_inputs(x, y, flow, dw, db, 1.25, None, pad_to=8)
+            lib.roma_local_corr_set_path(1)
+            d1 = ops.refiner_inputs(x, y, flow, dw, db, 1.25, None, pad_to=8)
+        finally:
+            lib.roma_local_corr_set_path(DEFAULT_PATH)
+        assert torch.equal(d2, d1)
+        want = F.grid_sample(y.float(), flow.permute(0, 2, 3, 1), align_corners=False, mode="bilinear")
+        eps = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
+        assert bool(((d2[:, C:2 * C].float() - want).abs() <= 0.51 * 2 * eps * want.abs() + 2e-5).all())
