@@ -155,8 +155,11 @@ int roma_match_epilogue(const float* flow, roma_strides4 flow_strides,
  * workspace: roma_gp_workspace_bytes(B, Nx, Ny, C, D) bytes, 256-byte aligned.
  */
 size_t roma_gp_workspace_bytes(int B, int Nx, int Ny, int C, int D);
-/* Testing / profiling aid: 0 = auto (tcgen05 tensor-core path when the shapes allow, default), 1 = force the fp32
- * SIMT path, 2 = require the tcgen05 path (ROMA_ERR_UNSUPPORTED from roma_gp_posterior when it cannot be used). */
+/* Testing / profiling aid: 0 = auto (default): tcgen05 tensor-core path when the shapes allow, fp32 operands of the solve
+ * split into THREE bf16 planes (fp32-grade products; what parity with the reference needs on ill-conditioned K_yy);
+ * 1 = force the fp32 SIMT path; 2 = require the tcgen05 path (3-plane solve; ROMA_ERR_UNSUPPORTED from roma_gp_posterior
+ * when it cannot be used); 3 = tcgen05 path with a TWO-plane solve (3 instead of 6 MMAs per k-step, ~2^-16 relative
+ * products: 20 % faster, measurably less accurate — opt-in). */
 int roma_gp_set_path(int path);
 /* Schedule of the tcgen05 factorisation: 1 (default) = two lanes — the dependent chain diag -> panel -> syrk of the
  * blocked Cholesky on a high-priority helper stream owned by the library (one per device), the block-column

@@ -147,7 +147,11 @@ extern "C" int roma_gp_posterior(const void* x, const void* y, const float* pos_
         gp::WorkspaceTC w = gp::carve_tc(workspace, B, Nx, Ny, D);
         ROMA_REQUIRE(workspace_bytes >= w.bytes, ROMA_ERR_WORKSPACE, "roma_gp_posterior: workspace %zu < required %zu", workspace_bytes, w.bytes);
 #define ROMA_GP_TC(TT, SP) gp::run_tc<TT, SP>((const TT*)x, (const TT*)y, pos_w, pos_b, mu, B, Nx, Ny, C, D, hy, wy, T, sigma_noise, eps, w, st)
-        const bool two = (path != 2);      // auto: 2-plane solve (3 MMAs per k-step); path 2 keeps 3 planes
+        // auto / path 2: 3-plane solve (6 MMAs per k-step, fp32-grade products).  The 2-plane solve (path 3: 3 MMAs, ~2^-16
+        // relative) is 20 % faster but NOT accurate enough when K_yy is ill-conditioned: on photographs with flat regions
+        // (config 1, sacre_coeur) its 1e-4-level error in mu flips near-tied coarse arg-maxes on 0.14 % of the pixels, while
+        // the 3-plane solve agrees with the reference on the same GPU to 3e-6 everywhere (tools/config1_gp_paths.py)
+        const bool two = (path == 3);
         switch (dtype) {
             case ROMA_F32:  return two ? ROMA_GP_TC(float, 2) : ROMA_GP_TC(float, 3);
             case ROMA_F16:  return two ? ROMA_GP_TC(__half, 2) : ROMA_GP_TC(__half, 3);

@@ -77,6 +77,36 @@ __device__ __forceinline__ bool tile_window_fits(const GatherParams& p, int b, i
     return lo_x != INT_MAX && (long long)hi_x - lo_x + W2 <= pw && (long long)hi_y - lo_y + W2 <= pw;
 }
 
+// The per-pixel kernel's side of the same decision, for FOUR horizontally adjacent tiles at once (one prologue — flow loads,
+// window bases, reduction, barrier — per 256 pixels instead of per 64): thread t looks at pixel t & 63 of tile
+// 4 * blockIdx.x + (t >> 6).  bit q of the result is set when tile q belongs to local_corr_tile_kernel (or lies outside the image).
+// red: 32 ints of shared scratch.  Same arithmetic as tile_window_fits: both kernels must agree on every tile.
+constexpr int kPxTilesPerCta = 4;
+__device__ __forceinline__ unsigned tiles_fit4(const GatherParams& p, int b, int ty0, int txq0, int pw, int* red) {
+    const int t = threadIdx.x, q = t >> 6, m = t & 63;
+    int lo_x = INT_MAX, hi_x = INT_MIN, lo_y = INT_MAX, hi_y = INT_MIN;
+    const int y = ty0 + (m >> 3), x = (txq0 + q) * kTileSide + (m & 7);
+    if (y < p.h && x < p.w) {
+        const float* f = p.flow + (long long)b * p.fs.b + (long long)y * p.fs.y + (long long)x * p.fs.x;
+        int x0, y0; float wx0, wx1, wy0, wy1;
+        sample_coords(__ldg(f), __ldg(f + p.fs.c), p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+        lo_x = hi_x = x0; lo_y = hi_y = y0;
+    }
+    lo_x = __reduce_min_sync(0xffffffffu, lo_x); hi_x = __reduce_max_sync(0xffffffffu, hi_x);
+    lo_y = __reduce_min_sync(0xffffffffu, lo_y); hi_y = __reduce_max_sync(0xffffffffu, hi_y);
+    if ((t & 31) == 0) { int* r = red + (t >> 5) * 4; r[0] = lo_x; r[1] = hi_x; r[2] = lo_y; r[3] = hi_y; }
+    __syncthreads();
+    const int W2 = 2 * p.r + 2;
+    unsigned fits = 0u;
+#pragma unroll
+    for (int k = 0; k < kPxTilesPerCta; ++k) {
+        const int* r = red + k * 8;
+        const int lx = min(r[0], r[4]), hx = max(r[1], r[5]), ly = min(r[2], r[6]), hy = max(r[3], r[7]);
+        if (lx == INT_MAX || ((long long)hx - lx + W2 <= pw && (long long)hy - ly + W2 <= pw)) fits |= 1u << k;
+    }
+    return fits;
+}
+
 __device__ __forceinline__ void tmem_ld4_nowait(uint32_t taddr, float* v) {
     uint32_t* r = reinterpret_cast<uint32_t*>(v);
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
@@ -138,7 +168,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
 
     if (warp == 0) {
         if (lane == 0) {                                         // ---- TMA producer ----
-            for (int it = 0; it < 2 * nkb; ++it) {
+            for (int it = 0; it < ((p.dbg & 2) ? 0 : 2 * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
                 if (it >= 2) tc::mbar_wait(&empty_bar[s], (uint32_t)(((it >> 1) - 1) & 1));
                 unsigned char* sa = smem + (size_t)s * G::STAGE;
@@ -150,7 +180,12 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {                                         // ---- MMA issuer ----
-            for (int it = 0; it < 2 * nkb; ++it) {
+            if (p.dbg & 2) {                                     // timing aid: no main loop (the products are garbage)
+                tc::umma_commit(&done_bar);
+                tc::mbar_wait(&free_bar, 0);
+                tc::umma_commit(&done_bar);
+            }
+            for (int it = 0; it < ((p.dbg & 2) ? 0 : 2 * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
                 if (pass == 1 && kb == 0) { tc::mbar_wait(&free_bar, 0); tc::tc_fence_after(); }   // pass 0 drained from TMEM
                 tc::mbar_wait(&full_bar[s], (uint32_t)((it >> 1) & 1));
@@ -173,7 +208,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
         for (int pass = 0; pass < 2; ++pass) {
             tc::mbar_wait(&done_bar, (uint32_t)pass);
             tc::tc_fence_after();
-            for (int qy = 0; qy < G::ROWS; ++qy) {
+            for (int qy = 0; qy < ((p.dbg & 4) ? 0 : G::ROWS); ++qy) {
                 constexpr int NL = (G::PW + 3) / 4;
                 float v[NL * 4];
 #pragma unroll
@@ -196,7 +231,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
         // one per pixel (the first version handled a pixel at a time: 2/3 of the CTA's life was these four warps waiting)
         const int sw = (warp & 1) + ((warp >> 2) << 1);             // 0..3: pixels [16 sw, 16 sw + 16)
         const int nvec = p.C / 8;
-        const int nitems = 16 * nvec;
+        const int nitems = (p.dbg & 1) ? 0 : 16 * nvec;
         const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
         const long long rowpix0 = (long long)b * p.h;
         auto pixel_of = [&](int m, long long& pix) -> bool {
@@ -279,7 +314,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc(tmem_base, kTmemCols);
     // ---- blend: corr[ky][kx] = wy0 (wx0 D[ky][kx] + wx1 D[ky][kx+1]) + wy1 (wx0 D[ky+1][kx] + wx1 D[ky+1][kx+1]) ----
-    if (p.off_corr >= 0) {
+    if (p.off_corr >= 0 && !(p.dbg & 8)) {
         const float inv_sqrt_c = rsqrtf((float)p.C);
         for (int idx = tid; idx < kTilePx * G::K; idx += 256) {
             const int m = idx / G::K, k = idx - m * G::K;

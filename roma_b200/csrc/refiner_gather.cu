@@ -30,6 +30,7 @@ struct GatherParams {
     long long npix;
     int tile_px;     // pixels per CTA tile (local-corr kernel)
     int covered;     // channels written by the enabled segments; [covered, dch) is zero-filled pitch padding
+    int dbg;         // timing aid for local_corr_tile_kernel (bit 0: no streaming segments, 1: no main loop, 2: no extraction, 3: no blend)
     int tile_pw;     // > 0: 8 x 8 pixel tiles (grid = tiles_x, tiles_y, B); the per-pixel kernel SKIPS tiles whose windows fit
                      // a tile_pw x tile_pw patch (they are computed by local_corr_tile_kernel, local_corr_tile.cuh)
 };
@@ -384,19 +385,21 @@ local_corr_mma_kernel(const GatherParams p) {
     long long tile_start = (long long)blockIdx.x * p.tile_px;
     int tile_n = p.tile_px;
     const bool tiled = p.tile_pw > 0;
+    unsigned fits = 0u;
     if (tiled) {
-        // 8 x 8 tiles; the tiles whose windows fit the shared patch belong to local_corr_tile_kernel
-        __shared__ int red[8];
-        bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
-        if (tile_window_fits(p, blockIdx.z, blockIdx.y * kTileSide, blockIdx.x * kTileSide, p.tile_pw, red,
-                             valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0)) return;
-        tile_n = kTilePx;
+        // four 8 x 8 tiles per CTA; the tiles whose windows fit the shared patch belong to local_corr_tile_kernel
+        __shared__ int red[32];
+        fits = tiles_fit4(p, blockIdx.z, blockIdx.y * kTileSide, blockIdx.x * kPxTilesPerCta, p.tile_pw, red);
+        if (fits == 0xfu) return;
+        tile_n = kPxTilesPerCta * kTilePx;
     } else if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
 
     for (int lp = warp; lp < tile_n; lp += 8) {
         long long pix = tile_start + lp;
         if (tiled) {
-            const int ty = blockIdx.y * kTileSide + (lp >> 3), tx = blockIdx.x * kTileSide + (lp & 7);
+            const int q = lp >> 6, m = lp & 63;
+            if ((fits >> q) & 1u) continue;
+            const int ty = blockIdx.y * kTileSide + (m >> 3), tx = (blockIdx.x * kPxTilesPerCta + q) * kTileSide + (m & 7);
             if (ty >= p.h || tx >= p.w) continue;
             pix = ((long long)blockIdx.z * p.h + ty) * p.w + tx;
         }
@@ -659,7 +662,8 @@ gather_only_kernel(const GatherParams p, long long nthreads, int cpp) {
 
 // 0 (default): shared-patch tcgen05 tiles for coherent tiles (r = 2, 3) + per-pixel tensor-core kernel for the rest;
 // 1: SIMT FMA dot products (v2); 2: per-pixel tensor-core kernel for every pixel (the round-1 default)
-static std::atomic<int> g_local_corr_path{2};   // TODO(validated on the GPU): 0
+static std::atomic<int> g_local_corr_path{0};
+static std::atomic<int> g_tile_dbg{0};          // roma_local_corr_set_path(path | dbg << 8): phases of the tile kernel switched off (timing only)
 
 // Shared-patch path: both kernels over the same (tiles_x, tiles_y, B) grid; every tile is taken by exactly one of them.
 // ROMA_ERR_UNSUPPORTED (silently, no message) when the feature maps cannot be described to TMA -> caller falls back.
@@ -684,13 +688,15 @@ static int launch_tiled_r(GatherParams p, cudaStream_t st, int dtype) {
         DeviceOnce::done(configured);
     }
     p.tile_pw = G::PW;
+    p.dbg = g_tile_dbg.load();
     const dim3 grid((unsigned)cdiv(p.w, kTileSide), (unsigned)cdiv(p.h, kTileSide), (unsigned)p.B);
     local_corr_tile_kernel<T, R><<<grid, 256, G::SMEM, st>>>(p, maps);
+    const dim3 gpx((unsigned)cdiv((int)grid.x, kPxTilesPerCta), grid.y, grid.z);
     switch (p.C) {
-        case 512: local_corr_mma_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
-        case 256: local_corr_mma_kernel<T, 4><<<grid, 256, 0, st>>>(p); break;
-        case 128: local_corr_mma_kernel<T, 2><<<grid, 256, 0, st>>>(p); break;
-        default:  local_corr_mma_kernel<T, 1><<<grid, 256, 0, st>>>(p); break;
+        case 512: local_corr_mma_kernel<T, 8><<<gpx, 256, 0, st>>>(p); break;
+        case 256: local_corr_mma_kernel<T, 4><<<gpx, 256, 0, st>>>(p); break;
+        case 128: local_corr_mma_kernel<T, 2><<<gpx, 256, 0, st>>>(p); break;
+        default:  local_corr_mma_kernel<T, 1><<<gpx, 256, 0, st>>>(p); break;
     }
     return check_launch("roma_refiner_gather(local_corr_tile + local_corr_mma)", 2);
 }
@@ -900,8 +906,9 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
 }  // namespace roma
 
 extern "C" int roma_local_corr_set_path(int path) {
-    if (path < 0 || path > 2) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 default, 1 SIMT, 2 per-pixel tensor-core only)", path);
-    roma::g_local_corr_path.store(path);
+    if (path < 0 || (path & 0xff) > 2 || (path >> 8) > 15) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 default, 1 SIMT, 2 per-pixel tensor-core only)", path);
+    roma::g_local_corr_path.store(path & 0xff);
+    roma::g_tile_dbg.store(path >> 8);
     return ROMA_OK;
 }
 
@@ -943,7 +950,7 @@ extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* 
     p.disp_w = disp_w; p.disp_b = disp_b; p.disp_scale = disp_scale;
     p.d = d; p.dch = d_channels; p.off_x = off_x; p.off_xhat = off_xhat; p.off_emb = off_emb; p.off_corr = off_corr;
     p.B = B; p.C = C; p.h = h; p.w = w; p.h1 = h1; p.w1 = w1; p.E = E; p.r = r;
-    p.npix = (long long)B * h * w; p.tile_px = 0; p.covered = covered; p.tile_pw = 0;
+    p.npix = (long long)B * h * w; p.tile_px = 0; p.covered = covered; p.tile_pw = 0; p.dbg = 0;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (dtype) {
         case ROMA_F32:  return launch_gather<float>(p, st);

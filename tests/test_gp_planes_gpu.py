@@ -22,6 +22,7 @@ def test_gp_planes_equals_split_on_the_fly(cuda, side_x, side_y, B, dtype):
     pw, pb = torch.randn(D, 2, generator=g) * 0.5, torch.randn(D, generator=g) * 0.5
     cl = lambda t: t.to(cuda).contiguous(memory_format=torch.channels_last)
     try:
+        lib.roma_gp_set_path(3)                                              # the plane form exists for the 2-plane solve (opt-in)
         lib.roma_gp_set_planes(0)
         mu0 = ops.gp_posterior(cl(x), cl(y), pw.to(cuda), pb.to(cuda))
         lib.roma_gp_set_planes(1)
@@ -30,6 +31,7 @@ def test_gp_planes_equals_split_on_the_fly(cuda, side_x, side_y, B, dtype):
         mu2 = ops.gp_posterior(cl(x), cl(y), pw.to(cuda), pb.to(cuda))
     finally:
         lib.roma_gp_set_planes(PLANES_DEFAULT)
+        lib.roma_gp_set_path(0)
     want = O.gp_posterior(x[:1].float(), y[:1].float(), pw, pb, dtype=torch.float64)
     e0 = (mu0[:1].cpu().double() - want).abs().max().item()
     e1 = (mu1[:1].cpu().double() - want).abs().max().item()

@@ -222,7 +222,7 @@ def test_gp_tcgen05_path(ops, cuda, dtype, h1, w1, h2, w2, path):
     want = O.gp_posterior(x.float(), y.float(), pw, pb, dtype=torch.float64)
     ref32 = O.gp_posterior(x.float(), y.float(), pw, pb)
     try:
-        assert lib.roma_gp_set_path(path) == 0        # 2: 3-plane solve GEMMs, 3: 2-plane (the default)
+        assert lib.roma_gp_set_path(path) == 0        # 2: 3-plane solve GEMMs (the default), 3: 2-plane (opt-in)
         got_tc = ops.gp_posterior(x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda))
         assert lib.roma_gp_set_path(1) == 0
         got_simt = ops.gp_posterior(x.to(cuda), y.to(cuda), pw.to(cuda), pb.to(cuda))

@@ -11,7 +11,7 @@ import torch.nn.functional as F
 from oracle import roma_oracle as O
 
 pytestmark = pytest.mark.gpu
-DEFAULT_PATH = 2          # library default of roma_local_corr_set_path
+DEFAULT_PATH = 0          # library default of roma_local_corr_set_path
 
 
 @pytest.fixture(scope="module")

@@ -76,6 +76,8 @@ def test_config1_sacre_coeur_560_864(golden, cuda, weights, tag, tmp_path, capsy
         model = roma_b200.roma_outdoor(cuda, w, dino, coarse_res=560, upsample_res=864, amp_dtype=dt)
         warp, cert = model.match(pA, pB, device="cuda")
         assert warp.shape == (864, 1728, 4) and cert.shape == (864, 1728)
+        if name == "fp32":
+            warp32 = warp
         ws, cs = _stats(warp[::sub, ::sub].cpu(), g["warp"]), _stats(cert[::sub, ::sub].cpu(), g["certainty"])
         f_cpu = _frac_above(warp[::sub, ::sub].cpu(), g["warp"], WARP_TOL)
         report[name] = (ws, cs, f_cpu)
@@ -92,7 +94,12 @@ def test_config1_sacre_coeur_560_864(golden, cuda, weights, tag, tmp_path, capsy
         for ln in lines:
             print(f"\nconfig 1 [{tag}] " + ln, end="")
     if ref_warp is not None:
-        assert report["fp32"][3][0] < WARP_TOL and report["fp32"][4][0] < CERT_TOL         # (i): the same GPU, fp32
+        f_gpu = _frac_above(warp32, ref_warp, WARP_TOL)
+        if tag == "sensitised":        # well-conditioned arg-max (the reference's CUDA and CPU runs agree everywhere): strict
+            assert f_ref == 0.0
+            assert report["fp32"][3][0] < WARP_TOL and report["fp32"][4][0] < CERT_TOL      # (i): the same GPU, fp32
+        else:                          # default init: the reference disagrees with ITSELF (CUDA vs CPU) on f_ref of the pixels
+            assert f_gpu <= 1.5 * f_ref + 1e-3 and report["fp32"][4][0] < CERT_TOL
         assert report["fp32"][2] <= 1.5 * f_ref + 1e-3                                      # (ii): no further from the CPU than the reference is
     assert report["fp32"][2] < 0.05 and report["fp32"][0][2] < 5e-3
     # 16-bit bodies (the reference ships fp16 autocast): mean deviation inside the documented budget

@@ -11,7 +11,7 @@ from oracle import roma_oracle as O
 side = int(sys.argv[1]) if len(sys.argv) > 1 else 40
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 16
 dt = getattr(torch, sys.argv[3]) if len(sys.argv) > 3 else torch.bfloat16
-paths = tuple(int(p) for p in sys.argv[4].split(",")) if len(sys.argv) > 4 else (2, 3, 1)
+paths = tuple(int(p) for p in sys.argv[4].split(",")) if len(sys.argv) > 4 else (2, 3, 1)      # 2 = default (3-plane)
 real = len(sys.argv) > 5 and sys.argv[5] == "real"
 lib = _lib.load()
 PLANES_DEFAULT = 0
