@@ -781,6 +781,91 @@ gather_only_v2_kernel(const GatherParams p, unsigned nthreads) {
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Kernel C2: the finest visits of roma_outdoor — C = 9 channels (proj["1"], 18-byte rows: only 2-byte aligned), E = 6,
+// d row = [x(9) | x_hat(9) | emb(6)] = 24 elements = 48 bytes.  Kernel C issues 45 two-byte loads per pixel and stages
+// rows through shared memory; here a thread reads each 18-byte row as FIVE aligned 32-bit words (funnel-shifted when the
+// row starts on an odd half-word), blends channel pairs with packed fp32 FMAs and writes its 48-byte row with three
+// 16-byte stores.  Same products and order per element: bit-identical output.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void load_row9(const T* ptr, uint32_t (&w)[5]) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(ptr);
+    const uint32_t* q = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+    uint32_t r[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) r[i] = __ldg(q + i);
+    if (a & 2) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) w[i] = __funnelshift_r(r[i], r[i + 1], 16);
+        w[4] = r[4] >> 16;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) w[i] = r[i];
+        w[4] = r[4] & 0xffffu;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_c9_kernel(const GatherParams p, unsigned npix) {
+    static_assert(sizeof(T) == 2, "16-bit features");
+    const unsigned pix = blockIdx.x * 256u + threadIdx.x;
+    if (pix >= npix) return;
+    const unsigned hw = (unsigned)(p.h * p.w);
+    const unsigned bb = pix / hw, rem = pix - bb * hw;
+    const unsigned yy0 = rem / (unsigned)p.w;
+    const int b = (int)bb, y = (int)yy0, x = (int)(rem - yy0 * (unsigned)p.w);
+    const float* fl = p.flow + (long long)b * p.fs.b + (long long)y * p.fs.y + (long long)x * p.fs.x;
+    const float gx = __ldg(fl), gy = __ldg(fl + p.fs.c);
+    const T* f0 = reinterpret_cast<const T*>(p.f0);
+    const T* f1b = reinterpret_cast<const T*>(p.f1) + (long long)b * p.h1 * p.w1 * 9;
+    int x0, y0; float wx0, wx1, wy0, wy1;
+    sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+    uint32_t xw[5], tap[4][5]; float wgt[4];
+    load_row9<T>(f0 + (long long)pix * 9, xw);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
+        const bool in = yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+        wgt[t] = in ? ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0) : 0.f;
+        if (in) load_row9<T>(f1b + ((long long)yy * p.w1 + xx) * 9, tap[t]);
+        else {
+#pragma unroll
+            for (int i = 0; i < 5; ++i) tap[t][i] = 0u;
+        }
+    }
+    float2 acc[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) acc[i] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const float2 ww = make_float2(wgt[t], wgt[t]);
+#pragma unroll
+        for (int i = 0; i < 5; ++i) acc[i] = __ffma2_rn(ww, unpack_pair<T>(tap[t][i]), acc[i]);
+    }
+    const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+    const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+    unsigned short o[24];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) o[i] = (unsigned short)((i & 1) ? (xw[i >> 1] >> 16) : (xw[i >> 1] & 0xffffu));
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+        const T v = Elem<T>::from_f((i & 1) ? acc[i >> 1].y : acc[i >> 1].x);
+        o[9 + i] = *reinterpret_cast<const unsigned short*>(&v);
+    }
+#pragma unroll
+    for (int e = 0; e < 6; ++e) {
+        const T v = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx, fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
+        o[18 + e] = *reinterpret_cast<const unsigned short*>(&v);
+    }
+    uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.d) + (long long)pix * 24);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        dst[k] = make_uint4((uint32_t)o[8 * k] | ((uint32_t)o[8 * k + 1] << 16), (uint32_t)o[8 * k + 2] | ((uint32_t)o[8 * k + 3] << 16),
+                            (uint32_t)o[8 * k + 4] | ((uint32_t)o[8 * k + 5] << 16), (uint32_t)o[8 * k + 6] | ((uint32_t)o[8 * k + 7] << 16));
+}
+
 template <typename T>
 static bool launch_gather_v2(const GatherParams& p, cudaStream_t st) {
     if constexpr (sizeof(T) == 2) {
@@ -887,6 +972,20 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
         const long long n = p.npix * cpp;
         if (n < (1ll << 31)) gather_only_kernel<T, kVec, true><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);
         else gather_only_kernel<T, kVec, false><<<cdiv(n, 256), 256, 0, st>>>(p, n, cpp);
+    } else if (sizeof(T) == 2 && p.C == 9 && p.E == 6 && p.dch == 24 && p.off_x == 0 && p.off_xhat == 9 && p.off_emb == 18 && d16 &&
+               ((reinterpret_cast<uintptr_t>(p.f0) | reinterpret_cast<uintptr_t>(p.f1)) & 3u) == 0 && p.npix < (1ll << 31) &&
+               g_local_corr_path.load() != 1) {
+        // the last two bytes of the last aligned word of a row may lie past an odd-sized tensor: stay inside the allocation
+        // (feature tensors here are batch * h * w * 9 halves: the total is even exactly when the pixel count is even)
+        if constexpr (sizeof(T) == 2) {
+            const bool even0 = ((p.npix) & 1) == 0, even1 = (((long long)p.B * p.h1 * p.w1) & 1) == 0;
+            if (even0 && even1) {
+                gather_c9_kernel<T><<<cdiv(p.npix, 256), 256, 0, st>>>(p, (unsigned)p.npix);
+                return check_launch("roma_refiner_gather(gather_c9)");
+            }
+        }
+        const size_t smem = (size_t)256 * p.dch * sizeof(T) + 32;
+        gather_rowstage_kernel<T><<<cdiv(p.npix, 256), 256, smem, st>>>(p);
     } else if ((size_t)256 * p.dch * sizeof(T) + 32 <= 96 * 1024 && p.C <= 64) {
         // small, unalignable rows (the 9-channel finest scale): one thread per pixel + staged span write
         const size_t smem = (size_t)256 * p.dch * sizeof(T) + 32;

@@ -112,7 +112,7 @@ def test_tile_kernel_takes_the_coherent_tiles(ops, cuda):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
-@pytest.mark.parametrize("C,E,h,w", [(64, 16, 53, 47), (8, 0, 9, 11), (128, 8, 16, 16), (512, 64, 10, 12)])
+@pytest.mark.parametrize("C,E,h,w", [(64, 16, 53, 47), (8, 0, 9, 11), (128, 8, 16, 16), (512, 64, 10, 12), (9, 6, 20, 22), (9, 6, 33, 18), (9, 6, 5, 7)])
 def test_gather_only_v2_is_bit_identical_to_the_chunk_per_thread_kernel(ops, cuda, C, E, h, w, dtype):
     """r = 0 visits (scale 2, Tiny-RoMa): gather_only_v2_kernel (a thread per (pixel, x / x_hat chunk pair), packed fp32
     FMAs) against gather_only_kernel (a thread per 16-byte chunk; roma_local_corr_set_path(1) keeps it): same bits."""
