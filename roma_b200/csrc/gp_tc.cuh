@@ -253,7 +253,7 @@ extern std::atomic<int> g_lanes;         // 1 (default): two-lane schedule; 0: e
 
 struct WorkspaceTC {
     float *xn, *yn, *A, *R, *Ld;
-    uint16_t *Ah, *Al, *Rh, *Rl;         // bf16 hi / lo planes of the finished panels of A (= L) and R (= [Z^T ; W^T])
+    uint16_t *Apl[3], *Rpl[3];           // bf16 planes (hi, mid, lo) of the finished panels of A (= L) and R (= [Z^T ; W^T])
     int Mp, nb;
     size_t bytes;
 };
@@ -273,10 +273,8 @@ static inline WorkspaceTC carve_tc(void* base, int B, int Nx, int Ny, int D) {
     w.A = take((size_t)B * w.Mp * w.Mp);
     w.R = take((size_t)B * (D + Nx) * w.Mp);
     w.Ld = take((size_t)B * w.nb * kDB * kDB);
-    w.Ah = reinterpret_cast<uint16_t*>(take(((size_t)B * w.Mp * w.Mp + 1) / 2));
-    w.Al = reinterpret_cast<uint16_t*>(take(((size_t)B * w.Mp * w.Mp + 1) / 2));
-    w.Rh = reinterpret_cast<uint16_t*>(take(((size_t)B * (D + Nx) * w.Mp + 1) / 2));
-    w.Rl = reinterpret_cast<uint16_t*>(take(((size_t)B * (D + Nx) * w.Mp + 1) / 2));
+    for (int q = 0; q < 3; ++q) w.Apl[q] = reinterpret_cast<uint16_t*>(take(((size_t)B * w.Mp * w.Mp + 1) / 2));
+    for (int q = 0; q < 3; ++q) w.Rpl[q] = reinterpret_cast<uint16_t*>(take(((size_t)B * (D + Nx) * w.Mp + 1) / 2));
     w.bytes = off;
     return w;
 }
@@ -335,7 +333,7 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
     }
 
     Lanes* lanes = (g_lanes.load() != 0 && nb > 1 && nb <= kMaxLaneBlocks) ? lanes_for_current_device() : nullptr;
-    const bool planes = lanes != nullptr && SOLVE_SPLIT == 2 && g_planes.load() != 0 && w.Ah != nullptr;
+    const bool planes = lanes != nullptr && g_planes.load() != 0 && w.Apl[0] != nullptr;
     std::unique_lock<std::mutex> lanes_lock;
     if (lanes) {
         lanes_lock = std::unique_lock<std::mutex>(lanes->enqueue);
@@ -373,12 +371,11 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
                     const long long offL = (long long)k0 * Mp;
                     int q = 0;
                     if (rem > 0) {
-                        L.p[q].Ah = w.Ah + offL + (long long)kDB * Mp; L.p[q].Al = w.Al + offL + (long long)kDB * Mp;
-                        L.p[q].Bh = w.Ah + offL; L.p[q].Bl = w.Al + offL;
+                        for (int s = 0; s < SOLVE_SPLIT; ++s) { L.p[q].Apl[s] = w.Apl[s] + offL + (long long)kDB * Mp; L.p[q].Bpl[s] = w.Apl[s] + offL; }
                         ++q;
                     }
-                    L.p[q].Ah = w.Rh; L.p[q].Al = w.Rl; L.p[q].Bh = w.Ah + offL; L.p[q].Bl = w.Al + offL;
-                    if ((rc = launch_gemm_planes(L, B, st, "gp update (planes)", &done))) return rc;
+                    for (int s = 0; s < SOLVE_SPLIT; ++s) { L.p[q].Apl[s] = w.Rpl[s]; L.p[q].Bpl[s] = w.Apl[s] + offL; }
+                    if ((rc = launch_gemm_planes<SOLVE_SPLIT>(L, B, st, "gp update (planes)", &done))) return rc;
                 }
                 if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update"))) return rc;
                 ROMA_CU(cudaEventRecord(lanes->upd[k], st));
@@ -388,7 +385,7 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
                 Launch L{};
                 L.p[0] = make_problem(Ap, Linv, Ap, rem, kDB, kDB, Mp, kDB, Mp, sA, sLd, sA, EPI_STORE);
                 const long long offP = (long long)(k0 + kDB) * Mp + k0;
-                if (planes) { L.p[0].Ph = w.Ah + offP; L.p[0].Pl = w.Al + offP; }      // the finished panel, split once
+                if (planes) { L.p[0].nplanes = SOLVE_SPLIT; for (int s = 0; s < SOLVE_SPLIT; ++s) L.p[0].Pout[s] = w.Apl[s] + offP; }   // the finished panel, split once
                 L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
                 if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, sc, "gp panel A"))) return rc;
                 ROMA_CU(cudaEventRecord(lanes->panel[k], sc));
@@ -398,8 +395,8 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
                 S.nprob = 1; S.tiles0 = S.p[0].tiles_m;
                 bool done = false;
                 if (planes) {
-                    S.p[0].Ah = S.p[0].Bh = w.Ah + offP; S.p[0].Al = S.p[0].Bl = w.Al + offP;
-                    if ((rc = launch_gemm_planes(S, B, sc, "gp syrk (planes)", &done))) return rc;
+                    for (int s = 0; s < SOLVE_SPLIT; ++s) S.p[0].Apl[s] = S.p[0].Bpl[s] = w.Apl[s] + offP;
+                    if ((rc = launch_gemm_planes<SOLVE_SPLIT>(S, B, sc, "gp syrk (planes)", &done))) return rc;
                 }
                 if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(S, B, sc, "gp syrk"))) return rc;
             }
@@ -407,7 +404,7 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
             {
                 Launch L{};
                 L.p[0] = make_problem(w.R + k0, Linv, w.R + k0, RR, kDB, kDB, Mp, kDB, Mp, sR, sLd, sR, EPI_STORE);
-                if (planes) { L.p[0].Ph = w.Rh + k0; L.p[0].Pl = w.Rl + k0; }
+                if (planes) { L.p[0].nplanes = SOLVE_SPLIT; for (int s = 0; s < SOLVE_SPLIT; ++s) L.p[0].Pout[s] = w.Rpl[s] + k0; }
                 L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
                 if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp panel R"))) return rc;
             }
@@ -448,8 +445,8 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
         L.nprob = 1; L.tiles0 = L.p[0].tiles_m * L.p[0].tiles_n;
         bool done = false;
         if (planes) {
-            L.p[0].Ah = w.Rh + (long long)D * Mp; L.p[0].Al = w.Rl + (long long)D * Mp; L.p[0].Bh = w.Rh; L.p[0].Bl = w.Rl;
-            if ((rc = launch_gemm_planes(L, B, st, "gp posterior (planes)", &done))) return rc;
+            for (int s = 0; s < SOLVE_SPLIT; ++s) { L.p[0].Apl[s] = w.Rpl[s] + (long long)D * Mp; L.p[0].Bpl[s] = w.Rpl[s]; }
+            if ((rc = launch_gemm_planes<SOLVE_SPLIT>(L, B, st, "gp posterior (planes)", &done))) return rc;
         }
         if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp posterior"))) return rc;
     }

@@ -12,9 +12,10 @@
 // fp32 accumulator in TMEM, and each pixel picks its (2r+2)^2 neighbour products out of its TMEM lane and blends them with
 // the shared bilinear weights exactly like the per-pixel kernels.  ~13 KB per pixel through L2 instead of 64 + 4.
 //
-// Tiles whose windows do not fit the patch (incoherent flow, flow discontinuities, non-finite flow) are left to the
-// per-pixel kernel, which runs over the same tile grid and takes exactly the tiles this kernel declines: both evaluate
-// tile_window_fits() on the same inputs.
+// Tiles whose windows do not fit the patch (incoherent flow, flow discontinuities, non-finite flow) take the per-pixel
+// form inside the SAME CTA (local_corr_px, one warp per pixel): one launch, one decision per tile.  (A first version ran
+// the per-pixel kernel as a second launch over the same grid; its ~35 k CTAs that only re-derived the verdict and exited
+// cost 0.17 / 0.8 ms at s8' / s4' — measured with the phase switches of roma_local_corr_set_path.)
 //
 // CTA = 256 threads, 2 CTAs / SM (<= 256 TMEM columns, ~100 KB of shared memory each):
 //   warp 0 lane 0  TMA producer (2-stage ring over the C / 64 k-blocks, two patch halves = two passes over K)
@@ -120,7 +121,7 @@ __host__ __device__ constexpr uint32_t instr_desc_n(uint32_t fmt, uint32_t n) {
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 
-template <typename T, int R>
+template <typename T, int R, int VPL>
 __global__ void __launch_bounds__(256, 2)
 local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps maps) {
     using G = TileGeom<R>;
@@ -136,7 +137,18 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tx0 = blockIdx.x * kTileSide, ty0 = blockIdx.y * kTileSide, b = blockIdx.z;
     bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
-    if (!tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0)) return;
+    if (!tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0)) {
+        // incoherent tile (or a flow discontinuity / non-finite flow): every pixel pulls its own window — the per-pixel form,
+        // one warp per pixel, its scratch carved out of this CTA's dynamic shared memory
+        unsigned char* base = smem_raw + ((16u - (tc::smem_u32(smem_raw) & 15u)) & 15u);
+        float* Dsm = reinterpret_cast<float*>(base) + warp * (G::NN + 4);
+        T* f0w = reinterpret_cast<T*>(base + 8 * (G::NN + 4) * sizeof(float)) + warp * (64 * VPL);
+        for (int lp = warp; lp < kTilePx; lp += 8) {
+            const int y = ty0 + (lp >> 3), x = tx0 + (lp & 7);
+            if (y < p.h && x < p.w) local_corr_px<T, VPL>(p, ((long long)b * p.h + y) * p.w + x, lane, Dsm, f0w);
+        }
+        return;
+    }
     if (tid < kTilePx) {
         s_x0[tid] = valid ? x0 : INT_MIN; s_y0[tid] = y0;
         s_w[tid][0] = wx0; s_w[tid][1] = wx1; s_w[tid][2] = wy0; s_w[tid][3] = wy1;
@@ -149,7 +161,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     constexpr uint32_t idesc = instr_desc_n(kFmt, (uint32_t)G::NPAD);
     constexpr uint32_t kTmemCols = 256;
 
-    if (warp == 0) tc::tmem_alloc(&tmem_slot, kTmemCols);
+    if (warp == 0 && !(p.dbg & 32)) tc::tmem_alloc(&tmem_slot, kTmemCols);
     if (tid == 0) {
         for (int s = 0; s < 2; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
         tc::mbar_init(&done_bar, 1);
@@ -166,7 +178,8 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     const T* f1 = reinterpret_cast<const T*>(p.f1);
     T* dout = reinterpret_cast<T*>(p.d);
 
-    if (warp == 0) {
+    if (p.dbg & 16) {
+    } else if (warp == 0) {
         if (lane == 0) {                                         // ---- TMA producer ----
             for (int it = 0; it < ((p.dbg & 2) ? 0 : 2 * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
@@ -312,7 +325,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     }
     tc::tc_fence_before();
     __syncthreads();
-    if (warp == 0) tc::tmem_dealloc(tmem_base, kTmemCols);
+    if (warp == 0 && !(p.dbg & 32)) tc::tmem_dealloc(tmem_base, kTmemCols);
     // ---- blend: corr[ky][kx] = wy0 (wx0 D[ky][kx] + wx1 D[ky][kx+1]) + wy1 (wx0 D[ky+1][kx] + wx1 D[ky+1][kx+1]) ----
     if (p.off_corr >= 0 && !(p.dbg & 8)) {
         const float inv_sqrt_c = rsqrtf((float)p.C);

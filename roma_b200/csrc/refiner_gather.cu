@@ -59,10 +59,6 @@ __device__ __forceinline__ void sample_coords(float gx, float gy, int w1, int h1
     wy0 = (fy + 1.f) - iy; wy1 = iy - fy;
 }
 
-}  // namespace roma
-#include "local_corr_tile.cuh"
-namespace roma {
-
 // ------------------------------------------------------------------------------------------------
 // Kernel A: r > 0.  One warp per pixel; CTA tile = tile_px consecutive (b,y,x)-flattened pixels.
 // ------------------------------------------------------------------------------------------------
@@ -364,146 +360,135 @@ template <> struct Mma16816<float> {
     static __device__ __forceinline__ void run(float (&)[4], uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
 };
 
+// One pixel by one warp: the body shared by the flat per-pixel kernel and the incoherent tiles of local_corr_tile_kernel.
+// Dsm: (2r+2)^2 floats, f0w: 64 * VPL elements (16-byte aligned), both private to the warp.
 template <typename T, int VPL>
-__global__ void __launch_bounds__(256, 2)
-local_corr_mma_kernel(const GatherParams p) {
+__device__ __forceinline__ void local_corr_px(const GatherParams& p, long long pix, int lane, float* Dsm, T* f0w) {
     static_assert(sizeof(T) == 2, "local_corr_mma is for 16-bit feature types");
-    constexpr int kMaxNN = 256;                  // (2r+2)^2 for r <= 7
-    __shared__ float Dall[8][kMaxNN + 4];
-    __shared__ __align__(16) T f0s[8][64 * VPL];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t4 = lane & 3;
     const int W2 = 2 * p.r + 2, NN = W2 * W2, K1 = 2 * p.r + 1, K = K1 * K1;
-    float* Dsm = Dall[warp];
-    T* f0w = f0s[warp];
     const float inv_sqrt_c = rsqrtf((float)p.C);
     const T* f0 = reinterpret_cast<const T*>(p.f0);
     const T* f1 = reinterpret_cast<const T*>(p.f1);
     T* dout = reinterpret_cast<T*>(p.d);
     const int covered = p.covered;
+    int b, y, x; float gx, gy;
+    pixel_coords(p, pix, b, y, x, gx, gy);
+    int x0, y0; float wx0, wx1, wy0, wy1;
+    sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
+    T* row = dout + pix * p.dch;
 
-    long long tile_start = (long long)blockIdx.x * p.tile_px;
-    int tile_n = p.tile_px;
-    const bool tiled = p.tile_pw > 0;
-    unsigned fits = 0u;
-    if (tiled) {
-        // four 8 x 8 tiles per CTA; the tiles whose windows fit the shared patch belong to local_corr_tile_kernel
-        __shared__ int red[32];
-        fits = tiles_fit4(p, blockIdx.z, blockIdx.y * kTileSide, blockIdx.x * kPxTilesPerCta, p.tile_pw, red);
-        if (fits == 0xfu) return;
-        tile_n = kPxTilesPerCta * kTilePx;
-    } else if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
-
-    for (int lp = warp; lp < tile_n; lp += 8) {
-        long long pix = tile_start + lp;
-        if (tiled) {
-            const int q = lp >> 6, m = lp & 63;
-            if ((fits >> q) & 1u) continue;
-            const int ty = blockIdx.y * kTileSide + (m >> 3), tx = (blockIdx.x * kPxTilesPerCta + q) * kTileSide + (m & 7);
-            if (ty >= p.h || tx >= p.w) continue;
-            pix = ((long long)blockIdx.z * p.h + ty) * p.w + tx;
-        }
-        int b, y, x; float gx, gy;
-        pixel_coords(p, pix, b, y, x, gx, gy);
-        int x0, y0; float wx0, wx1, wy0, wy1;
-        sample_coords(gx, gy, p.w1, p.h1, x0, y0, wx0, wx1, wy0, wy1);
-        T* row = dout + pix * p.dch;
-
-        // f0 row -> shared (B operand of every MMA of this pixel) and -> the x segment of d
-        const T* f0p = f0 + pix * p.C;
+    // f0 row -> shared (B operand of every MMA of this pixel) and -> the x segment of d
+    const T* f0p = f0 + pix * p.C;
 #pragma unroll
-        for (int q = 0; q < (8 * VPL + 31) / 32; ++q) {
+    for (int q = 0; q < (8 * VPL + 31) / 32; ++q) {
+        const int v = lane + 32 * q;
+        if (v < 8 * VPL) {
+            const uint4 raw = ldg16(f0p + v * 8);
+            *reinterpret_cast<uint4*>(f0w + v * 8) = raw;
+            if (p.off_x >= 0) *reinterpret_cast<uint4*>(row + p.off_x + v * 8) = raw;
+        }
+    }
+    __syncwarp();
+    const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
+    for (int n0 = 0; n0 < NN; n0 += 8) {
+        // A-fragment rows 2j and 2j+1 are the two 64-byte halves of a 128-byte piece of neighbour n0 + j (rows
+        // 8.. : neighbour n0 + 4 + j), so the 8 lanes of a quarter-warp read ONE full line per 16-byte load
+        // (4 L1 wavefronts per instruction, not 8).  The B fragment carries the matching f0 channels in the
+        // column of the same parity: D[g][g & 1] is the partial dot product of row g, and the two halves meet
+        // with one shuffle.
+        const T* src[2];
+#pragma unroll
+        for (int hr = 0; hr < 2; ++hr) {
+            const int n = n0 + (g >> 1) + 4 * hr;
+            const int j = n / W2, i = n - j * W2;
+            const int yy = y0 + j - p.r, xx = x0 + i - p.r;
+            const bool ok = n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+            src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + 32 * (g & 1) + t4 * 8 : nullptr;
+        }
+        float dA[4] = {0.f, 0.f, 0.f, 0.f}, dB[4] = {0.f, 0.f, 0.f, 0.f};
+        uint4 u[2][VPL];
+#pragma unroll
+        for (int kb = 0; kb < VPL; ++kb) {
+#pragma unroll
+            for (int hr = 0; hr < 2; ++hr)
+                u[hr][kb] = src[hr] ? ldg16(src[hr] + 64 * kb) : make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int kb = 0; kb < VPL; ++kb) {
+            const uint4 fb = *reinterpret_cast<const uint4*>(f0w + 64 * kb + 32 * (g & 1) + t4 * 8);
+            Mma16816<T>::run(dA, u[0][kb].x, u[1][kb].x, u[0][kb].y, u[1][kb].y, fb.x, fb.y);
+            Mma16816<T>::run(dB, u[0][kb].z, u[1][kb].z, u[0][kb].w, u[1][kb].w, fb.z, fb.w);
+        }
+        float vlo = (g & 1) ? dA[1] + dB[1] : dA[0] + dB[0];
+        float vhi = (g & 1) ? dA[3] + dB[3] : dA[2] + dB[2];
+        vlo += __shfl_xor_sync(0xffffffffu, vlo, 4);
+        vhi += __shfl_xor_sync(0xffffffffu, vhi, 4);
+        if (t4 == 0 && (g & 1) == 0) {
+            if (n0 + (g >> 1) < NN) Dsm[n0 + (g >> 1)] = vlo;
+            if (n0 + 4 + (g >> 1) < NN) Dsm[n0 + 4 + (g >> 1)] = vhi;
+        }
+    }
+    __syncwarp();
+    // x_hat: 4-tap blend of the centre neighbours, lanes over the row's 16-byte vectors (lines just loaded: L1 hits)
+    if (p.off_xhat >= 0) {
+#pragma unroll
+        for (int q = 0; q < (VPL + 3) / 4; ++q) {
             const int v = lane + 32 * q;
             if (v < 8 * VPL) {
-                const uint4 raw = ldg16(f0p + v * 8);
-                *reinterpret_cast<uint4*>(f0w + v * 8) = raw;
-                if (p.off_x >= 0) *reinterpret_cast<uint4*>(row + p.off_x + v * 8) = raw;
-            }
-        }
-        __syncwarp();
-        const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
-        for (int n0 = 0; n0 < NN; n0 += 8) {
-            // A-fragment rows 2j and 2j+1 are the two 64-byte halves of a 128-byte piece of neighbour n0 + j (rows
-            // 8.. : neighbour n0 + 4 + j), so the 8 lanes of a quarter-warp read ONE full line per 16-byte load
-            // (4 L1 wavefronts per instruction, not 8).  The B fragment carries the matching f0 channels in the
-            // column of the same parity: D[g][g & 1] is the partial dot product of row g, and the two halves meet
-            // with one shuffle.
-            const T* src[2];
+                float xh[8];
 #pragma unroll
-            for (int hr = 0; hr < 2; ++hr) {
-                const int n = n0 + (g >> 1) + 4 * hr;
-                const int j = n / W2, i = n - j * W2;
-                const int yy = y0 + j - p.r, xx = x0 + i - p.r;
-                const bool ok = n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
-                src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + 32 * (g & 1) + t4 * 8 : nullptr;
-            }
-            float dA[4] = {0.f, 0.f, 0.f, 0.f}, dB[4] = {0.f, 0.f, 0.f, 0.f};
-            uint4 u[2][VPL];
+                for (int e = 0; e < 8; ++e) xh[e] = 0.f;
 #pragma unroll
-            for (int kb = 0; kb < VPL; ++kb) {
+                for (int t = 0; t < 4; ++t) {
+                    const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
+                    if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
+                        const float wgt = ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0);
+                        float f[8];
+                        unpack16<T>(ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C + v * 8), f);
 #pragma unroll
-                for (int hr = 0; hr < 2; ++hr)
-                    u[hr][kb] = src[hr] ? ldg16(src[hr] + 64 * kb) : make_uint4(0u, 0u, 0u, 0u);
-            }
-#pragma unroll
-            for (int kb = 0; kb < VPL; ++kb) {
-                const uint4 fb = *reinterpret_cast<const uint4*>(f0w + 64 * kb + 32 * (g & 1) + t4 * 8);
-                Mma16816<T>::run(dA, u[0][kb].x, u[1][kb].x, u[0][kb].y, u[1][kb].y, fb.x, fb.y);
-                Mma16816<T>::run(dB, u[0][kb].z, u[1][kb].z, u[0][kb].w, u[1][kb].w, fb.z, fb.w);
-            }
-            float vlo = (g & 1) ? dA[1] + dB[1] : dA[0] + dB[0];
-            float vhi = (g & 1) ? dA[3] + dB[3] : dA[2] + dB[2];
-            vlo += __shfl_xor_sync(0xffffffffu, vlo, 4);
-            vhi += __shfl_xor_sync(0xffffffffu, vhi, 4);
-            if (t4 == 0 && (g & 1) == 0) {
-                if (n0 + (g >> 1) < NN) Dsm[n0 + (g >> 1)] = vlo;
-                if (n0 + 4 + (g >> 1) < NN) Dsm[n0 + 4 + (g >> 1)] = vhi;
-            }
-        }
-        __syncwarp();
-        // x_hat: 4-tap blend of the centre neighbours, lanes over the row's 16-byte vectors (lines just loaded: L1 hits)
-        if (p.off_xhat >= 0) {
-#pragma unroll
-            for (int q = 0; q < (VPL + 3) / 4; ++q) {
-                const int v = lane + 32 * q;
-                if (v < 8 * VPL) {
-                    float xh[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) xh[e] = 0.f;
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
-                        if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
-                            const float wgt = ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0);
-                            float f[8];
-                            unpack16<T>(ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C + v * 8), f);
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) xh[e] = fmaf(wgt, f[e], xh[e]);
-                        }
+                        for (int e = 0; e < 8; ++e) xh[e] = fmaf(wgt, f[e], xh[e]);
                     }
-                    *reinterpret_cast<uint4*>(row + p.off_xhat + v * 8) = pack16<T>(xh);
                 }
+                *reinterpret_cast<uint4*>(row + p.off_xhat + v * 8) = pack16<T>(xh);
             }
         }
-        if (p.off_corr >= 0) {
-            for (int k = lane; k < K; k += 32) {
-                const int ky = k / K1, kx = k - ky * K1;
-                const float* D0 = Dsm + ky * W2 + kx;
-                const float c = wy0 * (wx0 * D0[0] + wx1 * D0[1]) + wy1 * (wx0 * D0[W2] + wx1 * D0[W2 + 1]);
-                row[p.off_corr + k] = Elem<T>::from_f(c * inv_sqrt_c);
-            }
-        }
-        if (p.off_emb >= 0 && p.E > 0) {
-            const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
-            const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
-            for (int e = lane; e < p.E; e += 32)
-                row[p.off_emb + e] = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx,
-                                                          fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
-        }
-        if (lane < p.dch - covered) row[covered + lane] = Elem<T>::from_f(0.f);      // zero the pitch padding (< 8 channels)
-        __syncwarp();
     }
+    if (p.off_corr >= 0) {
+        for (int k = lane; k < K; k += 32) {
+            const int ky = k / K1, kx = k - ky * K1;
+            const float* D0 = Dsm + ky * W2 + kx;
+            const float c = wy0 * (wx0 * D0[0] + wx1 * D0[1]) + wy1 * (wx0 * D0[W2] + wx1 * D0[W2 + 1]);
+            row[p.off_corr + k] = Elem<T>::from_f(c * inv_sqrt_c);
+        }
+    }
+    if (p.off_emb >= 0 && p.E > 0) {
+        const float dx = p.disp_scale * (gx - pixel_center(x, p.w));
+        const float dy = p.disp_scale * (gy - pixel_center(y, p.h));
+        for (int e = lane; e < p.E; e += 32)
+            row[p.off_emb + e] = Elem<T>::from_f(fmaf(__ldg(p.disp_w + 2 * e), dx,
+                                                      fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
+    }
+    if (lane < p.dch - covered) row[covered + lane] = Elem<T>::from_f(0.f);      // zero the pitch padding (< 8 channels)
+    __syncwarp();
 }
+
+template <typename T, int VPL>
+__global__ void __launch_bounds__(256, 2)
+local_corr_mma_kernel(const GatherParams p) {
+    constexpr int kMaxNN = 256;                  // (2r+2)^2 for r <= 7
+    __shared__ float Dall[8][kMaxNN + 4];
+    __shared__ __align__(16) T f0s[8][64 * VPL];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long tile_start = (long long)blockIdx.x * p.tile_px;
+    int tile_n = p.tile_px;
+    if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
+    for (int lp = warp; lp < tile_n; lp += 8) local_corr_px<T, VPL>(p, tile_start + lp, lane, Dall[warp], f0s[warp]);
+}
+
+}  // namespace roma
+#include "local_corr_tile.cuh"
+namespace roma {
 
 // ------------------------------------------------------------------------------------------------
 // Kernel C: r == 0 with rows that cannot be vectorised (C*sizeof(T) not a multiple of 16, e.g. the 9-channel
@@ -683,22 +668,19 @@ static int launch_tiled_r(GatherParams p, cudaStream_t st, int dtype) {
         tma::encode_tiled(&maps.f1, dtype, 4, p.f1, d1, s1, b1, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return ROMA_ERR_UNSUPPORTED;
     static DeviceOnce::Flags configured;
     if (DeviceOnce::pending(configured)) {
-        cudaError_t err = cudaFuncSetAttribute(local_corr_tile_kernel<T, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+        cudaError_t err = cudaFuncSetAttribute(local_corr_tile_kernel<T, R, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+        if (err == cudaSuccess) err = cudaFuncSetAttribute(local_corr_tile_kernel<T, R, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
         if (err != cudaSuccess) return fail((int)err, "roma_refiner_gather: smem opt-in (%zu B): %s", G::SMEM, cudaGetErrorString(err));
         DeviceOnce::done(configured);
     }
     p.tile_pw = G::PW;
     p.dbg = g_tile_dbg.load();
     const dim3 grid((unsigned)cdiv(p.w, kTileSide), (unsigned)cdiv(p.h, kTileSide), (unsigned)p.B);
-    local_corr_tile_kernel<T, R><<<grid, 256, G::SMEM, st>>>(p, maps);
-    const dim3 gpx((unsigned)cdiv((int)grid.x, kPxTilesPerCta), grid.y, grid.z);
     switch (p.C) {
-        case 512: local_corr_mma_kernel<T, 8><<<gpx, 256, 0, st>>>(p); break;
-        case 256: local_corr_mma_kernel<T, 4><<<gpx, 256, 0, st>>>(p); break;
-        case 128: local_corr_mma_kernel<T, 2><<<gpx, 256, 0, st>>>(p); break;
-        default:  local_corr_mma_kernel<T, 1><<<gpx, 256, 0, st>>>(p); break;
+        case 512: local_corr_tile_kernel<T, R, 8><<<grid, 256, G::SMEM, st>>>(p, maps); break;
+        default:  local_corr_tile_kernel<T, R, 4><<<grid, 256, G::SMEM, st>>>(p, maps); break;
     }
-    return check_launch("roma_refiner_gather(local_corr_tile + local_corr_mma)", 2);
+    return check_launch("roma_refiner_gather(local_corr_tile)");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -915,7 +897,7 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
             p.tile_px = 32;
             const int grid = cdiv(p.npix, p.tile_px);
             if constexpr (sizeof(T) == 2) {
-                if (g_local_corr_path.load() == 0 && (p.r == 2 || p.r == 3) && p.h == p.h1 && p.w == p.w1 && p.off_corr >= 0) {
+                if (g_local_corr_path.load() == 0 && (p.r == 2 || p.r == 3) && (p.C == 512 || p.C == 256) && p.h == p.h1 && p.w == p.w1 && p.off_corr >= 0) {
                     // shared-patch tiles (coherent flow) + per-pixel kernel for the tiles that decline (local_corr_tile.cuh)
                     const int rc = launch_tiled<T>(p, st);
                     if (rc != ROMA_ERR_UNSUPPORTED) return rc;
@@ -1005,7 +987,7 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
 }  // namespace roma
 
 extern "C" int roma_local_corr_set_path(int path) {
-    if (path < 0 || (path & 0xff) > 2 || (path >> 8) > 15) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 default, 1 SIMT, 2 per-pixel tensor-core only)", path);
+    if (path < 0 || (path & 0xff) > 2 || (path >> 8) > 63) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 default, 1 SIMT, 2 per-pixel tensor-core only)", path);
     roma::g_local_corr_path.store(path & 0xff);
     roma::g_tile_dbg.store(path >> 8);
     return ROMA_OK;

@@ -51,11 +51,11 @@ struct Problem {
     // the 4x4-strided subset) and writes the record to part[((b * slots + slot) * 6 + field) * M + m],
     // slot = 2 * tn + half, slots = 2 * tiles_n.  Column n is pixel (n / w1, n % w1) of image 1.
     float* part; float scale; int w1; float lx0, lxs, ly0, lys;
-    // bf16 hi / lo planes of the stored result (v = hi + lo up to 2^-17 relative), same indexing as C (b * sC + m * ldc + n):
+    // bf16 planes of the stored result (v = p0 + p1 (+ p2): 2^-17 / 2^-25 relative), same indexing as C (b * sC + m * ldc + n):
     // written by the epilogue when non-null, consumed as ready-made split operands by gemm_planes_kernel (below)
-    uint16_t* Ph; uint16_t* Pl;
-    // split operands of gemm_planes_kernel: hi / lo planes of A and B (pre-offset like A and B; element = bf16)
-    const uint16_t* Ah; const uint16_t* Al; const uint16_t* Bh; const uint16_t* Bl;
+    uint16_t* Pout[3]; int nplanes;     // nplanes = 2 (hi, lo) or 3 (hi, mid, lo); 0 = no plane output
+    // split operands of gemm_planes_kernel: the planes of A and B (pre-offset like A and B; element = bf16)
+    const uint16_t* Apl[3]; const uint16_t* Bpl[3];
 };
 
 struct Launch {
@@ -309,24 +309,25 @@ __device__ __forceinline__ void tile_epilogue(const Problem& P, int b, int m0, i
             for (int i = 0; i < 32; ++i)
                 if (nb0 + i < P.store_n) Ctb[(long long)(nb0 + i) * P.ldct + m] = v[i];      // lanes -> consecutive m: coalesced
         }
-        if (P.Ph && m < P.store_m && nb0 + 32 <= P.store_n) {                                // finished panel -> bf16 hi / lo planes
-            uint16_t* ph = P.Ph + (long long)b * P.sC + (long long)m * P.ldc + nb0;
-            uint16_t* pl = P.Pl + (long long)b * P.sC + (long long)m * P.ldc + nb0;
+        if (P.nplanes && m < P.store_m && nb0 + 32 <= P.store_n) {                           // finished panel -> bf16 planes
+            const long long off = (long long)b * P.sC + (long long)m * P.ldc + nb0;
 #pragma unroll
-            for (int i = 0; i < 32; i += 8) {
-                uint4 hv, lv;
-                uint32_t* h32 = reinterpret_cast<uint32_t*>(&hv);
-                uint32_t* l32 = reinterpret_cast<uint32_t*>(&lv);
+            for (int pl = 0; pl < 3; ++pl) {
+                if (pl >= P.nplanes) break;
+                uint16_t* dst = P.Pout[pl] + off;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const __nv_bfloat16 h0 = __float2bfloat16_rn(v[i + 2 * e]), h1 = __float2bfloat16_rn(v[i + 2 * e + 1]);
-                    const __nv_bfloat16 l0 = __float2bfloat16_rn(v[i + 2 * e] - __bfloat162float(h0));
-                    const __nv_bfloat16 l1 = __float2bfloat16_rn(v[i + 2 * e + 1] - __bfloat162float(h1));
-                    h32[e] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-                    l32[e] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+                for (int i = 0; i < 32; i += 8) {
+                    uint4 hv;
+                    uint32_t* h32 = reinterpret_cast<uint32_t*>(&hv);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[i + 2 * e]), h1 = __float2bfloat16_rn(v[i + 2 * e + 1]);
+                        v[i + 2 * e] -= __bfloat162float(h0);                                  // the remainder feeds the next plane
+                        v[i + 2 * e + 1] -= __bfloat162float(h1);
+                        h32[e] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+                    }
+                    *reinterpret_cast<uint4*>(dst + i) = hv;
                 }
-                *reinterpret_cast<uint4*>(ph + i) = hv;
-                *reinterpret_cast<uint4*>(pl + i) = lv;
             }
         }
     }
@@ -562,15 +563,17 @@ static int launch_gemm_nt_16(const Launch& L, int batch, cudaStream_t st, const 
 // like gemm_nt_tma_kernel: warp 0 lane 0 produces, warp 1 lane 0 issues tcgen05.mma and releases stages by
 // tcgen05.commit, all 8 warps run the epilogue.  3 stages x 32 KB: two CTAs per SM, one tile's epilogue (EPI_SUB reads and
 // rewrites 64 KB of C) under the other's main loop.
-struct PlaneMaps { CUtensorMap ah[2], al[2], bh[2], bl[2]; };
+struct PlaneMaps { CUtensorMap a[2][3], b[2][3]; };      // [problem][plane]
 constexpr int kPlStages = 3;
 constexpr size_t kPlSmem = (size_t)kPlStages * 2 * kPlaneBytes + 1024;
 
-template <int kUnused>      // a template only for its linkage: this header is included by several translation units
+// SPLIT = 2: pairs (0,0) | (0,1) (1,0); SPLIT = 3: (0,0) | (0,1) (1,0) (0,2) (1,1) (2,0)  — the first into the main tile
+template <int SPLIT>
 __global__ void __launch_bounds__(kThreads, 2) gemm_planes_kernel(const Launch L, const __grid_constant__ PlaneMaps maps) {
     extern __shared__ unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kPlStages], empty_bar[kPlStages], done_bar;
     __shared__ uint32_t tmem_slot;
+    constexpr int NP = SPLIT * (SPLIT + 1) / 2;              // plane pairs per k-block: 3 or 6
 
     int t = blockIdx.x;
     const int pi = (L.nprob > 1 && t >= L.tiles0) ? 1 : 0;
@@ -582,7 +585,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_planes_kernel(const Launch L
     const int m0 = tm * BM, n0 = tn * BN;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const int nit = 3 * ((P.K + BK - 1) / BK);
+    const int nit = NP * ((P.K + BK - 1) / BK);
     constexpr uint32_t idesc = instr_desc(1u);
 
     if (warp == 0) tmem_alloc(&tmem_slot, 256);
@@ -590,30 +593,33 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_planes_kernel(const Launch L
         for (int s = 0; s < kPlStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         mbar_init(&done_bar, 1);
         fence_barrier_init();
-        tma::prefetch_map(&maps.ah[pi]); tma::prefetch_map(&maps.al[pi]);
-        tma::prefetch_map(&maps.bh[pi]); tma::prefetch_map(&maps.bl[pi]);
+#pragma unroll
+        for (int q = 0; q < SPLIT; ++q) { tma::prefetch_map(&maps.a[pi][q]); tma::prefetch_map(&maps.b[pi][q]); }
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    // pair v -> (plane of A, plane of B), ordered by i + j
+    auto pa = [](int v) { return SPLIT == 2 ? (v == 2 ? 1 : 0) : (v == 2 ? 1 : v == 4 ? 1 : v == 5 ? 2 : 0); };
+    auto pb = [](int v) { return SPLIT == 2 ? (v == 1 ? 1 : 0) : (v == 1 ? 1 : v == 3 ? 2 : v == 4 ? 1 : 0); };
 
     if (warp == 0) {
         if (lane == 0) {                                         // ---- producer ----
             for (int it = 0; it < nit; ++it) {
-                const int s = it % kPlStages, kb = it / 3, v = it - 3 * kb;       // v: 0 = (hi, hi), 1 = (hi, lo), 2 = (lo, hi)
+                const int s = it % kPlStages, kb = it / NP, v = it - NP * kb;
                 if (it >= kPlStages) mbar_wait(&empty_bar[s], (uint32_t)((it / kPlStages - 1) & 1));
                 unsigned char* sa = smem + (size_t)s * 2 * kPlaneBytes;
                 tma::mbar_expect_tx(&full_bar[s], 2u * kPlaneBytes);
-                tma::load_3d(sa, v == 2 ? &maps.al[pi] : &maps.ah[pi], &full_bar[s], kb * BK, m0, b);
-                tma::load_3d(sa + kPlaneBytes, v == 1 ? &maps.bl[pi] : &maps.bh[pi], &full_bar[s], kb * BK, n0, b);
+                tma::load_3d(sa, &maps.a[pi][pa(v)], &full_bar[s], kb * BK, m0, b);
+                tma::load_3d(sa + kPlaneBytes, &maps.b[pi][pb(v)], &full_bar[s], kb * BK, n0, b);
             }
         }
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {                                         // ---- MMA issuer ----
             for (int it = 0; it < nit; ++it) {
-                const int s = it % kPlStages, kb = it / 3, v = it - 3 * kb;
+                const int s = it % kPlStages, kb = it / NP, v = it - NP * kb;
                 mbar_wait(&full_bar[s], (uint32_t)((it / kPlStages) & 1));
                 tc_fence_after();
                 const uint32_t a0 = smem_u32(smem + (size_t)s * 2 * kPlaneBytes), b0 = a0 + kPlaneBytes;
@@ -630,13 +636,14 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_planes_kernel(const Launch L
     }
     mbar_wait(&done_bar, 0);
     tc_fence_after();
-    tile_epilogue<2>(P, b, m0, n0, tmem_base, warp, lane);
+    tile_epilogue<2>(P, b, m0, n0, tmem_base, warp, lane);      // <2>: main + cross tile
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem_base, 256);
 }
 
-// false (nothing launched) when an operand cannot be described to TMA; the caller then takes the register-staged kernel
+// *launched = false (nothing launched) when an operand cannot be described to TMA; the caller then takes the register-staged kernel
+template <int SPLIT>
 static int launch_gemm_planes(const Launch& L, int batch, cudaStream_t st, const char* what, bool* launched) {
     *launched = false;
     int tiles = L.tiles0 + (L.nprob > 1 ? (L.p[1].diag_only ? L.p[1].tiles_m : L.p[1].tiles_m * L.p[1].tiles_n) : 0);
@@ -645,21 +652,21 @@ static int launch_gemm_planes(const Launch& L, int batch, cudaStream_t st, const
     bool ok = true;
     for (int i = 0; ok && i < L.nprob; ++i) {
         const Problem& P = L.p[i];
-        ok = P.Ah && P.Al && P.Bh && P.Bl &&
-             operand_map<__nv_bfloat16>(&maps.ah[i], P.Ah, P.M, P.K, P.lda, P.sA, batch, ROMA_BF16) &&
-             operand_map<__nv_bfloat16>(&maps.al[i], P.Al, P.M, P.K, P.lda, P.sA, batch, ROMA_BF16) &&
-             operand_map<__nv_bfloat16>(&maps.bh[i], P.Bh, P.N, P.K, P.ldb, P.sB, batch, ROMA_BF16) &&
-             operand_map<__nv_bfloat16>(&maps.bl[i], P.Bl, P.N, P.K, P.ldb, P.sB, batch, ROMA_BF16);
+        for (int q = 0; ok && q < SPLIT; ++q)
+            ok = P.Apl[q] && P.Bpl[q] &&
+                 operand_map<__nv_bfloat16>(&maps.a[i][q], P.Apl[q], P.M, P.K, P.lda, P.sA, batch, ROMA_BF16) &&
+                 operand_map<__nv_bfloat16>(&maps.b[i][q], P.Bpl[q], P.N, P.K, P.ldb, P.sB, batch, ROMA_BF16);
+        for (int q = SPLIT; ok && q < 3; ++q) { maps.a[i][q] = maps.a[i][0]; maps.b[i][q] = maps.b[i][0]; }
     }
     if (!ok) return ROMA_OK;
-    if (L.nprob < 2) { maps.ah[1] = maps.ah[0]; maps.al[1] = maps.al[0]; maps.bh[1] = maps.bh[0]; maps.bl[1] = maps.bl[0]; }
+    if (L.nprob < 2) for (int q = 0; q < 3; ++q) { maps.a[1][q] = maps.a[0][q]; maps.b[1][q] = maps.b[0][q]; }
     static DeviceOnce::Flags configured;
     if (DeviceOnce::pending(configured)) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_planes_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlSmem);
+        cudaError_t e = cudaFuncSetAttribute(gemm_planes_kernel<SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlSmem);
         if (e != cudaSuccess) return fail((int)e, "%s: smem opt-in (%zu B): %s", what, kPlSmem, cudaGetErrorString(e));
         DeviceOnce::done(configured);
     }
-    gemm_planes_kernel<0><<<dim3(tiles, batch), kThreads, kPlSmem, st>>>(L, maps);
+    gemm_planes_kernel<SPLIT><<<dim3(tiles, batch), kThreads, kPlSmem, st>>>(L, maps);
     *launched = true;
     return check_launch(what);
 }
@@ -674,7 +681,8 @@ static inline Problem make_problem(const void* A, const void* B, float* C, int M
     p.lower_only = 0; p.diag_only = 0; p.no_diag = 0; p.epi = epi; p.store_m = M; p.store_n = N;
     p.rn = p.cn = nullptr; p.srn = p.scn = 0; p.eps = 0.f; p.inv_T = 0.f; p.diag_add = 0.f;
     p.part = nullptr; p.scale = 1.f; p.w1 = 1; p.lx0 = p.lxs = p.ly0 = p.lys = 0.f;
-    p.Ph = p.Pl = nullptr; p.Ah = p.Al = p.Bh = p.Bl = nullptr;
+    p.nplanes = 0;
+    for (int i = 0; i < 3; ++i) { p.Pout[i] = nullptr; p.Apl[i] = nullptr; p.Bpl[i] = nullptr; }
     return p;
 }
 
