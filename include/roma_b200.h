@@ -97,6 +97,16 @@ int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_
                         void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,
                         int B, int C, int h, int w, int h1, int w1, int E, int r, int dtype,
                         void* stream);
+/* The same call with a workspace of roma_refiner_gather_workspace_bytes(B, h, w, r) bytes (one byte per 8 x 8 pixel tile; 0 for
+ * radii other than 2 and 3): enables the shared-patch tile kernel of path 0 above, which records there the tiles it took so that
+ * the per-pixel kernel launched after it skips them.  Without a workspace (or through roma_refiner_gather) every pixel takes
+ * the per-pixel kernel.  Same results either way up to the fp32 summation order of the correlations. */
+size_t roma_refiner_gather_workspace_bytes(int B, int h, int w, int r);
+int roma_refiner_gather_ws(const void* f0, const void* f1, const float* flow, roma_strides4 flow_strides,
+                           const float* disp_w, const float* disp_b, float disp_scale,
+                           void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,
+                           int B, int C, int h, int w, int h1, int w1, int E, int r, int dtype,
+                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * K3a  flow / certainty update + bilinear resample to the next scale.
@@ -166,10 +176,10 @@ int roma_gp_set_path(int path);
  * updates and all right-hand-side work one step behind on the caller's stream, ordered by events, forked from and
  * joined to the caller's stream inside the call; 0 = every launch on the caller's stream (left-looking). */
 int roma_gp_set_lanes(int on);
-/* 1: the finished panels of the factorisation (L and the solved right-hand sides) are ALSO written as bf16 hi / lo planes
+/* 1 (default): the finished panels of the factorisation (L and the solved right-hand sides) are ALSO written as bf16 hi / lo planes
  * by the panel kernels' epilogue, and the update / syrk / posterior GEMMs read those planes through TMA with no conversion
- * in their main loop (gemm_planes_kernel: 3-stage ring, three plane pairs per k-block); 0: fp32 operands re-split on the
- * fly at every visit (the round-1 form).  Needs the two-lane schedule and the 2-plane solve; same products either way. */
+ * in their main loop (gemm_planes_kernel: 3-stage ring, three / six plane pairs per k-block for the 2- / 3-plane solve);
+ * 0: fp32 operands re-split on the fly at every visit (the round-1 form).  Needs the two-lane schedule; same products either way. */
 int roma_gp_set_planes(int on);
 /* The tensor-core building block of K1, exposed for unit tests and timing: batched C = A * B^T with
  * A (batch, M, K), B (batch, N, K) row-major in `dtype`, C (batch, M, N) fp32.  fp32 operands are split on the

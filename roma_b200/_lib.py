@@ -34,6 +34,10 @@ SIGNATURES = {
     "roma_refiner_gather": (_i, [_vp, _vp, _vp, Strides4, _vp, _vp, _f,
                                  _vp, _i, _i, _i, _i, _i,
                                  _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "roma_refiner_gather_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "roma_refiner_gather_ws": (_i, [_vp, _vp, _vp, Strides4, _vp, _vp, _f,
+                                    _vp, _i, _i, _i, _i, _i,
+                                    _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "roma_flow_update_resample": (_i, [_vp, Strides4, _vp, Strides4, _vp, Strides4, _f, _f, _f,
                                        _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "roma_match_epilogue": (_i, [_vp, Strides4, _vp, Strides4, _vp, Strides4, _i, _i,

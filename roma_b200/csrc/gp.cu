@@ -104,7 +104,7 @@ extern "C" int roma_tc_set_tma(int on) {
 }
 namespace roma { namespace gp { static std::atomic<int> g_path{0}; } }   // 0 auto, 1 SIMT fp32, 2 tcgen05 (3-plane solve), 3 tcgen05 (2-plane solve)
 
-namespace roma { namespace gp { std::atomic<int> g_lanes{1}; std::atomic<int> g_planes{0}; } }
+namespace roma { namespace gp { std::atomic<int> g_lanes{1}; std::atomic<int> g_planes{1}; } }
 extern "C" int roma_gp_set_planes(int on) {
     roma::gp::g_planes.store(on ? 1 : 0);
     return ROMA_OK;

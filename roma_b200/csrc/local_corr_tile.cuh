@@ -12,10 +12,12 @@
 // fp32 accumulator in TMEM, and each pixel picks its (2r+2)^2 neighbour products out of its TMEM lane and blends them with
 // the shared bilinear weights exactly like the per-pixel kernels.  ~13 KB per pixel through L2 instead of 64 + 4.
 //
-// Tiles whose windows do not fit the patch (incoherent flow, flow discontinuities, non-finite flow) take the per-pixel
-// form inside the SAME CTA (local_corr_px, one warp per pixel): one launch, one decision per tile.  (A first version ran
-// the per-pixel kernel as a second launch over the same grid; its ~35 k CTAs that only re-derived the verdict and exited
-// cost 0.17 / 0.8 ms at s8' / s4' — measured with the phase switches of roma_local_corr_set_path.)
+// Tiles whose windows do not fit the patch (incoherent flow, flow discontinuities, non-finite flow) are left to the
+// per-pixel kernel: this kernel writes one byte per tile (taken / declined) into a caller-provided tile map and the
+// per-pixel kernel, launched next on the stream in its usual flat form, skips the pixels of the taken tiles.  (Tried and
+// measured: the per-pixel kernel re-deriving the verdict per tile — its ~35 k CTAs that only exit cost 0.17 / 0.8 ms at
+// s8' / s4'; the per-pixel form folded into this kernel — its 100 KB of shared memory per CTA shrink the L1 the
+// per-pixel form lives on: 0.85 -> 1.38 ms at s8' on incoherent flows.)
 //
 // CTA = 256 threads, 2 CTAs / SM (<= 256 TMEM columns, ~100 KB of shared memory each):
 //   warp 0 lane 0  TMA producer (2-stage ring over the C / 64 k-blocks, two patch halves = two passes over K)
@@ -28,7 +30,6 @@
 
 namespace roma {
 
-constexpr int kTileSide = 8, kTilePx = 64;
 
 template <int R> struct TileGeom {
     static constexpr int W2 = 2 * R + 2, NN = W2 * W2, K1 = 2 * R + 1, K = K1 * K1;
@@ -121,7 +122,7 @@ __host__ __device__ constexpr uint32_t instr_desc_n(uint32_t fmt, uint32_t n) {
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 
-template <typename T, int R, int VPL>
+template <typename T, int R>
 __global__ void __launch_bounds__(256, 2)
 local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps maps) {
     using G = TileGeom<R>;
@@ -137,18 +138,10 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tx0 = blockIdx.x * kTileSide, ty0 = blockIdx.y * kTileSide, b = blockIdx.z;
     bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
-    if (!tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0)) {
-        // incoherent tile (or a flow discontinuity / non-finite flow): every pixel pulls its own window — the per-pixel form,
-        // one warp per pixel, its scratch carved out of this CTA's dynamic shared memory
-        unsigned char* base = smem_raw + ((16u - (tc::smem_u32(smem_raw) & 15u)) & 15u);
-        float* Dsm = reinterpret_cast<float*>(base) + warp * (G::NN + 4);
-        T* f0w = reinterpret_cast<T*>(base + 8 * (G::NN + 4) * sizeof(float)) + warp * (64 * VPL);
-        for (int lp = warp; lp < kTilePx; lp += 8) {
-            const int y = ty0 + (lp >> 3), x = tx0 + (lp & 7);
-            if (y < p.h && x < p.w) local_corr_px<T, VPL>(p, ((long long)b * p.h + y) * p.w + x, lane, Dsm, f0w);
-        }
-        return;
-    }
+    const bool fits = tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0);
+    // the verdict goes to the tile map: the per-pixel kernel that follows on the stream skips the pixels of the tiles taken here
+    if (tid == 0) p.tile_flags[((long long)b * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = fits ? 1 : 0;
+    if (!fits) return;
     if (tid < kTilePx) {
         s_x0[tid] = valid ? x0 : INT_MIN; s_y0[tid] = y0;
         s_w[tid][0] = wx0; s_w[tid][1] = wx1; s_w[tid][2] = wy0; s_w[tid][3] = wy1;
@@ -212,39 +205,15 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
             }
         }
         __syncwarp();
-    } else if (warp == 4 || warp == 5) {                          // ---- TMEM lanes 0..63 -> window products ----
-        const int m = (warp - 4) * 32 + lane;
-        const int ox = s_x0[m] == INT_MIN ? 0 : s_x0[m] - p.r - X0, oy = s_y0[m] - p.r - Y0;
-        const bool live = s_x0[m] != INT_MIN;
-        float* Dm = Dwin + m * G::DSTRIDE;
-        const uint32_t tlane = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
-        for (int pass = 0; pass < 2; ++pass) {
-            tc::mbar_wait(&done_bar, (uint32_t)pass);
-            tc::tc_fence_after();
-            for (int qy = 0; qy < ((p.dbg & 4) ? 0 : G::ROWS); ++qy) {
-                constexpr int NL = (G::PW + 3) / 4;
-                float v[NL * 4];
-#pragma unroll
-                for (int q = 0; q < NL; ++q) tmem_ld4_nowait(tlane + (uint32_t)(qy * G::PW + 4 * q), v + 4 * q);
-                tmem_wait_ld();
-                const int j = pass * G::ROWS + qy - oy;
-                if (live && (unsigned)j < (unsigned)G::W2) {
-                    float* dst = Dm + j * G::W2 - ox;
-#pragma unroll
-                    for (int t = 0; t < G::PW; ++t)
-                        if ((unsigned)(t - ox) < (unsigned)G::W2) dst[t] = v[t];
-                }
-            }
-            tc::tc_fence_before();
-            if (pass == 0) mbar_arrive(&free_bar);
-        }
-    } else {                                                      // ---- streaming segments: warps 2, 3, 6, 7 ----
+    }
+    if (!(p.dbg & 16) && warp >= 2) {                             // ---- streaming segments: warps 2..7 (4, 5: before their extraction) ----
         // 16 pixels per warp, items = (pixel, 16-byte vector) pairs spread over the lanes and processed FOUR AT A TIME: all
         // the loads of a group (4 x f0 or 16 x f1 taps) are issued before any is used — one L2 round trip per group instead of
         // one per pixel (the first version handled a pixel at a time: 2/3 of the CTA's life was these four warps waiting)
-        const int sw = (warp & 1) + ((warp >> 2) << 1);             // 0..3: pixels [16 sw, 16 sw + 16)
+        const int sw = warp - 2;                                    // 0..5: pixels [m_lo, m_hi): 11, 11, 11, 11, 10, 10
+        const int m_lo = sw * 11 - (sw > 4 ? 1 : 0), m_hi = m_lo + (sw < 4 ? 11 : 10);
         const int nvec = p.C / 8;
-        const int nitems = (p.dbg & 1) ? 0 : 16 * nvec;
+        const int nitems = (p.dbg & 1) ? 0 : (m_hi - m_lo) * nvec;
         const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
         const long long rowpix0 = (long long)b * p.h;
         auto pixel_of = [&](int m, long long& pix) -> bool {
@@ -260,7 +229,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
                     const int q = q0 + 32 * u;
                     dst[u] = nullptr;
                     long long pix;
-                    if (q < nitems && pixel_of(16 * sw + q / nvec, pix)) {
+                    if (q < nitems && pixel_of(m_lo + q / nvec, pix)) {
                         const int vv = q % nvec;
                         v[u] = ldg16(f0 + pix * p.C + vv * 8);
                         dst[u] = dout + pix * p.dch + p.off_x + vv * 8;
@@ -278,7 +247,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
                     const int q = q0 + 32 * u;
                     dst[u] = nullptr;
                     long long pix;
-                    const int m = 16 * sw + (q < nitems ? q / nvec : 0);
+                    const int m = m_lo + (q < nitems ? q / nvec : 0);
                     if (q < nitems && pixel_of(m, pix)) {
                         const int vv = q % nvec, px0 = s_x0[m], py0 = s_y0[m];
                         dst[u] = dout + pix * p.dch + p.off_xhat + vv * 8;
@@ -308,7 +277,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
                 }
             }
         }
-        for (int m = 16 * sw; m < 16 * sw + 16; ++m) {
+        for (int m = m_lo; m < m_hi; ++m) {
             long long pix;
             if (!pixel_of(m, pix)) continue;
             const int y = ty0 + (m >> 3), x = tx0 + (m & 7);
@@ -321,6 +290,33 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
                                                               fmaf(__ldg(p.disp_w + 2 * e + 1), dy, __ldg(p.disp_b + e))));
             }
             if (lane < p.dch - p.covered) row[p.covered + lane] = Elem<T>::from_f(0.f);
+        }
+    }
+    if (!(p.dbg & 16) && (warp == 4 || warp == 5)) {              // ---- TMEM lanes 0..63 -> window products ----
+        const int m = (warp - 4) * 32 + lane;
+        const int ox = s_x0[m] == INT_MIN ? 0 : s_x0[m] - p.r - X0, oy = s_y0[m] - p.r - Y0;
+        const bool live = s_x0[m] != INT_MIN;
+        float* Dm = Dwin + m * G::DSTRIDE;
+        const uint32_t tlane = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
+        for (int pass = 0; pass < 2; ++pass) {
+            tc::mbar_wait(&done_bar, (uint32_t)pass);
+            tc::tc_fence_after();
+            for (int qy = 0; qy < ((p.dbg & 4) ? 0 : G::ROWS); ++qy) {
+                constexpr int NL = (G::PW + 3) / 4;
+                float v[NL * 4];
+#pragma unroll
+                for (int q = 0; q < NL; ++q) tmem_ld4_nowait(tlane + (uint32_t)(qy * G::PW + 4 * q), v + 4 * q);
+                tmem_wait_ld();
+                const int j = pass * G::ROWS + qy - oy;
+                if (live && (unsigned)j < (unsigned)G::W2) {
+                    float* dst = Dm + j * G::W2 - ox;
+#pragma unroll
+                    for (int t = 0; t < G::PW; ++t)
+                        if ((unsigned)(t - ox) < (unsigned)G::W2) dst[t] = v[t];
+                }
+            }
+            tc::tc_fence_before();
+            if (pass == 0) mbar_arrive(&free_bar);
         }
     }
     tc::tc_fence_before();

@@ -22,6 +22,8 @@
 
 namespace roma {
 
+constexpr int kTileSide = 8, kTilePx = 64;      // shared-patch tiles of local_corr_tile.cuh
+
 struct GatherParams {
     const void* f0; const void* f1; const float* flow; roma_strides4 fs;
     const float* disp_w; const float* disp_b; float disp_scale;
@@ -31,6 +33,7 @@ struct GatherParams {
     int tile_px;     // pixels per CTA tile (local-corr kernel)
     int covered;     // channels written by the enabled segments; [covered, dch) is zero-filled pitch padding
     int dbg;         // timing aid for local_corr_tile_kernel (bit 0: no streaming segments, 1: no main loop, 2: no extraction, 3: no blend)
+    unsigned char* tile_flags;   // per 8 x 8 tile: 1 = computed by local_corr_tile_kernel (the per-pixel kernel skips its pixels); or null
     int tile_pw;     // > 0: 8 x 8 pixel tiles (grid = tiles_x, tiles_y, B); the per-pixel kernel SKIPS tiles whose windows fit
                      // a tile_pw x tile_pw patch (they are computed by local_corr_tile_kernel, local_corr_tile.cuh)
 };
@@ -483,7 +486,17 @@ local_corr_mma_kernel(const GatherParams p) {
     const long long tile_start = (long long)blockIdx.x * p.tile_px;
     int tile_n = p.tile_px;
     if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
-    for (int lp = warp; lp < tile_n; lp += 8) local_corr_px<T, VPL>(p, tile_start + lp, lane, Dall[warp], f0s[warp]);
+    const int tiles_x = (p.w + kTileSide - 1) / kTileSide, tiles_y = (p.h + kTileSide - 1) / kTileSide;
+    for (int lp = warp; lp < tile_n; lp += 8) {
+        const long long pix = tile_start + lp;
+        if (p.tile_flags) {                                      // pixels of the tiles the shared-patch kernel took
+            const int hw = p.h * p.w;
+            const int b = (int)(pix / hw), rem = (int)(pix - (long long)b * hw);
+            const int y = rem / p.w, x = rem - y * p.w;
+            if (p.tile_flags[((long long)b * tiles_y + (y >> 3)) * tiles_x + (x >> 3)]) continue;
+        }
+        local_corr_px<T, VPL>(p, pix, lane, Dall[warp], f0s[warp]);
+    }
 }
 
 }  // namespace roma
@@ -668,19 +681,21 @@ static int launch_tiled_r(GatherParams p, cudaStream_t st, int dtype) {
         tma::encode_tiled(&maps.f1, dtype, 4, p.f1, d1, s1, b1, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return ROMA_ERR_UNSUPPORTED;
     static DeviceOnce::Flags configured;
     if (DeviceOnce::pending(configured)) {
-        cudaError_t err = cudaFuncSetAttribute(local_corr_tile_kernel<T, R, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
-        if (err == cudaSuccess) err = cudaFuncSetAttribute(local_corr_tile_kernel<T, R, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+        cudaError_t err = cudaFuncSetAttribute(local_corr_tile_kernel<T, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
         if (err != cudaSuccess) return fail((int)err, "roma_refiner_gather: smem opt-in (%zu B): %s", G::SMEM, cudaGetErrorString(err));
         DeviceOnce::done(configured);
     }
     p.tile_pw = G::PW;
     p.dbg = g_tile_dbg.load();
     const dim3 grid((unsigned)cdiv(p.w, kTileSide), (unsigned)cdiv(p.h, kTileSide), (unsigned)p.B);
+    local_corr_tile_kernel<T, R><<<grid, 256, G::SMEM, st>>>(p, maps);
+    p.tile_px = 32;
+    const int gpx = cdiv(p.npix, p.tile_px);
     switch (p.C) {
-        case 512: local_corr_tile_kernel<T, R, 8><<<grid, 256, G::SMEM, st>>>(p, maps); break;
-        default:  local_corr_tile_kernel<T, R, 4><<<grid, 256, G::SMEM, st>>>(p, maps); break;
+        case 512: local_corr_mma_kernel<T, 8><<<gpx, 256, 0, st>>>(p); break;
+        default:  local_corr_mma_kernel<T, 4><<<gpx, 256, 0, st>>>(p); break;
     }
-    return check_launch("roma_refiner_gather(local_corr_tile)");
+    return check_launch("roma_refiner_gather(local_corr_tile + local_corr_mma)", 2);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -897,11 +912,12 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
             p.tile_px = 32;
             const int grid = cdiv(p.npix, p.tile_px);
             if constexpr (sizeof(T) == 2) {
-                if (g_local_corr_path.load() == 0 && (p.r == 2 || p.r == 3) && (p.C == 512 || p.C == 256) && p.h == p.h1 && p.w == p.w1 && p.off_corr >= 0) {
+                if (g_local_corr_path.load() == 0 && p.tile_flags && (p.r == 2 || p.r == 3) && (p.C == 512 || p.C == 256) && p.h == p.h1 && p.w == p.w1 && p.off_corr >= 0) {
                     // shared-patch tiles (coherent flow) + per-pixel kernel for the tiles that decline (local_corr_tile.cuh)
                     const int rc = launch_tiled<T>(p, st);
                     if (rc != ROMA_ERR_UNSUPPORTED) return rc;
                 }
+                p.tile_flags = nullptr;
                 if (g_local_corr_path.load() == 0 || g_local_corr_path.load() == 2) {
                     switch (p.C) {
                         case 512: local_corr_mma_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
@@ -993,11 +1009,25 @@ extern "C" int roma_local_corr_set_path(int path) {
     return ROMA_OK;
 }
 
+extern "C" size_t roma_refiner_gather_workspace_bytes(int B, int h, int w, int r) {
+    if (B <= 0 || h <= 0 || w <= 0 || (r != 2 && r != 3)) return 0;
+    return ((size_t)B * ((h + roma::kTileSide - 1) / roma::kTileSide) * ((w + roma::kTileSide - 1) / roma::kTileSide) + 255) & ~(size_t)255;
+}
+
 extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_strides4 fs,
                                    const float* disp_w, const float* disp_b, float disp_scale,
                                    void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,
                                    int B, int C, int h, int w, int h1, int w1, int E, int r, int dtype,
                                    void* stream) {
+    return roma_refiner_gather_ws(f0, f1, flow, fs, disp_w, disp_b, disp_scale, d, d_channels, off_x, off_xhat, off_emb, off_corr,
+                                  B, C, h, w, h1, w1, E, r, dtype, nullptr, 0, stream);
+}
+
+extern "C" int roma_refiner_gather_ws(const void* f0, const void* f1, const float* flow, roma_strides4 fs,
+                                      const float* disp_w, const float* disp_b, float disp_scale,
+                                      void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,
+                                      int B, int C, int h, int w, int h1, int w1, int E, int r, int dtype,
+                                      void* workspace, size_t workspace_bytes, void* stream) {
     using namespace roma;
     ROMA_REQUIRE(f1 && flow && d, ROMA_ERR_BAD_ARG, "roma_refiner_gather: null pointer");
     ROMA_REQUIRE(B > 0 && C > 0 && h > 0 && w > 0 && h1 > 0 && w1 > 0 && r >= 0 && E >= 0 && d_channels > 0,
@@ -1032,6 +1062,8 @@ extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* 
     p.d = d; p.dch = d_channels; p.off_x = off_x; p.off_xhat = off_xhat; p.off_emb = off_emb; p.off_corr = off_corr;
     p.B = B; p.C = C; p.h = h; p.w = w; p.h1 = h1; p.w1 = w1; p.E = E; p.r = r;
     p.npix = (long long)B * h * w; p.tile_px = 0; p.covered = covered; p.tile_pw = 0; p.dbg = 0;
+    p.tile_flags = (workspace && workspace_bytes >= roma_refiner_gather_workspace_bytes(B, h, w, r) && roma_refiner_gather_workspace_bytes(B, h, w, r) > 0)
+                       ? reinterpret_cast<unsigned char*>(workspace) : nullptr;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (dtype) {
         case ROMA_F32:  return launch_gather<float>(p, st);

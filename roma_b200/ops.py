@@ -156,11 +156,13 @@ def refiner_inputs(x: torch.Tensor, y: Optional[torch.Tensor], flow: torch.Tenso
     else:
         parts = [(x, y, flow, d)]
     for xp, yp, fp_, dp in parts:
+        nws = lib.roma_refiner_gather_workspace_bytes(xp.shape[0], h, w, r)      # tile map of the shared-patch kernel (r = 2, 3)
+        ws = torch.empty(nws, device=dev, dtype=torch.uint8) if nws else None
         _run("roma_refiner_gather", dict(B=xp.shape[0], C=Cc, h=h, w=w, r=r, E=E, esize=x.element_size()),
-             lambda: lib.roma_refiner_gather(
+             lambda: lib.roma_refiner_gather_ws(
                  _ptr(xp), _ptr(yp), _ptr(fp_), _s4(fp_), _ptr(disp_w), _ptr(disp_b), float(disp_scale),
                  _ptr(dp), dch, 0, Cc, (2 * Cc if E else -1), (2 * Cc + E if r > 0 else -1),
-                 xp.shape[0], Cc, h, w, h1, w1, E, r, _DT[x.dtype], _stream(dev)))
+                 xp.shape[0], Cc, h, w, h1, w1, E, r, _DT[x.dtype], _ptr(ws), nws, _stream(dev)))
     return d
 
 

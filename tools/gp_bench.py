@@ -14,7 +14,7 @@ dt = getattr(torch, sys.argv[3]) if len(sys.argv) > 3 else torch.bfloat16
 paths = tuple(int(p) for p in sys.argv[4].split(",")) if len(sys.argv) > 4 else (2, 3, 1)      # 2 = default (3-plane)
 real = len(sys.argv) > 5 and sys.argv[5] == "real"
 lib = _lib.load()
-PLANES_DEFAULT = 0
+PLANES_DEFAULT = 1
 dev = torch.device("cuda:0")
 g = torch.Generator().manual_seed(3)
 C = D = 512
@@ -36,7 +36,7 @@ N = side * side
 flops = B * (2.0 * N * N * C * 2 + N ** 3 / 3 + 2.0 * N * N * D + 2.0 * N * N * D)
 names = {1: "simt", 2: "tcgen05 split3", 3: "tcgen05 split2"}
 for path in paths:
-    for lanes, planes in (((1, 1), (1, 0), (0, 0)) if path == 3 else ((1, 0), (0, 0)) if path != 1 else ((1, 0),)):
+    for lanes, planes in (((1, 1), (1, 0), (0, 0)) if path != 1 else ((1, 0),)):
         lib.roma_gp_set_path(path)
         lib.roma_gp_set_lanes(lanes)
         lib.roma_gp_set_planes(planes)
