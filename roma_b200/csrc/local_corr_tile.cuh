@@ -6,7 +6,7 @@
 // The per-pixel kernels (local_corr_mma_kernel) drag every pixel's own (2r+2)^2 x C window through L2 -> L1 -> registers:
 // 64 KB per pixel at C = 512, r = 3 — 12 GB per launch for 0.8 GB of compulsory HBM traffic, L2-bandwidth-bound.  When the
 // flow is coherent the windows of neighbouring pixels overlap almost entirely: the 64 pixels of an 8 x 8 tile need a
-// patch of at most PW x PW positions of f1 (PW = 7 + (2r+2) + 5 of slack), so the tile's f0 rows (A, 64 x C) and the patch
+// patch of at most PW x PW positions of f1 (PW = 7 + (2r+2) + 11..12 of slack: displacement gradients up to ~1 px / px), so the tile's f0 rows (A, 64 x C) and the patch
 // (B, PW^2 x C) are loaded ONCE by TMA (4-D boxes (64 ch, x, y, 1) straight into the UMMA K-major SWIZZLE_128B layout;
 // out-of-image positions are zero-filled by the copy engine = padding_mode "zeros"), D = A B^T runs on tcgen05 with the
 // fp32 accumulator in TMEM, and each pixel picks its (2r+2)^2 neighbour products out of its TMEM lane and blends them with
@@ -33,15 +33,18 @@ namespace roma {
 
 template <int R> struct TileGeom {
     static constexpr int W2 = 2 * R + 2, NN = W2 * W2, K1 = 2 * R + 1, K = K1 * K1;
-    static constexpr int PW = 7 + W2 + 5;                       // patch side: 18 (r = 2), 20 (r = 3)
-    static constexpr int ROWS = PW / 2;                         // patch rows per pass (two passes)
-    static constexpr int NCOL = ROWS * PW;                      // D columns in use per pass: 162 / 200
-    static constexpr int NPAD = (NCOL + 15) / 16 * 16;          // MMA N: 176 / 208
+    static constexpr int NPASS = 3;                             // the patch is multiplied in NPASS row bands (<= 256 TMEM columns each)
+    static constexpr int PW = R == 2 ? 24 : 27;                 // patch side = 7 + W2 + slack: slack 11 (r = 2), 12 (r = 3) positions
+    static constexpr int ROWS = PW / NPASS;                     // patch rows per pass: 8 / 9
+    static constexpr int NCOL = ROWS * PW;                      // D columns in use per pass: 192 / 243
+    static constexpr int NPAD = (NCOL + 15) / 16 * 16;          // MMA N: 192 / 256
     static constexpr int BBYTES = (NPAD * 128 + 1023) / 1024 * 1024;
-    static constexpr int STAGE = 16384 + BBYTES;                // A: 128 rows (64 loaded) + B
+    // A: 64 rows loaded (8 KB); the MMA reads 128 rows, rows 64..127 = the first 8 KB of B (their products are never read)
+    static constexpr int AOFF = 8192;
+    static constexpr int STAGE = AOFF + BBYTES;
     static constexpr int DSTRIDE = NN + 1;                      // staged products per pixel (+1: bank spread)
     static constexpr size_t SMEM = 1024 + 2 * (size_t)STAGE + (size_t)kTilePx * DSTRIDE * sizeof(float);
-    static_assert(PW % 2 == 0 && NPAD <= 256, "patch pass must fit one MMA and 256 TMEM columns");
+    static_assert(PW % NPASS == 0 && NPAD <= 256 && BBYTES >= 8192, "patch pass must fit one MMA and 256 TMEM columns");
 };
 
 struct TileMaps { CUtensorMap f0, f1; };
@@ -174,29 +177,30 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     if (p.dbg & 16) {
     } else if (warp == 0) {
         if (lane == 0) {                                         // ---- TMA producer ----
-            for (int it = 0; it < ((p.dbg & 2) ? 0 : 2 * nkb); ++it) {
+            for (int it = 0; it < ((p.dbg & 2) ? 0 : G::NPASS * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
                 if (it >= 2) tc::mbar_wait(&empty_bar[s], (uint32_t)(((it >> 1) - 1) & 1));
                 unsigned char* sa = smem + (size_t)s * G::STAGE;
                 tma::mbar_expect_tx(&full_bar[s], (uint32_t)(kTilePx * 128 + G::NCOL * 128));
                 tma::load_4d(sa, &maps.f0, &full_bar[s], kb * 64, tx0, ty0, b);
-                tma::load_4d(sa + 16384, &maps.f1, &full_bar[s], kb * 64, X0, Y0 + pass * G::ROWS, b);
+                tma::load_4d(sa + G::AOFF, &maps.f1, &full_bar[s], kb * 64, X0, Y0 + pass * G::ROWS, b);
             }
         }
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {                                         // ---- MMA issuer ----
             if (p.dbg & 2) {                                     // timing aid: no main loop (the products are garbage)
-                tc::umma_commit(&done_bar);
-                tc::mbar_wait(&free_bar, 0);
-                tc::umma_commit(&done_bar);
+                for (int pass = 0; pass < G::NPASS; ++pass) {
+                    if (pass) tc::mbar_wait(&free_bar, (uint32_t)((pass - 1) & 1));
+                    tc::umma_commit(&done_bar);
+                }
             }
-            for (int it = 0; it < ((p.dbg & 2) ? 0 : 2 * nkb); ++it) {
+            for (int it = 0; it < ((p.dbg & 2) ? 0 : G::NPASS * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
-                if (pass == 1 && kb == 0) { tc::mbar_wait(&free_bar, 0); tc::tc_fence_after(); }   // pass 0 drained from TMEM
+                if (pass > 0 && kb == 0) { tc::mbar_wait(&free_bar, (uint32_t)((pass - 1) & 1)); tc::tc_fence_after(); }   // previous band drained from TMEM
                 tc::mbar_wait(&full_bar[s], (uint32_t)((it >> 1) & 1));
                 tc::tc_fence_after();
-                const uint32_t a0 = tc::smem_u32(smem + (size_t)s * G::STAGE), b0 = a0 + 16384;
+                const uint32_t a0 = tc::smem_u32(smem + (size_t)s * G::STAGE), b0 = a0 + G::AOFF;
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk)
                     tc::umma_f16(tmem_base, tc::smem_desc_sw128(a0 + kk * 32), tc::smem_desc_sw128(b0 + kk * 32), idesc, (kb | kk) ? 1u : 0u);
@@ -298,8 +302,8 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
         const bool live = s_x0[m] != INT_MIN;
         float* Dm = Dwin + m * G::DSTRIDE;
         const uint32_t tlane = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
-        for (int pass = 0; pass < 2; ++pass) {
-            tc::mbar_wait(&done_bar, (uint32_t)pass);
+        for (int pass = 0; pass < G::NPASS; ++pass) {
+            tc::mbar_wait(&done_bar, (uint32_t)(pass & 1));
             tc::tc_fence_after();
             for (int qy = 0; qy < ((p.dbg & 4) ? 0 : G::ROWS); ++qy) {
                 constexpr int NL = (G::PW + 3) / 4;
@@ -316,7 +320,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
                 }
             }
             tc::tc_fence_before();
-            if (pass == 0) mbar_arrive(&free_bar);
+            if (pass + 1 < G::NPASS) mbar_arrive(&free_bar);
         }
     }
     tc::tc_fence_before();

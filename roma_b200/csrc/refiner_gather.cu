@@ -486,15 +486,25 @@ local_corr_mma_kernel(const GatherParams p) {
     const long long tile_start = (long long)blockIdx.x * p.tile_px;
     int tile_n = p.tile_px;
     if (tile_start + tile_n > p.npix) tile_n = (int)(p.npix - tile_start);
-    const int tiles_x = (p.w + kTileSide - 1) / kTileSide, tiles_y = (p.h + kTileSide - 1) / kTileSide;
-    for (int lp = warp; lp < tile_n; lp += 8) {
-        const long long pix = tile_start + lp;
-        if (p.tile_flags) {                                      // pixels of the tiles the shared-patch kernel took
+    // pixels of the tiles the shared-patch kernel took are skipped: the (up to 4) tile-map bytes of this warp's pixels are
+    // fetched together up front (lane i <-> pixel warp + 8 i), not one dependent load per pixel
+    unsigned skip = 0u;
+    if (p.tile_flags) {
+        const int tiles_x = (p.w + kTileSide - 1) / kTileSide, tiles_y = (p.h + kTileSide - 1) / kTileSide;
+        const int lp = warp + 8 * lane;
+        bool taken = false;
+        if (lp < tile_n) {
+            const long long pix = tile_start + lp;
             const int hw = p.h * p.w;
             const int b = (int)(pix / hw), rem = (int)(pix - (long long)b * hw);
             const int y = rem / p.w, x = rem - y * p.w;
-            if (p.tile_flags[((long long)b * tiles_y + (y >> 3)) * tiles_x + (x >> 3)]) continue;
+            taken = p.tile_flags[((long long)b * tiles_y + (y >> 3)) * tiles_x + (x >> 3)] != 0;
         }
+        skip = __ballot_sync(0xffffffffu, taken);
+    }
+    for (int lp = warp; lp < tile_n; lp += 8) {
+        const long long pix = tile_start + lp;
+        if ((skip >> (lp >> 3)) & 1u) continue;
         local_corr_px<T, VPL>(p, pix, lane, Dall[warp], f0s[warp]);
     }
 }

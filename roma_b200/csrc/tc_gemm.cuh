@@ -564,16 +564,18 @@ static int launch_gemm_nt_16(const Launch& L, int batch, cudaStream_t st, const 
 // tcgen05.commit, all 8 warps run the epilogue.  3 stages x 32 KB: two CTAs per SM, one tile's epilogue (EPI_SUB reads and
 // rewrites 64 KB of C) under the other's main loop.
 struct PlaneMaps { CUtensorMap a[2][3], b[2][3]; };      // [problem][plane]
-constexpr int kPlStages = 3;
-constexpr size_t kPlSmem = (size_t)kPlStages * 2 * kPlaneBytes + 1024;
+// One stage = ALL planes of both operands for one 64-wide k-block (2 * SPLIT x 16 KB: 64 / 96 KB), so every plane is fetched
+// once per k-block (a first version moved one (A plane, B plane) pair per stage: 6 pairs = 12 plane loads per k-block at 3
+// planes, and the update GEMMs became L2-bandwidth-bound at 8 TB/s).  One stage per CTA, two CTAs per SM: while one CTA's
+// MMAs run the other's TMA loads land; the epilogue of one overlaps the main loop of the other.
+template <int SPLIT> constexpr size_t planes_smem() { return (size_t)2 * SPLIT * kPlaneBytes + 1024; }
 
 // SPLIT = 2: pairs (0,0) | (0,1) (1,0); SPLIT = 3: (0,0) | (0,1) (1,0) (0,2) (1,1) (2,0)  — the first into the main tile
 template <int SPLIT>
 __global__ void __launch_bounds__(kThreads, 2) gemm_planes_kernel(const Launch L, const __grid_constant__ PlaneMaps maps) {
     extern __shared__ unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t full_bar[kPlStages], empty_bar[kPlStages], done_bar;
+    __shared__ __align__(8) uint64_t full_bar, empty_bar, done_bar;
     __shared__ uint32_t tmem_slot;
-    constexpr int NP = SPLIT * (SPLIT + 1) / 2;              // plane pairs per k-block: 3 or 6
 
     int t = blockIdx.x;
     const int pi = (L.nprob > 1 && t >= L.tiles0) ? 1 : 0;
@@ -585,13 +587,12 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_planes_kernel(const Launch L
     const int m0 = tm * BM, n0 = tn * BN;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const int nit = NP * ((P.K + BK - 1) / BK);
+    const int nkb = (P.K + BK - 1) / BK;
     constexpr uint32_t idesc = instr_desc(1u);
 
     if (warp == 0) tmem_alloc(&tmem_slot, 256);
     if (tid == 0) {
-        for (int s = 0; s < kPlStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        mbar_init(&done_bar, 1);
+        mbar_init(&full_bar, 1); mbar_init(&empty_bar, 1); mbar_init(&done_bar, 1);
         fence_barrier_init();
 #pragma unroll
         for (int q = 0; q < SPLIT; ++q) { tma::prefetch_map(&maps.a[pi][q]); tma::prefetch_map(&maps.b[pi][q]); }
@@ -600,35 +601,41 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_planes_kernel(const Launch L
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
-    // pair v -> (plane of A, plane of B), ordered by i + j
-    auto pa = [](int v) { return SPLIT == 2 ? (v == 2 ? 1 : 0) : (v == 2 ? 1 : v == 4 ? 1 : v == 5 ? 2 : 0); };
-    auto pb = [](int v) { return SPLIT == 2 ? (v == 1 ? 1 : 0) : (v == 1 ? 1 : v == 3 ? 2 : v == 4 ? 1 : 0); };
 
     if (warp == 0) {
         if (lane == 0) {                                         // ---- producer ----
-            for (int it = 0; it < nit; ++it) {
-                const int s = it % kPlStages, kb = it / NP, v = it - NP * kb;
-                if (it >= kPlStages) mbar_wait(&empty_bar[s], (uint32_t)((it / kPlStages - 1) & 1));
-                unsigned char* sa = smem + (size_t)s * 2 * kPlaneBytes;
-                tma::mbar_expect_tx(&full_bar[s], 2u * kPlaneBytes);
-                tma::load_3d(sa, &maps.a[pi][pa(v)], &full_bar[s], kb * BK, m0, b);
-                tma::load_3d(sa + kPlaneBytes, &maps.b[pi][pb(v)], &full_bar[s], kb * BK, n0, b);
+            for (int kb = 0; kb < nkb; ++kb) {
+                if (kb > 0) mbar_wait(&empty_bar, (uint32_t)((kb - 1) & 1));
+                tma::mbar_expect_tx(&full_bar, (uint32_t)(2 * SPLIT) * kPlaneBytes);
+#pragma unroll
+                for (int q = 0; q < SPLIT; ++q) {
+                    tma::load_3d(smem + (size_t)q * kPlaneBytes, &maps.a[pi][q], &full_bar, kb * BK, m0, b);
+                    tma::load_3d(smem + (size_t)(SPLIT + q) * kPlaneBytes, &maps.b[pi][q], &full_bar, kb * BK, n0, b);
+                }
             }
         }
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {                                         // ---- MMA issuer ----
-            for (int it = 0; it < nit; ++it) {
-                const int s = it % kPlStages, kb = it / NP, v = it - NP * kb;
-                mbar_wait(&full_bar[s], (uint32_t)((it / kPlStages) & 1));
+            const uint32_t a0 = smem_u32(smem), b0 = a0 + SPLIT * kPlaneBytes;
+            for (int kb = 0; kb < nkb; ++kb) {
+                mbar_wait(&full_bar, (uint32_t)(kb & 1));
                 tc_fence_after();
-                const uint32_t a0 = smem_u32(smem + (size_t)s * 2 * kPlaneBytes), b0 = a0 + kPlaneBytes;
 #pragma unroll
                 for (int kk = 0; kk < BK / 16; ++kk) {
-                    if (v == 0) umma_f16(tmem_base, smem_desc_sw128(a0 + kk * 32), smem_desc_sw128(b0 + kk * 32), idesc, (kb | kk) ? 1u : 0u);
-                    else umma_f16(tmem_base + 128u, smem_desc_sw128(a0 + kk * 32), smem_desc_sw128(b0 + kk * 32), idesc, (kb | kk | (v - 1)) ? 1u : 0u);
+#pragma unroll
+                    for (int i = 0; i < SPLIT; ++i) {
+#pragma unroll
+                        for (int j = 0; j < SPLIT; ++j) {
+                            if (i + j >= SPLIT) continue;
+                            const uint64_t ad = smem_desc_sw128(a0 + i * kPlaneBytes + kk * 32);
+                            const uint64_t bd = smem_desc_sw128(b0 + j * kPlaneBytes + kk * 32);
+                            if (i + j == 0) umma_f16(tmem_base, ad, bd, idesc, (kb | kk) ? 1u : 0u);
+                            else umma_f16(tmem_base + 128u, ad, bd, idesc, (kb | kk | (i + j - 1) | i) ? 1u : 0u);
+                        }
+                    }
                 }
-                umma_commit(&empty_bar[s]);
+                umma_commit(&empty_bar);
             }
             umma_commit(&done_bar);
         }
@@ -662,11 +669,11 @@ static int launch_gemm_planes(const Launch& L, int batch, cudaStream_t st, const
     if (L.nprob < 2) for (int q = 0; q < 3; ++q) { maps.a[1][q] = maps.a[0][q]; maps.b[1][q] = maps.b[0][q]; }
     static DeviceOnce::Flags configured;
     if (DeviceOnce::pending(configured)) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_planes_kernel<SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlSmem);
-        if (e != cudaSuccess) return fail((int)e, "%s: smem opt-in (%zu B): %s", what, kPlSmem, cudaGetErrorString(e));
+        cudaError_t e = cudaFuncSetAttribute(gemm_planes_kernel<SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)planes_smem<SPLIT>());
+        if (e != cudaSuccess) return fail((int)e, "%s: smem opt-in (%zu B): %s", what, planes_smem<SPLIT>(), cudaGetErrorString(e));
         DeviceOnce::done(configured);
     }
-    gemm_planes_kernel<SPLIT><<<dim3(tiles, batch), kThreads, kPlSmem, st>>>(L, maps);
+    gemm_planes_kernel<SPLIT><<<dim3(tiles, batch), kThreads, planes_smem<SPLIT>(), st>>>(L, maps);
     *launched = true;
     return check_launch(what);
 }

@@ -34,24 +34,27 @@ __device__ __forceinline__ float3 updated_at(const UpdParams& p, int b, int y, i
     return make_float3(fx, fy, c);
 }
 
+// IDX = unsigned when every index fits 32 bits (the emulated 64-bit divisions were a third of the instructions), else long long
+template <typename IDX>
 __global__ void __launch_bounds__(256) flow_update_resample_kernel(const UpdParams p) {
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < p.n_src + p.n_dst; idx += stride) {
-        if (idx < p.n_src) {
+    const IDX stride = (IDX)gridDim.x * blockDim.x;
+    const IDX n_src = (IDX)p.n_src, n_all = (IDX)(p.n_src + p.n_dst);
+    for (IDX idx = (IDX)blockIdx.x * blockDim.x + threadIdx.x; idx < n_all; idx += stride) {
+        if (idx < n_src) {
             // phase 1: updated values at this scale
-            const int hw = p.h * p.w;
+            const IDX hw = (IDX)(p.h * p.w);
             const int b = (int)(idx / hw);
-            const int rem = (int)(idx - (long long)b * hw);
+            const int rem = (int)(idx - (IDX)b * hw);
             const int y = rem / p.w, x = rem - y * p.w;
             const float3 v = updated_at(p, b, y, x);
             if (p.flow_out) reinterpret_cast<float2*>(p.flow_out)[idx] = make_float2(v.x, v.y);
             if (p.cert_out) p.cert_out[idx] = v.z;
         } else {
             // phase 2: bilinear resample (ATen upsample_bilinear2d, align_corners=False) of the updated fields
-            const long long o = idx - p.n_src;
-            const int hw2 = p.h2 * p.w2;
+            const IDX o = idx - n_src;
+            const IDX hw2 = (IDX)(p.h2 * p.w2);
             const int b = (int)(o / hw2);
-            const int rem = (int)(o - (long long)b * hw2);
+            const int rem = (int)(o - (IDX)b * hw2);
             const int y2 = rem / p.w2, x2 = rem - y2 * p.w2;
             int ya, yb, xa, xb; float ly, lx;
             bilinear_src(y2, p.rh, p.h, ya, yb, ly);
@@ -77,14 +80,15 @@ struct EpiParams {
     float rh16, rw16;
 };
 
+template <typename IDX>
 __global__ void __launch_bounds__(256) match_epilogue_kernel(const EpiParams p) {
     const int Wout = p.symmetric ? 2 * p.W : p.W;
-    const long long n = (long long)p.B * p.H * Wout;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
-        const int hw = p.H * Wout;
+    const IDX n = (IDX)((long long)p.B * p.H * Wout);
+    const IDX stride = (IDX)gridDim.x * blockDim.x;
+    for (IDX idx = (IDX)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
+        const IDX hw = (IDX)(p.H * Wout);
         const int b = (int)(idx / hw);
-        const int rem = (int)(idx - (long long)b * hw);
+        const int rem = (int)(idx - (IDX)b * hw);
         const int y = rem / Wout, xo = rem - y * Wout;
         const bool right = xo >= p.W;               // symmetric: right half holds B->A of decoder element b+B
         const int x = right ? xo - p.W : xo;
@@ -148,7 +152,10 @@ extern "C" int roma_flow_update_resample(const float* flow_in, roma_strides4 fs,
     p.n_src = (flow_out || cert_out) ? (long long)B * h * w : 0;
     p.n_dst = resample ? (long long)B * h2 * w2 : 0;
     if (p.n_src + p.n_dst == 0) return ROMA_OK;
-    flow_update_resample_kernel<<<stream_grid(p.n_src + p.n_dst), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
+    if (p.n_src + p.n_dst < (1ll << 31))
+        flow_update_resample_kernel<unsigned><<<stream_grid(p.n_src + p.n_dst), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
+    else
+        flow_update_resample_kernel<long long><<<stream_grid(p.n_src + p.n_dst), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
     return check_launch("roma_flow_update_resample");
 }
 
@@ -169,6 +176,7 @@ extern "C" int roma_match_epilogue(const float* flow, roma_strides4 fs,
     p.rh16 = cert16 ? (float)h16 / (float)H : 1.f;
     p.rw16 = cert16 ? (float)w16 / (float)W : 1.f;
     const long long n = (long long)B * H * (symmetric ? 2 * W : W);
-    match_epilogue_kernel<<<stream_grid(n), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
+    if (n < (1ll << 31)) match_epilogue_kernel<unsigned><<<stream_grid(n), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
+    else match_epilogue_kernel<long long><<<stream_grid(n), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
     return check_launch("roma_match_epilogue");
 }
