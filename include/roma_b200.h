@@ -97,10 +97,15 @@ int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_
                         void* d, int d_channels, int off_x, int off_xhat, int off_emb, int off_corr,
                         int B, int C, int h, int w, int h1, int w1, int E, int r, int dtype,
                         void* stream);
-/* The same call with a workspace of roma_refiner_gather_workspace_bytes(B, h, w, r) bytes (one byte per 8 x 8 pixel tile; 0 for
- * radii other than 2 and 3): enables the shared-patch tile kernel of path 0 above, which records there the tiles it took so that
- * the per-pixel kernel launched after it skips them.  Without a workspace (or through roma_refiner_gather) every pixel takes
- * the per-pixel kernel.  Same results either way up to the fp32 summation order of the correlations. */
+/* The same call with a workspace of roma_refiner_gather_workspace_bytes(B, h, w, r) bytes (16-byte aligned), which enables, for
+ * 16-bit features on the aligned fast path:
+ *   r = 2, 3: the shared-patch tile kernel of path 0 above — one byte per 8 x 8 pixel tile, where it records the tiles it took so
+ *             that the per-pixel kernel launched after it skips them;
+ *   r = 7 on maps of <= 4096 positions (scale 16: 40 x 40, 48 x 48): the FULL correlation f0 . f1^T (B x hw x hw fp32 in the
+ *             workspace: 164 MB at B = 16, 40 x 40) as one TMA-fed tcgen05 GEMM, whatever the flow; the per-pixel kernel then
+ *             gathers its (2r+2)^2 = 256 products per pixel from its row instead of pulling 256 KB of features per pixel.
+ * 0 for other radii.  Without a workspace (or through roma_refiner_gather) every pixel takes the per-pixel kernel.  Same
+ * results either way up to the fp32 summation order of the correlations. */
 size_t roma_refiner_gather_workspace_bytes(int B, int h, int w, int r);
 int roma_refiner_gather_ws(const void* f0, const void* f1, const float* flow, roma_strides4 flow_strides,
                            const float* disp_w, const float* disp_b, float disp_scale,

@@ -23,6 +23,7 @@
 namespace roma {
 
 constexpr int kTileSide = 8, kTilePx = 64;      // shared-patch tiles of local_corr_tile.cuh
+constexpr int kScoresMaxTokens = 4096;          // r = 7: full-correlation GEMM up to 64 x 64 maps (workspace B * n^2 * 4 bytes)
 
 struct GatherParams {
     const void* f0; const void* f1; const float* flow; roma_strides4 fs;
@@ -33,6 +34,8 @@ struct GatherParams {
     int tile_px;     // pixels per CTA tile (local-corr kernel)
     int covered;     // channels written by the enabled segments; [covered, dch) is zero-filled pitch padding
     int dbg;         // timing aid for local_corr_tile_kernel (bit 0: no streaming segments, 1: no main loop, 2: no extraction, 3: no blend)
+    const float* scores;         // r = 7 on small maps: the FULL correlation f0 . f1^T (B, h*w, h1*w1) fp32 from one tensor-core GEMM; the
+                                 // per-pixel kernel then reads its (2r+2)^2 products from its row of it instead of computing them
     unsigned char* tile_flags;   // per 8 x 8 tile: 1 = computed by local_corr_tile_kernel (the per-pixel kernel skips its pixels); or null
     int tile_pw;     // > 0: 8 x 8 pixel tiles (grid = tiles_x, tiles_y, B); the per-pixel kernel SKIPS tiles whose windows fit
                      // a tile_pw x tile_pw patch (they are computed by local_corr_tile_kernel, local_corr_tile.cuh)
@@ -394,6 +397,15 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
     }
     __syncwarp();
     const T* f1b = f1 + (long long)b * p.h1 * p.w1 * p.C;
+    if (p.scores) {
+        const int n1 = p.h1 * p.w1;
+        const float* srow = p.scores + ((long long)b * p.h * p.w + (long long)y * p.w + x) * n1;
+        for (int n = lane; n < NN; n += 32) {
+            const int j = n / W2, i = n - j * W2;
+            const int yy = y0 + j - p.r, xx = x0 + i - p.r;
+            Dsm[n] = (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) ? __ldg(srow + yy * p.w1 + xx) : 0.f;
+        }
+    } else
     for (int n0 = 0; n0 < NN; n0 += 8) {
         // A-fragment rows 2j and 2j+1 are the two 64-byte halves of a 128-byte piece of neighbour n0 + j (rows
         // 8.. : neighbour n0 + 4 + j), so the 8 lanes of a quarter-warp read ONE full line per 16-byte load
@@ -922,6 +934,18 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
             p.tile_px = 32;
             const int grid = cdiv(p.npix, p.tile_px);
             if constexpr (sizeof(T) == 2) {
+                if (p.scores && g_local_corr_path.load() == 0) {
+                    // r = 7 on a small map: all (h w) x (h1 w1) products as ONE batched tcgen05 GEMM (TMA-fed, fp32 accumulate of the same
+                    // 16-bit products), whatever the flow; the per-pixel kernel below only gathers and blends
+                    tc::Launch L{};
+                    const int n0 = p.h * p.w, n1 = p.h1 * p.w1;
+                    L.p[0] = tc::make_problem(p.f0, p.f1, const_cast<float*>(p.scores), n0, n1, p.C, p.C, p.C, n1,
+                                              (long long)n0 * p.C, (long long)n1 * p.C, (long long)n0 * n1, tc::EPI_STORE);
+                    L.nprob = 1; L.tiles0 = L.p[0].tiles_m * L.p[0].tiles_n;
+                    const int rc = tc::launch_gemm_nt_16<T>(L, p.B, st, "roma_refiner_gather(full correlation)",
+                                                            std::is_same<T, __half>::value ? ROMA_F16 : ROMA_BF16);
+                    if (rc) return rc;
+                } else p.scores = nullptr;
                 if (g_local_corr_path.load() == 0 && p.tile_flags && (p.r == 2 || p.r == 3) && (p.C == 512 || p.C == 256) && p.h == p.h1 && p.w == p.w1 && p.off_corr >= 0) {
                     // shared-patch tiles (coherent flow) + per-pixel kernel for the tiles that decline (local_corr_tile.cuh)
                     const int rc = launch_tiled<T>(p, st);
@@ -1020,6 +1044,8 @@ extern "C" int roma_local_corr_set_path(int path) {
 }
 
 extern "C" size_t roma_refiner_gather_workspace_bytes(int B, int h, int w, int r) {
+    if (B > 0 && h > 0 && w > 0 && r == 7 && (long long)h * w <= roma::kScoresMaxTokens)          // full correlation (B, hw, hw) fp32
+        return ((size_t)B * h * w * h * w * sizeof(float) + 255) & ~(size_t)255;
     if (B <= 0 || h <= 0 || w <= 0 || (r != 2 && r != 3)) return 0;
     return ((size_t)B * ((h + roma::kTileSide - 1) / roma::kTileSide) * ((w + roma::kTileSide - 1) / roma::kTileSide) + 255) & ~(size_t)255;
 }
@@ -1072,8 +1098,10 @@ extern "C" int roma_refiner_gather_ws(const void* f0, const void* f1, const floa
     p.d = d; p.dch = d_channels; p.off_x = off_x; p.off_xhat = off_xhat; p.off_emb = off_emb; p.off_corr = off_corr;
     p.B = B; p.C = C; p.h = h; p.w = w; p.h1 = h1; p.w1 = w1; p.E = E; p.r = r;
     p.npix = (long long)B * h * w; p.tile_px = 0; p.covered = covered; p.tile_pw = 0; p.dbg = 0;
-    p.tile_flags = (workspace && workspace_bytes >= roma_refiner_gather_workspace_bytes(B, h, w, r) && roma_refiner_gather_workspace_bytes(B, h, w, r) > 0)
-                       ? reinterpret_cast<unsigned char*>(workspace) : nullptr;
+    const size_t need_ws = roma_refiner_gather_workspace_bytes(B, h, w, r);
+    const bool have_ws = workspace && need_ws > 0 && workspace_bytes >= need_ws && (reinterpret_cast<uintptr_t>(workspace) & 15u) == 0;
+    p.tile_flags = (have_ws && r != 7) ? reinterpret_cast<unsigned char*>(workspace) : nullptr;
+    p.scores = (have_ws && r == 7 && h == h1 && w == w1 && off_corr >= 0 && dtype != ROMA_F32 && C % 8 == 0) ? reinterpret_cast<const float*>(workspace) : nullptr;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (dtype) {
         case ROMA_F32:  return launch_gather<float>(p, st);

@@ -54,7 +54,8 @@ def _both_paths(ops, x, y, flow, dw, db, r):
         lib.roma_local_corr_set_path(0)
         n0 = lib.roma_kernel_launches()
         d_tile = ops.refiner_inputs(x, y, flow, dw, db, 1.25, r, pad_to=8)
-        assert lib.roma_kernel_launches() - n0 == (2 if x.shape[1] in (256, 512) else 1)     # tile kernel (writes the tile map) + per-pixel kernel
+        # r = 2, 3 at C = 256 / 512: tile kernel (writes the tile map) + per-pixel kernel; r = 7: full-correlation GEMM + per-pixel gather
+        assert lib.roma_kernel_launches() - n0 == (2 if (r == 7 or x.shape[1] in (256, 512)) else 1)
         lib.roma_local_corr_set_path(2)
         d_px = ops.refiner_inputs(x, y, flow, dw, db, 1.25, r, pad_to=8)
     finally:
@@ -64,7 +65,8 @@ def _both_paths(ops, x, y, flow, dw, db, r):
 
 @pytest.mark.parametrize("kind", ["coherent", "shifted", "mixed", "stretch", "incoherent"])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
-@pytest.mark.parametrize("C,r,h,w,E", [(512, 3, 108, 108, 64), (256, 2, 54, 75, 32), (64, 3, 21, 37, 0), (128, 2, 8, 8, 16)])
+@pytest.mark.parametrize("C,r,h,w,E", [(512, 3, 108, 108, 64), (256, 2, 54, 75, 32), (64, 3, 21, 37, 0), (128, 2, 8, 8, 16),
+                                       (512, 7, 40, 40, 128), (64, 7, 13, 19, 8)])
 def test_tile_kernel_vs_per_pixel_kernel_and_oracle(ops, cuda, C, r, h, w, E, dtype, kind):
     B = 2
     g = torch.Generator(device="cuda").manual_seed(C + r + h)
