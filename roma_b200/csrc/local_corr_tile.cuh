@@ -54,7 +54,7 @@ struct TileMaps { CUtensorMap f0, f1; };
 // red: 8 ints of shared scratch.
 __device__ __forceinline__ bool tile_window_fits(const GatherParams& p, int b, int ty0, int tx0, int pw, int* red,
                                                  bool& valid, int& x0, int& y0, float& wx0, float& wx1, float& wy0, float& wy1,
-                                                 float& gx, float& gy, int& X0, int& Y0) {
+                                                 float& gx, float& gy, int& X0, int& Y0, int* rows_needed = nullptr) {
     const int m = threadIdx.x;
     valid = false;
     x0 = y0 = 0; wx0 = wx1 = wy0 = wy1 = 0.f; gx = gy = 0.f;
@@ -78,6 +78,7 @@ __device__ __forceinline__ bool tile_window_fits(const GatherParams& p, int b, i
     lo_y = min(red[2], red[6]); hi_y = max(red[3], red[7]);
     const int W2 = 2 * p.r + 2;
     X0 = lo_x - p.r; Y0 = lo_y - p.r;
+    if (rows_needed) *rows_needed = lo_x == INT_MAX ? 0 : (int)min((long long)hi_y - lo_y + W2, (long long)pw);
     // a non-finite flow clamps to +-2^20 in sample_coords: the spans below then exceed any patch
     return lo_x != INT_MAX && (long long)hi_x - lo_x + W2 <= pw && (long long)hi_y - lo_y + W2 <= pw;
 }
@@ -141,7 +142,10 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tx0 = blockIdx.x * kTileSide, ty0 = blockIdx.y * kTileSide, b = blockIdx.z;
     bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
-    const bool fits = tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0);
+    int rows_needed = 0;
+    const bool fits = tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0, &rows_needed);
+    // row bands of the patch actually touched by the tile's windows: a smooth flow needs 2 of the 3
+    const int npass = min(G::NPASS, (rows_needed + G::ROWS - 1) / G::ROWS);
     // the verdict goes to the tile map: the per-pixel kernel that follows on the stream skips the pixels of the tiles taken here
     if (tid == 0) p.tile_flags[((long long)b * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = fits ? 1 : 0;
     if (!fits) return;
@@ -177,7 +181,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     if (p.dbg & 16) {
     } else if (warp == 0) {
         if (lane == 0) {                                         // ---- TMA producer ----
-            for (int it = 0; it < ((p.dbg & 2) ? 0 : G::NPASS * nkb); ++it) {
+            for (int it = 0; it < ((p.dbg & 2) ? 0 : npass * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
                 if (it >= 2) tc::mbar_wait(&empty_bar[s], (uint32_t)(((it >> 1) - 1) & 1));
                 unsigned char* sa = smem + (size_t)s * G::STAGE;
@@ -190,12 +194,12 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     } else if (warp == 1) {
         if (lane == 0) {                                         // ---- MMA issuer ----
             if (p.dbg & 2) {                                     // timing aid: no main loop (the products are garbage)
-                for (int pass = 0; pass < G::NPASS; ++pass) {
+                for (int pass = 0; pass < npass; ++pass) {
                     if (pass) tc::mbar_wait(&free_bar, (uint32_t)((pass - 1) & 1));
                     tc::umma_commit(&done_bar);
                 }
             }
-            for (int it = 0; it < ((p.dbg & 2) ? 0 : G::NPASS * nkb); ++it) {
+            for (int it = 0; it < ((p.dbg & 2) ? 0 : npass * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
                 if (pass > 0 && kb == 0) { tc::mbar_wait(&free_bar, (uint32_t)((pass - 1) & 1)); tc::tc_fence_after(); }   // previous band drained from TMEM
                 tc::mbar_wait(&full_bar[s], (uint32_t)((it >> 1) & 1));
@@ -302,7 +306,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
         const bool live = s_x0[m] != INT_MIN;
         float* Dm = Dwin + m * G::DSTRIDE;
         const uint32_t tlane = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
-        for (int pass = 0; pass < G::NPASS; ++pass) {
+        for (int pass = 0; pass < npass; ++pass) {
             tc::mbar_wait(&done_bar, (uint32_t)(pass & 1));
             tc::tc_fence_after();
             for (int qy = 0; qy < ((p.dbg & 4) ? 0 : G::ROWS); ++qy) {
@@ -320,7 +324,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
                 }
             }
             tc::tc_fence_before();
-            if (pass + 1 < G::NPASS) mbar_arrive(&free_bar);
+            if (pass + 1 < npass) mbar_arrive(&free_bar);
         }
     }
     tc::tc_fence_before();

@@ -556,13 +556,12 @@ static int launch_gemm_nt_16(const Launch& L, int batch, cudaStream_t st, const 
 }
 
 // ---------------------------------------------------------------------------------------------- split operands from planes
-// C = epi(A * B^T) for fp32-grade operands that already exist as bf16 hi / lo planes (written once by the epilogue of
-// the kernel that produced them): no conversion in the main loop.  Per 64-wide k-block three (A plane, B plane) pairs
-// travel through the ring — (hi, hi) into the main accumulator tile, (hi, lo) and (lo, hi) into the cross-term tile (TMEM
-// columns 128..255, see gemm_nt_kernel) — each pair = two SWIZZLE_128B boxes of 16 KB landed by TMA.  Warp-specialised
-// like gemm_nt_tma_kernel: warp 0 lane 0 produces, warp 1 lane 0 issues tcgen05.mma and releases stages by
-// tcgen05.commit, all 8 warps run the epilogue.  3 stages x 32 KB: two CTAs per SM, one tile's epilogue (EPI_SUB reads and
-// rewrites 64 KB of C) under the other's main loop.
+// C = epi(A * B^T) for fp32-grade operands that already exist as bf16 planes (hi, [mid,] lo — written once by the epilogue
+// of the kernel that produced them): no conversion in the main loop.  Per 64-wide k-block the planes of both operands land
+// in shared memory by TMA (SWIZZLE_128B boxes of 16 KB, K-major) and the plane pairs with i + j < SPLIT are multiplied:
+// (hi, hi) into the main accumulator tile, the others into the cross-term tile (TMEM columns 128..255, see gemm_nt_kernel).
+// Warp-specialised like gemm_nt_tma_kernel: warp 0 lane 0 produces, warp 1 lane 0 issues tcgen05.mma and releases the
+// stage by tcgen05.commit, all 8 warps run the epilogue (EPI_SUB reads and rewrites 64 KB of C; EPI_STORE may emit planes).
 struct PlaneMaps { CUtensorMap a[2][3], b[2][3]; };      // [problem][plane]
 // One stage = ALL planes of both operands for one 64-wide k-block (2 * SPLIT x 16 KB: 64 / 96 KB), so every plane is fetched
 // once per k-block (a first version moved one (A plane, B plane) pair per stage: 6 pairs = 12 plane loads per k-block at 3
