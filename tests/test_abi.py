@@ -28,6 +28,11 @@ def test_library_loads_and_exports_everything():
     assert lib.roma_gp_workspace_bytes(2, 1600, 1600, 512, 512) > 2 * 1600 * 1600 * 4
     assert lib.roma_kde_workspace_bytes(1000) >= 4000
     assert lib.roma_match_keypoints_workspace_bytes(10, 10) > 0
+    assert lib.roma_match_keypoints_static_max_points() == 16384
+    # tile map of the shared-patch local-correlation kernel (one byte per 8 x 8 tile); full correlation for r = 7; nothing otherwise
+    assert lib.roma_refiner_gather_workspace_bytes(16, 108, 108, 3) >= 16 * 14 * 14
+    assert lib.roma_refiner_gather_workspace_bytes(16, 40, 40, 7) >= 16 * 1600 * 1600 * 4
+    assert lib.roma_refiner_gather_workspace_bytes(16, 432, 432, 0) == 0 and lib.roma_refiner_gather_workspace_bytes(2, 100, 100, 7) == 0
 
 
 def test_bad_arguments_are_rejected_without_a_gpu():
