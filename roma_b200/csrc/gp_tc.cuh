@@ -67,8 +67,10 @@ posenc_t_kernel(float* __restrict__ R, const float* __restrict__ pw, const float
 constexpr int kDiagLd = kDB + 1;
 constexpr size_t kDiagSmem = (size_t)2 * kDB * kDiagLd * sizeof(float) + 32 * 33 * sizeof(float) + kDB * sizeof(float);
 
+// pre != 0: the block first receives the rank-128 update of the block column just finished, S -= L_{k,k-1} L_{k,k-1}^T (fp32
+// FMAs, lower triangle), which takes the syrk launch for THIS tile — and one cross-stream hand-off — off the dependent chain.
 __global__ void __launch_bounds__(256)
-diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0, long long sA, long long sLd, int kblk) {
+diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0, long long sA, long long sLd, int kblk, int pre) {
     extern __shared__ float dsm[];
     float (*S)[kDiagLd] = reinterpret_cast<float (*)[kDiagLd]>(dsm);
     float (*V)[kDiagLd] = reinterpret_cast<float (*)[kDiagLd]>(dsm + kDB * kDiagLd);
@@ -86,6 +88,46 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
         V[r][c] = 0.f; V[r][c + 1] = 0.f; V[r][c + 2] = 0.f; V[r][c + 3] = 0.f;
     }
     __syncthreads();
+    if (pre) {
+        const float* Lp = Ab - kDB;                                   // L_{k,k-1}: rows of this block, the 128 columns to its left
+        for (int e = tid; e < kDB * (kDB / 4); e += 256) {
+            const int r = e >> 5, c = (e & 31) * 4;
+            const float4 v = *reinterpret_cast<const float4*>(Lp + (long long)r * ld + c);
+            V[r][c] = v.x; V[r][c + 1] = v.y; V[r][c + 2] = v.z; V[r][c + 3] = v.w;
+        }
+        __syncthreads();
+        // 4 x 4 blocks of the lower triangle: 32 x 33 / 2 = 528 blocks over 256 threads
+        for (int e = tid; e < 528; e += 256) {
+            int rr = (int)((sqrtf(8.f * (float)e + 1.f) - 1.f) * 0.5f);
+            while (rr * (rr + 1) / 2 > e) --rr;
+            while ((rr + 1) * (rr + 2) / 2 <= e) ++rr;
+            const int cc = e - rr * (rr + 1) / 2;
+            const int r = rr * 4, c = cc * 4;
+            float acc[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 8
+            for (int t = 0; t < kDB; ++t) {
+                float ar[4], ac[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { ar[i] = V[r + i][t]; ac[i] = V[c + i][t]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(ar[i], ac[j], acc[i][j]);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (c + j <= r + i) S[r + i][c + j] -= acc[i][j];
+        }
+        __syncthreads();
+        for (int e = tid; e < kDB * kDB; e += 256) V[e >> 7][e & 127] = 0.f;
+        __syncthreads();
+    }
 
     for (int jb = 0; jb < 4; ++jb) {
         const int j0 = jb * 32;
@@ -222,8 +264,8 @@ diag_block_kernel(float* __restrict__ A, float* __restrict__ Ld, int ld, int k0,
 // is still "asynchronous on the passed stream" (and capturable into a CUDA graph).
 constexpr int kMaxLaneBlocks = 64;
 struct Lanes {
-    cudaStream_t chain = nullptr;
-    cudaEvent_t fork = nullptr, diag[kMaxLaneBlocks], upd[kMaxLaneBlocks], panel[kMaxLaneBlocks];
+    cudaStream_t chain = nullptr, abulk = nullptr;      // dependent chain (diag, panel A) / its feeders (update A, syrk)
+    cudaEvent_t fork = nullptr, diag[kMaxLaneBlocks], upd[kMaxLaneBlocks], panel[kMaxLaneBlocks], syrk[kMaxLaneBlocks];
     bool ok = false;
     std::mutex enqueue;   // held while one call enqueues its two-lane schedule: cudaStreamWaitEvent snapshots an event at call
                           // time, so whole-call mutual exclusion of the ENQUEUE makes concurrent host threads on one device safe
@@ -240,11 +282,13 @@ static Lanes* lanes_for_current_device() {
     int least = 0, greatest = 0;
     if (cudaDeviceGetStreamPriorityRange(&least, &greatest) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     if (cudaStreamCreateWithPriority(&l->chain, cudaStreamNonBlocking, greatest) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaStreamCreateWithPriority(&l->abulk, cudaStreamNonBlocking, greatest) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     bool ok = cudaEventCreateWithFlags(&l->fork, cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; ok && i < kMaxLaneBlocks; ++i)
         ok = cudaEventCreateWithFlags(&l->diag[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&l->upd[i], cudaEventDisableTiming) == cudaSuccess &&
-             cudaEventCreateWithFlags(&l->panel[i], cudaEventDisableTiming) == cudaSuccess;
+             cudaEventCreateWithFlags(&l->panel[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&l->syrk[i], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { cudaGetLastError(); return nullptr; }
     l->ok = true;
     return l;
@@ -337,80 +381,97 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
     std::unique_lock<std::mutex> lanes_lock;
     if (lanes) {
         lanes_lock = std::unique_lock<std::mutex>(lanes->enqueue);
-        // 3'. two-lane schedule.  Diagonal tiles are kept up to date right-looking (syrk after every panel), the rest of
-        //     the block column and the right-hand sides left-looking, one step behind the chain.
-        //       chain (sc):  diag(k) . [wait upd(k)] panel_A(k) . syrk(k)
-        //       bulk  (st):  [wait panel(k-1)] update_off(k): A[k+1:, k] and R[:, k] . [wait diag(k)] panel_R(k)
-        cudaStream_t sc = lanes->chain;
+        // 3'. two-lane schedule.  Diagonal tiles are kept up to date right-looking, the rest of the block column and the
+        //     right-hand sides left-looking, one step behind the chain.  The chain holds two launches per step:
+        //       chain  (sc):  [wait syrk(k-2)] diag(k) (+ its own rank-128 update from column k-1) . [wait upd(k)] panel_A(k)
+        //       feeder (sb):  [wait panel(k-1)] update_A(k): A[k+1:, k] . syrk(k-1): diagonal tiles i >= k+1
+        //       caller (st):  [wait panel(k-1)] update_R(k): R[:, k] . [wait diag(k)] panel_R(k)   — the right-hand sides only trail
+        //     (round 1 / early round 2: syrk(k) sat on the chain between panel_A(k) and diag(k+1), and update_A waited behind
+        //     the 17 right-hand-side tiles of the same launch.)
+        cudaStream_t sc = lanes->chain, sb = lanes->abulk;
 #define ROMA_CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail((int)e_, "gp lanes: %s", cudaGetErrorString(e_)); } while (0)
         ROMA_CU(cudaEventRecord(lanes->fork, st));
         ROMA_CU(cudaStreamWaitEvent(sc, lanes->fork, 0));
+        ROMA_CU(cudaStreamWaitEvent(sb, lanes->fork, 0));
         for (int k = 0; k < nb; ++k) {
             const int k0 = k * kDB, rem = Mp - k0 - kDB;
             const float* Lk = w.A + (long long)k0 * Mp;                 // L_{k,0:k}: 128 rows x k0
             const float* Linv = w.Ld + (long long)k * kDB * kDB;
             float* Ap = w.A + (long long)(k0 + kDB) * Mp + k0;          // block column k below the diagonal
-            diag_block_kernel<<<B, 256, kDiagSmem, sc>>>(w.A, w.Ld, Mp, k0, sA, sLd, k);
+            const long long offL = (long long)k0 * Mp;
+            // ---- chain: diag(k) with the rank-128 update of column k-1 folded in; it needs the syrk of columns <= k-2 (bulk) ----
+            if (k >= 2) ROMA_CU(cudaStreamWaitEvent(sc, lanes->syrk[k - 2], 0));
+            diag_block_kernel<<<B, 256, kDiagSmem, sc>>>(w.A, w.Ld, Mp, k0, sA, sLd, k, k > 0 ? 1 : 0);
             if ((rc = check_launch("gp diag"))) return rc;
             ROMA_CU(cudaEventRecord(lanes->diag[k], sc));
+            // ---- bulk: the part of the left-looking update that gates the chain first: A[k+1:, k] -= L[k+1:, 0:k] L[k, 0:k]^T ----
             if (k > 0) {
-                ROMA_CU(cudaStreamWaitEvent(st, lanes->panel[k - 1], 0));       // L[:, 0:k] complete
-                Launch L{};
-                int np = 0;
+                ROMA_CU(cudaStreamWaitEvent(sb, lanes->panel[k - 1], 0));       // L[:, 0:k] complete
+                ROMA_CU(cudaStreamWaitEvent(st, lanes->panel[k - 1], 0));
                 if (rem > 0) {
-                    L.p[np] = make_problem(Lk + (long long)kDB * Mp, Lk, Ap, rem, kDB, k0, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
-                    L.tiles0 = L.p[np].tiles_m;
-                    ++np;
-                }
-                L.p[np] = make_problem(w.R, Lk, w.R + k0, RR, kDB, k0, Mp, Mp, Mp, sR, sA, sR, EPI_SUB);
-                if (np == 0) L.tiles0 = L.p[0].tiles_m;
-                L.nprob = np + 1;
-                bool done = false;
-                if (planes) {
-                    // operands from the planes: L[k0+128:, 0:k0] / R[:, 0:k0] against L[k0:k0+128, 0:k0]
-                    const long long offL = (long long)k0 * Mp;
-                    int q = 0;
-                    if (rem > 0) {
-                        for (int s = 0; s < SOLVE_SPLIT; ++s) { L.p[q].Apl[s] = w.Apl[s] + offL + (long long)kDB * Mp; L.p[q].Bpl[s] = w.Apl[s] + offL; }
-                        ++q;
+                    Launch L{};
+                    L.p[0] = make_problem(Lk + (long long)kDB * Mp, Lk, Ap, rem, kDB, k0, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
+                    L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
+                    bool done = false;
+                    if (planes) {
+                        for (int q = 0; q < SOLVE_SPLIT; ++q) { L.p[0].Apl[q] = w.Apl[q] + offL + (long long)kDB * Mp; L.p[0].Bpl[q] = w.Apl[q] + offL; }
+                        if ((rc = launch_gemm_planes<SOLVE_SPLIT>(L, B, sb, "gp update A (planes)", &done))) return rc;
                     }
-                    for (int s = 0; s < SOLVE_SPLIT; ++s) { L.p[q].Apl[s] = w.Rpl[s]; L.p[q].Bpl[s] = w.Apl[s] + offL; }
-                    if ((rc = launch_gemm_planes<SOLVE_SPLIT>(L, B, st, "gp update (planes)", &done))) return rc;
+                    if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, sb, "gp update A"))) return rc;
                 }
-                if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update"))) return rc;
-                ROMA_CU(cudaEventRecord(lanes->upd[k], st));
+                ROMA_CU(cudaEventRecord(lanes->upd[k], sb));
             }
+            // ---- chain: panel A(k) ----
             if (rem > 0) {
                 if (k > 0) ROMA_CU(cudaStreamWaitEvent(sc, lanes->upd[k], 0));
                 Launch L{};
                 L.p[0] = make_problem(Ap, Linv, Ap, rem, kDB, kDB, Mp, kDB, Mp, sA, sLd, sA, EPI_STORE);
                 const long long offP = (long long)(k0 + kDB) * Mp + k0;
-                if (planes) { L.p[0].nplanes = SOLVE_SPLIT; for (int s = 0; s < SOLVE_SPLIT; ++s) L.p[0].Pout[s] = w.Apl[s] + offP; }   // the finished panel, split once
+                if (planes) { L.p[0].nplanes = SOLVE_SPLIT; for (int q = 0; q < SOLVE_SPLIT; ++q) L.p[0].Pout[q] = w.Apl[q] + offP; }   // the finished panel, split once
                 L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
                 if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, sc, "gp panel A"))) return rc;
                 ROMA_CU(cudaEventRecord(lanes->panel[k], sc));
-                Launch S{};                                             // A_ii -= L_ik L_ik^T for every i > k
-                S.p[0] = make_problem(Ap, Ap, w.A + (long long)(k0 + kDB) * Mp + (k0 + kDB), rem, rem, kDB, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
-                S.p[0].diag_only = 1;
-                S.nprob = 1; S.tiles0 = S.p[0].tiles_m;
+            }
+            // ---- bulk: diagonal tiles i >= k+1 -= L_{i,k-1} L_{i,k-1}^T (tile k took its own update inside diag(k)) ----
+            if (k > 0) {
+                if (rem > 0) {
+                    float* Aq = w.A + (long long)(k0 + kDB) * Mp + (k0 - kDB);      // block column k-1, rows below block k
+                    const long long offQ = (long long)(k0 + kDB) * Mp + (k0 - kDB);
+                    Launch S{};
+                    S.p[0] = make_problem(Aq, Aq, w.A + (long long)(k0 + kDB) * Mp + (k0 + kDB), rem, rem, kDB, Mp, Mp, Mp, sA, sA, sA, EPI_SUB);
+                    S.p[0].diag_only = 1;
+                    S.nprob = 1; S.tiles0 = S.p[0].tiles_m;
+                    bool done = false;
+                    if (planes) {
+                        for (int q = 0; q < SOLVE_SPLIT; ++q) S.p[0].Apl[q] = S.p[0].Bpl[q] = w.Apl[q] + offQ;
+                        if ((rc = launch_gemm_planes<SOLVE_SPLIT>(S, B, sb, "gp syrk (planes)", &done))) return rc;
+                    }
+                    if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(S, B, sb, "gp syrk"))) return rc;
+                }
+                ROMA_CU(cudaEventRecord(lanes->syrk[k - 1], sb));
+                // ---- bulk: right-hand sides R[:, k] -= R[:, 0:k] L[k, 0:k]^T ----
+                Launch L{};
+                L.p[0] = make_problem(w.R, Lk, w.R + k0, RR, kDB, k0, Mp, Mp, Mp, sR, sA, sR, EPI_SUB);
+                L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
                 bool done = false;
                 if (planes) {
-                    for (int s = 0; s < SOLVE_SPLIT; ++s) S.p[0].Apl[s] = S.p[0].Bpl[s] = w.Apl[s] + offP;
-                    if ((rc = launch_gemm_planes<SOLVE_SPLIT>(S, B, sc, "gp syrk (planes)", &done))) return rc;
+                    for (int q = 0; q < SOLVE_SPLIT; ++q) { L.p[0].Apl[q] = w.Rpl[q]; L.p[0].Bpl[q] = w.Apl[q] + offL; }
+                    if ((rc = launch_gemm_planes<SOLVE_SPLIT>(L, B, st, "gp update R (planes)", &done))) return rc;
                 }
-                if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(S, B, sc, "gp syrk"))) return rc;
+                if (!done && (rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update R"))) return rc;
             }
             ROMA_CU(cudaStreamWaitEvent(st, lanes->diag[k], 0));
             {
                 Launch L{};
                 L.p[0] = make_problem(w.R + k0, Linv, w.R + k0, RR, kDB, kDB, Mp, kDB, Mp, sR, sLd, sR, EPI_STORE);
-                if (planes) { L.p[0].nplanes = SOLVE_SPLIT; for (int s = 0; s < SOLVE_SPLIT; ++s) L.p[0].Pout[s] = w.Rpl[s] + k0; }
+                if (planes) { L.p[0].nplanes = SOLVE_SPLIT; for (int q = 0; q < SOLVE_SPLIT; ++q) L.p[0].Pout[q] = w.Rpl[q] + k0; }
                 L.nprob = 1; L.tiles0 = L.p[0].tiles_m;
                 if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp panel R"))) return rc;
             }
         }
+        if (nb >= 2) ROMA_CU(cudaStreamWaitEvent(st, lanes->syrk[nb - 2], 0));          // join the feeder lane (its last record)
 #undef ROMA_CU
-        // the chain's last operation is diag(nb-1), which panel_R(nb-1) waited for: the lanes are joined
+        // the chain's last operation is diag(nb-1), which panel_R(nb-1) waited for: all lanes are joined
     } else
     // 3. left-looking blocked Cholesky with the transposed right-hand sides riding along
     for (int k = 0; k < nb; ++k) {
@@ -423,7 +484,7 @@ static int run_tc(const T* x, const T* y, const float* pos_w, const float* pos_b
             L.nprob = 2; L.tiles0 = L.p[0].tiles_m;
             if ((rc = launch_gemm_nt<float, SOLVE_SPLIT>(L, B, st, "gp update"))) return rc;
         }
-        diag_block_kernel<<<B, 256, kDiagSmem, st>>>(w.A, w.Ld, Mp, k0, sA, sLd, k);
+        diag_block_kernel<<<B, 256, kDiagSmem, st>>>(w.A, w.Ld, Mp, k0, sA, sLd, k, 0);
         if ((rc = check_launch("gp diag"))) return rc;
         {
             const float* Linv = w.Ld + (long long)k * kDB * kDB;
