@@ -176,10 +176,11 @@ size_t roma_gp_workspace_bytes(int B, int Nx, int Ny, int C, int D);
  * when it cannot be used); 3 = tcgen05 path with a TWO-plane solve (3 instead of 6 MMAs per k-step, ~2^-16 relative
  * products: 20 % faster, measurably less accurate — opt-in). */
 int roma_gp_set_path(int path);
-/* Schedule of the tcgen05 factorisation: 1 (default) = two lanes — the dependent chain diag -> panel -> syrk of the
- * blocked Cholesky on a high-priority helper stream owned by the library (one per device), the block-column
- * updates and all right-hand-side work one step behind on the caller's stream, ordered by events, forked from and
- * joined to the caller's stream inside the call; 0 = every launch on the caller's stream (left-looking). */
+/* Schedule of the tcgen05 factorisation: 1 (default) = lanes — the dependent chain of the blocked Cholesky (diag, which also
+ * applies the rank-128 update of the previous block column to its own tile, and panel A) on a high-priority helper stream,
+ * its feeders (update of the next block column, syrk of the remaining diagonal tiles) on a second one — both owned by the
+ * library, one pair per device — and all right-hand-side work trailing on the caller's stream; ordered by events, forked
+ * from and joined to the caller's stream inside the call; 0 = every launch on the caller's stream (left-looking). */
 int roma_gp_set_lanes(int on);
 /* 1 (default): the finished panels of the factorisation (L and the solved right-hand sides) are ALSO written as bf16 hi / lo planes
  * by the panel kernels' epilogue, and the update / syrk / posterior GEMMs read those planes through TMA with no conversion
