@@ -368,11 +368,14 @@ template <> struct Mma16816<float> {
 
 // One pixel by one warp: the body shared by the flat per-pixel kernel and the incoherent tiles of local_corr_tile_kernel.
 // Dsm: (2r+2)^2 floats, f0w: 64 * VPL elements (16-byte aligned), both private to the warp.
-template <typename T, int VPL>
+// R > 0: the radius is a compile-time constant (2, 3: the loop over the (2r+2)^2 neighbours is unrolled, so the loads of
+// several groups of 8 neighbours are in flight together and the / W2, % W2 index arithmetic folds away); R = 0: p.r at run time.
+template <typename T, int VPL, int R = 0>
 __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long pix, int lane, float* Dsm, T* f0w) {
     static_assert(sizeof(T) == 2, "local_corr_mma is for 16-bit feature types");
     const int g = lane >> 2, t4 = lane & 3;
-    const int W2 = 2 * p.r + 2, NN = W2 * W2, K1 = 2 * p.r + 1, K = K1 * K1;
+    const int r_ = R > 0 ? R : p.r;
+    const int W2 = 2 * r_ + 2, NN = W2 * W2, K1 = 2 * r_ + 1, K = K1 * K1;
     const float inv_sqrt_c = rsqrtf((float)p.C);
     const T* f0 = reinterpret_cast<const T*>(p.f0);
     const T* f1 = reinterpret_cast<const T*>(p.f1);
@@ -402,11 +405,12 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
         const float* srow = p.scores + ((long long)b * p.h * p.w + (long long)y * p.w + x) * n1;
         for (int n = lane; n < NN; n += 32) {
             const int j = n / W2, i = n - j * W2;
-            const int yy = y0 + j - p.r, xx = x0 + i - p.r;
+            const int yy = y0 + j - r_, xx = x0 + i - r_;
             Dsm[n] = (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) ? __ldg(srow + yy * p.w1 + xx) : 0.f;
         }
     } else
-    for (int n0 = 0; n0 < NN; n0 += 8) {
+#pragma unroll
+    for (int n0 = 0; n0 < (R > 0 ? (2 * R + 2) * (2 * R + 2) : NN); n0 += 8) {
         // A-fragment rows 2j and 2j+1 are the two 64-byte halves of a 128-byte piece of neighbour n0 + j (rows
         // 8.. : neighbour n0 + 4 + j), so the 8 lanes of a quarter-warp read ONE full line per 16-byte load
         // (4 L1 wavefronts per instruction, not 8).  The B fragment carries the matching f0 channels in the
@@ -417,7 +421,7 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
         for (int hr = 0; hr < 2; ++hr) {
             const int n = n0 + (g >> 1) + 4 * hr;
             const int j = n / W2, i = n - j * W2;
-            const int yy = y0 + j - p.r, xx = x0 + i - p.r;
+            const int yy = y0 + j - r_, xx = x0 + i - r_;
             const bool ok = n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
             src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + 32 * (g & 1) + t4 * 8 : nullptr;
         }
@@ -488,7 +492,7 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
     __syncwarp();
 }
 
-template <typename T, int VPL>
+template <typename T, int VPL, int R = 0>
 __global__ void __launch_bounds__(256, 2)
 local_corr_mma_kernel(const GatherParams p) {
     constexpr int kMaxNN = 256;                  // (2r+2)^2 for r <= 7
@@ -517,7 +521,7 @@ local_corr_mma_kernel(const GatherParams p) {
     for (int lp = warp; lp < tile_n; lp += 8) {
         const long long pix = tile_start + lp;
         if ((skip >> (lp >> 3)) & 1u) continue;
-        local_corr_px<T, VPL>(p, pix, lane, Dall[warp], f0s[warp]);
+        local_corr_px<T, VPL, R>(p, pix, lane, Dall[warp], f0s[warp]);
     }
 }
 
@@ -714,8 +718,8 @@ static int launch_tiled_r(GatherParams p, cudaStream_t st, int dtype) {
     p.tile_px = 32;
     const int gpx = cdiv(p.npix, p.tile_px);
     switch (p.C) {
-        case 512: local_corr_mma_kernel<T, 8><<<gpx, 256, 0, st>>>(p); break;
-        default:  local_corr_mma_kernel<T, 4><<<gpx, 256, 0, st>>>(p); break;
+        case 512: local_corr_mma_kernel<T, 8, R><<<gpx, 256, 0, st>>>(p); break;
+        default:  local_corr_mma_kernel<T, 4, R><<<gpx, 256, 0, st>>>(p); break;
     }
     return check_launch("roma_refiner_gather(local_corr_tile + local_corr_mma)", 2);
 }
@@ -953,6 +957,8 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
                 }
                 p.tile_flags = nullptr;
                 if (g_local_corr_path.load() == 0 || g_local_corr_path.load() == 2) {
+                    if (p.r == 3 && p.C == 512 && !p.scores) { local_corr_mma_kernel<T, 8, 3><<<grid, 256, 0, st>>>(p); return check_launch("roma_refiner_gather(local_corr_mma)"); }
+                    if (p.r == 2 && p.C == 256 && !p.scores) { local_corr_mma_kernel<T, 4, 2><<<grid, 256, 0, st>>>(p); return check_launch("roma_refiner_gather(local_corr_mma)"); }
                     switch (p.C) {
                         case 512: local_corr_mma_kernel<T, 8><<<grid, 256, 0, st>>>(p); break;
                         case 256: local_corr_mma_kernel<T, 4><<<grid, 256, 0, st>>>(p); break;
