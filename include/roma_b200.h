@@ -99,8 +99,8 @@ int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_
                         void* stream);
 /* The same call with a workspace of roma_refiner_gather_workspace_bytes(B, h, w, r) bytes (16-byte aligned), which enables, for
  * 16-bit features on the aligned fast path:
- *   r = 2, 3: the shared-patch tile kernel of path 0 above — one byte per 8 x 8 pixel tile, where it records the tiles it took so
- *             that the per-pixel kernel launched after it skips them;
+ *   r = 2, 3: the shared-patch tile kernel of path 0 above — one byte per 8 x 8 pixel tile (the tile map: which tiles the tile
+ *             kernel takes, so that the per-pixel kernel launched after it skips them);
  *   r = 7 on maps of <= 4096 positions (scale 16: 40 x 40, 48 x 48): the FULL correlation f0 . f1^T (B x hw x hw fp32 in the
  *             workspace: 164 MB at B = 16, 40 x 40) as one TMA-fed tcgen05 GEMM, whatever the flow; the per-pixel kernel then
  *             gathers its (2r+2)^2 = 256 products per pixel from its row instead of pulling 256 KB of features per pixel.

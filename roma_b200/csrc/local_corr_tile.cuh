@@ -13,8 +13,9 @@
 // the shared bilinear weights exactly like the per-pixel kernels.  ~13 KB per pixel through L2 instead of 64 + 4.
 //
 // Tiles whose windows do not fit the patch (incoherent flow, flow discontinuities, non-finite flow) are left to the
-// per-pixel kernel: this kernel writes one byte per tile (taken / declined) into a caller-provided tile map and the
-// per-pixel kernel, launched next on the stream in its usual flat form, skips the pixels of the taken tiles.  (Tried and
+// per-pixel kernel: tile_verdict_kernel (64 threads per tile) writes one byte per tile (taken / declined) into a tile map in
+// the caller's workspace; this kernel's CTAs (one per tile, raster order) exit at once on a declined tile; the per-pixel
+// kernel, launched next in its usual flat form, skips the pixels of the taken tiles.  (Tried and
 // measured: the per-pixel kernel re-deriving the verdict per tile — its ~35 k CTAs that only exit cost 0.17 / 0.8 ms at
 // s8' / s4'; the per-pixel form folded into this kernel — its 100 KB of shared memory per CTA shrink the L1 the
 // per-pixel form lives on: 0.85 -> 1.38 ms at s8' on incoherent flows.)
@@ -126,9 +127,26 @@ __host__ __device__ constexpr uint32_t instr_desc_n(uint32_t fmt, uint32_t n) {
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 
+// One CTA of 64 threads per tile: the verdict (tile map byte).  Thousands of these CTAs are resident at once, so the verdicts
+// of an all-incoherent field (random-init weights) cost ~7 us; the tile kernel's CTAs then exit on their first (one-byte) load
+// instead of each loading its tile's 64 flow vectors and reducing them under a 100-KB-shared-memory residency of two per SM.
+// (Tried: a compact work list appended with atomicAdd — the list comes out in the arrival order of ~3000 concurrently
+// resident verdict CTAs, i.e. scrambled over all batch elements, and the tile kernel lost its L2 locality: 0.52 -> 0.75 ms.)
+__global__ void __launch_bounds__(64)
+tile_verdict_kernel(const GatherParams p, int pw) {
+    __shared__ int red[8];
+    bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
+    const bool fits = tile_window_fits(p, blockIdx.z, blockIdx.y * kTileSide, blockIdx.x * kTileSide, pw, red,
+                                       valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0);
+    if (threadIdx.x == 0) {
+        const int tile = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        p.tile_flags[tile] = fits ? 1 : 0;
+    }
+}
+
 template <typename T, int R>
 __global__ void __launch_bounds__(256, 2)
-local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps maps) {
+local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps maps, int tiles_x, int tiles_y) {
     using G = TileGeom<R>;
     static_assert(sizeof(T) == 2, "16-bit features");
     extern __shared__ unsigned char smem_raw[];
@@ -140,23 +158,11 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     __shared__ float2 s_g[kTilePx];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int tx0 = blockIdx.x * kTileSide, ty0 = blockIdx.y * kTileSide, b = blockIdx.z;
-    bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
-    int rows_needed = 0;
-    const bool fits = tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0, &rows_needed);
-    // row bands of the patch actually touched by the tile's windows: a smooth flow needs 2 of the 3
-    const int npass = min(G::NPASS, (rows_needed + G::ROWS - 1) / G::ROWS);
-    // the verdict goes to the tile map: the per-pixel kernel that follows on the stream skips the pixels of the tiles taken here
-    if (tid == 0) p.tile_flags[((long long)b * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = fits ? 1 : 0;
-    if (!fits) return;
-    if (tid < kTilePx) {
-        s_x0[tid] = valid ? x0 : INT_MIN; s_y0[tid] = y0;
-        s_w[tid][0] = wx0; s_w[tid][1] = wx1; s_w[tid][2] = wy0; s_w[tid][3] = wy1;
-        s_g[tid] = make_float2(gx, gy);
-    }
+    if (!p.tile_flags[blockIdx.x]) return;                        // declined by tile_verdict_kernel: the per-pixel kernel's
     unsigned char* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     float* Dwin = reinterpret_cast<float*>(smem + 2 * (size_t)G::STAGE);
-    const int nkb = p.C / 64;
+    const int nkb = p.C / 64;                                     // even (C = 256, 512): every tile uses each ring stage an even
+                                                                  // number of times, so the full / empty parities restart at 0
     constexpr uint32_t kFmt = std::is_same<T, __half>::value ? 0u : 1u;
     constexpr uint32_t idesc = instr_desc_n(kFmt, (uint32_t)G::NPAD);
     constexpr uint32_t kTmemCols = 256;
@@ -177,6 +183,24 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     const T* f0 = reinterpret_cast<const T*>(p.f0);
     const T* f1 = reinterpret_cast<const T*>(p.f1);
     T* dout = reinterpret_cast<T*>(p.d);
+    uint32_t done_base = 0, free_base = 0;                        // phases of done_bar / free_bar consumed by earlier tiles
+
+    // one tile per CTA, raster order (x fastest, then y, then batch element): neighbouring tiles run together and share
+    // their overlapping patches in the L2.  (The loop form is kept for experiments with persistent grids.)
+    for (int tile = blockIdx.x; tile == (int)blockIdx.x; tile += gridDim.x) {
+    const int b = tile / (tiles_x * tiles_y), trem = tile - b * tiles_x * tiles_y;
+    const int ty0 = (trem / tiles_x) * kTileSide, tx0 = (trem % tiles_x) * kTileSide;
+    bool valid; int x0, y0, X0, Y0; float wx0, wx1, wy0, wy1, gx, gy;
+    int rows_needed = 0;
+    tile_window_fits(p, b, ty0, tx0, G::PW, red, valid, x0, y0, wx0, wx1, wy0, wy1, gx, gy, X0, Y0, &rows_needed);
+    // row bands of the patch actually touched by the tile's windows: a smooth flow needs 2 of the 3
+    const int npass = min(G::NPASS, (rows_needed + G::ROWS - 1) / G::ROWS);
+    if (tid < kTilePx) {
+        s_x0[tid] = valid ? x0 : INT_MIN; s_y0[tid] = y0;
+        s_w[tid][0] = wx0; s_w[tid][1] = wx1; s_w[tid][2] = wy0; s_w[tid][3] = wy1;
+        s_g[tid] = make_float2(gx, gy);
+    }
+    __syncthreads();
 
     if (p.dbg & 16) {
     } else if (warp == 0) {
@@ -195,13 +219,13 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
         if (lane == 0) {                                         // ---- MMA issuer ----
             if (p.dbg & 2) {                                     // timing aid: no main loop (the products are garbage)
                 for (int pass = 0; pass < npass; ++pass) {
-                    if (pass) tc::mbar_wait(&free_bar, (uint32_t)((pass - 1) & 1));
+                    if (pass) tc::mbar_wait(&free_bar, (free_base + (uint32_t)(pass - 1)) & 1u);
                     tc::umma_commit(&done_bar);
                 }
             }
             for (int it = 0; it < ((p.dbg & 2) ? 0 : npass * nkb); ++it) {
                 const int s = it & 1, pass = it / nkb, kb = it - pass * nkb;
-                if (pass > 0 && kb == 0) { tc::mbar_wait(&free_bar, (uint32_t)((pass - 1) & 1)); tc::tc_fence_after(); }   // previous band drained from TMEM
+                if (pass > 0 && kb == 0) { tc::mbar_wait(&free_bar, (free_base + (uint32_t)(pass - 1)) & 1u); tc::tc_fence_after(); }   // previous band drained from TMEM
                 tc::mbar_wait(&full_bar[s], (uint32_t)((it >> 1) & 1));
                 tc::tc_fence_after();
                 const uint32_t a0 = tc::smem_u32(smem + (size_t)s * G::STAGE), b0 = a0 + G::AOFF;
@@ -307,7 +331,7 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
         float* Dm = Dwin + m * G::DSTRIDE;
         const uint32_t tlane = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
         for (int pass = 0; pass < npass; ++pass) {
-            tc::mbar_wait(&done_bar, (uint32_t)(pass & 1));
+            tc::mbar_wait(&done_bar, (done_base + (uint32_t)pass) & 1u);
             tc::tc_fence_after();
             for (int qy = 0; qy < ((p.dbg & 4) ? 0 : G::ROWS); ++qy) {
                 constexpr int NL = (G::PW + 3) / 4;
@@ -329,7 +353,8 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
     }
     tc::tc_fence_before();
     __syncthreads();
-    if (warp == 0 && !(p.dbg & 32)) tc::tmem_dealloc(tmem_base, kTmemCols);
+    tc::tc_fence_after();
+    done_base += (uint32_t)npass; free_base += (uint32_t)(npass - 1);
     // ---- blend: corr[ky][kx] = wy0 (wx0 D[ky][kx] + wx1 D[ky][kx+1]) + wy1 (wx0 D[ky+1][kx] + wx1 D[ky+1][kx+1]) ----
     if (p.off_corr >= 0 && !(p.dbg & 8)) {
         const float inv_sqrt_c = rsqrtf((float)p.C);
@@ -344,6 +369,11 @@ local_corr_tile_kernel(const GatherParams p, const __grid_constant__ TileMaps ma
             dout[(((long long)b * p.h + y) * p.w + x) * p.dch + p.off_corr + k] = Elem<T>::from_f(c * inv_sqrt_c);
         }
     }
+    __syncthreads();                                              // Dwin / s_* are rewritten by the next tile
+    }   // tile
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0 && !(p.dbg & 32)) tc::tmem_dealloc(tmem_base, kTmemCols);
 }
 
 }  // namespace roma

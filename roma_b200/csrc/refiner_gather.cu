@@ -713,15 +713,19 @@ static int launch_tiled_r(GatherParams p, cudaStream_t st, int dtype) {
     }
     p.tile_pw = G::PW;
     p.dbg = g_tile_dbg.load();
-    const dim3 grid((unsigned)cdiv(p.w, kTileSide), (unsigned)cdiv(p.h, kTileSide), (unsigned)p.B);
-    local_corr_tile_kernel<T, R><<<grid, 256, G::SMEM, st>>>(p, maps);
+    const int tiles_x = cdiv(p.w, kTileSide), tiles_y = cdiv(p.h, kTileSide);
+    const long long ntiles = (long long)p.B * tiles_x * tiles_y;
+    if (ntiles >= (1ll << 31)) return ROMA_ERR_UNSUPPORTED;
+    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)p.B);
+    tile_verdict_kernel<<<grid, 64, 0, st>>>(p, G::PW);
+    local_corr_tile_kernel<T, R><<<(unsigned)ntiles, 256, G::SMEM, st>>>(p, maps, tiles_x, tiles_y);
     p.tile_px = 32;
     const int gpx = cdiv(p.npix, p.tile_px);
     switch (p.C) {
         case 512: local_corr_mma_kernel<T, 8, R><<<gpx, 256, 0, st>>>(p); break;
         default:  local_corr_mma_kernel<T, 4, R><<<gpx, 256, 0, st>>>(p); break;
     }
-    return check_launch("roma_refiner_gather(local_corr_tile + local_corr_mma)", 2);
+    return check_launch("roma_refiner_gather(tile_verdict + local_corr_tile + local_corr_mma)", 3);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1045,7 +1049,7 @@ static int launch_gather(GatherParams p, cudaStream_t st) {
 extern "C" int roma_local_corr_set_path(int path) {
     if (path < 0 || (path & 0xff) > 2 || (path >> 8) > 63) return roma::fail(ROMA_ERR_BAD_ARG, "roma_local_corr_set_path: path %d (0 default, 1 SIMT, 2 per-pixel tensor-core only)", path);
     roma::g_local_corr_path.store(path & 0xff);
-    roma::g_tile_dbg.store(path >> 8);
+    roma::g_tile_dbg.store((path >> 8) & 63);
     return ROMA_OK;
 }
 
@@ -1053,7 +1057,8 @@ extern "C" size_t roma_refiner_gather_workspace_bytes(int B, int h, int w, int r
     if (B > 0 && h > 0 && w > 0 && r == 7 && (long long)h * w <= roma::kScoresMaxTokens)          // full correlation (B, hw, hw) fp32
         return ((size_t)B * h * w * h * w * sizeof(float) + 255) & ~(size_t)255;
     if (B <= 0 || h <= 0 || w <= 0 || (r != 2 && r != 3)) return 0;
-    return ((size_t)B * ((h + roma::kTileSide - 1) / roma::kTileSide) * ((w + roma::kTileSide - 1) / roma::kTileSide) + 255) & ~(size_t)255;
+    const size_t ntiles = (size_t)B * ((h + roma::kTileSide - 1) / roma::kTileSide) * ((w + roma::kTileSide - 1) / roma::kTileSide);
+    return (ntiles + 255) & ~(size_t)255;                                                            // tile map
 }
 
 extern "C" int roma_refiner_gather(const void* f0, const void* f1, const float* flow, roma_strides4 fs,

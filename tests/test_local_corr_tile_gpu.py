@@ -54,8 +54,9 @@ def _both_paths(ops, x, y, flow, dw, db, r):
         lib.roma_local_corr_set_path(0)
         n0 = lib.roma_kernel_launches()
         d_tile = ops.refiner_inputs(x, y, flow, dw, db, 1.25, r, pad_to=8)
-        # r = 2, 3 at C = 256 / 512: tile kernel (writes the tile map) + per-pixel kernel; r = 7: full-correlation GEMM + per-pixel gather
-        assert lib.roma_kernel_launches() - n0 == (2 if (r == 7 or x.shape[1] in (256, 512)) else 1)
+        # r = 2, 3 at C = 256 / 512: verdict kernel (tile map + work list) + persistent tile kernel + per-pixel kernel;
+        # r = 7: full-correlation GEMM + per-pixel gather
+        assert lib.roma_kernel_launches() - n0 == (2 if r == 7 else 3 if x.shape[1] in (256, 512) else 1)
         lib.roma_local_corr_set_path(2)
         d_px = ops.refiner_inputs(x, y, flow, dw, db, 1.25, r, pad_to=8)
     finally:
