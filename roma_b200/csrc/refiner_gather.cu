@@ -426,18 +426,22 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
             src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + 32 * (g & 1) + t4 * 8 : nullptr;
         }
         float dA[4] = {0.f, 0.f, 0.f, 0.f}, dB[4] = {0.f, 0.f, 0.f, 0.f};
-        uint4 u[2][VPL];
+        constexpr int KCH = VPL;      // (C = 512 in two chunks of 256 at 3 CTAs / SM: 0.74 -> 0.78 ms at s8' — that shape is L2-bound)
 #pragma unroll
-        for (int kb = 0; kb < VPL; ++kb) {
+        for (int k0 = 0; k0 < VPL; k0 += KCH) {
+            uint4 u[2][KCH];
 #pragma unroll
-            for (int hr = 0; hr < 2; ++hr)
-                u[hr][kb] = src[hr] ? ldg16(src[hr] + 64 * kb) : make_uint4(0u, 0u, 0u, 0u);
-        }
+            for (int kb = 0; kb < KCH; ++kb) {
 #pragma unroll
-        for (int kb = 0; kb < VPL; ++kb) {
-            const uint4 fb = *reinterpret_cast<const uint4*>(f0w + 64 * kb + 32 * (g & 1) + t4 * 8);
-            Mma16816<T>::run(dA, u[0][kb].x, u[1][kb].x, u[0][kb].y, u[1][kb].y, fb.x, fb.y);
-            Mma16816<T>::run(dB, u[0][kb].z, u[1][kb].z, u[0][kb].w, u[1][kb].w, fb.z, fb.w);
+                for (int hr = 0; hr < 2; ++hr)
+                    u[hr][kb] = src[hr] ? ldg16(src[hr] + 64 * (k0 + kb)) : make_uint4(0u, 0u, 0u, 0u);
+            }
+#pragma unroll
+            for (int kb = 0; kb < KCH; ++kb) {
+                const uint4 fb = *reinterpret_cast<const uint4*>(f0w + 64 * (k0 + kb) + 32 * (g & 1) + t4 * 8);
+                Mma16816<T>::run(dA, u[0][kb].x, u[1][kb].x, u[0][kb].y, u[1][kb].y, fb.x, fb.y);
+                Mma16816<T>::run(dB, u[0][kb].z, u[1][kb].z, u[0][kb].w, u[1][kb].w, fb.z, fb.w);
+            }
         }
         float vlo = (g & 1) ? dA[1] + dB[1] : dA[0] + dB[0];
         float vhi = (g & 1) ? dA[3] + dB[3] : dA[2] + dB[2];
@@ -493,7 +497,8 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
 }
 
 template <typename T, int VPL, int R = 0>
-__global__ void __launch_bounds__(256, 2)
+// C = 256, r = 2 (scale 4) is latency-bound: 4 CTAs / SM at 64 registers beat 2 at 115 (1.53 -> 1.28 ms at s4', incoherent)
+__global__ void __launch_bounds__(256, (R == 2 && VPL <= 4) ? 4 : 2)
 local_corr_mma_kernel(const GatherParams p) {
     constexpr int kMaxNN = 256;                  // (2r+2)^2 for r <= 7
     __shared__ float Dall[8][kMaxNN + 4];
