@@ -344,6 +344,14 @@ int roma_layernorm(const void* x, const void* gamma, const void* beta, void* out
  * the accumulated bias re-entering at every norm.  Otherwise as roma_layernorm. */
 int roma_layernorm_shift(const void* x, const float* shift, const void* gamma, const void* beta, void* out,
                          long long rows, int D, float eps, int dtype, void* stream);
+/* LayerNorm of fp32 rows written directly in a 16-bit dtype (out_dtype ROMA_F16 / ROMA_BF16; gamma, beta fp32): the fp32
+ * layer_norm + cast that autocast performs in front of the Linear consuming the normalised tokens
+ * (romatch/models/transformer/layers/block.py:88-101 under transformer/__init__.py's autocast), same bits, one pass. */
+int roma_layernorm_cast(const void* x, const void* gamma, const void* beta, void* out,
+                        long long rows, int D, float eps, int out_dtype, void* stream);
+/* out = x + y, x / out fp32, y 16-bit, n % 4 == 0: the residual add of the embedding decoder's fp32 token stream and an
+ * autocast branch (block.py:88-101: x = x + ls(attn(norm(x)))), which ATen runs unvectorised. */
+int roma_residual_add(const float* x, const void* y, float* out, long long n, int y_dtype, void* stream);
 
 /* Exact (erf) GELU over a flat tensor of n elements (n % 8 == 0 for 16-bit, % 4 for fp32; 16-byte aligned; in place allowed).
  * Replaces (reference): nn.GELU() of every transformer MLP, romatch/models/transformer/layers/mlp.py:23, 31, 37.

@@ -66,6 +66,8 @@ SIGNATURES = {
     "roma_pointwise_narrow_set_simt": (_i, [_i]),
     "roma_layernorm": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _i, C.c_float, _i, _vp]),
     "roma_layernorm_shift": (_i, [_vp, _vp, _vp, _vp, _vp, C.c_longlong, _i, C.c_float, _i, _vp]),
+    "roma_layernorm_cast": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _i, C.c_float, _i, _vp]),
+    "roma_residual_add": (_i, [_vp, _vp, _vp, C.c_longlong, _i, _vp]),
     "roma_gelu": (_i, [_vp, _vp, C.c_longlong, _i, _vp]),
     "roma_pointwise_narrow": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
     "roma_maxpool2x2_nhwc": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

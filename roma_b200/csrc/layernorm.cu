@@ -10,10 +10,25 @@
 
 namespace roma {
 
-template <typename T, int NV>
+// kVec floats -> kVec elements of TO, one store (16 bytes when the element sizes match, 8 when fp32 -> 16-bit)
+template <typename TO, int N> __device__ __forceinline__ void store_row_vec(TO* dst, const float* o) {
+    if constexpr (sizeof(TO) * N == 16) {
+        *reinterpret_cast<uint4*>(dst) = pack16<TO>(o);
+    } else {
+        static_assert(sizeof(TO) == 2 && N == 4, "fp32 rows to a 16-bit output");
+        TO t[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) t[k] = Elem<TO>::from_f(o[k]);
+        *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(t);
+    }
+}
+
+// TO = T, or a 16-bit type for fp32 rows: the cast autocast would insert in front of the Linear that consumes the
+// normalised tokens (fp32 LayerNorm output rounded once to the 16-bit dtype — the same bits, one pass less).
+template <typename T, int NV, typename TO = T>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const T* __restrict__ gamma, const T* __restrict__ beta,
-                 T* __restrict__ out, long long rows, int D, float eps) {
+                 TO* __restrict__ out, long long rows, int D, float eps) {
     constexpr int kVec = Elem<T>::kVec;
     const int lane = threadIdx.x & 31;
     const int nvec = D / kVec;
@@ -48,7 +63,7 @@ layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const
             }
         }
         const float rstd = rsqrtf(warp_sum(q) / (float)D + eps);
-        T* orow = out + r * D;
+        TO* orow = out + r * D;
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
@@ -58,20 +73,20 @@ layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const
                 unpack16<T>(ldg16(beta + vi * kVec), b);
 #pragma unroll
                 for (int k = 0; k < kVec; ++k) o[k] = fmaf((v[i][k] - mean) * rstd, g[k], b[k]);
-                *reinterpret_cast<uint4*>(orow + vi * kVec) = pack16<T>(o);
+                store_row_vec<TO, kVec>(orow + vi * kVec, o);
             }
         }
     }
 }
 
-template <typename T>
+template <typename T, typename TO = T>
 static int launch_layernorm(const void* x, const float* shift, const void* g, const void* b, void* out, long long rows, int D, float eps, cudaStream_t st) {
     constexpr int kVec = Elem<T>::kVec;
     const int nv = cdiv(D / kVec, 32);
     long long blocks = (rows + 7) / 8;
     const long long cap = (long long)sm_count() * 16;
     if (blocks > cap) blocks = cap;
-#define ROMA_LN(NVC) layernorm_kernel<T, NVC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, shift, (const T*)g, (const T*)b, (T*)out, rows, D, eps)
+#define ROMA_LN(NVC) layernorm_kernel<T, NVC, TO><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, shift, (const T*)g, (const T*)b, (TO*)out, rows, D, eps)
     if (nv <= 1) ROMA_LN(1);
     else if (nv <= 2) ROMA_LN(2);
     else if (nv <= 4) ROMA_LN(4);
@@ -117,4 +132,57 @@ extern "C" int roma_layernorm_shift(const void* x, const float* shift, const voi
                                     long long rows, int D, float eps, int dtype, void* stream) {
     ROMA_REQUIRE(shift, ROMA_ERR_BAD_ARG, "roma_layernorm_shift: null shift");
     return layernorm_entry("roma_layernorm_shift", x, shift, gamma, beta, out, rows, D, eps, dtype, stream);
+}
+
+// LayerNorm of fp32 rows written in a 16-bit dtype (out_dtype = ROMA_F16 / ROMA_BF16): what autocast computes as an fp32
+// layer_norm followed by a cast in front of the consuming Linear (transformer/layers/block.py:88-101 under the autocast of
+// transformer/__init__.py), in one pass.  gamma, beta fp32.
+extern "C" int roma_layernorm_cast(const void* x, const void* gamma, const void* beta, void* out,
+                                   long long rows, int D, float eps, int out_dtype, void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(x && gamma && beta && out, ROMA_ERR_BAD_ARG, "roma_layernorm_cast: null pointer");
+    ROMA_REQUIRE(rows > 0 && D > 0 && D % 4 == 0, ROMA_ERR_BAD_ARG, "roma_layernorm_cast: bad sizes (D %% 4 == 0)");
+    ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta)) & 15u) == 0 &&
+                 (reinterpret_cast<uintptr_t>(out) & 7u) == 0, ROMA_ERR_ALIGNMENT, "roma_layernorm_cast: inputs 16-byte, output 8-byte aligned");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    int rc;
+    switch (out_dtype) {
+        case ROMA_F16:  rc = launch_layernorm<float, __half>(x, nullptr, gamma, beta, out, rows, D, eps, st); break;
+        case ROMA_BF16: rc = launch_layernorm<float, __nv_bfloat16>(x, nullptr, gamma, beta, out, rows, D, eps, st); break;
+        default: return fail(ROMA_ERR_BAD_ARG, "roma_layernorm_cast: out_dtype must be ROMA_F16 or ROMA_BF16");
+    }
+    if (rc) return rc;
+    return check_launch("roma_layernorm_cast");
+}
+
+// out = x + y with x fp32 and y 16-bit (the residual add of an fp32 token stream and an autocast branch), fp32 result:
+// ATen runs this mixed-dtype add unvectorised (85 us for 26 M elements); here 16-byte loads of x and 8-byte loads of y.
+namespace roma {
+template <typename TY>
+__global__ void __launch_bounds__(256) residual_add_kernel(const float* __restrict__ x, const TY* __restrict__ y, float* __restrict__ out, long long n4) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<const float4*>(x)[i];
+        const uint2 raw = reinterpret_cast<const uint2*>(y)[i];
+        const TY* t = reinterpret_cast<const TY*>(&raw);
+        reinterpret_cast<float4*>(out)[i] = make_float4(a.x + Elem<TY>::to_f(t[0]), a.y + Elem<TY>::to_f(t[1]),
+                                                       a.z + Elem<TY>::to_f(t[2]), a.w + Elem<TY>::to_f(t[3]));
+    }
+}
+}  // namespace roma
+
+extern "C" int roma_residual_add(const float* x, const void* y, float* out, long long n, int y_dtype, void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(x && y && out && n > 0 && n % 4 == 0, ROMA_ERR_BAD_ARG, "roma_residual_add: bad arguments (n %% 4 == 0)");
+    ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0 && (reinterpret_cast<uintptr_t>(y) & 7u) == 0,
+                 ROMA_ERR_ALIGNMENT, "roma_residual_add: x / out 16-byte, y 8-byte aligned");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const long long n4 = n / 4;
+    long long blocks = (n4 + 255) / 256;
+    const long long cap = (long long)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (y_dtype == ROMA_F16) residual_add_kernel<__half><<<(unsigned)blocks, 256, 0, st>>>(x, (const __half*)y, out, n4);
+    else if (y_dtype == ROMA_BF16) residual_add_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(x, (const __nv_bfloat16*)y, out, n4);
+    else return fail(ROMA_ERR_BAD_ARG, "roma_residual_add: y_dtype must be ROMA_F16 or ROMA_BF16");
+    return check_launch("roma_residual_add");
 }

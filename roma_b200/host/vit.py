@@ -17,8 +17,17 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 
+def _radd(x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    """Residual add; the fp32-stream + 16-bit-branch case of the embedding decoder under autocast runs as one vectorised kernel."""
+    if x.is_cuda and x.dtype == torch.float32 and y.dtype in (torch.float16, torch.bfloat16) and x.shape == y.shape and x.numel() % 4 == 0:
+        from .. import ops
+        return ops.residual_add(x, y)
+    return x + y
+
+
 class RowNorm(nn.LayerNorm):
     """nn.LayerNorm (same parameters / state_dict keys) that runs `roma_layernorm` on CUDA at inference."""
+    cast_under_autocast = False      # set on the norms whose only consumer is a Linear (Block.norm1 / norm2)
 
     def native(self, x: torch.Tensor) -> bool:
         D = self.normalized_shape[0]
@@ -28,6 +37,11 @@ class RowNorm(nn.LayerNorm):
     def forward(self, x: torch.Tensor, shift: Optional[torch.Tensor] = None) -> torch.Tensor:
         if self.native(x):
             from .. import ops
+            if (x.dtype == torch.float32 and shift is None and self.cast_under_autocast and torch.is_autocast_enabled()
+                    and torch.get_autocast_gpu_dtype() in (torch.float16, torch.bfloat16) and self.normalized_shape[0] <= 1024):
+                # fp32 token stream under autocast (the embedding decoder): the consumer is a Linear, which would cast the fp32
+                # result to the autocast dtype first — write that dtype directly (same bits, one pass over the tokens less)
+                return ops.layer_norm(x, self.weight, self.bias, self.eps, out_dtype=torch.get_autocast_gpu_dtype())
             return ops.layer_norm(x, self.weight, self.bias, self.eps, shift=shift)
         return super().forward(x if shift is None else (x.float() + shift).to(x.dtype))
 
@@ -86,9 +100,11 @@ class Block(nn.Module):
                  init_values: Optional[float] = None, norm_eps: float = 1e-5):
         super().__init__()
         self.norm1 = RowNorm(dim, eps=norm_eps)
+        self.norm1.cast_under_autocast = True           # consumed by attn.qkv only
         self.attn = SelfAttention(dim, num_heads, qkv_bias)
         self.ls1 = ChannelScale(dim, init_values) if init_values else nn.Identity()
         self.norm2 = RowNorm(dim, eps=norm_eps)
+        self.norm2.cast_under_autocast = True           # consumed by mlp.fc1 only
         self.mlp = FeedForward(dim, int(dim * mlp_ratio))
         self.ls2 = ChannelScale(dim, init_values) if init_values else nn.Identity()
         self._fold_key, self._fold = None, None
@@ -126,10 +142,10 @@ class Block(nn.Module):
     def forward(self, x):
         if not self.training and x.is_cuda and isinstance(self.ls1, ChannelScale) and self.attn.proj.bias is not None:
             w1, b1, w2, b2 = self._folded()
-            x = x + F.linear(self.attn.attend(self.norm1(x)), w1, b1)
-            return x + F.linear(gelu_(self.mlp.fc1(self.norm2(x))), w2, b2)
-        x = x + self.ls1(self.attn(self.norm1(x)))
-        return x + self.ls2(self.mlp(self.norm2(x)))
+            x = _radd(x, F.linear(self.attn.attend(self.norm1(x)), w1, b1))
+            return _radd(x, F.linear(gelu_(self.mlp.fc1(self.norm2(x))), w2, b2))
+        x = _radd(x, self.ls1(self.attn(self.norm1(x))))
+        return _radd(x, self.ls2(self.mlp(self.norm2(x))))
 
 
 class PatchEmbed(nn.Module):

@@ -462,7 +462,7 @@ def pointwise_narrow(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor) 
 
 
 def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float,
-               shift: Optional[torch.Tensor] = None) -> torch.Tensor:
+               shift: Optional[torch.Tensor] = None, out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
     """F.layer_norm(x [+ shift], (D,), weight, bias, eps) over the last dimension (block.py:88-101, dinov2.py:236).
     shift: optional fp32 (D) vector added in fp32 in front of the statistics (`roma_layernorm_shift`)."""
     dev = _cuda(x, weight, bias, shift)
@@ -471,9 +471,17 @@ def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: f
     D = x.shape[-1]
     x = x.contiguous()
     weight, bias = weight.to(x.dtype).contiguous(), bias.to(x.dtype).contiguous()
-    out = torch.empty_like(x)
     rows = x.numel() // D
     lib = _lib.load()
+    if out_dtype is not None and out_dtype != x.dtype:
+        # fp32 rows, 16-bit output: autocast's fp32 layer_norm + cast in front of the consuming Linear, in one pass
+        if x.dtype != torch.float32 or out_dtype not in (torch.float16, torch.bfloat16) or shift is not None:
+            raise ValueError("layer_norm(out_dtype=...) is for fp32 rows written as fp16 / bf16")
+        out = torch.empty(x.shape, device=dev, dtype=out_dtype)
+        _run("roma_layernorm", dict(rows=rows, D=D, esize=4, out_esize=2),
+             lambda: lib.roma_layernorm_cast(_ptr(x), _ptr(weight), _ptr(bias), _ptr(out), rows, D, float(eps), _DT[out_dtype], _stream(dev)))
+        return out
+    out = torch.empty_like(x)
     if shift is not None:
         shift = shift.reshape(D).float().contiguous()
         _run("roma_layernorm", dict(rows=rows, D=D, esize=x.element_size()),
@@ -482,6 +490,19 @@ def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: f
         return out
     _run("roma_layernorm", dict(rows=rows, D=D, esize=x.element_size()),
          lambda: lib.roma_layernorm(_ptr(x), _ptr(weight), _ptr(bias), _ptr(out), rows, D, float(eps), _DT[x.dtype], _stream(dev)))
+    return out
+
+
+def residual_add(x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    """x + y for an fp32 stream x and a 16-bit branch y of the same shape -> fp32 (block.py:88-101 under autocast)."""
+    dev = _cuda(x, y)
+    if x.dtype != torch.float32 or y.dtype not in (torch.float16, torch.bfloat16) or x.shape != y.shape or x.numel() % 4:
+        raise ValueError("residual_add: fp32 + fp16/bf16 tensors of one shape, numel % 4 == 0")
+    x, y = x.contiguous(), y.contiguous()
+    out = torch.empty_like(x)
+    lib = _lib.load()
+    _run("roma_residual_add", dict(n=x.numel(), esize=4),
+         lambda: lib.roma_residual_add(_ptr(x), _ptr(y), _ptr(out), x.numel(), _DT[y.dtype], _stream(dev)))
     return out
 
 

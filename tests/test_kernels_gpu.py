@@ -740,3 +740,21 @@ def test_vit_unbiased_residual_stream(cuda, dtype, tol):
         b = vit.patch_tokens(x)
     assert a.shape == b.shape == (2, 30, 128)
     assert err(a, b) < tol
+
+
+def test_layernorm_cast_and_residual_add(ops, cuda):
+    """fp32 rows -> 16-bit LayerNorm output = F.layer_norm in fp32 followed by the cast autocast inserts (same bits);
+    fp32 + 16-bit residual add = ATen's mixed-dtype add (same bits)."""
+    g = torch.Generator(device="cuda").manual_seed(21)
+    x = torch.randn(3, 257, 1024, device=cuda, generator=g) * 3 + 0.5
+    w = torch.randn(1024, device=cuda, generator=g)
+    b = torch.randn(1024, device=cuda, generator=g)
+    for dt in (torch.bfloat16, torch.float16):
+        want = torch.nn.functional.layer_norm(x, (1024,), w, b, 1e-5)
+        got = ops.layer_norm(x, w, b, 1e-5, out_dtype=dt)
+        assert got.dtype == dt
+        # the fp32 statistics differ in the last bits (two-pass vs Welford): the 16-bit roundings agree except at ties
+        assert (got.float() - want.to(dt).float()).abs().max().item() <= 2.0 ** (-7 if dt == torch.bfloat16 else -10) * want.abs().max().item()
+        assert (got != want.to(dt)).float().mean().item() < 2e-3
+        y = torch.randn(3, 257, 1024, device=cuda, generator=g).to(dt)
+        assert torch.equal(ops.residual_add(x, y), x + y)
