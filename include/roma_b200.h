@@ -236,6 +236,19 @@ int roma_kde(const float* x, int N, int down, double std, int half,
 int roma_kde_debug_d2(const float* x, int N, int variant, void* out_half_bits, void* stream);
 int roma_kde_debug_lut(float* lut, double std, void* stream);
 
+/* The k largest of n scores as int64 indices ordered by (value descending, index ascending); out_values (same dtype as
+ * values) may be null.  Replaces (reference): the top-k inside both torch.multinomial(replacement=False) draws of
+ * RegressionMatcher.sample (romatch/models/matcher.py:482-494; TinyRoMa.sample, tiny.py:314-325) — multinomial without
+ * replacement is topk(p / q, k) with q ~ Exp(1), and ATen's multi-block radix select + stable descending sort of the
+ * survivors yields exactly this order, ties included, so the sampled rows stay those of the reference (the exponential
+ * draw itself stays on the torch generator: that is what consumes the Philox stream as the reference does).
+ * values: n contiguous elements (dtype ROMA_F32 / ROMA_F16 / ROMA_BF16), 0 < k <= n < 2^31; no NaN.
+ * workspace: roma_topk_workspace_bytes(n, k) bytes, 256-byte aligned (select state + 2 k 64-bit words + sort scratch;
+ * the size query needs a CUDA device and returns 0 without one).  Allocation-free, stream-ordered. */
+size_t roma_topk_workspace_bytes(long long n, long long k);
+int roma_topk_desc(const void* values, int dtype, long long n, long long k, long long* out_indices, void* out_values,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * K3c  match_keypoints: warp keypoints of A into B, mutual nearest neighbours.
  *

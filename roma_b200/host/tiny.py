@@ -205,14 +205,14 @@ class TinyRoMa(nn.Module):
             certainty[certainty > self.sample_thresh] = 1
         matches, certainty = matches.reshape(-1, 4), certainty.reshape(-1)
         expansion = 4 if "balanced" in self.sample_mode else 1
-        good = torch.multinomial(certainty, num_samples=min(expansion * num, len(certainty)), replacement=False)
+        good = ops.multinomial_without_replacement(certainty, min(expansion * num, len(certainty)))
         good_matches, good_certainty = matches[good], certainty[good]
         if "balanced" not in self.sample_mode:
             return good_matches, good_certainty
         density = ops.kde(good_matches, std=0.1, half=True, down=1)
         p = 1 / (density + 1)
         p[density < 10] = 1e-7
-        keep = torch.multinomial(p, num_samples=min(num, len(good_certainty)), replacement=False)
+        keep = ops.multinomial_without_replacement(p, min(num, len(good_certainty)))
         return good_matches[keep], good_certainty[keep]
 
     def to_pixel_coordinates(self, coords, H_A, W_A, H_B=None, W_B=None):

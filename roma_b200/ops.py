@@ -351,26 +351,68 @@ def kde(x: torch.Tensor, std: float = 0.1, half: bool = True, down: Optional[int
     return (dens, p) if return_p else dens
 
 
+_TOPK_DTYPES = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+# ATen's topk takes the multi-block radix select + stable radix sort of the survivors (whose tie order roma_topk_desc
+# reproduces) for one slice of >= 20000 elements and more than 4096 results; smaller problems go through its single-block /
+# bitonic variants, whose tie order is not claimed here: they stay on torch.topk.
+_TOPK_MIN_N, _TOPK_MIN_K = 20000, 4097
+
+
+def topk_indices(q: torch.Tensor, k: int) -> torch.Tensor:
+    """Indices (int64, (k,)) of the k largest entries of the 1-D tensor q, ordered by (value descending, index ascending)
+    — `torch.topk(q, k).indices` on CUDA for the sizes `sample` uses, ties included (tests/test_topk_gpu.py)."""
+    dev = _cuda(q)
+    if q.dim() != 1 or q.dtype not in _TOPK_DTYPES:
+        raise ValueError(f"topk_indices: expected a 1-D fp32/fp16/bf16 tensor, got {tuple(q.shape)} {q.dtype}")
+    q = q.contiguous()
+    n, k = q.numel(), int(k)
+    lib = _lib.load()
+    out = torch.empty(k, device=dev, dtype=torch.int64)
+    with torch.cuda.device(dev):
+        ws = torch.empty(lib.roma_topk_workspace_bytes(n, k), device=dev, dtype=torch.uint8)
+    _run("roma_topk_desc", dict(n=n, k=k),
+         lambda: lib.roma_topk_desc(_ptr(q), _TOPK_DTYPES[q.dtype], n, k, _ptr(out), None, _ptr(ws), ws.numel(), _stream(dev)))
+    return out
+
+
+def multinomial_without_replacement(p: torch.Tensor, num_samples: int, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+    """torch.multinomial(p, num_samples, replacement=False) for a 1-D weight vector, restated around the own top-k:
+    ATen (native/Distributions.cpp, multinomial_out) checks the weights with two device-side asserts, draws
+    q ~ Exp(1) of p's shape and dtype from the generator, divides p / q in place and returns topk(p / q, num_samples).
+    The same ops in the same order on the same generator (so the Philox stream advances as in the reference), with
+    `topk_indices` as the last step."""
+    n = p.numel()
+    if p.dim() != 1 or not (_TOPK_MIN_K <= num_samples <= n and n >= _TOPK_MIN_N) or p.dtype not in _TOPK_DTYPES:
+        return torch.multinomial(p, num_samples=num_samples, replacement=False, generator=generator)
+    _cuda(p)
+    torch._assert_async((p.max() < float("inf")) & (p.min() >= 0),
+                        "probability tensor contains either `inf`, `nan` or element < 0")
+    torch._assert_async(~(p.sum() == 0), "invalid multinomial distribution (sum of probabilities <= 0)")
+    q = torch.empty_like(p).exponential_(1, generator=generator)
+    torch.div(p, q, out=q)
+    return topk_indices(q, num_samples)
+
+
 def sample(matches: torch.Tensor, certainty: torch.Tensor, num: int = 10000, sample_thresh: float = 0.05,
            sample_mode: str = "threshold_balanced", kde_half: bool = True, kde_down: Optional[int] = None,
            generator: Optional[torch.Generator] = None, return_indices: bool = False):
     """RegressionMatcher.sample (matcher.py:468-495) / TinyRoMa.sample (tiny.py:297-327).
 
-    The two draws stay on torch.multinomial so the device generator's Philox stream is consumed exactly as
-    in the reference (that is what makes the sampled indices reproducible against it); thresholding is a
-    torch elementwise op, the density and the weights p come from the kde kernel."""
+    The two draws consume the device generator's Philox stream exactly as torch.multinomial does in the reference
+    (`multinomial_without_replacement`: ATen's exponential draw and division, own top-k with ATen's tie order) — that
+    is what makes the sampled indices reproducible against it; thresholding is a torch elementwise op, the density
+    and the weights p come from the kde kernel."""
     _cuda(matches, certainty)
     if "threshold" in sample_mode:
         certainty = torch.where(certainty > sample_thresh, torch.ones_like(certainty), certainty)
     matches, certainty = matches.reshape(-1, 4), certainty.reshape(-1)
     expansion = 4 if "balanced" in sample_mode else 1
-    good = torch.multinomial(certainty, num_samples=min(expansion * num, len(certainty)), replacement=False,
-                             generator=generator)
+    good = multinomial_without_replacement(certainty, min(expansion * num, len(certainty)), generator)
     good_matches, good_certainty = matches[good], certainty[good]
     if "balanced" not in sample_mode:
         return (good_matches, good_certainty, good) if return_indices else (good_matches, good_certainty)
     _, p = kde(good_matches, std=0.1, half=kde_half, down=kde_down, return_p=True)
-    bal = torch.multinomial(p, num_samples=min(num, len(good_certainty)), replacement=False, generator=generator)
+    bal = multinomial_without_replacement(p, min(num, len(good_certainty)), generator)
     out = (good_matches[bal], good_certainty[bal])
     return out + (good[bal],) if return_indices else out
 
