@@ -90,7 +90,10 @@ struct DwOut {
     bool full, relu;
 };
 
-template <typename T, bool FIRST, bool LAST, int I>
+// FAST (compile time): the strip lies inside the image, all four columns exist and the ReLU is on — the completed row is
+// stored unconditionally, so a whole 5-row chunk is ONE basic block and ptxas overlaps the next row's LDS / unpack with
+// this row's FFMA2s; CP > 0 additionally makes the column offsets immediates of the stores.
+template <typename T, bool FIRST, bool LAST, int I, bool FAST = false, int CP = 0>
 __device__ __forceinline__ void dw_row(const float2 (&v)[kDwNV], DwOut<T>& out, int r, int h, const float2 (&wv)[25], float2 bv,
                                        float2 (&acc)[5][kDwTW]) {
     using P = Pair<T>;
@@ -107,6 +110,17 @@ __device__ __forceinline__ void dw_row(const float2 (&v)[kDwNV], DwOut<T>& out, 
         for (int dx = 0; dx < 5; ++dx)
 #pragma unroll
             for (int ox = 0; ox < kDwTW; ++ox) acc[slot][ox] = __ffma2_rn(v[ox + dx], wv[dy * 5 + dx], acc[slot][ox]);
+    }
+    if (FAST) {
+        if (!(FIRST && I < 4)) {
+            const int slot = (I + 1) % 5;
+            T* op = out.orow;
+#pragma unroll
+            for (int ox = 0; ox < kDwTW; ++ox)
+                P::store_relu(op + ox * (CP > 0 ? CP : out.col_stride), acc[slot][ox].x, acc[slot][ox].y);
+            out.orow += out.row_stride;
+        }
+        return;
     }
     if (!(FIRST && I < 4)) {
         const int slot = (I + 1) % 5;
@@ -139,11 +153,12 @@ __device__ __forceinline__ void dw_row(const float2 (&v)[kDwNV], DwOut<T>& out, 
 struct DwTmaParams {
     int h, w, Cp, relu;
     int ppb, rpb, pair_groups;
+    int fast;                        // w % 4 == 0 and ReLU on: strips inside the image take the branch-free store path
     int row_bytes, pix_bytes;        // of the shared tile
     int chunk_stride, chunk_bytes;   // 5-row box: distance between boxes in shared memory (128-aligned), bytes transferred
 };
 
-template <typename T, bool FIRST, bool LAST>
+template <typename T, bool FIRST, bool LAST, bool FAST = false, int CP = 0>
 __device__ __forceinline__ void dw_chunk_smem(const unsigned char* __restrict__ rows, int row_bytes, int pix_bytes, DwOut<T>& out,
                                               int r0, int h, const float2 (&wv)[25], float2 bv, float2 (&acc)[5][kDwTW]) {
     using P = Pair<T>;
@@ -154,14 +169,14 @@ __device__ __forceinline__ void dw_chunk_smem(const unsigned char* __restrict__ 
         float2 v[kDwNV];
 #pragma unroll
         for (int j = 0; j < kDwNV; ++j) v[j] = P::unpack(*reinterpret_cast<const Raw*>(rp + j * pix_bytes));
-        dw_row<T, FIRST, LAST, I>(v, out, r0 + I, h, wv, bv, acc);
+        dw_row<T, FIRST, LAST, I, FAST, CP>(v, out, r0 + I, h, wv, bv, acc);
     };
     step(std::integral_constant<int, 0>{}); step(std::integral_constant<int, 1>{}); step(std::integral_constant<int, 2>{});
     step(std::integral_constant<int, 3>{}); step(std::integral_constant<int, 4>{});
 }
 
 // PPB > 0 fixes the pairs per block at compile time (tile strides become immediates); PPB == 0 reads them from pr.
-template <typename T, int PPB>
+template <typename T, int PPB, int CP = 0>
 __global__ void __launch_bounds__(kDwThreads, 4)
 dwconv5_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restrict__ wgt, const float* __restrict__ bias,
                    T* __restrict__ out, const DwTmaParams pr) {
@@ -234,6 +249,22 @@ dwconv5_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __restr
             if (tid == 0) issue(ch + kDwRing);
         }
     };
+    if (pr.fast && y0 + kDwRYL <= h) {       // block-uniform: whole strip inside the image, w % 4 == 0, ReLU on
+        tma::mbar_wait(&bars[0], 0);
+        dw_chunk_smem<T, true, false, true, CP>(tb, p.row_bytes, p.pix_bytes, o, y0 - 2, h, wv, bv, acc);
+        refill(0);
+#pragma unroll 1
+        for (int ch = 1; ch < kDwChunksL - 1; ++ch) {
+            tma::mbar_wait(&bars[ch % kDwRing], (uint32_t)((ch / kDwRing) & 1));
+            dw_chunk_smem<T, false, false, true, CP>(tb + (ch % kDwRing) * p.chunk_stride, p.row_bytes, p.pix_bytes, o, y0 - 2 + 5 * ch, h,
+                                                     wv, bv, acc);
+            refill(ch);
+        }
+        tma::mbar_wait(&bars[(kDwChunksL - 1) % kDwRing], (uint32_t)(((kDwChunksL - 1) / kDwRing) & 1));
+        dw_chunk_smem<T, false, true, true, CP>(tb + ((kDwChunksL - 1) % kDwRing) * p.chunk_stride, p.row_bytes, p.pix_bytes, o,
+                                                y0 - 2 + 5 * (kDwChunksL - 1), h, wv, bv, acc);
+        return;
+    }
     tma::mbar_wait(&bars[0], 0);
     dw_chunk_smem<T, true, false>(tb, p.row_bytes, p.pix_bytes, o, y0 - 2, h, wv, bv, acc);
     refill(0);
@@ -263,6 +294,7 @@ static int launch_dw_tma(const void* x, const float* weight, const float* bias, 
     const int tcols = rpb * kDwTW + 4;
     DwTmaParams p;
     p.h = h; p.w = w; p.Cp = C; p.relu = relu; p.ppb = ppb; p.rpb = rpb; p.pair_groups = pair_groups;
+    p.fast = (relu && w % kDwTW == 0) ? 1 : 0;
     p.pix_bytes = 2 * ppb * esz;
     p.row_bytes = tcols * p.pix_bytes;
     p.chunk_bytes = 5 * p.row_bytes;
@@ -277,7 +309,12 @@ static int launch_dw_tma(const void* x, const float* weight, const float* bias, 
 
     const dim3 grid((unsigned)(pair_groups * cdiv(runs, rpb)), (unsigned)strips, (unsigned)B);
     using Kernel = void (*)(const CUtensorMap, const float*, const float*, T*, const DwTmaParams);
-    Kernel kernel = ppb == 32 ? dwconv5_tma_kernel<T, 32> : ppb == 24 ? dwconv5_tma_kernel<T, 24>
+    // the four refiner widths above the finest scale get their channel count at compile time (store offsets become immediates)
+    Kernel kernel = (ppb == 24 && C == 144) ? dwconv5_tma_kernel<T, 24, 144>
+                  : (ppb == 32 && C == 576) ? dwconv5_tma_kernel<T, 32, 576>
+                  : (ppb == 32 && C == 1144) ? dwconv5_tma_kernel<T, 32, 1144>
+                  : (ppb == 32 && C == 1384) ? dwconv5_tma_kernel<T, 32, 1384>
+                  : ppb == 32 ? dwconv5_tma_kernel<T, 32> : ppb == 24 ? dwconv5_tma_kernel<T, 24>
                   : ppb == 12 ? dwconv5_tma_kernel<T, 12> : dwconv5_tma_kernel<T, 0>;
     // opt in to > 48 KB of dynamic shared memory (idempotent, cheap; done per call to stay per-instantiation correct)
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
@@ -389,20 +426,25 @@ dwconv5_pw24_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __
         const float2 bvv = __ldg(reinterpret_cast<const float2*>(bias + c));
         const unsigned char* tb = tile + run_l * kDwTW * kPwPixBytes + pair_l * 4;
         float2 acc[5][kDwTW];
-        tma::mbar_wait(&bars[0], 0);
-        dw_chunk_smem<T, true, false>(tb, kPwRowBytes, kPwPixBytes, o, y0 - 2, h, wv, bvv, acc);
+        // FAST (ReLU on): rows are written to the tile unconditionally — phase 2 masks what lies outside the image
+        auto phase1 = [&](auto fast) {
+            constexpr bool F = decltype(fast)::value;
+            tma::mbar_wait(&bars[0], 0);
+            dw_chunk_smem<T, true, false, F, kPwC>(tb, kPwRowBytes, kPwPixBytes, o, y0 - 2, h, wv, bvv, acc);
 #pragma unroll 1
-        for (int ch = 1; ch < kDwChunks - 1; ++ch) {
-            if (ch < nch) {
-                tma::mbar_wait(&bars[ch], 0);
-                dw_chunk_smem<T, false, false>(tb + ch * kPwChunkStride, kPwRowBytes, kPwPixBytes, o, y0 - 2 + 5 * ch, h, wv, bvv, acc);
+            for (int ch = 1; ch < kDwChunks - 1; ++ch) {
+                if (ch < nch) {
+                    tma::mbar_wait(&bars[ch], 0);
+                    dw_chunk_smem<T, false, false, F, kPwC>(tb + ch * kPwChunkStride, kPwRowBytes, kPwPixBytes, o, y0 - 2 + 5 * ch, h, wv, bvv, acc);
+                }
             }
-        }
-        if (nch == kDwChunks) {
-            tma::mbar_wait(&bars[kDwChunks - 1], 0);
-            dw_chunk_smem<T, false, true>(tb + (kDwChunks - 1) * kPwChunkStride, kPwRowBytes, kPwPixBytes, o, y0 - 2 + 5 * (kDwChunks - 1), h,
-                                          wv, bvv, acc);
-        }
+            if (nch == kDwChunks) {
+                tma::mbar_wait(&bars[kDwChunks - 1], 0);
+                dw_chunk_smem<T, false, true, F, kPwC>(tb + (kDwChunks - 1) * kPwChunkStride, kPwRowBytes, kPwPixBytes, o,
+                                                       y0 - 2 + 5 * (kDwChunks - 1), h, wv, bvv, acc);
+            }
+        };
+        if (relu) phase1(std::true_type{}); else phase1(std::false_type{});
     }
     __syncthreads();
 

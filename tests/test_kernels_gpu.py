@@ -475,7 +475,10 @@ def test_tiny_corr_tensor_cores_config5_shape(ops, cuda):
 # --------------------------------------------------------------------------------------------- (f-2)
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2), (torch.float16, 3e-3)])
 @pytest.mark.parametrize("B,C,h,w", [(2, 24, 17, 23), (1, 144, 9, 8), (2, 576, 5, 13), (1, 2, 40, 3), (1, 1144, 33, 21),
-                                     (1, 40, 16, 64), (3, 72, 31, 4), (1, 10, 37, 41)])
+                                     (1, 40, 16, 64), (3, 72, 31, 4), (1, 10, 37, 41),
+                                     # strips of 36 rows inside the image with w % 4 == 0: the branch-free store path, at the
+                                     # four compile-time refiner widths and a runtime one, each followed by a partial strip
+                                     (1, 144, 80, 16), (1, 576, 40, 8), (1, 1144, 37, 12), (1, 1384, 72, 4), (2, 40, 75, 20)])
 @pytest.mark.parametrize("path", [0, 1])
 def test_dwconv5x5_bias_relu(ops, cuda, dtype, tol, B, C, h, w, path):
     """Depthwise 5x5 + bias + ReLU vs F.conv2d(groups=C) + relu in fp32 on the same (rounded) inputs; path 0 takes
