@@ -334,6 +334,7 @@ static int launch_dw_tma(const void* x, const float* weight, const float* bias, 
 // the two-kernel path (16-bit activation between the convolutions, fp32 accumulation in both).
 constexpr int kPwC = 24, kPwPPB = 12, kPwRPB = 10;                 // channels, pairs and 4-column runs per block
 constexpr int kPwCols = kPwRPB * kDwTW;                            // 40 output columns per tile
+constexpr int kPwSub = 3;                                          // consecutive 16-row strips per block
 constexpr int kPwPixBytes = 2 * kPwPPB * 2, kPwRowBytes = (kPwCols + 4) * kPwPixBytes, kPwChunkBytes = 5 * kPwRowBytes;
 constexpr int kPwChunkStride = (kPwChunkBytes + 127) / 128 * 128;
 constexpr int kPwObufBytes = kDwRY * kPwCols * kPwC * 2;
@@ -369,22 +370,24 @@ dwconv5_pw24_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __
     T* obuf = reinterpret_cast<T*>(tile + kDwChunks * kPwChunkStride + 128);          // [16 rows][40 cols][24 ch]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int rg = blockIdx.x, b = blockIdx.z, y0 = blockIdx.y * kDwRY;
-    int nch = kDwChunks;
-    while (nch > 1 && y0 + 5 * (nch - 1) - 4 >= h) --nch;
+    const int rg = blockIdx.x, b = blockIdx.z, ybase = blockIdx.y * (kDwRY * kPwSub);
+    // chunks of the 16-row strip starting at row y that complete at least one output row inside the image
+    auto chunks_of = [&](int y) { int n = kDwChunks; while (n > 1 && y + 5 * (n - 1) - 4 >= h) --n; return n; };
+    auto issue_strip = [&](int y) {                                  // thread 0: the strip's 5-row boxes, one mbarrier each
+        const int n = chunks_of(y);
+        for (int k = 0; k < n; ++k) {
+            tma::mbar_expect_tx(&bars[k], (uint32_t)kPwChunkBytes);
+            tma::load_4d(tile + k * kPwChunkStride, &map, &bars[k], 0, rg * kPwCols - 2, y - 2 + 5 * k, b);
+        }
+    };
 
     if (tid == 0) {
         tma::prefetch_map(&map);
-        for (int k = 0; k < nch; ++k) tma::mbar_init(&bars[k], 1);
+        for (int k = 0; k < kDwChunks; ++k) tma::mbar_init(&bars[k], 1);
         tma::fence_barrier_init();
     }
     __syncthreads();
-    if (tid == 0) {
-        for (int k = 0; k < nch; ++k) {
-            tma::mbar_expect_tx(&bars[k], (uint32_t)kPwChunkBytes);
-            tma::load_4d(tile + k * kPwChunkStride, &map, &bars[k], 0, rg * kPwCols - 2, y0 - 2 + 5 * k, b);
-        }
-    }
+    if (tid == 0) issue_strip(ybase);
 
     // B fragments of the 1x1 convolution: B[k][n] = W[n][k]; b0 = (k = 16 ks + 2t, +1; n = 8 nt + g), b1 = 8 further in k
     const int g = lane >> 2, t4 = lane & 3;
@@ -407,79 +410,93 @@ dwconv5_pw24_tma_kernel(const __grid_constant__ CUtensorMap map, const float* __
         bv[nt][1] = __ldg(pw_b + nt * 8 + 2 * t4 + 1);
     }
 
-    // ---- phase 1: depthwise 5x5 + bias + ReLU into the shared-memory tile --------------------------------------
+    // A block walks kPwSub consecutive 16-row strips: weights and fragments are loaded once, and the boxes of the next strip
+    // are issued right after the barrier that ends phase 1 (all four slots are free then), so they arrive under phase 2.
     const int runs = (w + kDwTW - 1) / kDwTW;
     const int pair_l = tid % kPwPPB, run_l = tid / kPwPPB;
     const int run = rg * kPwRPB + run_l;
-    if (run_l < kPwRPB && run < runs) {
-        const int c = pair_l * 2;
-        DwOut<T> o;
-        o.row_stride = kPwCols * kPwC;
-        o.col_stride = kPwC;
-        o.orow = obuf + run_l * kDwTW * kPwC + c;
-        o.storemask = (1u << kDwTW) - 1u;
-        o.full = true;
-        o.relu = relu != 0;
-        float2 wv[25];
+    const bool ph1 = run_l < kPwRPB && run < runs;
+    const int c = pair_l * 2;
+    float2 wv[25];
 #pragma unroll
-        for (int k = 0; k < 25; ++k) wv[k] = __ldg(reinterpret_cast<const float2*>(wgt + k * kPwC + c));
-        const float2 bvv = __ldg(reinterpret_cast<const float2*>(bias + c));
-        const unsigned char* tb = tile + run_l * kDwTW * kPwPixBytes + pair_l * 4;
-        float2 acc[5][kDwTW];
-        // FAST (ReLU on): rows are written to the tile unconditionally — phase 2 masks what lies outside the image
-        auto phase1 = [&](auto fast) {
-            constexpr bool F = decltype(fast)::value;
-            tma::mbar_wait(&bars[0], 0);
-            dw_chunk_smem<T, true, false, F, kPwC>(tb, kPwRowBytes, kPwPixBytes, o, y0 - 2, h, wv, bvv, acc);
-#pragma unroll 1
-            for (int ch = 1; ch < kDwChunks - 1; ++ch) {
-                if (ch < nch) {
-                    tma::mbar_wait(&bars[ch], 0);
-                    dw_chunk_smem<T, false, false, F, kPwC>(tb + ch * kPwChunkStride, kPwRowBytes, kPwPixBytes, o, y0 - 2 + 5 * ch, h, wv, bvv, acc);
-                }
-            }
-            if (nch == kDwChunks) {
-                tma::mbar_wait(&bars[kDwChunks - 1], 0);
-                dw_chunk_smem<T, false, true, F, kPwC>(tb + (kDwChunks - 1) * kPwChunkStride, kPwRowBytes, kPwPixBytes, o,
-                                                       y0 - 2 + 5 * (kDwChunks - 1), h, wv, bvv, acc);
-            }
-        };
-        if (relu) phase1(std::true_type{}); else phase1(std::false_type{});
-    }
-    __syncthreads();
-
-    // ---- phase 2: 1x1 convolution of the tile on tensor cores, 16 pixels per MMA tile --------------------------
+    for (int k = 0; k < 25; ++k) wv[k] = ph1 ? __ldg(reinterpret_cast<const float2*>(wgt + k * kPwC + c)) : make_float2(0.f, 0.f);
+    const float2 bvv = ph1 ? __ldg(reinterpret_cast<const float2*>(bias + c)) : make_float2(0.f, 0.f);
+    const unsigned char* tb = tile + run_l * kDwTW * kPwPixBytes + pair_l * 4;
     const uint32_t* ob32 = reinterpret_cast<const uint32_t*>(obuf);
     T* outb = out + (long long)b * h * w * kPwC;
     const int x_base = rg * kPwCols;
-#pragma unroll 2
-    for (int mt = warp; mt < kDwRY * kPwCols / 16; mt += kDwThreads / 32) {
-        const int qlo = mt * 16 + g, qhi = qlo + 8;
-        uint32_t a0[4], a1[4];
-        a0[0] = ob32[qlo * 12 + t4];     a0[1] = ob32[qhi * 12 + t4];
-        a0[2] = ob32[qlo * 12 + 4 + t4]; a0[3] = ob32[qhi * 12 + 4 + t4];
-        a1[0] = ob32[qlo * 12 + 8 + t4]; a1[1] = ob32[qhi * 12 + 8 + t4];
-        a1[2] = 0u; a1[3] = 0u;                                       // k = 24..31 do not exist
-        const int ylo = y0 + qlo / kPwCols, xlo = x_base + qlo % kPwCols;
-        const int yhi = y0 + qhi / kPwCols, xhi = x_base + qhi % kPwCols;
-        const bool vlo = ylo < h && xlo < w, vhi = yhi < h && xhi < w;
-        T* plo = outb + ((long long)ylo * w + xlo) * kPwC + 2 * t4;
-        T* phi = outb + ((long long)yhi * w + xhi) * kPwC + 2 * t4;
-#pragma unroll
-        for (int nt = 0; nt < 3; ++nt) {
-            float c[4] = {bv[nt][0], bv[nt][1], bv[nt][0], bv[nt][1]};
-            dw_mma16816<T>(c, a0, bf[0][nt][0], bf[0][nt][1]);
-            dw_mma16816<T>(c, a1, bf[1][nt][0], bf[1][nt][1]);
-            if (vlo) *reinterpret_cast<uint32_t*>(plo + nt * 8) = dw_pack2<T>(c[0], c[1]);
-            if (vhi) *reinterpret_cast<uint32_t*>(phi + nt * 8) = dw_pack2<T>(c[2], c[3]);
+
+#pragma unroll 1
+    for (int ss = 0; ss < kPwSub; ++ss) {
+        const int y0 = ybase + ss * kDwRY;
+        if (y0 >= h) break;                                          // block-uniform
+        const int nch = chunks_of(y0);
+        const uint32_t par = (uint32_t)(ss & 1);                     // every barrier completes once per strip
+        // ---- phase 1: depthwise 5x5 + bias + ReLU into the shared-memory tile ----------------------------------
+        if (ph1) {
+            DwOut<T> o;
+            o.row_stride = kPwCols * kPwC;
+            o.col_stride = kPwC;
+            o.orow = obuf + run_l * kDwTW * kPwC + c;
+            o.storemask = (1u << kDwTW) - 1u;
+            o.full = true;
+            o.relu = relu != 0;
+            float2 acc[5][kDwTW];
+            // FAST (ReLU on): rows are written to the tile unconditionally — phase 2 masks what lies outside the image
+            auto phase1 = [&](auto fast) {
+                constexpr bool F = decltype(fast)::value;
+                tma::mbar_wait(&bars[0], par);
+                dw_chunk_smem<T, true, false, F, kPwC>(tb, kPwRowBytes, kPwPixBytes, o, y0 - 2, h, wv, bvv, acc);
+#pragma unroll 1
+                for (int ch = 1; ch < kDwChunks - 1; ++ch) {
+                    if (ch < nch) {
+                        tma::mbar_wait(&bars[ch], par);
+                        dw_chunk_smem<T, false, false, F, kPwC>(tb + ch * kPwChunkStride, kPwRowBytes, kPwPixBytes, o, y0 - 2 + 5 * ch, h, wv,
+                                                                bvv, acc);
+                    }
+                }
+                if (nch == kDwChunks) {
+                    tma::mbar_wait(&bars[kDwChunks - 1], par);
+                    dw_chunk_smem<T, false, true, F, kPwC>(tb + (kDwChunks - 1) * kPwChunkStride, kPwRowBytes, kPwPixBytes, o,
+                                                           y0 - 2 + 5 * (kDwChunks - 1), h, wv, bvv, acc);
+                }
+            };
+            if (relu) phase1(std::true_type{}); else phase1(std::false_type{});
         }
+        __syncthreads();                                             // tile complete, every input slot consumed
+        if (tid == 0 && ss + 1 < kPwSub && y0 + kDwRY < h) issue_strip(y0 + kDwRY);
+
+        // ---- phase 2: 1x1 convolution of the tile on tensor cores, 16 pixels per MMA tile ----------------------
+#pragma unroll 2
+        for (int mt = warp; mt < kDwRY * kPwCols / 16; mt += kDwThreads / 32) {
+            const int qlo = mt * 16 + g, qhi = qlo + 8;
+            uint32_t a0[4], a1[4];
+            a0[0] = ob32[qlo * 12 + t4];     a0[1] = ob32[qhi * 12 + t4];
+            a0[2] = ob32[qlo * 12 + 4 + t4]; a0[3] = ob32[qhi * 12 + 4 + t4];
+            a1[0] = ob32[qlo * 12 + 8 + t4]; a1[1] = ob32[qhi * 12 + 8 + t4];
+            a1[2] = 0u; a1[3] = 0u;                                   // k = 24..31 do not exist
+            const int ylo = y0 + qlo / kPwCols, xlo = x_base + qlo % kPwCols;
+            const int yhi = y0 + qhi / kPwCols, xhi = x_base + qhi % kPwCols;
+            const bool vlo = ylo < h && xlo < w, vhi = yhi < h && xhi < w;
+            T* plo = outb + ((long long)ylo * w + xlo) * kPwC + 2 * t4;
+            T* phi = outb + ((long long)yhi * w + xhi) * kPwC + 2 * t4;
+#pragma unroll
+            for (int nt = 0; nt < 3; ++nt) {
+                float cc[4] = {bv[nt][0], bv[nt][1], bv[nt][0], bv[nt][1]};
+                dw_mma16816<T>(cc, a0, bf[0][nt][0], bf[0][nt][1]);
+                dw_mma16816<T>(cc, a1, bf[1][nt][0], bf[1][nt][1]);
+                if (vlo) *reinterpret_cast<uint32_t*>(plo + nt * 8) = dw_pack2<T>(cc[0], cc[1]);
+                if (vhi) *reinterpret_cast<uint32_t*>(phi + nt * 8) = dw_pack2<T>(cc[2], cc[3]);
+            }
+        }
+        if (ss + 1 < kPwSub) __syncthreads();                        // the tile is rewritten by the next strip's phase 1
     }
 }
 
 template <typename T>
 static int launch_dw_pw24(const void* x, const float* weight, const float* bias, const float* pw_w, const float* pw_b, void* out,
                           int B, int h, int w, int relu, int dtype, cudaStream_t st) {
-    const int runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRY - 1) / kDwRY;
+    const int runs = (w + kDwTW - 1) / kDwTW, strips = (h + kDwRY * kPwSub - 1) / (kDwRY * kPwSub);
     CUtensorMap map;
     const uint64_t dims[4] = {(uint64_t)kPwC, (uint64_t)w, (uint64_t)h, (uint64_t)B};
     const uint64_t strides[3] = {(uint64_t)kPwC * 2, (uint64_t)w * kPwC * 2, (uint64_t)h * w * kPwC * 2};

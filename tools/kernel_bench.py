@@ -173,6 +173,17 @@ def main():
                  alg_MB=round(alg / 1e6, 1), GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4),
                  fp32_TFLOPs=round(2 * macs / ms / 1e9, 2))
 
+    if want("fused24"):
+        # the whole finest-scale refiner block (depthwise 5x5 + BN + ReLU + 1x1, 24 channels) as one launch
+        for name, side in (("s1", 560), ("s1u", 864)):
+            x = torch.randn(B, side, side, 24, device=dev, dtype=dt).permute(0, 3, 1, 2)
+            wt, bs = torch.randn(25, 24, device=dev) * 0.2, torch.randn(24, device=dev)
+            pw, pb = torch.randn(24, 24, device=dev) * 0.2, torch.randn(24, device=dev)
+            alg = 2 * x.numel() * x.element_size()
+            ms = timeit(lambda: ops.dwconv5x5_pointwise(x, wt, bs, pw, pb, relu=True), args.iters, flush)
+            emit(kernel="dwconv5x5_pointwise", visit=name, side=side, batch=B, dtype=args.dtype, ms=round(ms, 4),
+                 alg_MB=round(alg / 1e6, 1), GBps=round(alg / ms / 1e6, 1), frac_hbm=round(alg / ms / 1e6 / PEAKS["hbm_gbs"], 4))
+
     if want("narrow"):
         for name, Cin, Cout, side in (("pw24 s1u", 24, 24, 864), ("pw24 s1", 24, 24, 560), ("proj1 864", 64, 9, 864)):
             x = torch.randn(B, side, side, Cin, device=dev, dtype=dt).permute(0, 3, 1, 2)
