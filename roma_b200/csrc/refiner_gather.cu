@@ -416,14 +416,19 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
         // (4 L1 wavefronts per instruction, not 8).  The B fragment carries the matching f0 channels in the
         // column of the same parity: D[g][g & 1] is the partial dot product of row g, and the two halves meet
         // with one shuffle.
+        // Addresses are formed unconditionally from CLAMPED coordinates (always inside the map) and only the loads are
+        // predicated: a conditional 64-bit address computation compiles to a branch per neighbour, which cut every group of
+        // 8 neighbours into separate basic blocks and kept the next group's loads from being scheduled under this group's MMAs.
         const T* src[2];
+        bool okn[2];
 #pragma unroll
         for (int hr = 0; hr < 2; ++hr) {
             const int n = n0 + (g >> 1) + 4 * hr;
             const int j = n / W2, i = n - j * W2;
             const int yy = y0 + j - r_, xx = x0 + i - r_;
-            const bool ok = n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
-            src[hr] = ok ? f1b + ((long long)yy * p.w1 + xx) * p.C + 32 * (g & 1) + t4 * 8 : nullptr;
+            okn[hr] = n < NN && yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+            const int yc = min(max(yy, 0), p.h1 - 1), xc = min(max(xx, 0), p.w1 - 1);
+            src[hr] = f1b + ((long long)yc * p.w1 + xc) * p.C + 32 * (g & 1) + t4 * 8;
         }
         float dA[4] = {0.f, 0.f, 0.f, 0.f}, dB[4] = {0.f, 0.f, 0.f, 0.f};
         constexpr int KCH = VPL;      // (C = 512 in two chunks of 256 at 3 CTAs / SM: 0.74 -> 0.78 ms at s8' — that shape is L2-bound)
@@ -434,7 +439,7 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
             for (int kb = 0; kb < KCH; ++kb) {
 #pragma unroll
                 for (int hr = 0; hr < 2; ++hr)
-                    u[hr][kb] = src[hr] ? ldg16(src[hr] + 64 * (k0 + kb)) : make_uint4(0u, 0u, 0u, 0u);
+                    u[hr][kb] = okn[hr] ? ldg16(src[hr] + 64 * (k0 + kb)) : make_uint4(0u, 0u, 0u, 0u);
             }
 #pragma unroll
             for (int kb = 0; kb < KCH; ++kb) {
@@ -462,16 +467,24 @@ __device__ __forceinline__ void local_corr_px(const GatherParams& p, long long p
                 float xh[8];
 #pragma unroll
                 for (int e = 0; e < 8; ++e) xh[e] = 0.f;
+                // the four taps are loaded together from clamped (always valid) addresses; a tap outside the map is left out
+                // by predicating its FMAs — same values as skipping it, without a branch (and a load latency) per tap
+                uint4 raw[4];
+                bool okt[4];
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
                     const int yy = y0 + (t >> 1), xx = x0 + (t & 1);
-                    if (yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1) {
-                        const float wgt = ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0);
-                        float f[8];
-                        unpack16<T>(ldg16(f1b + ((long long)yy * p.w1 + xx) * p.C + v * 8), f);
+                    okt[t] = yy >= 0 && yy < p.h1 && xx >= 0 && xx < p.w1;
+                    const int yc = min(max(yy, 0), p.h1 - 1), xc = min(max(xx, 0), p.w1 - 1);
+                    raw[t] = ldg16(f1b + ((long long)yc * p.w1 + xc) * p.C + v * 8);
+                }
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) xh[e] = fmaf(wgt, f[e], xh[e]);
-                    }
+                for (int t = 0; t < 4; ++t) {
+                    const float wgt = ((t >> 1) ? wy1 : wy0) * ((t & 1) ? wx1 : wx0);
+                    float f[8];
+                    unpack16<T>(raw[t], f);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) xh[e] = okt[t] ? fmaf(wgt, f[e], xh[e]) : xh[e];
                 }
                 *reinterpret_cast<uint4*>(row + p.off_xhat + v * 8) = pack16<T>(xh);
             }
