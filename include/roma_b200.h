@@ -362,6 +362,12 @@ int roma_layernorm_shift(const void* x, const float* shift, const void* gamma, c
  * (romatch/models/transformer/layers/block.py:88-101 under transformer/__init__.py's autocast), same bits, one pass. */
 int roma_layernorm_cast(const void* x, const void* gamma, const void* beta, void* out,
                         long long rows, int D, float eps, int out_dtype, void* stream);
+/* sum = x + y (rounded to the storage dtype, as ATen's add) and out = LayerNorm(sum), one pass: the residual add of a
+ * pre-norm block and the norm that follows it (block.py:88-101: x = x + ls(attn(norm1(x))); ... norm2(x); the second add
+ * of a block pairs with the next block's norm1 / the final norm).  All tensors of one dtype; sum may alias x (in place);
+ * out must be distinct.  Same bits as roma-less `x + y` followed by roma_layernorm. */
+int roma_add_layernorm(const void* x, const void* y, const void* gamma, const void* beta, void* sum, void* out,
+                       long long rows, int D, float eps, int dtype, void* stream);
 /* out = x + y, x / out fp32, y 16-bit, n % 4 == 0: the residual add of the embedding decoder's fp32 token stream and an
  * autocast branch (block.py:88-101: x = x + ls(attn(norm(x)))), which ATen runs unvectorised. */
 int roma_residual_add(const float* x, const void* y, float* out, long long n, int y_dtype, void* stream);

@@ -68,6 +68,7 @@ SIGNATURES = {
     "roma_layernorm_shift": (_i, [_vp, _vp, _vp, _vp, _vp, C.c_longlong, _i, C.c_float, _i, _vp]),
     "roma_layernorm_cast": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _i, C.c_float, _i, _vp]),
     "roma_residual_add": (_i, [_vp, _vp, _vp, C.c_longlong, _i, _vp]),
+    "roma_add_layernorm": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_longlong, _i, C.c_float, _i, _vp]),
     "roma_topk_workspace_bytes": (C.c_size_t, [C.c_longlong, C.c_longlong]),
     "roma_topk_desc": (_i, [_vp, _i, C.c_longlong, C.c_longlong, _vp, _vp, _vp, C.c_size_t, _vp]),
     "roma_gelu": (_i, [_vp, _vp, C.c_longlong, _i, _vp]),

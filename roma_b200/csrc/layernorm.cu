@@ -79,6 +79,84 @@ layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const
     }
 }
 
+// s = x + y (rounded to T, as ATen's add of two T tensors) written to `sum` (may alias x) and LayerNorm(s) written to
+// `out`: the residual add of a pre-norm transformer block together with the norm that follows it — one read of x and
+// y, one write of each result, instead of add (2 reads, 1 write) + LayerNorm (1 read, 1 write).  Same bits as the pair.
+template <typename T, int NV>
+__global__ void __launch_bounds__(256)
+add_layernorm_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ gamma, const T* __restrict__ beta,
+                     T* __restrict__ sum, T* __restrict__ out, long long rows, int D, float eps) {
+    constexpr int kVec = Elem<T>::kVec;
+    const int lane = threadIdx.x & 31;
+    const int nvec = D / kVec;
+    const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows; r += warps) {
+        const T* xr = x + r * D;
+        const T* yr = y + r * D;
+        T* sr = sum + r * D;
+        float v[NV][kVec];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+                float a[kVec], b[kVec];
+                unpack16<T>(ldg16(xr + vi * kVec), a);
+                unpack16<T>(ldg16(yr + vi * kVec), b);
+#pragma unroll
+                for (int k = 0; k < kVec; ++k) v[i][k] = Elem<T>::to_f(Elem<T>::from_f(a[k] + b[k]));   // the stored (rounded) sum
+                *reinterpret_cast<uint4*>(sr + vi * kVec) = pack16<T>(v[i]);
+#pragma unroll
+                for (int k = 0; k < kVec; ++k) s += v[i][k];
+            } else {
+#pragma unroll
+                for (int k = 0; k < kVec; ++k) v[i][k] = 0.f;
+            }
+        }
+        const float mean = warp_sum(s) / (float)D;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            if (lane + 32 * i < nvec) {
+#pragma unroll
+                for (int k = 0; k < kVec; ++k) { const float d = v[i][k] - mean; q = fmaf(d, d, q); }
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(q) / (float)D + eps);
+        T* orow = out + r * D;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+                float g[kVec], b[kVec], o[kVec];
+                unpack16<T>(ldg16(gamma + vi * kVec), g);
+                unpack16<T>(ldg16(beta + vi * kVec), b);
+#pragma unroll
+                for (int k = 0; k < kVec; ++k) o[k] = fmaf((v[i][k] - mean) * rstd, g[k], b[k]);
+                store_row_vec<T, kVec>(orow + vi * kVec, o);
+            }
+        }
+    }
+}
+
+template <typename T>
+static int launch_add_layernorm(const void* x, const void* y, const void* g, const void* b, void* sum, void* out, long long rows, int D,
+                                float eps, cudaStream_t st) {
+    constexpr int kVec = Elem<T>::kVec;
+    const int nv = cdiv(D / kVec, 32);
+    long long blocks = (rows + 7) / 8;
+    const long long cap = (long long)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+#define ROMA_ALN(NVC) add_layernorm_kernel<T, NVC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, (const T*)y, (const T*)g, (const T*)b, (T*)sum, (T*)out, rows, D, eps)
+    if (nv <= 1) ROMA_ALN(1);
+    else if (nv <= 2) ROMA_ALN(2);
+    else if (nv <= 4) ROMA_ALN(4);
+    else if (nv <= 8) ROMA_ALN(8);
+    else return fail(ROMA_ERR_UNSUPPORTED, "roma_add_layernorm: D = %d too wide (max %d)", D, 8 * 32 * kVec);
+#undef ROMA_ALN
+    return 0;
+}
+
 template <typename T, typename TO = T>
 static int launch_layernorm(const void* x, const float* shift, const void* g, const void* b, void* out, long long rows, int D, float eps, cudaStream_t st) {
     constexpr int kVec = Elem<T>::kVec;
@@ -185,4 +263,28 @@ extern "C" int roma_residual_add(const float* x, const void* y, float* out, long
     else if (y_dtype == ROMA_BF16) residual_add_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(x, (const __nv_bfloat16*)y, out, n4);
     else return fail(ROMA_ERR_BAD_ARG, "roma_residual_add: y_dtype must be ROMA_F16 or ROMA_BF16");
     return check_launch("roma_residual_add");
+}
+
+// sum = x + y and out = LayerNorm(sum) in one pass (x, y, sum, out, gamma, beta of one dtype; sum may alias x).
+extern "C" int roma_add_layernorm(const void* x, const void* y, const void* gamma, const void* beta, void* sum, void* out,
+                                  long long rows, int D, float eps, int dtype, void* stream) {
+    using namespace roma;
+    ROMA_REQUIRE(x && y && gamma && beta && sum && out, ROMA_ERR_BAD_ARG, "roma_add_layernorm: null pointer");
+    ROMA_REQUIRE(rows > 0 && D > 0, ROMA_ERR_BAD_ARG, "roma_add_layernorm: bad sizes");
+    const int kvec = dtype == ROMA_F32 ? 4 : 8;
+    ROMA_REQUIRE(D % kvec == 0, ROMA_ERR_UNSUPPORTED, "roma_add_layernorm: D = %d must be a multiple of %d", D, kvec);
+    ROMA_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(sum) |
+                   reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta)) & 15u) == 0,
+                 ROMA_ERR_ALIGNMENT, "roma_add_layernorm: pointers must be 16-byte aligned");
+    ROMA_REQUIRE(out != x && out != y && out != sum, ROMA_ERR_BAD_ARG, "roma_add_layernorm: out must not alias an input or sum");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    int rc;
+    switch (dtype) {
+        case ROMA_F32:  rc = launch_add_layernorm<float>(x, y, gamma, beta, sum, out, rows, D, eps, st); break;
+        case ROMA_F16:  rc = launch_add_layernorm<__half>(x, y, gamma, beta, sum, out, rows, D, eps, st); break;
+        case ROMA_BF16: rc = launch_add_layernorm<__nv_bfloat16>(x, y, gamma, beta, sum, out, rows, D, eps, st); break;
+        default: return fail(ROMA_ERR_BAD_ARG, "roma_add_layernorm: unknown dtype %d", dtype);
+    }
+    if (rc) return rc;
+    return check_launch("roma_add_layernorm");
 }

@@ -139,6 +139,24 @@ class Block(nn.Module):
         x2.addmm_(gelu_(self.mlp.fc1(self.norm2(x, shift))).reshape(B * N, -1), w2.t())
         return x, shift + b2.float()
 
+    def fusable(self, x) -> bool:
+        """16-bit CUDA inference with LayerScale: the residual adds can ride the LayerNorm that follows them."""
+        return self.foldable(x) and x.dtype in (torch.float16, torch.bfloat16) and x.is_contiguous()
+
+    def forward_deferred(self, x, pending, next_norm_of=None):
+        """One block with its residual adds fused into the following norms (`roma_add_layernorm`: sum and LayerNorm(sum) in
+        one pass, same bits as add + norm).  `pending` is the previous block's second branch, not yet added to x (None for
+        the first block).  Returns (x, pending'): the stream after this block's FIRST add and this block's second branch."""
+        from .. import ops
+        w1, b1, w2, b2 = self._folded()
+        if pending is None:
+            n1 = self.norm1(x)
+        else:
+            x, n1 = ops.add_layer_norm(x, pending, self.norm1.weight, self.norm1.bias, self.norm1.eps, inplace=True)
+        a = F.linear(self.attn.attend(n1), w1, b1)
+        x, n2 = ops.add_layer_norm(x, a, self.norm2.weight, self.norm2.bias, self.norm2.eps, inplace=True)
+        return x, F.linear(gelu_(self.mlp.fc1(n2)), w2, b2)
+
     def forward(self, x):
         if not self.training and x.is_cuda and isinstance(self.ls1, ChannelScale) and self.attn.proj.bias is not None:
             w1, b1, w2, b2 = self._folded()
@@ -208,6 +226,7 @@ class DinoViT(nn.Module):
                         nn.init.zeros_(m.bias)
         self.requires_grad_(False)
         self._pos_cache = {}
+        self.fused_residual_norm = True  # residual adds ride the LayerNorm that follows them (Block.forward_deferred; same bits)
         self.unbiased_residual = False   # opt-in: residual branches as in-place accumulating GEMMs (Block.forward_unbiased);
                                          # measured neutral on the power-capped step (95.9 vs 95.2 / 96.3 ms), so off by default
 
@@ -240,6 +259,12 @@ class DinoViT(nn.Module):
             for blk in self.blocks:
                 t, shift = blk.forward_unbiased(t, shift)
             return self.norm(t, shift)[:, 1:]
+        if self.fused_residual_norm and not torch.is_grad_enabled() and all(blk.fusable(t) for blk in self.blocks) and self.norm.native(t):
+            from .. import ops
+            pending = None                                                  # t is a fresh tensor: updated in place from here on
+            for blk in self.blocks:
+                t, pending = blk.forward_deferred(t, pending)
+            return ops.add_layer_norm(t, pending, self.norm.weight, self.norm.bias, self.norm.eps, inplace=True)[1][:, 1:]
         for blk in self.blocks:
             t = blk(t)
         return self.norm(t)[:, 1:]

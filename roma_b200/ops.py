@@ -535,6 +535,28 @@ def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: f
     return out
 
 
+def add_layer_norm(x: torch.Tensor, y: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float,
+                   inplace: bool = False):
+    """(x + y, F.layer_norm(x + y)) in one pass for x, y of one dtype and shape (block.py:88-101: a residual add and the norm
+    that follows it).  inplace=True writes the sum over x.  Same bits as the two ATen / roma ops run one after the other."""
+    dev = _cuda(x, y, weight, bias)
+    if x.dtype not in _DT or y.dtype != x.dtype or x.shape != y.shape:
+        raise ValueError("add_layer_norm: x and y must share dtype and shape")
+    D = x.shape[-1]
+    if inplace and not x.is_contiguous():
+        raise ValueError("add_layer_norm(inplace=True) needs a contiguous x")
+    x, y = x.contiguous(), y.contiguous()
+    weight, bias = weight.to(x.dtype).contiguous(), bias.to(x.dtype).contiguous()
+    rows = x.numel() // D
+    total = x if inplace else torch.empty_like(x)
+    out = torch.empty_like(x)
+    lib = _lib.load()
+    _run("roma_add_layernorm", dict(rows=rows, D=D, esize=x.element_size()),
+         lambda: lib.roma_add_layernorm(_ptr(x), _ptr(y), _ptr(weight), _ptr(bias), _ptr(total), _ptr(out), rows, D, float(eps),
+                                        _DT[x.dtype], _stream(dev)))
+    return total, out
+
+
 def residual_add(x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
     """x + y for an fp32 stream x and a 16-bit branch y of the same shape -> fp32 (block.py:88-101 under autocast)."""
     dev = _cuda(x, y)

@@ -761,3 +761,39 @@ def test_layernorm_cast_and_residual_add(ops, cuda):
         assert (got != want.to(dt)).float().mean().item() < 2e-3
         y = torch.randn(3, 257, 1024, device=cuda, generator=g).to(dt)
         assert torch.equal(ops.residual_add(x, y), x + y)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("rows,D", [(1601 * 2, 1024), (77, 384), (5, 8)])
+def test_add_layernorm_is_add_then_layernorm(ops, cuda, dtype, rows, D):
+    """roma_add_layernorm: the sum is ATen's x + y bit for bit, the norm is roma_layernorm of that sum bit for bit; in place too."""
+    g = torch.Generator().manual_seed(rows + D)
+    x = (torch.randn(rows, D, generator=g) * 3).to(dtype).to(cuda)
+    y = torch.randn(rows, D, generator=g).to(dtype).to(cuda)
+    w, b = (torch.rand(D, generator=g) + 0.5).to(dtype).to(cuda), torch.randn(D, generator=g).to(dtype).to(cuda)
+    want_sum = x + y
+    want_norm = ops.layer_norm(want_sum, w, b, 1e-6)
+    s, n = ops.add_layer_norm(x, y, w, b, 1e-6)
+    assert torch.equal(s, want_sum) and torch.equal(n, want_norm)
+    xi = x.clone()
+    s2, n2 = ops.add_layer_norm(xi, y, w, b, 1e-6, inplace=True)
+    assert s2.data_ptr() == xi.data_ptr() and torch.equal(xi, want_sum) and torch.equal(n2, want_norm)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_vit_fused_residual_norm_is_bit_identical(cuda, dtype):
+    """DinoViT with the residual adds fused into the following norms returns the same bits as the plain block loop."""
+    from roma_b200.host.vit import DinoViT
+    torch.manual_seed(3)
+    vit = DinoViT(img_size=70, patch_size=14, embed_dim=256, depth=3, num_heads=4).to(cuda).to(dtype).eval()
+    with torch.no_grad():
+        for p in vit.parameters():
+            if p.dim() == 1:
+                p.add_(torch.randn_like(p) * 0.1)
+    x = torch.randn(2, 3, 70, 84, device=cuda, dtype=dtype)
+    with torch.inference_mode():
+        vit.fused_residual_norm = True
+        a = vit.patch_tokens(x)
+        vit.fused_residual_norm = False
+        b = vit.patch_tokens(x)
+    assert a.shape == b.shape == (2, 30, 256) and torch.equal(a, b)
