@@ -25,7 +25,9 @@ template <typename TO, int N> __device__ __forceinline__ void store_row_vec(TO* 
 
 // TO = T, or a 16-bit type for fp32 rows: the cast autocast would insert in front of the Linear that consumes the
 // normalised tokens (fp32 LayerNorm output rounded once to the 16-bit dtype — the same bits, one pass less).
-template <typename T, int NV, typename TO = T>
+// FULL: D == 32 * NV * kVec — every lane owns NV whole vectors, so the row's loads carry no predicate and are all issued
+// before the first use (with the `vi < nvec` tests each vector was its own basic block: load, wait, use, next load).
+template <typename T, int NV, typename TO = T, bool FULL = false>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const T* __restrict__ gamma, const T* __restrict__ beta,
                  TO* __restrict__ out, long long rows, int D, float eps) {
@@ -40,24 +42,33 @@ layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
-            if (vi < nvec) {
+            if (FULL || vi < nvec) {
                 unpack16<T>(ldg16(xr + vi * kVec), v[i]);
-                if (shift) {                     // residual stream stored without its accumulated bias vector (see header)
-#pragma unroll
-                    for (int k = 0; k < kVec; ++k) v[i][k] += __ldg(shift + vi * kVec + k);
-                }
-#pragma unroll
-                for (int k = 0; k < kVec; ++k) s += v[i][k];
             } else {
 #pragma unroll
                 for (int k = 0; k < kVec; ++k) v[i][k] = 0.f;
             }
         }
+        if (shift) {                             // residual stream stored without its accumulated bias vector (see header)
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const int vi = lane + 32 * i;
+                if (FULL || vi < nvec) {
+#pragma unroll
+                    for (int k = 0; k < kVec; ++k) v[i][k] += __ldg(shift + vi * kVec + k);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+#pragma unroll
+            for (int k = 0; k < kVec; ++k) s += v[i][k];     // lanes beyond the row hold zeros
+        }
         const float mean = warp_sum(s) / (float)D;
         float q = 0.f;
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
-            if (lane + 32 * i < nvec) {
+            if (FULL || lane + 32 * i < nvec) {
 #pragma unroll
                 for (int k = 0; k < kVec; ++k) { const float d = v[i][k] - mean; q = fmaf(d, d, q); }
             }
@@ -67,7 +78,7 @@ layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
-            if (vi < nvec) {
+            if (FULL || vi < nvec) {
                 float g[kVec], b[kVec], o[kVec];
                 unpack16<T>(ldg16(gamma + vi * kVec), g);
                 unpack16<T>(ldg16(beta + vi * kVec), b);
@@ -82,7 +93,7 @@ layernorm_kernel(const T* __restrict__ x, const float* __restrict__ shift, const
 // s = x + y (rounded to T, as ATen's add of two T tensors) written to `sum` (may alias x) and LayerNorm(s) written to
 // `out`: the residual add of a pre-norm transformer block together with the norm that follows it — one read of x and
 // y, one write of each result, instead of add (2 reads, 1 write) + LayerNorm (1 read, 1 write).  Same bits as the pair.
-template <typename T, int NV>
+template <typename T, int NV, bool FULL = false>
 __global__ void __launch_bounds__(256)
 add_layernorm_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ gamma, const T* __restrict__ beta,
                      T* __restrict__ sum, T* __restrict__ out, long long rows, int D, float eps) {
@@ -99,7 +110,7 @@ add_layernorm_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* 
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
-            if (vi < nvec) {
+            if (FULL || vi < nvec) {
                 float a[kVec], b[kVec];
                 unpack16<T>(ldg16(xr + vi * kVec), a);
                 unpack16<T>(ldg16(yr + vi * kVec), b);
@@ -117,7 +128,7 @@ add_layernorm_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* 
         float q = 0.f;
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
-            if (lane + 32 * i < nvec) {
+            if (FULL || lane + 32 * i < nvec) {
 #pragma unroll
                 for (int k = 0; k < kVec; ++k) { const float d = v[i][k] - mean; q = fmaf(d, d, q); }
             }
@@ -127,7 +138,7 @@ add_layernorm_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* 
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
-            if (vi < nvec) {
+            if (FULL || vi < nvec) {
                 float g[kVec], b[kVec], o[kVec];
                 unpack16<T>(ldg16(gamma + vi * kVec), g);
                 unpack16<T>(ldg16(beta + vi * kVec), b);
@@ -147,7 +158,8 @@ static int launch_add_layernorm(const void* x, const void* y, const void* g, con
     long long blocks = (rows + 7) / 8;
     const long long cap = (long long)sm_count() * 16;
     if (blocks > cap) blocks = cap;
-#define ROMA_ALN(NVC) add_layernorm_kernel<T, NVC><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, (const T*)y, (const T*)g, (const T*)b, (T*)sum, (T*)out, rows, D, eps)
+#define ROMA_ALN(NVC) do { if (D == 32 * NVC * kVec) add_layernorm_kernel<T, NVC, true><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, (const T*)y, (const T*)g, (const T*)b, (T*)sum, (T*)out, rows, D, eps); \
+                           else add_layernorm_kernel<T, NVC, false><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, (const T*)y, (const T*)g, (const T*)b, (T*)sum, (T*)out, rows, D, eps); } while (0)
     if (nv <= 1) ROMA_ALN(1);
     else if (nv <= 2) ROMA_ALN(2);
     else if (nv <= 4) ROMA_ALN(4);
@@ -164,7 +176,8 @@ static int launch_layernorm(const void* x, const float* shift, const void* g, co
     long long blocks = (rows + 7) / 8;
     const long long cap = (long long)sm_count() * 16;
     if (blocks > cap) blocks = cap;
-#define ROMA_LN(NVC) layernorm_kernel<T, NVC, TO><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, shift, (const T*)g, (const T*)b, (TO*)out, rows, D, eps)
+#define ROMA_LN(NVC) do { if (D == 32 * NVC * kVec) layernorm_kernel<T, NVC, TO, true><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, shift, (const T*)g, (const T*)b, (TO*)out, rows, D, eps); \
+                          else layernorm_kernel<T, NVC, TO, false><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, shift, (const T*)g, (const T*)b, (TO*)out, rows, D, eps); } while (0)
     if (nv <= 1) ROMA_LN(1);
     else if (nv <= 2) ROMA_LN(2);
     else if (nv <= 4) ROMA_LN(4);

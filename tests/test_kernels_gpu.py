@@ -764,9 +764,11 @@ def test_layernorm_cast_and_residual_add(ops, cuda):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
-@pytest.mark.parametrize("rows,D", [(1601 * 2, 1024), (77, 384), (5, 8)])
+@pytest.mark.parametrize("rows,D", [(1601 * 2, 1024), (77, 384), (5, 8), (33, 768), (9, 256), (3, 2048), (11, 512), (7, 128)])
 def test_add_layernorm_is_add_then_layernorm(ops, cuda, dtype, rows, D):
     """roma_add_layernorm: the sum is ATen's x + y bit for bit, the norm is roma_layernorm of that sum bit for bit; in place too."""
+    if dtype == torch.float32 and D > 1024:
+        pytest.skip("fp32 rows: D <= 1024")
     g = torch.Generator().manual_seed(rows + D)
     x = (torch.randn(rows, D, generator=g) * 3).to(dtype).to(cuda)
     y = torch.randn(rows, D, generator=g).to(dtype).to(cuda)
@@ -797,3 +799,20 @@ def test_vit_fused_residual_norm_is_bit_identical(cuda, dtype):
         vit.fused_residual_norm = False
         b = vit.patch_tokens(x)
     assert a.shape == b.shape == (2, 30, 256) and torch.equal(a, b)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 3e-2), (torch.float16, 4e-3)])
+@pytest.mark.parametrize("D", [8, 128, 256, 384, 512, 768, 1024, 2048])
+def test_layernorm_all_row_widths(ops, cuda, dtype, tol, D):
+    """roma_layernorm vs F.layer_norm in fp32 over rows that fill the lanes' vectors exactly (predicate-free variant)
+    and rows that do not; the row after the last one is poisoned to catch reads past a row."""
+    if dtype == torch.float32 and D > 1024:
+        pytest.skip("fp32 rows: D <= 1024")
+    g = torch.Generator().manual_seed(D)
+    x = (torch.randn(19, D, generator=g) * 2 + 0.3).to(dtype)
+    w = (1 + 0.1 * torch.randn(D, generator=g)).to(dtype); b = (0.1 * torch.randn(D, generator=g)).to(dtype)
+    want = torch.nn.functional.layer_norm(x.float(), (D,), w.float(), b.float(), 1e-6)
+    buf = torch.full((20, D), float("nan"), dtype=dtype, device=cuda)
+    buf[:19] = x.to(cuda)
+    got = ops.layer_norm(buf[:19], w.to(cuda), b.to(cuda), 1e-6)
+    assert got.dtype == dtype and torch.isfinite(got).all() and err(got, want) < tol
