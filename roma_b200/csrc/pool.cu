@@ -37,23 +37,32 @@ template <> __device__ __forceinline__ uint4 max16<__nv_bfloat16>(uint4 a, uint4
     return r;
 }
 
-template <typename T>
+// I: index type — unsigned int whenever every element offset of x fits 32 bits (all encoder shapes): the three div / mod pairs of
+// the output decode are 64-bit software routines otherwise (~300 instructions per 16-byte vector against 4 loads and 1 store).
+template <typename T, typename I>
 __global__ void __launch_bounds__(256)
 maxpool2_kernel(const T* __restrict__ x, T* __restrict__ out, int h, int w, int C, int ho, int wo, long long nvec_out) {
     constexpr int kVec = Elem<T>::kVec;
-    const int vpp = C / kVec;                                   // 16-byte vectors per pixel
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec_out; i += stride) {
-        const int v = (int)(i % vpp);
-        long long t = i / vpp;
-        const int xo = (int)(t % wo); t /= wo;
-        const int yo = (int)(t % ho);
-        const long long b = t / ho;
-        const T* p = x + ((b * h + 2 * yo) * w + 2 * xo) * C + (long long)v * kVec;
+    const I vpp = (I)(C / kVec);                                // 16-byte vectors per pixel
+    const I stride = (I)gridDim.x * blockDim.x, n = (I)nvec_out;
+    for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const I v = i % vpp;
+        I t = i / vpp;
+        const I xo = t % (I)wo; t /= (I)wo;
+        const I yo = t % (I)ho;
+        const I b = t / (I)ho;
+        const T* p = x + ((b * (I)h + 2 * yo) * (I)w + 2 * xo) * (I)C + v * kVec;
         const uint4 a = ldg16(p), bq = ldg16(p + C);
-        const uint4 c = ldg16(p + (long long)w * C), d = ldg16(p + (long long)w * C + C);
+        const uint4 c = ldg16(p + (I)w * (I)C), d = ldg16(p + (I)w * (I)C + C);
         *reinterpret_cast<uint4*>(out + i * kVec) = max16<T>(max16<T>(a, bq), max16<T>(c, d));
     }
+}
+
+template <typename T>
+static void launch_maxpool2(const void* x, void* out, int B, int h, int w, int C, int ho, int wo, long long nvec, unsigned blocks, cudaStream_t st) {
+    const bool small = (long long)B * h * w * C < (1ll << 32) && nvec + (long long)blocks * 256 < (1ll << 32);
+    if (small) maxpool2_kernel<T, unsigned int><<<blocks, 256, 0, st>>>((const T*)x, (T*)out, h, w, C, ho, wo, nvec);
+    else maxpool2_kernel<T, long long><<<blocks, 256, 0, st>>>((const T*)x, (T*)out, h, w, C, ho, wo, nvec);
 }
 
 }  // namespace roma
@@ -73,9 +82,9 @@ extern "C" int roma_maxpool2x2_nhwc(const void* x, void* out, int B, int h, int 
     if (blocks > cap) blocks = cap;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (dtype) {
-        case ROMA_F32:  maxpool2_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((const float*)x, (float*)out, h, w, C, ho, wo, nvec); break;
-        case ROMA_F16:  maxpool2_kernel<__half><<<(unsigned)blocks, 256, 0, st>>>((const __half*)x, (__half*)out, h, w, C, ho, wo, nvec); break;
-        case ROMA_BF16: maxpool2_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, h, w, C, ho, wo, nvec); break;
+        case ROMA_F32:  launch_maxpool2<float>(x, out, B, h, w, C, ho, wo, nvec, (unsigned)blocks, st); break;
+        case ROMA_F16:  launch_maxpool2<__half>(x, out, B, h, w, C, ho, wo, nvec, (unsigned)blocks, st); break;
+        case ROMA_BF16: launch_maxpool2<__nv_bfloat16>(x, out, B, h, w, C, ho, wo, nvec, (unsigned)blocks, st); break;
         default: return fail(ROMA_ERR_BAD_ARG, "roma_maxpool2x2_nhwc: unknown dtype %d", dtype);
     }
     return check_launch("roma_maxpool2x2_nhwc");
